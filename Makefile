@@ -1,0 +1,50 @@
+# Top-level build: product libraries (CUDA, sm_100a only), host application, oracle.
+#   make            -> everything
+#   make product    -> owl_path_tracer_b200/lib/libb200pt.so, libb200pt_host.so, bin/path_tracer
+#   make oracle     -> oracle/liboracle.so, oracle/liboracle_det.so   (test infrastructure)
+#   make emu        -> tests/emu/libemu.so  (host emulation of the kernels' per-lane logic; tests only)
+NVCC ?= /usr/local/cuda/bin/nvcc
+CXX ?= g++
+PKG = owl_path_tracer_b200
+CSRC = $(PKG)/csrc
+HOST = $(PKG)/host
+LIB = $(PKG)/lib
+BIN = $(PKG)/bin
+
+NVFLAGS = -std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false \
+          -Xcompiler -fPIC -Xcompiler -ffp-contract=off --expt-relaxed-constexpr -cudart static
+CXXFLAGS = -std=c++17 -O2 -fPIC -Wall -Wno-unused-function
+
+CUHDR = $(wildcard $(CSRC)/*.h) include/b200pt.h
+HOSTHDR = $(wildcard $(HOST)/*.hpp) include/b200pt.h include/b200pt_host.h
+
+all: product oracle emu
+product: $(LIB)/libb200pt.so $(LIB)/libb200pt_host.so $(BIN)/path_tracer
+
+$(LIB)/%.o: $(CSRC)/%.cu $(CUHDR)
+	@mkdir -p $(LIB)
+	$(NVCC) $(NVFLAGS) -Xptxas -v -c -o $@ $< 2> $(LIB)/$*.ptxas.log || (cat $(LIB)/$*.ptxas.log; exit 1)
+
+$(LIB)/libb200pt.so: $(LIB)/api.o $(LIB)/wavefront.o $(LIB)/bvh_build.o
+	$(NVCC) -shared -cudart static -gencode arch=compute_100a,code=sm_100a -o $@ $^
+
+HOSTSRC = $(HOST)/loaders.cpp $(HOST)/procedural.cpp $(HOST)/application.cpp $(HOST)/host_api.cpp
+$(LIB)/libb200pt_host.so: $(HOSTSRC) $(HOSTHDR) $(LIB)/libb200pt.so
+	$(CXX) $(CXXFLAGS) -shared -o $@ $(HOSTSRC) -L$(LIB) -lb200pt -lz -Wl,-rpath,'$$ORIGIN'
+
+$(BIN)/path_tracer: $(HOST)/main.cpp $(LIB)/libb200pt_host.so
+	@mkdir -p $(BIN)
+	$(CXX) $(CXXFLAGS) -fPIE -o $@ $(HOST)/main.cpp -L$(LIB) -lb200pt_host -lb200pt -Wl,-rpath,'$$ORIGIN/../lib'
+
+oracle:
+	$(MAKE) -C oracle
+
+emu: tests/emu/libemu.so
+tests/emu/libemu.so: tests/emu/emu.cpp $(CUHDR)
+	$(CXX) -std=c++17 -O2 -fPIC -shared -ffp-contract=off -fno-fast-math -Wall -Wno-unused-function -Wno-unknown-pragmas -pthread -o $@ $<
+
+clean:
+	rm -rf $(LIB) $(BIN) tests/emu/libemu.so
+	$(MAKE) -C oracle clean
+
+.PHONY: all product oracle emu clean

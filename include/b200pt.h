@@ -1,0 +1,199 @@
+/* b200pt.h — C ABI of the B200-native render loop (libb200pt.so).
+ *
+ * This header is the drop-in boundary for the render path of
+ * jctemp/owl-path-tracer.  The reference has no plugin API; the seam is the set
+ * of OWL C-API calls its host makes (path_tracer/src/application.cpp through
+ * path_tracer/src/owl.hpp).  Each entry point below names the reference call
+ * site(s) it replaces.  Everything here is plain C: opaque context pointer,
+ * POD structs, raw pointers + sizes, int status codes (0 = ok).  Nothing throws
+ * across the boundary; b200pt_last_error() returns a thread-local message.
+ *
+ * Ownership: the caller keeps ownership of every input pointer and may free it
+ * as soon as the call returns.  The library owns all device memory.  Pointers
+ * returned by b200pt_framebuffer_* are borrowed and stay valid until the next
+ * render, resize or destroy.
+ *
+ * Threading: one host thread per context (same as the reference: one launch
+ * params object, one stream).  No CPU fallback exists: every call fails with
+ * B200PT_ERR_CUDA when no sm_100 device can be used.
+ */
+#ifndef B200PT_H
+#define B200PT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200PT_VERSION 100
+
+enum b200pt_status {
+    B200PT_OK = 0,
+    B200PT_ERR_INVALID = 1,   /* bad argument / call order                        */
+    B200PT_ERR_CUDA = 2,      /* CUDA runtime / no device                          */
+    B200PT_ERR_EMPTY = 3,     /* build_accel with no geometry ("no geometries",
+                                 application.cpp:133)                              */
+    B200PT_ERR_BOUNDS = 4     /* index out of range (device get_data trap,
+                                 macros.hpp:5-11, checked on the host at upload)   */
+};
+
+/* How samples are split over ranks. */
+enum b200pt_shard_mode {
+    B200PT_SHARD_SPP = 0,     /* rank r renders spp/world samples of every pixel with
+                                 its own RNG stream random(x, y + r*H)            */
+    B200PT_SHARD_ROWS = 1     /* rank r renders rows y%world==r with all samples and
+                                 the reference stream random(x, y): the N-rank sum
+                                 is bit-identical to the 1-rank image             */
+};
+
+/* replaces create_context(nullptr, 1) + create_module (application.cpp:62-63,
+ * owl.hpp:22-37): which GPU, and this process's place in a multi-GPU job. */
+typedef struct b200pt_config {
+    int32_t device_ordinal;   /* CUDA device to use                               */
+    int32_t rank;             /* 0 .. world_size-1                                */
+    int32_t world_size;       /* number of cooperating processes (1 = reference)  */
+    int32_t shard_mode;       /* enum b200pt_shard_mode                           */
+    int32_t flags;            /* B200PT_FLAG_* bits                               */
+} b200pt_config;
+
+#define B200PT_FLAG_COUNTERS   1  /* count nodes/triangles visited (slower; for the
+                                     roofline's algorithmic bytes)                 */
+#define B200PT_FLAG_HOST_BVH   2  /* reserved                                       */
+#define B200PT_FLAG_TIMING     4  /* CUDA events around every extend / shade launch
+                                     (fills extend_ms / shade_ms in b200pt_stats)   */
+
+/* material_data, device_global.hpp:19-36 — 17 floats, 68 bytes, same order. */
+typedef struct b200pt_material {
+    float base_color[3];
+    float subsurface;
+    float metallic;
+    float specular;
+    float specular_tint;
+    float roughness;
+    float anisotropic;
+    float sheen;
+    float sheen_tint;
+    float clearcoat;
+    float clearcoat_gloss;
+    float ior;
+    float specular_transmission;
+    float specular_transmission_roughness;
+    float emission;
+} b200pt_material;
+
+/* hit_data subset (device.hpp:14-26) for the parity hook. mesh < 0 = miss. */
+typedef struct b200pt_hit {
+    int32_t mesh;             /* mesh_index (order of b200pt_add_mesh calls)       */
+    int32_t prim;             /* primitive index inside that mesh                  */
+    float t, u, v;            /* OptiX barycentric convention: P=(1-u-v)p0+u p1+v p2 */
+} b200pt_hit;
+
+typedef struct b200pt_stats {
+    double render_ms;         /* device time of the last render (CUDA events)      */
+    double extend_ms;         /* share spent in the extend (traversal) kernel      */
+    double shade_ms;          /* share spent in the shade kernel                   */
+    double other_ms;          /* raygen/resolve/queue bookkeeping                  */
+    double build_ms;          /* last b200pt_build_accel                           */
+    uint64_t rays;            /* radiance segments traced (primary + bounce)       */
+    uint64_t paths;           /* camera samples started                            */
+    uint64_t nodes_visited;   /* 8-wide nodes fetched   (FLAG_COUNTERS only)       */
+    uint64_t tris_tested;     /* triangles intersected  (FLAG_COUNTERS only)       */
+    uint64_t kernel_launches; /* kernels launched by the last render               */
+    uint64_t iterations;      /* wavefront iterations of the last render           */
+    uint32_t bvh_nodes;       /* 8-wide nodes in the tree                          */
+    uint32_t bvh_tris;        /* triangles referenced by the tree                  */
+    uint64_t bvh_bytes;       /* nodes*80 + tris*48                                */
+} b200pt_stats;
+
+typedef struct b200pt_ctx b200pt_ctx;
+
+const char* b200pt_last_error(void);
+int b200pt_version(void);
+
+/* create_context / destroy_context  (application.cpp:62, Main.cpp:30). */
+int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out);
+int b200pt_destroy(b200pt_ctx* ctx);
+
+/* One call per entity, replaces the per-entity block of bind_sbt_data
+ * (application.cpp:197-246): 4 device buffers + owlGeomCreate + mesh_index /
+ * material_index + optional RGBA8 NEAREST/CLAMP texture (already v-flipped by the
+ * caller exactly as the reference does).  verts/normals: nv*3 floats; uvs: nv*2
+ * floats or NULL; idx: nt*3 int32 (local to this mesh).  Returns the mesh index in
+ * *mesh_index (= call order, mesh_id++ at application.cpp:211). */
+int b200pt_add_mesh(b200pt_ctx* ctx, const float* verts, const float* normals, const float* uvs,
+                    int32_t nv, const int32_t* idx, int32_t nt, int32_t material_index,
+                    const uint8_t* tex_rgba, int32_t tex_w, int32_t tex_h, int32_t* mesh_index);
+
+/* init_owl_world (application.cpp:131-140): all meshes -> one acceleration
+ * structure, built on the GPU (LBVH -> 8-wide compressed).  B200PT_ERR_EMPTY when
+ * no mesh was added. */
+int b200pt_build_accel(b200pt_ctx* ctx);
+
+/* material buffer upload (application.cpp:257-259) and its per-frame re-upload
+ * reset_field (application.cpp:297-304).  Cheap; never rebuilds the BVH. */
+int b200pt_set_materials(b200pt_ctx* ctx, const b200pt_material* m, int32_t nm);
+
+/* environment texture + launch params (application.cpp:253-254, 285-289).
+ * rgba may be NULL / w,h 0 ("environment_map" handle 0, device.cu:138). */
+int b200pt_set_environment(b200pt_ctx* ctx, const uint8_t* rgba, int32_t w, int32_t h,
+                           int32_t use, int32_t auto_, const float color[3], float intensity);
+
+/* camera_data (camera.hpp:16-22) as bound at application.cpp:272-275. */
+int b200pt_set_camera(b200pt_ctx* ctx, const float origin[3], const float llc[3],
+                      const float horizontal[3], const float vertical[3]);
+
+/* fb_size, max_samples, max_path_depth (application.cpp:255,271,277-278). */
+int b200pt_set_render(b200pt_ctx* ctx, int32_t width, int32_t height, int32_t max_samples,
+                      int32_t max_path_depth);
+
+/* render_frame's owlLaunch2D (application.cpp:366), blocking like
+ * owlLaunch+owlLaunchSync (extern/owl/owl/impl.cpp:252-261).
+ * world_size==1: complete frame.  world_size>1: b200pt_render only renders this
+ * rank's share into the float4 sum buffer; the caller sums the buffers of all
+ * ranks into rank 0's (one NCCL reduce over b200pt_accum_buffer) and then calls
+ * b200pt_resolve on rank 0. */
+int b200pt_render(b200pt_ctx* ctx);
+int b200pt_accum_buffer(b200pt_ctx* ctx, void** device_ptr, size_t* n_floats);
+int b200pt_resolve(b200pt_ctx* ctx);
+
+/* Same frame, but the caller's HOST settings are re-uploaded and the RGBA8 frame is
+ * copied back into host memory inside the call (the "e2e" path of bench.py:
+ * materials H2D + render + D2H framebuffer, what test_loop does per frame). */
+int b200pt_render_to_host(b200pt_ctx* ctx, const b200pt_material* m, int32_t nm,
+                          uint32_t* rgba_out /* W*H, row 0 = top */);
+
+/* buffer_to_pointer(framebuffer) (application.cpp:368): RGBA8, row 0 = top
+ * (device.cu:251 flip applied), host pointer. */
+int b200pt_framebuffer_rgba8(b200pt_ctx* ctx, const uint32_t** out);
+/* mean radiance before quantisation, float RGBA, same row order (for relMSE). */
+int b200pt_framebuffer_f32(b200pt_ctx* ctx, const float** out);
+
+/* Parity hook: closest hit of sample 0's camera ray for every pixel, out[W*H],
+ * index x + W*y with y as launched (no flip). */
+int b200pt_primary_hits(b200pt_ctx* ctx, b200pt_hit* out);
+
+/* Parity hook: closest hit for caller-supplied rays (n rays; o,d as n*3 floats). */
+int b200pt_trace(b200pt_ctx* ctx, const float* origins, const float* dirs, int32_t n,
+                 float tmin, float tmax, b200pt_hit* out);
+
+int b200pt_get_stats(b200pt_ctx* ctx, b200pt_stats* out);
+
+/* Parity hook for the BSDF (disney/disney.cuh:31-66) evaluated on the device:
+ * for each of n cases: material index, local wo[3], previous lobe, RNG state in ->
+ * f[3], wi[3], pdf, lobe, RNG state out.  Arrays are n-long (wo/f/wi n*3). */
+int b200pt_sample_disney(b200pt_ctx* ctx, int32_t n, const int32_t* material, const float* wo,
+                         const int32_t* lobe_in, const uint32_t* rng_in, float* f, float* wi,
+                         float* pdf, int32_t* lobe_out, uint32_t* rng_out);
+
+/* Copy the device-built 8-wide BVH back to the host (80-byte nodes, 48-byte
+ * triangles) so the oracle-side checker can walk the same topology and count
+ * node/triangle visits for the roofline.  Call with NULL pointers to get sizes. */
+int b200pt_export_bvh(b200pt_ctx* ctx, void* nodes, uint32_t* n_nodes, void* tris,
+                      uint32_t* n_tris);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PT_H */

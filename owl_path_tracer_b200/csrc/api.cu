@@ -1,0 +1,609 @@
+// api.cu — implementation of the C ABI declared in include/b200pt.h.
+// No CPU fallback: without a usable CUDA device b200pt_create fails.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "device_ctx.h"
+
+using namespace pt;
+
+static thread_local std::string g_error;
+extern "C" const char* b200pt_last_error(void) { return g_error.c_str(); }
+extern "C" int b200pt_version(void) { return B200PT_VERSION; }
+
+static int fail(int code, const std::string& msg) {
+    g_error = msg;
+    return code;
+}
+#define CU(x)                                                                                        \
+    do {                                                                                             \
+        cudaError_t e_ = (x);                                                                        \
+        if (e_ != cudaSuccess) return fail(B200PT_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct b200pt_ctx {
+    b200pt_config cfg{};
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // host staging of the flattened scene (kept: parity hooks map triangle ids back)
+    std::vector<f4> h_pos, h_nrm;
+    std::vector<f2> h_uv;
+    std::vector<int32_t> h_idx4;
+    std::vector<MeshInfo> h_meshes;
+    std::vector<uint32_t> h_texels;
+    float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, max_abs = 0;
+    bool any_uv = false;
+    // device scene
+    f4 *d_pos = nullptr, *d_nrm = nullptr;
+    f2* d_uv = nullptr;
+    int32_t* d_idx4 = nullptr;
+    MeshInfo* d_meshes = nullptr;
+    uint32_t *d_texels = nullptr, *d_env = nullptr;
+    Material* d_mats = nullptr;
+    int n_mats = 0;
+    DeviceBVH bvh;
+    bool built = false;
+    // settings
+    int env_w = 0, env_h = 0, env_use = 0, env_auto = 0;
+    float env_color[3] = {0, 0, 0}, env_intensity = 0;
+    float cam[12] = {0};
+    int width = 0, height = 0, max_samples = 0, max_depth = 0;
+    // lanes + outputs
+    LaneArrays la;
+    f4* d_frame = nullptr;      // full-frame sum buffer when lanes != pixels (ROWS sharding)
+    uint32_t* d_rgba = nullptr;
+    f4* d_mean = nullptr;
+    uint32_t* h_rgba = nullptr;  // pinned
+    float* h_mean = nullptr;     // pinned
+    size_t fb_pixels = 0;
+    bool rendered = false, resolved = false;
+    b200pt_stats stats{};
+    std::vector<cudaEvent_t> ev_pool;
+};
+
+static void free_lanes(b200pt_ctx* c) {
+    cudaFree(c->la.ray_o); cudaFree(c->la.ray_d); cudaFree(c->la.thr); cudaFree(c->la.sum); cudaFree(c->la.hit);
+    cudaFree(c->la.queue[0]); cudaFree(c->la.queue[1]); cudaFree(c->la.counts); cudaFree(c->la.walk_counters);
+    cudaFree(c->d_frame); cudaFree(c->d_rgba); cudaFree(c->d_mean);
+    if (c->h_rgba) cudaFreeHost(c->h_rgba);
+    if (c->h_mean) cudaFreeHost(c->h_mean);
+    c->la = LaneArrays{};
+    c->d_frame = nullptr; c->d_rgba = nullptr; c->d_mean = nullptr; c->h_rgba = nullptr; c->h_mean = nullptr;
+    c->fb_pixels = 0;
+}
+static void free_scene(b200pt_ctx* c) {
+    cudaFree(c->d_pos); cudaFree(c->d_nrm); cudaFree(c->d_uv); cudaFree(c->d_idx4); cudaFree(c->d_meshes);
+    cudaFree(c->d_texels); cudaFree(c->bvh.nodes); cudaFree(c->bvh.tris);
+    c->d_pos = c->d_nrm = nullptr; c->d_uv = nullptr; c->d_idx4 = nullptr; c->d_meshes = nullptr; c->d_texels = nullptr;
+    c->bvh = DeviceBVH{};
+    c->built = false;
+}
+
+// samples per pixel this rank renders, and the lane -> pixel mapping
+static int rank_samples(const b200pt_ctx* c) {
+    if (c->cfg.world_size <= 1 || c->cfg.shard_mode == B200PT_SHARD_ROWS) return c->max_samples;
+    return c->max_samples / c->cfg.world_size + (c->cfg.rank < c->max_samples % c->cfg.world_size ? 1 : 0);
+}
+static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
+    SceneView sv{};
+    sv.nodes = c->bvh.nodes;
+    sv.tris = c->bvh.tris;
+    sv.idx4 = c->d_idx4;
+    sv.vpos = c->d_pos;
+    sv.vnrm = c->d_nrm;
+    sv.vuv = c->d_uv;
+    sv.meshes = c->d_meshes;
+    sv.materials = c->d_mats;
+    sv.texels = c->d_texels;
+    sv.env = c->d_env;
+    sv.env_w = c->env_w;
+    sv.env_h = c->env_h;
+    sv.env_use = c->env_use;
+    sv.env_auto = c->env_auto;
+    memcpy(sv.env_color, c->env_color, 12);
+    sv.env_intensity = c->env_intensity;
+    memcpy(sv.cam_origin, c->cam, 12);
+    memcpy(sv.cam_llc, c->cam + 3, 12);
+    memcpy(sv.cam_horizontal, c->cam + 6, 12);
+    memcpy(sv.cam_vertical, c->cam + 9, 12);
+    sv.width = c->width;
+    sv.height = c->height;
+    sv.max_samples = full_frame ? c->max_samples : rank_samples(c);
+    sv.max_depth = c->max_depth;
+    sv.n_materials = c->n_mats;
+    sv.row_first = 0;
+    sv.row_step = 1;
+    sv.seed_row_offset = 0;
+    sv.n_lanes = c->width * c->height;
+    if (!full_frame && c->cfg.world_size > 1) {
+        if (c->cfg.shard_mode == B200PT_SHARD_ROWS) {
+            sv.row_first = c->cfg.rank;
+            sv.row_step = c->cfg.world_size;
+            const int rows = c->height > c->cfg.rank ? (c->height - c->cfg.rank + c->cfg.world_size - 1) / c->cfg.world_size : 0;
+            sv.n_lanes = c->width * rows;
+        } else {
+            sv.seed_row_offset = c->cfg.rank * c->height;
+        }
+    }
+    return sv;
+}
+
+extern "C" int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
+    if (!cfg || !out) return fail(B200PT_ERR_INVALID, "b200pt_create: null argument");
+    if (cfg->world_size < 1 || cfg->rank < 0 || cfg->rank >= cfg->world_size)
+        return fail(B200PT_ERR_INVALID, "b200pt_create: bad rank/world_size");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(B200PT_ERR_CUDA, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0") +
+                                         " (this library has no CPU path)");
+    if (cfg->device_ordinal < 0 || cfg->device_ordinal >= ndev) return fail(B200PT_ERR_INVALID, "bad device ordinal");
+    CU(cudaSetDevice(cfg->device_ordinal));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, cfg->device_ordinal));
+    if (prop.major != 10)
+        return fail(B200PT_ERR_CUDA, "device is sm_" + std::to_string(prop.major * 10 + prop.minor) + "; this library is built for sm_100a only");
+    b200pt_ctx* c = new b200pt_ctx();
+    c->cfg = *cfg;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->ev0));
+    CU(cudaEventCreate(&c->ev1));
+    *out = c;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_destroy(b200pt_ctx* c) {
+    if (!c) return B200PT_OK;
+    cudaSetDevice(c->cfg.device_ordinal);
+    cudaStreamSynchronize(c->stream);
+    free_lanes(c);
+    free_scene(c);
+    cudaFree(c->d_env);
+    cudaFree(c->d_mats);
+    for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
+    cudaEventDestroy(c->ev0);
+    cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_add_mesh(b200pt_ctx* c, const float* verts, const float* normals, const float* uvs, int32_t nv,
+                               const int32_t* idx, int32_t nt, int32_t material_index, const uint8_t* tex_rgba,
+                               int32_t tex_w, int32_t tex_h, int32_t* mesh_index) {
+    if (!c || !verts || !normals || !idx || nv <= 0 || nt <= 0) return fail(B200PT_ERR_INVALID, "add_mesh: null/empty input (vertices, normals and indices are required)");
+    if (material_index < 0) return fail(B200PT_ERR_INVALID, "add_mesh: negative material index");
+    if (tex_rgba && (!uvs || tex_w <= 0 || tex_h <= 0)) return fail(B200PT_ERR_INVALID, "add_mesh: texture needs uvs and a size");
+    for (size_t i = 0; i < 3 * (size_t)nt; ++i)
+        if (idx[i] < 0 || idx[i] >= nv) return fail(B200PT_ERR_BOUNDS, "add_mesh: vertex index out of range");
+    const int32_t vbase = (int32_t)c->h_pos.size();
+    const int32_t tbase = (int32_t)(c->h_idx4.size() / 4);
+    const int32_t mesh = (int32_t)c->h_meshes.size();
+    for (int i = 0; i < nv; ++i) {
+        const float x = verts[3 * i], y = verts[3 * i + 1], z = verts[3 * i + 2];
+        c->h_pos.push_back(f4{x, y, z, 0.0f});
+        c->h_nrm.push_back(f4{normals[3 * i], normals[3 * i + 1], normals[3 * i + 2], 0.0f});
+        c->h_uv.push_back(uvs ? f2{uvs[2 * i], uvs[2 * i + 1]} : f2{0.0f, 0.0f});
+        const float p[3] = {x, y, z};
+        for (int a = 0; a < 3; ++a) {
+            c->lo[a] = fminf(c->lo[a], p[a]);
+            c->hi[a] = fmaxf(c->hi[a], p[a]);
+            c->max_abs = fmaxf(c->max_abs, fabsf(p[a]));
+        }
+    }
+    for (int t = 0; t < nt; ++t) {
+        c->h_idx4.push_back(vbase + idx[3 * t]);
+        c->h_idx4.push_back(vbase + idx[3 * t + 1]);
+        c->h_idx4.push_back(vbase + idx[3 * t + 2]);
+        c->h_idx4.push_back(mesh);
+    }
+    MeshInfo mi{};
+    mi.first_tri = tbase;
+    mi.material = material_index;
+    mi.tex_offset = -1;
+    mi.has_uv = uvs ? 1 : 0;
+    if (tex_rgba) {
+        mi.tex_offset = (int32_t)c->h_texels.size();
+        mi.tex_w = tex_w;
+        mi.tex_h = tex_h;
+        const uint32_t* px = reinterpret_cast<const uint32_t*>(tex_rgba);
+        c->h_texels.insert(c->h_texels.end(), px, px + (size_t)tex_w * tex_h);
+    }
+    c->h_meshes.push_back(mi);
+    c->built = false;
+    if (mesh_index) *mesh_index = mesh;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_build_accel(b200pt_ctx* c) {
+    if (!c) return fail(B200PT_ERR_INVALID, "build_accel: null context");
+    if (c->h_meshes.empty()) return fail(B200PT_ERR_EMPTY, "no geometries");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    free_scene(c);
+    const size_t nv = c->h_pos.size(), nt = c->h_idx4.size() / 4;
+    CU(cudaMalloc(&c->d_pos, sizeof(f4) * nv));
+    CU(cudaMalloc(&c->d_nrm, sizeof(f4) * nv));
+    CU(cudaMalloc(&c->d_uv, sizeof(f2) * nv));
+    CU(cudaMalloc(&c->d_idx4, sizeof(int32_t) * 4 * nt));
+    CU(cudaMalloc(&c->d_meshes, sizeof(MeshInfo) * c->h_meshes.size()));
+    CU(cudaMemcpyAsync(c->d_pos, c->h_pos.data(), sizeof(f4) * nv, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_nrm, c->h_nrm.data(), sizeof(f4) * nv, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_uv, c->h_uv.data(), sizeof(f2) * nv, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_idx4, c->h_idx4.data(), sizeof(int32_t) * 4 * nt, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_meshes, c->h_meshes.data(), sizeof(MeshInfo) * c->h_meshes.size(), cudaMemcpyHostToDevice, c->stream));
+    if (!c->h_texels.empty()) {
+        CU(cudaMalloc(&c->d_texels, sizeof(uint32_t) * c->h_texels.size()));
+        CU(cudaMemcpyAsync(c->d_texels, c->h_texels.data(), sizeof(uint32_t) * c->h_texels.size(), cudaMemcpyHostToDevice, c->stream));
+    }
+    CU(cudaEventRecord(c->ev0, c->stream));
+    std::string err;
+    if (!build_bvh_device(c->d_pos, c->d_idx4, (uint32_t)nt, c->lo, c->hi, c->max_abs, &c->bvh, c->stream, err))
+        return fail(B200PT_ERR_CUDA, "bvh build: " + err);
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->stats.build_ms = ms;
+    c->stats.bvh_nodes = c->bvh.n_nodes;
+    c->stats.bvh_tris = c->bvh.n_tris;
+    c->stats.bvh_bytes = (uint64_t)c->bvh.n_nodes * sizeof(Node8) + (uint64_t)c->bvh.n_tris * sizeof(Tri48);
+    c->built = true;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_set_materials(b200pt_ctx* c, const b200pt_material* m, int32_t nm) {
+    if (!c || !m || nm <= 0) return fail(B200PT_ERR_INVALID, "set_materials: null/empty");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    for (const MeshInfo& mi : c->h_meshes)
+        if (mi.material >= nm) return fail(B200PT_ERR_BOUNDS, "set_materials: a mesh refers to material " + std::to_string(mi.material));
+    std::vector<Material> tmp((size_t)nm);
+    for (int i = 0; i < nm; ++i) {
+        memset(&tmp[i], 0, sizeof(Material));
+        memcpy(&tmp[i], &m[i], sizeof(b200pt_material));
+    }
+    if (nm != c->n_mats) {
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_mats);
+        c->d_mats = nullptr;
+        CU(cudaMalloc(&c->d_mats, sizeof(Material) * (size_t)nm));
+        c->n_mats = nm;
+    }
+    CU(cudaMemcpyAsync(c->d_mats, tmp.data(), sizeof(Material) * (size_t)nm, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));  // tmp goes out of scope
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_set_environment(b200pt_ctx* c, const uint8_t* rgba, int32_t w, int32_t h, int32_t use, int32_t auto_,
+                                      const float color[3], float intensity) {
+    if (!c || !color) return fail(B200PT_ERR_INVALID, "set_environment: null");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_env);
+    c->d_env = nullptr;
+    c->env_w = c->env_h = 0;
+    if (rgba && w > 0 && h > 0) {
+        CU(cudaMalloc(&c->d_env, (size_t)w * h * 4));
+        CU(cudaMemcpy(c->d_env, rgba, (size_t)w * h * 4, cudaMemcpyHostToDevice));
+        c->env_w = w;
+        c->env_h = h;
+    }
+    c->env_use = use != 0;
+    c->env_auto = auto_ != 0;
+    memcpy(c->env_color, color, 12);
+    c->env_intensity = intensity;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_set_camera(b200pt_ctx* c, const float origin[3], const float llc[3], const float horizontal[3],
+                                 const float vertical[3]) {
+    if (!c || !origin || !llc || !horizontal || !vertical) return fail(B200PT_ERR_INVALID, "set_camera: null");
+    memcpy(c->cam, origin, 12);
+    memcpy(c->cam + 3, llc, 12);
+    memcpy(c->cam + 6, horizontal, 12);
+    memcpy(c->cam + 9, vertical, 12);
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_set_render(b200pt_ctx* c, int32_t width, int32_t height, int32_t max_samples, int32_t max_path_depth) {
+    if (!c || width <= 0 || height <= 0 || max_samples <= 0 || max_path_depth < 0)
+        return fail(B200PT_ERR_INVALID, "set_render: bad size / sample count");
+    if (max_samples >= (1 << 20) || max_path_depth > 255)
+        return fail(B200PT_ERR_INVALID, "set_render: max_samples < 2^20 and max_path_depth <= 255 supported");
+    if ((int64_t)width * height > (int64_t)1 << 30) return fail(B200PT_ERR_INVALID, "set_render: frame too large");
+    c->width = width;
+    c->height = height;
+    c->max_samples = max_samples;
+    c->max_depth = max_path_depth;
+    c->rendered = c->resolved = false;
+    return B200PT_OK;
+}
+
+// ---------------------------------------------------------------------------- render
+static int ensure_lanes(b200pt_ctx* c, const SceneView& sv) {
+    const size_t px = (size_t)c->width * c->height;
+    const uint32_t need = (uint32_t)std::max(sv.n_lanes, 1);
+    if (c->la.capacity < need || c->fb_pixels != px) {
+        CU(cudaStreamSynchronize(c->stream));
+        free_lanes(c);
+        CU(cudaMalloc(&c->la.ray_o, sizeof(f4) * need));
+        CU(cudaMalloc(&c->la.ray_d, sizeof(f4) * need));
+        CU(cudaMalloc(&c->la.thr, sizeof(f4) * need));
+        CU(cudaMalloc(&c->la.sum, sizeof(f4) * need));
+        CU(cudaMalloc(&c->la.hit, sizeof(f4) * need));
+        CU(cudaMalloc(&c->la.queue[0], sizeof(uint32_t) * need));
+        CU(cudaMalloc(&c->la.queue[1], sizeof(uint32_t) * need));
+        CU(cudaMalloc(&c->la.counts, sizeof(uint32_t) * (kBatch + 1)));
+        CU(cudaMalloc(&c->la.walk_counters, sizeof(unsigned long long) * 2));
+        c->la.capacity = need;
+        if (c->cfg.world_size > 1 && c->cfg.shard_mode == B200PT_SHARD_ROWS) CU(cudaMalloc(&c->d_frame, sizeof(f4) * px));
+        CU(cudaMalloc(&c->d_rgba, sizeof(uint32_t) * px));
+        CU(cudaMalloc(&c->d_mean, sizeof(f4) * px));
+        CU(cudaMallocHost(&c->h_rgba, sizeof(uint32_t) * px));
+        CU(cudaMallocHost(&c->h_mean, sizeof(float) * 4 * px));
+        c->fb_pixels = px;
+    }
+    return B200PT_OK;
+}
+
+static int check_ready(b200pt_ctx* c, const char* who) {
+    if (!c) return fail(B200PT_ERR_INVALID, std::string(who) + ": null context");
+    if (!c->built) return fail(B200PT_ERR_INVALID, std::string(who) + ": call b200pt_build_accel first");
+    if (!c->d_mats) return fail(B200PT_ERR_INVALID, std::string(who) + ": call b200pt_set_materials first");
+    if (c->width <= 0) return fail(B200PT_ERR_INVALID, std::string(who) + ": call b200pt_set_render first");
+    return B200PT_OK;
+}
+
+static int render_local(b200pt_ctx* c) {
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    const SceneView sv = make_view(c, false);
+    if (int r = ensure_lanes(c, sv)) return r;
+    const bool count = (c->cfg.flags & B200PT_FLAG_COUNTERS) != 0;
+    const bool timing = (c->cfg.flags & 4) != 0;
+    cudaStream_t st = c->stream;
+    b200pt_stats& S = c->stats;
+    S.render_ms = S.extend_ms = S.shade_ms = S.other_ms = 0;
+    S.rays = S.paths = S.nodes_visited = S.tris_tested = S.kernel_launches = S.iterations = 0;
+
+    CU(cudaEventRecord(c->ev0, st));
+    CU(cudaMemsetAsync(c->la.counts, 0, sizeof(uint32_t) * (kBatch + 1), st));
+    CU(cudaMemsetAsync(c->la.walk_counters, 0, sizeof(unsigned long long) * 2, st));
+    uint32_t active = 0;
+    if (sv.n_lanes > 0 && sv.max_samples > 0 && sv.max_depth > 0) {
+        launch_init_lanes(sv, c->la, st);
+        S.kernel_launches++;
+        active = (uint32_t)sv.n_lanes;
+        CU(cudaMemcpyAsync(c->la.counts, &active, sizeof active, cudaMemcpyHostToDevice, st));
+    } else {
+        CU(cudaMemsetAsync(c->la.sum, 0, sizeof(f4) * c->la.capacity, st));
+    }
+    if (timing && c->ev_pool.size() < (size_t)(2 * kBatch + 1)) {
+        while (c->ev_pool.size() < (size_t)(2 * kBatch + 1)) {
+            cudaEvent_t e;
+            CU(cudaEventCreate(&e));
+            c->ev_pool.push_back(e);
+        }
+    }
+    uint32_t h_counts[kBatch + 1];
+    while (active > 0) {
+        for (int k = 0; k < kBatch; ++k) {
+            if (timing) CU(cudaEventRecord(c->ev_pool[2 * k], st));
+            launch_extend(sv, c->la, k, active, count, st);
+            if (timing) CU(cudaEventRecord(c->ev_pool[2 * k + 1], st));
+            launch_shade(sv, c->la, k, active, st);
+        }
+        if (timing) CU(cudaEventRecord(c->ev_pool[2 * kBatch], st));
+        S.kernel_launches += 2 * kBatch;
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(h_counts, c->la.counts, sizeof h_counts, cudaMemcpyDeviceToHost, st));
+        // next batch starts from the last queue length; the other slots go back to zero
+        CU(cudaMemcpyAsync(c->la.counts, c->la.counts + kBatch, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        CU(cudaMemsetAsync(c->la.counts + 1, 0, sizeof(uint32_t) * kBatch, st));
+        CU(cudaStreamSynchronize(st));
+        for (int k = 0; k < kBatch; ++k) {
+            S.rays += h_counts[k];
+            if (h_counts[k]) S.iterations++;
+        }
+        if (timing) {
+            for (int k = 0; k < kBatch; ++k) {
+                float a = 0, b = 0;
+                cudaEventElapsedTime(&a, c->ev_pool[2 * k], c->ev_pool[2 * k + 1]);
+                cudaEventElapsedTime(&b, c->ev_pool[2 * k + 1], c->ev_pool[2 * k + 2]);
+                S.extend_ms += a;
+                S.shade_ms += b;
+            }
+        }
+        active = h_counts[kBatch];
+    }
+    if (c->d_frame) {  // ROWS sharding: lane sums -> full frame, zeros elsewhere
+        CU(cudaMemsetAsync(c->d_frame, 0, sizeof(f4) * c->fb_pixels, st));
+        if (sv.n_lanes > 0) launch_scatter_rows(sv, c->la.sum, c->d_frame, st);
+        S.kernel_launches++;
+    }
+    CU(cudaEventRecord(c->ev1, st));
+    CU(cudaStreamSynchronize(st));
+    CU(cudaGetLastError());
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    S.render_ms = ms;
+    S.other_ms = timing ? ms - S.extend_ms - S.shade_ms : 0;
+    S.paths = (uint64_t)std::max(sv.n_lanes, 0) * (uint64_t)sv.max_samples;
+    if (count) {
+        unsigned long long wc[2];
+        CU(cudaMemcpy(wc, c->la.walk_counters, sizeof wc, cudaMemcpyDeviceToHost));
+        S.nodes_visited = wc[0];
+        S.tris_tested = wc[1];
+    }
+    c->rendered = true;
+    c->resolved = false;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_resolve(b200pt_ctx* c) {
+    if (int r = check_ready(c, "resolve")) return r;
+    if (!c->rendered) return fail(B200PT_ERR_INVALID, "resolve: nothing rendered");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    const SceneView full = make_view(c, true);
+    const f4* src = c->d_frame ? c->d_frame : c->la.sum;
+    const float inv = 1.0f / static_cast<float>(c->max_samples);  // device.cu:247
+    launch_resolve(full, src, inv, c->d_rgba, c->d_mean, c->stream);
+    c->stats.kernel_launches++;
+    CU(cudaMemcpyAsync(c->h_rgba, c->d_rgba, sizeof(uint32_t) * c->fb_pixels, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->h_mean, c->d_mean, sizeof(f4) * c->fb_pixels, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    c->resolved = true;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_render(b200pt_ctx* c) {
+    if (int r = check_ready(c, "render")) return r;
+    if (int r = render_local(c)) return r;
+    if (c->cfg.world_size == 1) return b200pt_resolve(c);
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_accum_buffer(b200pt_ctx* c, void** device_ptr, size_t* n_floats) {
+    if (!c || !device_ptr || !n_floats) return fail(B200PT_ERR_INVALID, "accum_buffer: null");
+    if (!c->rendered) return fail(B200PT_ERR_INVALID, "accum_buffer: nothing rendered");
+    *device_ptr = c->d_frame ? (void*)c->d_frame : (void*)c->la.sum;
+    *n_floats = 4 * c->fb_pixels;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_render_to_host(b200pt_ctx* c, const b200pt_material* m, int32_t nm, uint32_t* rgba_out) {
+    if (!rgba_out) return fail(B200PT_ERR_INVALID, "render_to_host: null output");
+    if (m)
+        if (int r = b200pt_set_materials(c, m, nm)) return r;
+    if (int r = b200pt_render(c)) return r;
+    if (!c->resolved) return fail(B200PT_ERR_INVALID, "render_to_host: multi-rank contexts resolve on rank 0 after the reduce");
+    memcpy(rgba_out, c->h_rgba, sizeof(uint32_t) * c->fb_pixels);
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_framebuffer_rgba8(b200pt_ctx* c, const uint32_t** out) {
+    if (!c || !out) return fail(B200PT_ERR_INVALID, "framebuffer: null");
+    if (!c->resolved) return fail(B200PT_ERR_INVALID, "framebuffer: no resolved frame");
+    *out = c->h_rgba;
+    return B200PT_OK;
+}
+extern "C" int b200pt_framebuffer_f32(b200pt_ctx* c, const float** out) {
+    if (!c || !out) return fail(B200PT_ERR_INVALID, "framebuffer: null");
+    if (!c->resolved) return fail(B200PT_ERR_INVALID, "framebuffer: no resolved frame");
+    *out = c->h_mean;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_get_stats(b200pt_ctx* c, b200pt_stats* out) {
+    if (!c || !out) return fail(B200PT_ERR_INVALID, "stats: null");
+    *out = c->stats;
+    return B200PT_OK;
+}
+
+// ---------------------------------------------------------------------------- parity hooks
+static void hits_to_records(const b200pt_ctx* c, const std::vector<f4>& raw, float tmax, b200pt_hit* out) {
+    for (size_t i = 0; i < raw.size(); ++i) {
+        const uint32_t tri = f2u(raw[i].w);
+        if (tri == kNoHit) {
+            out[i] = b200pt_hit{-1, -1, tmax, 0.0f, 0.0f};
+        } else {
+            const int32_t mesh = c->h_idx4[4 * (size_t)tri + 3];
+            out[i] = b200pt_hit{mesh, (int32_t)tri - c->h_meshes[mesh].first_tri, raw[i].x, raw[i].y, raw[i].z};
+        }
+    }
+}
+
+extern "C" int b200pt_primary_hits(b200pt_ctx* c, b200pt_hit* out) {
+    if (int r = check_ready(c, "primary_hits")) return r;
+    if (!out) return fail(B200PT_ERR_INVALID, "primary_hits: null output");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    const SceneView full = make_view(c, true);
+    const size_t n = (size_t)c->width * c->height;
+    f4* d_hits = nullptr;
+    CU(cudaMalloc(&d_hits, sizeof(f4) * n));
+    launch_primary(full, d_hits, c->stream);
+    std::vector<f4> raw(n);
+    cudaError_t e = cudaMemcpyAsync(raw.data(), d_hits, sizeof(f4) * n, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_hits);
+    if (e != cudaSuccess) return fail(B200PT_ERR_CUDA, std::string("primary_hits: ") + cudaGetErrorString(e));
+    hits_to_records(c, raw, kTMax, out);
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_trace(b200pt_ctx* c, const float* origins, const float* dirs, int32_t n, float tmin, float tmax,
+                            b200pt_hit* out) {
+    if (!c || !c->built) return fail(B200PT_ERR_INVALID, "trace: call b200pt_build_accel first");
+    if (!origins || !dirs || !out || n <= 0) return fail(B200PT_ERR_INVALID, "trace: null/empty");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    SceneView sv{};
+    sv.nodes = c->bvh.nodes;
+    sv.tris = c->bvh.tris;
+    float *d_o = nullptr, *d_d = nullptr;
+    f4* d_hits = nullptr;
+    CU(cudaMalloc(&d_o, sizeof(float) * 3 * (size_t)n));
+    CU(cudaMalloc(&d_d, sizeof(float) * 3 * (size_t)n));
+    CU(cudaMalloc(&d_hits, sizeof(f4) * (size_t)n));
+    std::vector<f4> raw((size_t)n);
+    cudaError_t e = cudaMemcpyAsync(d_o, origins, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_d, dirs, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        launch_trace(sv, d_o, d_d, n, tmin, tmax, d_hits, c->stream);
+        e = cudaMemcpyAsync(raw.data(), d_hits, sizeof(f4) * (size_t)n, cudaMemcpyDeviceToHost, c->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_o); cudaFree(d_d); cudaFree(d_hits);
+    if (e != cudaSuccess) return fail(B200PT_ERR_CUDA, std::string("trace: ") + cudaGetErrorString(e));
+    hits_to_records(c, raw, tmax, out);
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_sample_disney(b200pt_ctx* c, int32_t n, const int32_t* material, const float* wo, const int32_t* lobe_in,
+                                    const uint32_t* rng_in, float* f, float* wi, float* pdf, int32_t* lobe_out,
+                                    uint32_t* rng_out) {
+    if (!c || !c->d_mats) return fail(B200PT_ERR_INVALID, "sample_disney: call b200pt_set_materials first");
+    if (n <= 0 || !material || !wo || !lobe_in || !rng_in || !f || !wi || !pdf || !lobe_out || !rng_out)
+        return fail(B200PT_ERR_INVALID, "sample_disney: null/empty");
+    for (int i = 0; i < n; ++i)
+        if (material[i] < 0 || material[i] >= c->n_mats) return fail(B200PT_ERR_BOUNDS, "sample_disney: material index out of range");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    const size_t N = (size_t)n;
+    char* d = nullptr;  // one allocation: material, lobe_in, rng_in, lobe_out, rng_out, pdf (4 B each), wo, f, wi (12 B each)
+    CU(cudaMalloc(&d, N * (6 * 4 + 3 * 12)));
+    int32_t* d_mat = (int32_t*)d;
+    int32_t* d_li = d_mat + N;
+    uint32_t* d_ri = (uint32_t*)(d_li + N);
+    int32_t* d_lo = (int32_t*)(d_ri + N);
+    uint32_t* d_ro = (uint32_t*)(d_lo + N);
+    float* d_pdf = (float*)(d_ro + N);
+    float* d_wo = d_pdf + N;
+    float* d_f = d_wo + 3 * N;
+    float* d_wi = d_f + 3 * N;
+    cudaStream_t st = c->stream;
+    cudaError_t e = cudaMemcpyAsync(d_mat, material, 4 * N, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_li, lobe_in, 4 * N, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_ri, rng_in, 4 * N, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_wo, wo, 12 * N, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        launch_sample_disney(c->d_mats, n, d_mat, d_wo, d_li, d_ri, d_f, d_wi, d_pdf, d_lo, d_ro, st);
+        e = cudaMemcpyAsync(f, d_f, 12 * N, cudaMemcpyDeviceToHost, st);
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(wi, d_wi, 12 * N, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(pdf, d_pdf, 4 * N, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(lobe_out, d_lo, 4 * N, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rng_out, d_ro, 4 * N, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(B200PT_ERR_CUDA, std::string("sample_disney: ") + cudaGetErrorString(e));
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_export_bvh(b200pt_ctx* c, void* nodes, uint32_t* n_nodes, void* tris, uint32_t* n_tris) {
+    if (!c || !c->built) return fail(B200PT_ERR_INVALID, "export_bvh: call b200pt_build_accel first");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    if (n_nodes) *n_nodes = c->bvh.n_nodes;
+    if (n_tris) *n_tris = c->bvh.n_tris;
+    if (nodes) CU(cudaMemcpy(nodes, c->bvh.nodes, sizeof(Node8) * (size_t)c->bvh.n_nodes, cudaMemcpyDeviceToHost));
+    if (tris) CU(cudaMemcpy(tris, c->bvh.tris, sizeof(Tri48) * (size_t)c->bvh.n_tris, cudaMemcpyDeviceToHost));
+    return B200PT_OK;
+}

@@ -1,0 +1,52 @@
+// device_ctx.h — context object behind the C ABI (include/b200pt.h) and the launch
+// wrappers shared between api.cu, wavefront.cu and bvh_build.cu.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/b200pt.h"
+#include "pt_integrator.h"
+
+namespace pt {
+
+struct DeviceBVH {
+    Node8* nodes = nullptr;
+    Tri48* tris = nullptr;
+    uint32_t n_nodes = 0, n_tris = 0;
+    int levels = 0;
+};
+
+bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const float scene_lo[3],
+                      const float scene_hi[3], float max_abs, DeviceBVH* out, cudaStream_t st, std::string& err);
+
+// per-lane state, structure of arrays, 16-byte elements (one LDG.128 / STG.128 each)
+struct LaneArrays {
+    f4* ray_o = nullptr;   // origin.xyz, -
+    f4* ray_d = nullptr;   // direction.xyz, control word (pack_ctl)
+    f4* thr = nullptr;     // throughput.xyz, RNG state
+    f4* sum = nullptr;     // sum of finished samples .xyz, -   (this is the accumulation buffer)
+    f4* hit = nullptr;     // t, u, v, triangle id
+    uint32_t* queue[2] = {nullptr, nullptr};
+    uint32_t* counts = nullptr;   // kBatch + 1 queue lengths
+    unsigned long long* walk_counters = nullptr;  // nodes, tris (FLAG_COUNTERS)
+    uint32_t capacity = 0;
+};
+
+constexpr int kBatch = 32;  // wavefront iterations between host checks (even)
+
+// launch wrappers (wavefront.cu)
+void launch_init_lanes(const SceneView& sv, const LaneArrays& la, cudaStream_t st);
+void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st);
+void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
+void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st);
+void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStream_t st);
+void launch_primary(const SceneView& sv, f4* hits, cudaStream_t st);
+void launch_trace(const SceneView& sv, const float* o, const float* d, int n, float tmin, float tmax, f4* hits,
+                  cudaStream_t st);
+void launch_sample_disney(const Material* mats, int n, const int32_t* material, const float* wo, const int32_t* lobe_in,
+                          const uint32_t* rng_in, float* f, float* wi, float* pdf, int32_t* lobe_out, uint32_t* rng_out,
+                          cudaStream_t st);
+
+}  // namespace pt

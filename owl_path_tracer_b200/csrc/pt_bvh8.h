@@ -1,0 +1,228 @@
+// pt_bvh8.h — compressed 8-wide BVH: node layout, ray/triangle test, closest-hit walk.
+//
+// This replaces what the reference gets from the OptiX driver (optixAccelBuild +
+// optixTrace on RT cores; call sites device.cu:133, application.cpp:131-140).  B200
+// has no RT cores, so traversal is ordinary SM code and the tree is laid out for
+// bytes: 80-byte nodes with 8-bit quantised child boxes (the layout of Ylitie,
+// Karras & Laine, "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide
+// BVHs", HPG 2017) and 48-byte triangles stored in node order.
+//
+// Result definition (the parity contract): the closest hit is the triangle with the
+// smallest Moller-Trumbore t in (tmin, tmax); equal t is broken towards the smaller
+// global triangle id.  That is independent of the tree and of the visiting order, so
+// the scalar oracle (own binary BVH or brute force) must return the same triangle
+// and the same (t,u,v) bits.  Child boxes are padded by the builder so that the
+// rounding of the slab test can never cull a triangle the test would accept.
+#pragma once
+#include "pt_defs.h"
+
+namespace pt {
+
+struct alignas(16) u4 {
+    uint32_t x, y, z, w;
+};
+struct alignas(16) f4 {
+    float x, y, z, w;
+};
+
+PT_HD uint32_t f2u(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(f);
+#else
+    union { float f; uint32_t u; } c;
+    c.f = f;
+    return c.u;
+#endif
+}
+PT_HD float u2f(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    union { float f; uint32_t u; } c;
+    c.u = u;
+    return c.f;
+#endif
+}
+PT_HD int popc32(uint32_t v) {
+#if defined(__CUDA_ARCH__)
+    return __popc(v);
+#else
+    return __builtin_popcount(v);
+#endif
+}
+PT_HD int msb32(uint32_t v) {  // index of highest set bit, v != 0
+#if defined(__CUDA_ARCH__)
+    return 31 - __clz(v);
+#else
+    return 31 - __builtin_clz(v);
+#endif
+}
+
+// 80-byte node as five 16-byte words:
+//  w0: px, py, pz, {ex, ey, ez, imask}
+//  w1: child_base, tri_base, meta[0..3], meta[4..7]
+//  w2: qlo_x[0..7], qlo_y[0..7]
+//  w3: qlo_z[0..7], qhi_x[0..7]
+//  w4: qhi_y[0..7], qhi_z[0..7]
+// meta[i]: 0 = empty; internal child: (1<<5) | (24+i); leaf: (unary tri count << 5) |
+// offset of its first triangle from tri_base (1..3 triangles -> 001, 011, 111).
+struct Node8 {
+    u4 w[5];
+};
+static_assert(sizeof(Node8) == 80, "Node8 is 80 bytes");
+
+// 48-byte triangle: v0 + edges, prepared once so the walk does no index chasing.
+//  a: v0.xyz, global triangle id (bits)   b: e1.xyz, 0   c: e2.xyz, 0
+struct Tri48 {
+    f4 a, b, c;
+};
+static_assert(sizeof(Tri48) == 48, "Tri48 is 48 bytes");
+
+struct Hit {
+    float t, u, v;
+    uint32_t tri;  // global triangle id, 0xFFFFFFFF = miss
+};
+constexpr uint32_t kNoHit = 0xFFFFFFFFu;
+constexpr int kStackSize = 32;  // node groups; the builder refuses deeper trees
+
+// Moller-Trumbore with edges e1 = v1 - v0, e2 = v2 - v0.  Expression order is part of
+// the parity contract (oracle/oracle.cpp ray_triangle mirrors it):
+//   p = d x e2, det = e1 . p, inv = 1/det, s = o - v0, u = (s . p) inv,
+//   q = s x e1, v = (d . q) inv, t = (e2 . q) inv;  accept 0<=u<=1, v>=0, u+v<=1,
+//   tmin < t < tmax.  Barycentrics follow OptiX: P = (1-u-v) v0 + u v1 + v v2.
+PT_HD bool ray_triangle(f3 o, f3 d, f3 v0, f3 e1, f3 e2, float tmin, float tmax, float& t, float& u,
+                        float& v) {
+    f3 p = cross(d, e2);
+    float det = dot(e1, p);
+    if (!(det != 0.0f)) return false;
+    float inv = 1.0f / det;
+    f3 s = o - v0;
+    float uu = dot(s, p) * inv;
+    if (!(uu >= 0.0f && uu <= 1.0f)) return false;
+    f3 q = cross(s, e1);
+    float vv = dot(d, q) * inv;
+    if (!(vv >= 0.0f && uu + vv <= 1.0f)) return false;
+    float tt = dot(e2, q) * inv;
+    if (!(tt > tmin && tt < tmax)) return false;
+    t = tt;
+    u = uu;
+    v = vv;
+    return true;
+}
+
+PT_HD float safe_rcp_dir(float d) {
+    float a = fabsf(d) < 1e-30f ? (d < 0.0f ? -1e-30f : 1e-30f) : d;
+    return 1.0f / a;
+}
+
+struct WalkCounters {
+    uint32_t nodes, tris;
+};
+
+// Closest-hit walk.  COUNT=true also counts node fetches and triangle tests.
+template <bool COUNT>
+PT_HD void walk_closest(const Node8* __restrict__ nodes, const Tri48* __restrict__ tris, f3 o, f3 d,
+                        float tmin, float tmax, Hit& hit, WalkCounters* wc) {
+    hit.t = tmax;
+    hit.u = 0.0f;
+    hit.v = 0.0f;
+    hit.tri = kNoHit;
+
+    const float idx = safe_rcp_dir(d.x), idy = safe_rcp_dir(d.y), idz = safe_rcp_dir(d.z);
+    const uint32_t octinv = (d.x < 0.0f ? 0u : 4u) | (d.y < 0.0f ? 0u : 2u) | (d.z < 0.0f ? 0u : 1u);
+
+    uint32_t stack_base[kStackSize];
+    uint32_t stack_mask[kStackSize];
+    int sp = 0;
+
+    uint32_t ng_base = 0, ng_mask = 0x80000000u;  // node group: root
+    for (;;) {
+        uint32_t tg_base = 0, tg_mask = 0;
+        if (ng_mask > 0x00FFFFFFu) {
+            // pop the nearest (octant order) child of the current node group
+            const int bit = msb32(ng_mask);
+            const uint32_t imask = ng_mask & 0xFFu;
+            ng_mask &= ~(1u << bit);
+            if (ng_mask > 0x00FFFFFFu) {
+                stack_base[sp] = ng_base;
+                stack_mask[sp] = ng_mask;
+                ++sp;
+            }
+            const uint32_t slot = (uint32_t)(bit - 24) ^ octinv;
+            const uint32_t rel = (uint32_t)popc32(imask & ~(0xFFFFFFFFu << slot));
+            const Node8* np = nodes + (ng_base + rel);
+            const u4 w0 = np->w[0], w1 = np->w[1], w2 = np->w[2], w3 = np->w[3], w4 = np->w[4];
+            if (COUNT) wc->nodes++;
+
+            const uint32_t e = w0.w;
+            const float sx = u2f((e & 0xFFu) << 23), sy = u2f(((e >> 8) & 0xFFu) << 23),
+                        sz = u2f(((e >> 16) & 0xFFu) << 23);
+            const float aix = sx * idx, aiy = sy * idy, aiz = sz * idz;
+            const float aox = (u2f(w0.x) - o.x) * idx, aoy = (u2f(w0.y) - o.y) * idy,
+                        aoz = (u2f(w0.z) - o.z) * idz;
+            uint32_t hitmask = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int sh = (i & 3) * 8;
+                const uint32_t meta = ((i < 4 ? w1.z : w1.w) >> sh) & 0xFFu;
+                if (meta == 0) continue;
+                const float lox = (float)(((i < 4 ? w2.x : w2.y) >> sh) & 0xFFu);
+                const float loy = (float)(((i < 4 ? w2.z : w2.w) >> sh) & 0xFFu);
+                const float loz = (float)(((i < 4 ? w3.x : w3.y) >> sh) & 0xFFu);
+                const float hix = (float)(((i < 4 ? w3.z : w3.w) >> sh) & 0xFFu);
+                const float hiy = (float)(((i < 4 ? w4.x : w4.y) >> sh) & 0xFFu);
+                const float hiz = (float)(((i < 4 ? w4.z : w4.w) >> sh) & 0xFFu);
+                const float nx = d.x < 0.0f ? hix : lox, fx = d.x < 0.0f ? lox : hix;
+                const float ny = d.y < 0.0f ? hiy : loy, fy = d.y < 0.0f ? loy : hiy;
+                const float nz = d.z < 0.0f ? hiz : loz, fz = d.z < 0.0f ? loz : hiz;
+                const float tn = fmaxf(fmaxf(fmaf(nx, aix, aox), fmaf(ny, aiy, aoy)),
+                                       fmaxf(fmaf(nz, aiz, aoz), tmin));
+                const float tf = fminf(fminf(fmaf(fx, aix, aox), fmaf(fy, aiy, aoy)),
+                                       fminf(fmaf(fz, aiz, aoz), hit.t));
+                if (tn <= tf) {
+                    const bool inner = (meta & 0x18u) == 0x18u;
+                    const uint32_t bidx = inner ? ((meta & 0x1Fu) ^ octinv) : (meta & 0x1Fu);
+                    hitmask |= (meta >> 5) << bidx;
+                }
+            }
+            ng_base = w1.x;
+            ng_mask = (hitmask & 0xFF000000u) | (e >> 24);
+            tg_base = w1.y;
+            tg_mask = hitmask & 0x00FFFFFFu;
+        } else {
+            tg_base = ng_base;
+            tg_mask = ng_mask;
+            ng_base = 0;
+            ng_mask = 0;
+        }
+
+        while (tg_mask != 0) {
+            const int bit = msb32(tg_mask);
+            tg_mask &= ~(1u << bit);
+            const Tri48* tp = tris + (tg_base + (uint32_t)bit);
+            const f4 a = tp->a, b = tp->b, c = tp->c;
+            if (COUNT) wc->tris++;
+            float t, u, v;
+            if (ray_triangle(o, d, f3{a.x, a.y, a.z}, f3{b.x, b.y, b.z}, f3{c.x, c.y, c.z}, tmin, tmax, t,
+                             u, v)) {
+                const uint32_t id = f2u(a.w);
+                if (t < hit.t || (t == hit.t && id < hit.tri)) {
+                    hit.t = t;
+                    hit.u = u;
+                    hit.v = v;
+                    hit.tri = id;
+                }
+            }
+        }
+
+        if (ng_mask <= 0x00FFFFFFu) {
+            if (sp == 0) break;
+            --sp;
+            ng_base = stack_base[sp];
+            ng_mask = stack_mask[sp];
+        }
+    }
+    if (hit.tri == kNoHit) hit.t = tmax;
+}
+
+}  // namespace pt

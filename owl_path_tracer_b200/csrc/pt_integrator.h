@@ -1,0 +1,217 @@
+// pt_integrator.h — per-lane logic of the wavefront: camera ray generation and the
+// shade step (one path vertex).  Together with walk_closest (pt_bvh8.h) this restates
+// __raygen__ray_gen and trace_path of the reference (device.cu:113-254) as a state
+// machine: a lane is one pixel, it owns the pixel's RNG stream and walks through that
+// pixel's samples one after the other, exactly in the order the reference's per-pixel
+// thread does.  Regenerating the next camera ray inside the shade step is
+// what keeps every lane busy until its pixel is finished.
+#pragma once
+#include "pt_bvh8.h"
+#include "pt_disney.h"
+
+namespace pt {
+
+struct MeshInfo {
+    int32_t first_tri;    // global id of this mesh's primitive 0
+    int32_t material;     // material_index (entity_data, device_global.hpp:38-44)
+    int32_t tex_offset;   // first texel in the texture pool, -1 = no texture
+    int32_t tex_w, tex_h;
+    int32_t has_uv;
+    int32_t pad0, pad1;
+};
+
+struct SceneView {
+    const Node8* nodes;
+    const Tri48* tris;
+    const int32_t* idx4;       // per global triangle: 3 global vertex ids + mesh index
+    const f4* vpos;            // per global vertex
+    const f4* vnrm;
+    const f2* vuv;
+    const MeshInfo* meshes;
+    const Material* materials;
+    const uint32_t* texels;    // RGBA8 pool (mesh textures)
+    const uint32_t* env;       // RGBA8 environment map or nullptr
+    int32_t env_w, env_h;
+    int32_t env_use, env_auto;
+    float env_color[3];
+    float env_intensity;
+    float cam_origin[3], cam_llc[3], cam_horizontal[3], cam_vertical[3];
+    int32_t width, height;     // full frame
+    int32_t max_samples;       // samples this rank renders per pixel
+    int32_t max_depth;
+    int32_t n_materials;
+    // lane -> pixel:  x = lane % width, y = row_first + row_step * (lane / width)
+    int32_t row_first, row_step;
+    int32_t seed_row_offset;   // added to y when seeding (per-rank streams: rank * height)
+    int32_t n_lanes;
+};
+
+// packed per-lane control word: sample index (20 bits) | depth (8 bits) | lobe+1 (3 bits)
+PT_HD uint32_t pack_ctl(uint32_t sample, uint32_t depth, int lobe) {
+    return (sample & 0xFFFFFu) | ((depth & 0xFFu) << 20) | (((uint32_t)(lobe + 1) & 7u) << 28);
+}
+PT_HD uint32_t ctl_sample(uint32_t c) { return c & 0xFFFFFu; }
+PT_HD uint32_t ctl_depth(uint32_t c) { return (c >> 20) & 0xFFu; }
+PT_HD int ctl_lobe(uint32_t c) { return (int)((c >> 28) & 7u) - 1; }
+
+PT_HD void lane_pixel(const SceneView& sv, uint32_t lane, int& x, int& y) {
+    x = (int)(lane % (uint32_t)sv.width);
+    y = sv.row_first + sv.row_step * (int)(lane / (uint32_t)sv.width);
+}
+
+// device.cu:231-241: jitter (x draw first), screen = (pixel + rand) / fb_size,
+// direction = normalize(llc + u*horizontal + v*vertical - origin)
+PT_HD void camera_ray(const SceneView& sv, int px, int py, uint32_t& rng, f3& o, f3& d) {
+    const float rx = rng_next(rng);
+    const float ry = rng_next(rng);
+    const float su = ((float)px + rx) / (float)sv.width;
+    const float sv_ = ((float)py + ry) / (float)sv.height;
+    const f3 org{sv.cam_origin[0], sv.cam_origin[1], sv.cam_origin[2]};
+    const f3 llc{sv.cam_llc[0], sv.cam_llc[1], sv.cam_llc[2]};
+    const f3 hor{sv.cam_horizontal[0], sv.cam_horizontal[1], sv.cam_horizontal[2]};
+    const f3 ver{sv.cam_vertical[0], sv.cam_vertical[1], sv.cam_vertical[2]};
+    o = org;
+    d = normalize(llc + su * hor + sv_ * ver - org);
+}
+
+// device.cu:23-39 + owl.hpp:248-257: RGBA8, point filter, clamp, normalised coords
+PT_HD f3 fetch_rgba8(const uint32_t* img, int w, int h, float u, float v) {
+    float fx = floorf(u * (float)w), fy = floorf(v * (float)h);
+    int ix = (fx >= 0.0f) ? (fx < (float)w ? (int)fx : w - 1) : 0;  // NaN -> 0
+    int iy = (fy >= 0.0f) ? (fy < (float)h ? (int)fy : h - 1) : 0;
+    const uint32_t p = img[(size_t)iy * (size_t)w + (size_t)ix];
+    return f3{(float)(p & 0xFFu) / 255.0f, (float)((p >> 8) & 0xFFu) / 255.0f,
+              (float)((p >> 16) & 0xFFu) / 255.0f};
+}
+
+// miss branch of trace_path, device.cu:136-148
+PT_HD f3 miss_radiance(const SceneView& sv, f3 dir) {
+    f3 rad = mk3(0.0f);
+    if (sv.env_use && sv.env) {
+        const float u = 0.5f + dm_atan2(dir.x, dir.z) / (2.0f * kPi);
+        const float v = 0.5f + dm_asin(dir.y) / kPi;
+        rad = rad + fetch_rgba8(sv.env, sv.env_w, sv.env_h, u, v);
+    } else if (sv.env_auto) {
+        rad = rad + lerp3(mk3(1.0f), f3{0.5f, 0.7f, 1.0f}, 0.5f * (dir.y + 1.0f));
+    } else {
+        rad = rad + f3{sv.env_color[0], sv.env_color[1], sv.env_color[2]};
+    }
+    return rad * sv.env_intensity;
+}
+
+// state of one lane as the shade step sees it
+struct LaneState {
+    f3 o, d;          // current ray
+    f3 thr;           // throughput
+    f3 contrib;       // value of the sample that just ended (valid when sample_ended)
+    bool sample_ended;
+    uint32_t rng;
+    uint32_t sample;  // index of the sample in flight
+    uint32_t depth;   // loop counter of trace_path
+    int lobe;         // sampled_lobe, persists across bounces (device.cu:127)
+};
+
+enum ShadeResult { LANE_CONTINUE = 0, LANE_DONE = 1 };
+
+PT_HD bool bad3(f3 v) {
+    return isinf(v.x) || isinf(v.y) || isinf(v.z) || isnan(v.x) || isnan(v.y) || isnan(v.z);
+}
+
+// finish the sample in flight with `contrib`, then start the next one or retire the lane
+PT_HD ShadeResult end_sample(const SceneView& sv, LaneState& L, int px, int py, f3 contrib) {
+    L.contrib = contrib;  // caller does color += trace_path(...), device.cu:243
+    L.sample_ended = true;
+    L.sample += 1;
+    if (L.sample >= (uint32_t)sv.max_samples) return LANE_DONE;
+    camera_ray(sv, px, py, L.rng, L.o, L.d);
+    L.thr = mk3(1.0f);
+    L.depth = 0;
+    L.lobe = LOBE_NONE;
+    return LANE_CONTINUE;
+}
+
+// One iteration of the loop body of trace_path (device.cu:130-215) for a lane whose
+// ray has just been traced.  Returns LANE_DONE when the pixel's last sample ended.
+PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, int px, int py) {
+    L.sample_ended = false;
+    if (hit.tri == kNoHit) {
+        const f3 rad = miss_radiance(sv, L.d);
+        return end_sample(sv, L, px, py, rad * L.thr);
+    }
+    const int32_t* ix = sv.idx4 + 4 * (size_t)hit.tri;
+    const int i0 = ix[0], i1 = ix[1], i2 = ix[2], mesh = ix[3];
+    const MeshInfo mi = sv.meshes[mesh];
+    Material m = sv.materials[mi.material];
+
+    if (m.emission > 0.0f) {  // device.cu:157-161: radiance = emission (overwrites)
+        return end_sample(sv, L, px, py, mk3(m.emission) * L.thr);
+    }
+
+    const float bu = hit.u, bv = hit.v;
+    const float bw = 1.0f - bu - bv;
+    const f4 p0 = sv.vpos[i0], p1 = sv.vpos[i1], p2 = sv.vpos[i2];
+    const f3 vp = bw * f3{p0.x, p0.y, p0.z} + bu * f3{p1.x, p1.y, p1.z} + bv * f3{p2.x, p2.y, p2.z};
+    const f4 n0 = sv.vnrm[i0], n1 = sv.vnrm[i1], n2 = sv.vnrm[i2];
+    const f3 vn = normalize(bw * f3{n0.x, n0.y, n0.z} + bu * f3{n1.x, n1.y, n1.z} + bv * f3{n2.x, n2.y, n2.z});
+    if (mi.tex_offset >= 0) {  // device.cu:75-94
+        const f2 t0 = sv.vuv[i0], t1 = sv.vuv[i1], t2 = sv.vuv[i2];
+        const float tu = bw * t0.x + bu * t1.x + bv * t2.x;
+        const float tv = bw * t0.y + bu * t1.y + bv * t2.y;
+        const f3 c = fetch_rgba8(sv.texels + mi.tex_offset, mi.tex_w, mi.tex_h, tu, tv);
+        m.base_color[0] = c.x;
+        m.base_color[1] = c.y;
+        m.base_color[2] = c.z;
+    }
+
+    // device.cu:176-181 and math.hpp:86-107
+    const f3 wo = -normalize(L.d);
+    f3 T;
+    if (vn.x != vn.y || vn.x != vn.z)
+        T = f3{vn.z - vn.y, vn.x - vn.z, vn.y - vn.x};
+    else
+        T = f3{vn.z - vn.y, vn.x + vn.z, -vn.y - vn.x};
+    T = normalize(T);
+    const f3 B = cross(vn, T);
+    const f3 lwo = normalize(f3{dot(wo, T), dot(wo, B), dot(wo, vn)});
+
+    // The reference re-traces the same ray when f is inf/nan (--depth; continue,
+    // device.cu:196-201).  The trace is deterministic, so the retry only redraws the
+    // BSDF sample; we loop here instead of going round the wavefront again.
+    for (int attempt = 0; attempt < 64; ++attempt) {
+        BsdfSample s;
+        s.wi = mk3(0.0f);
+        s.pdf = 0.0f;
+        s.f = mk3(0.0f);
+        sample_disney(m, lwo, L.rng, L.lobe, s);
+        const f3 wi = normalize(s.wi.x * T + s.wi.y * B + s.wi.z * vn);
+        if (s.pdf < 1E-5f) return end_sample(sv, L, px, py, mk3(0.0f) * L.thr);
+        if (bad3(s.f)) continue;
+        L.thr = L.thr * (s.f * fabsf(s.wi.z) / s.pdf);
+        L.o = vp;
+        L.d = wi;
+        const float bmax = fmaxf(L.thr.x, fmaxf(L.thr.y, L.thr.z));
+        if (L.lobe != LOBE_GLASS && L.depth > 3) {  // inverted, uncompensated RR (Q14)
+            const float q = fmaxf(.05f, 1.0f - bmax);
+            if (rng_next(L.rng) > q) return end_sample(sv, L, px, py, mk3(0.0f) * L.thr);
+        }
+        L.depth += 1;
+        if (L.depth >= (uint32_t)sv.max_depth) return end_sample(sv, L, px, py, mk3(0.0f) * L.thr);
+        return LANE_CONTINUE;
+    }
+    return end_sample(sv, L, px, py, mk3(0.0f) * L.thr);
+}
+
+// make_8bit / make_rgba, owl_device.h:79-91.  int(f*256) of NaN is 0 on the device
+// (cvt.rzi.s32.f32), made explicit here so host and device agree.
+PT_HD uint32_t to_8bit(float f) {
+    const float s = f * 256.f;
+    if (!(s == s)) return 0u;
+    if (s >= 255.0f) return 255u;
+    if (s <= 0.0f) return 0u;
+    return (uint32_t)(int)s;
+}
+PT_HD uint32_t to_rgba(f3 c) {
+    return (to_8bit(c.x) << 0) + (to_8bit(c.y) << 8) + (to_8bit(c.z) << 16) + (0xffU << 24);
+}
+
+}  // namespace pt

@@ -1,0 +1,212 @@
+// wavefront.cu — the kernels of the render loop (sm_100a).
+//
+//   k_init_lanes  raygen for sample 0 of every pixel            (device.cu:220-241)
+//   k_extend      closest hit of every queued ray               (replaces optixTrace, device.cu:133)
+//   k_shade       one path vertex: miss / emission / Disney sample / RR, next camera
+//                 ray when a sample ends, warp-ballot compaction of the surviving lanes
+//                                                              (device.cu:136-215, 229-243)
+//   k_resolve     mean, RGBA8 pack, row flip                    (device.cu:246-253)
+// plus small parity-hook kernels.  Compiled with -fmad=false: the arithmetic must round
+// like the scalar oracle's (pt_defs.h); the slab test uses explicit fmaf.
+#include "device_ctx.h"
+
+namespace pt {
+
+constexpr int kBlock = 128;
+
+__device__ __forceinline__ f4 ld4(const f4* p) {
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    return f4{v.x, v.y, v.z, v.w};
+}
+__device__ __forceinline__ void st4(f4* p, f4 v) { *reinterpret_cast<float4*>(p) = make_float4(v.x, v.y, v.z, v.w); }
+
+__global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays la) {
+    const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= (uint32_t)sv.n_lanes) return;
+    int px, py;
+    lane_pixel(sv, lane, px, py);
+    uint32_t rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset));  // device.cu:226
+    f3 o, d;
+    camera_ray(sv, px, py, rng, o, d);
+    st4(la.ray_o + lane, f4{o.x, o.y, o.z, 0.0f});
+    st4(la.ray_d + lane, f4{d.x, d.y, d.z, u2f(pack_ctl(0, 0, LOBE_NONE))});
+    st4(la.thr + lane, f4{1.0f, 1.0f, 1.0f, u2f(rng)});
+    st4(la.sum + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
+    la.queue[0][lane] = lane;
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kBlock) k_extend(SceneView sv, LaneArrays la, int k) {
+    const uint32_t n = la.counts[k];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    WalkCounters wc{0, 0};
+    if (i < n) {
+        const uint32_t lane = la.queue[k & 1][i];
+        const f4 o = ld4(la.ray_o + lane), d = ld4(la.ray_d + lane);
+        Hit h;
+        walk_closest<COUNT>(sv.nodes, sv.tris, f3{o.x, o.y, o.z}, f3{d.x, d.y, d.z}, kTMin, kTMax, h, &wc);
+        st4(la.hit + lane, f4{h.t, h.u, h.v, u2f(h.tri)});
+    }
+    if (COUNT) {
+        unsigned long long a = wc.nodes, b = wc.tris;
+        for (int s = 16; s > 0; s >>= 1) {
+            a += __shfl_down_sync(0xffffffffu, a, s);
+            b += __shfl_down_sync(0xffffffffu, b, s);
+        }
+        if ((threadIdx.x & 31) == 0 && (a | b)) {
+            atomicAdd(la.walk_counters + 0, a);
+            atomicAdd(la.walk_counters + 1, b);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_shade(SceneView sv, LaneArrays la, int k) {
+    const uint32_t n = la.counts[k];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool keep = false;
+    uint32_t lane = 0;
+    if (i < n) {
+        lane = la.queue[k & 1][i];
+        const f4 d = ld4(la.ray_d + lane), t = ld4(la.thr + lane), hv = ld4(la.hit + lane);
+        LaneState L;
+        L.o = mk3(0.0f);  // only written: the old origin is never needed again
+        L.d = f3{d.x, d.y, d.z};
+        L.thr = f3{t.x, t.y, t.z};
+        L.rng = f2u(t.w);
+        const uint32_t ctl = f2u(d.w);
+        L.sample = ctl_sample(ctl);
+        L.depth = ctl_depth(ctl);
+        L.lobe = ctl_lobe(ctl);
+        Hit h{hv.x, hv.y, hv.z, f2u(hv.w)};
+        int px, py;
+        lane_pixel(sv, lane, px, py);
+        const ShadeResult r = shade_lane(sv, L, h, px, py);
+        if (L.sample_ended) {  // color += trace_path(...), in sample order
+            f4 s = ld4(la.sum + lane);
+            s.x += L.contrib.x;
+            s.y += L.contrib.y;
+            s.z += L.contrib.z;
+            st4(la.sum + lane, s);
+        }
+        keep = r == LANE_CONTINUE;
+        if (keep) {
+            st4(la.ray_o + lane, f4{L.o.x, L.o.y, L.o.z, 0.0f});
+            st4(la.ray_d + lane, f4{L.d.x, L.d.y, L.d.z, u2f(pack_ctl(L.sample, L.depth, L.lobe))});
+            st4(la.thr + lane, f4{L.thr.x, L.thr.y, L.thr.z, u2f(L.rng)});
+        }
+    }
+    // warp-aggregated append to the next queue
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (m) {
+        const int lid = threadIdx.x & 31;
+        const int leader = __ffs(m) - 1;
+        uint32_t base = 0;
+        if (lid == leader) base = atomicAdd(la.counts + k + 1, (uint32_t)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (keep) la.queue[(k + 1) & 1][base + __popc(m & ((1u << lid) - 1u))] = lane;
+    }
+}
+
+// device.cu:246-253.  sum is indexed by lane; the frame is written row-flipped.
+__global__ void __launch_bounds__(256) k_resolve(SceneView sv, const f4* __restrict__ sum, float inv_spp,
+                                                 uint32_t* __restrict__ rgba, f4* __restrict__ mean) {
+    const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= (uint32_t)sv.n_lanes) return;
+    int px, py;
+    lane_pixel(sv, lane, px, py);
+    const f4 s = ld4(sum + lane);
+    const f3 c = f3{s.x, s.y, s.z} * inv_spp;
+    const size_t ofs = (size_t)px + (size_t)sv.width * (size_t)(sv.height - 1 - py);
+    rgba[ofs] = to_rgba(c);
+    st4(mean + ofs, f4{c.x, c.y, c.z, 1.0f});
+}
+
+// ROWS sharding: lane-indexed sums -> full-frame buffer (x + W*y), zero elsewhere
+__global__ void __launch_bounds__(256) k_scatter_rows(SceneView sv, const f4* __restrict__ sum, f4* __restrict__ frame) {
+    const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane >= (uint32_t)sv.n_lanes) return;
+    int px, py;
+    lane_pixel(sv, lane, px, py);
+    st4(frame + ((size_t)px + (size_t)sv.width * (size_t)py), ld4(sum + lane));
+}
+
+__global__ void __launch_bounds__(kBlock) k_primary(SceneView sv, f4* hits) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (uint32_t)(sv.width * sv.height)) return;
+    const int px = (int)(i % (uint32_t)sv.width), py = (int)(i / (uint32_t)sv.width);
+    uint32_t rng = rng_seed((uint32_t)px, (uint32_t)py);
+    f3 o, d;
+    camera_ray(sv, px, py, rng, o, d);
+    Hit h;
+    walk_closest<false>(sv.nodes, sv.tris, o, d, kTMin, kTMax, h, nullptr);
+    st4(hits + i, f4{h.t, h.u, h.v, u2f(h.tri)});
+}
+
+__global__ void __launch_bounds__(kBlock) k_trace(SceneView sv, const float* __restrict__ o, const float* __restrict__ d,
+                                                  int n, float tmin, float tmax, f4* hits) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Hit h;
+    walk_closest<false>(sv.nodes, sv.tris, f3{o[3 * i], o[3 * i + 1], o[3 * i + 2]},
+                        f3{d[3 * i], d[3 * i + 1], d[3 * i + 2]}, tmin, tmax, h, nullptr);
+    st4(hits + i, f4{h.t, h.u, h.v, u2f(h.tri)});
+}
+
+__global__ void k_sample_disney(const Material* __restrict__ mats, int n, const int32_t* material, const float* wo,
+                                const int32_t* lobe_in, const uint32_t* rng_in, float* f, float* wi, float* pdf,
+                                int32_t* lobe_out, uint32_t* rng_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Material m = mats[material[i]];
+    uint32_t rng = rng_in[i];
+    int lobe = lobe_in[i];
+    BsdfSample s;
+    s.wi = mk3(0.0f);
+    s.pdf = 0.0f;
+    s.f = mk3(0.0f);
+    sample_disney(m, f3{wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]}, rng, lobe, s);
+    f[3 * i] = s.f.x;
+    f[3 * i + 1] = s.f.y;
+    f[3 * i + 2] = s.f.z;
+    wi[3 * i] = s.wi.x;
+    wi[3 * i + 1] = s.wi.y;
+    wi[3 * i + 2] = s.wi.z;
+    pdf[i] = s.pdf;
+    lobe_out[i] = lobe;
+    rng_out[i] = rng;
+}
+
+static inline unsigned blocks(uint32_t n, int b) { return n ? (n + b - 1) / b : 1; }
+
+void launch_init_lanes(const SceneView& sv, const LaneArrays& la, cudaStream_t st) {
+    k_init_lanes<<<blocks(sv.n_lanes, kBlock), kBlock, 0, st>>>(sv, la);
+}
+void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st) {
+    if (count)
+        k_extend<true><<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
+    else
+        k_extend<false><<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
+}
+void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st) {
+    k_shade<<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
+}
+void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st) {
+    k_resolve<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, inv_spp, rgba, mean);
+}
+void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStream_t st) {
+    k_scatter_rows<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, frame);
+}
+void launch_primary(const SceneView& sv, f4* hits, cudaStream_t st) {
+    k_primary<<<blocks(sv.width * sv.height, kBlock), kBlock, 0, st>>>(sv, hits);
+}
+void launch_trace(const SceneView& sv, const float* o, const float* d, int n, float tmin, float tmax, f4* hits,
+                  cudaStream_t st) {
+    k_trace<<<blocks(n, kBlock), kBlock, 0, st>>>(sv, o, d, n, tmin, tmax, hits);
+}
+void launch_sample_disney(const Material* mats, int n, const int32_t* material, const float* wo, const int32_t* lobe_in,
+                          const uint32_t* rng_in, float* f, float* wi, float* pdf, int32_t* lobe_out, uint32_t* rng_out,
+                          cudaStream_t st) {
+    k_sample_disney<<<blocks(n, 128), 128, 0, st>>>(mats, n, material, wo, lobe_in, rng_in, f, wi, pdf, lobe_out, rng_out);
+}
+
+}  // namespace pt

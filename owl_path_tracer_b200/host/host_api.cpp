@@ -1,0 +1,169 @@
+// host_api.cpp — C entry points of libb200pt_host.so (declared in include/b200pt_host.h).
+// Lets a non-C++ caller (the ctypes binding in owl_path_tracer_b200/__init__.py, the
+// parity tests, bench.py) run the same loaders and application stages as the
+// path_tracer executable, and hand the loaded arrays to a checker.
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+#include "../../include/b200pt_host.h"
+#include "application.hpp"
+#include "loaders.hpp"
+#include "procedural.hpp"
+
+struct b200pt_scene {
+    host::program_data pdata;
+    host::test_data tdata;
+    std::vector<host::material_data> mats;  // scratch for b200pt_scene_materials
+};
+
+static thread_local std::string g_err;
+template <typename F>
+static int guard(F&& f) {
+    try {
+        f();
+        return 0;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+extern "C" {
+
+const char* b200pt_host_last_error(void) { return g_err.c_str(); }
+
+int b200pt_scene_load(const char* assets_path, const b200pt_load_options* o, b200pt_scene** out) {
+    return guard([&] {
+        host::load_options opt;
+        if (o) {
+            if (o->scene) opt.scene_override = o->scene;
+            opt.width = o->width;
+            opt.height = o->height;
+            opt.max_samples = o->max_samples;
+            opt.max_path_depth = o->max_path_depth;
+            opt.env_mode = o->env_mode;
+            opt.env_intensity = o->env_intensity;
+            opt.detail = o->detail;
+            opt.allow_procedural = o->no_procedural == 0;
+        }
+        auto* s = new b200pt_scene();
+        try {
+            host::init_program_data(s->pdata, s->tdata, assets_path, opt);
+        } catch (...) {
+            delete s;
+            throw;
+        }
+        *out = s;
+    });
+}
+
+void b200pt_scene_free(b200pt_scene* s) { delete s; }
+
+int b200pt_scene_info(const b200pt_scene* s, b200pt_scene_info_t* info) {
+    const host::program_data& p = s->pdata;
+    memset(info, 0, sizeof *info);
+    info->width = p.buffer_size[0];
+    info->height = p.buffer_size[1];
+    info->max_samples = p.max_samples;
+    info->max_path_depth = p.max_path_depth;
+    info->environment_use = p.environment_use;
+    info->environment_auto = p.environment_auto;
+    info->environment_color[0] = p.environment_color.x;
+    info->environment_color[1] = p.environment_color.y;
+    info->environment_color[2] = p.environment_color.z;
+    info->environment_intensity = p.environment_intensity;
+    info->env_w = p.environment_map.width;
+    info->env_h = p.environment_map.height;
+    info->env_rgba = p.environment_map.empty() ? nullptr : (const uint8_t*)p.environment_map.pixels.data();
+    memcpy(info->cam_origin, &p.cam.origin.x, 12);
+    memcpy(info->cam_llc, &p.cam.llc.x, 12);
+    memcpy(info->cam_horizontal, &p.cam.horizontal.x, 12);
+    memcpy(info->cam_vertical, &p.cam.vertical.x, 12);
+    info->n_entities = (int32_t)p.entities.size();
+    info->n_materials = (int32_t)p.materials.size();
+    info->n_notes = (int32_t)p.notes.size();
+    int64_t tris = 0;
+    for (const host::entity& e : p.entities) tris += (int64_t)p.meshes[e.mesh_index].second->indices.size() / 3;
+    info->n_triangles = tris;
+    return 0;
+}
+
+int b200pt_scene_entity(const b200pt_scene* s, int32_t i, b200pt_entity_view* v) {
+    const host::program_data& p = s->pdata;
+    if (i < 0 || i >= (int32_t)p.entities.size()) return 1;
+    const host::entity& e = p.entities[i];
+    const host::mesh& m = *p.meshes[e.mesh_index].second;
+    memset(v, 0, sizeof *v);
+    v->name = p.meshes[e.mesh_index].first.c_str();
+    v->verts = m.vertices.data();
+    v->normals = m.normals.size() == m.vertices.size() ? m.normals.data() : nullptr;
+    v->nv = (int32_t)(m.vertices.size() / 3);
+    v->uvs = (m.texcoords.size() / 2 == (size_t)v->nv && v->nv > 0) ? m.texcoords.data() : nullptr;
+    v->idx = m.indices.data();
+    v->nt = (int32_t)(m.indices.size() / 3);
+    v->material_index = e.material_id;
+    v->tex_rgba = e.texture.empty() ? nullptr : (const uint8_t*)e.texture.pixels.data();
+    v->tex_w = e.texture.width;
+    v->tex_h = e.texture.height;
+    return 0;
+}
+
+const b200pt_material* b200pt_scene_materials(b200pt_scene* s, int32_t* n) {
+    s->mats = host::material_array(s->pdata);
+    if (n) *n = (int32_t)s->mats.size();
+    return s->mats.data();
+}
+const char* b200pt_scene_material_name(const b200pt_scene* s, int32_t i) {
+    if (i < 0 || i >= (int32_t)s->pdata.materials.size()) return nullptr;
+    return s->pdata.materials[i].name.c_str();
+}
+const char* b200pt_scene_note(const b200pt_scene* s, int32_t i) {
+    if (i < 0 || i >= (int32_t)s->pdata.notes.size()) return nullptr;
+    return s->pdata.notes[i].c_str();
+}
+
+int b200pt_scene_set_material_attr(b200pt_scene* s, const char* material, const char* attr, float value) {
+    host::test_data t;
+    t.material_name = material;
+    t.attribute_name = attr;
+    return host::modify_material(s->pdata, t, value) ? 0 : 1;
+}
+int b200pt_scene_set_material_color(b200pt_scene* s, const char* material, const float rgb[3]) {
+    host::test_data t;
+    t.material_name = material;
+    return host::modify_material(s->pdata, t, host::vec3{rgb[0], rgb[1], rgb[2]}) ? 0 : 1;
+}
+
+int b200pt_scene_bind(const b200pt_scene* s, b200pt_ctx* ctx) {
+    return guard([&] { host::bind_scene(s->pdata, ctx); });
+}
+int b200pt_scene_test_loop(b200pt_scene* s, b200pt_ctx* ctx, const char* out_dir) {
+    return guard([&] { host::test_loop(ctx, s->pdata, s->tdata, out_dir); });
+}
+
+int b200pt_write_png(const char* path, int32_t w, int32_t h, const uint32_t* rgba) {
+    return guard([&] { host::write_png(path, w, h, rgba); });
+}
+int b200pt_write_obj(const b200pt_scene* s, const char* path) {
+    return guard([&] {
+        FILE* f = fopen(path, "w");
+        if (!f) throw std::runtime_error(std::string("cannot write ") + path);
+        size_t voff = 1;
+        for (const host::entity& e : s->pdata.entities) {
+            const host::mesh& m = *s->pdata.meshes[e.mesh_index].second;
+            fprintf(f, "o %s\n", s->pdata.meshes[e.mesh_index].first.c_str());
+            const size_t nv = m.vertices.size() / 3;
+            for (size_t i = 0; i < nv; ++i) fprintf(f, "v %.9g %.9g %.9g\n", m.vertices[3 * i], m.vertices[3 * i + 1], m.vertices[3 * i + 2]);
+            for (size_t i = 0; i < nv; ++i) fprintf(f, "vn %.9g %.9g %.9g\n", m.normals[3 * i], m.normals[3 * i + 1], m.normals[3 * i + 2]);
+            for (size_t t = 0; t < m.indices.size() / 3; ++t) {
+                const size_t a = voff + m.indices[3 * t], b = voff + m.indices[3 * t + 1], c = voff + m.indices[3 * t + 2];
+                fprintf(f, "f %zu//%zu %zu//%zu %zu//%zu\n", a, a, b, b, c, c);
+            }
+            voff += nv;
+        }
+        fclose(f);
+    });
+}
+
+}  // extern "C"

@@ -1,0 +1,600 @@
+// loaders.cpp — settings / scene / OBJ / image readers of the host application.
+// File formats and behaviour follow the reference's utils (path_tracer/src/utils/
+// parser.cpp, mesh_loader.cpp, image_buffer.cpp) and camera.cpp.
+#include "loaders.hpp"
+
+#include <zlib.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <filesystem>
+#include <fstream>
+#include <map>
+#include <sstream>
+#include <stdexcept>
+
+#include "json.hpp"
+
+namespace host {
+
+material_data default_material() {
+    material_data m{};
+    m.base_color[0] = m.base_color[1] = m.base_color[2] = 0.8f;
+    m.subsurface = 0.0f;
+    m.metallic = 0.0f;
+    m.specular = 0.5f;
+    m.specular_tint = 1.0f;
+    m.roughness = 0.5f;
+    m.anisotropic = 0.0f;
+    m.sheen = 0.0f;
+    m.sheen_tint = 1.0f;
+    m.clearcoat = 0.0f;
+    m.clearcoat_gloss = 0.03f;
+    m.ior = 1.45f;
+    m.specular_transmission = 0.0f;
+    m.specular_transmission_roughness = 0.0f;
+    m.emission = 0.0f;
+    return m;
+}
+
+// ------------------------------------------------------------------ camera.cpp:3-22
+static vec3 sub(vec3 a, vec3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+static vec3 mul(float s, vec3 a) { return {s * a.x, s * a.y, s * a.z}; }
+static vec3 divs(vec3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+static vec3 cross(vec3 a, vec3 b) { return {a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y}; }
+static vec3 normalize(vec3 v) {
+    float r = 1.f / sqrtf(v.x * v.x + v.y * v.y + v.z * v.z);
+    return {v.x * r, v.y * r, v.z * r};
+}
+
+camera_data to_camera_data(const camera& c, int width, int height) {
+    const float pi = 3.14159265358979323f;
+    const float aspect = static_cast<float>(width) / static_cast<float>(height);
+    const float theta = c.vertical_fov * pi / 180.0f;
+    const float h = tanf(theta / 2);
+    const float viewport_height = 2.0f * h;
+    const float viewport_width = aspect * viewport_height;
+    const vec3 origin = c.look_from;
+    const vec3 w = normalize(sub(c.look_from, c.look_at));
+    const vec3 u = normalize(cross(c.look_up, w));
+    const vec3 v = normalize(cross(w, u));
+    const vec3 horizontal = mul(viewport_width, u);
+    const vec3 vertical = mul(viewport_height, v);
+    const vec3 llc = sub(sub(sub(origin, divs(horizontal, 2.0f)), divs(vertical, 2.0f)), w);
+    return camera_data{origin, llc, horizontal, vertical};
+}
+
+// ------------------------------------------------------------------ parser.cpp
+static vec3 vec3_of(const Json& a) { return {a[0].as_float(), a[1].as_float(), a[2].as_float()}; }
+
+settings_data parse_settings(const std::string& path) {  // parser.cpp:81-117
+    printf("Parsing settings\n");
+    const Json config = Json::load(path);
+    settings_data data;
+    const Json& test = config["test"];
+    data.test.name = test["name"].as_string();
+    data.test.material_name = test["material_name"].as_string();
+    data.test.attribute_name = test["attribute_name"].as_string();
+    data.test.material_type = test["material_type"].as_int();
+    data.test.step_size = test["step_size"].as_float();
+    const Json& values = test["values"];
+    for (size_t i = 0; i < values.size(); ++i) {
+        if (values[i].is_array())
+            data.test.vec_values.push_back(vec3_of(values[i]));
+        else
+            data.test.flt_values.push_back(values[i].as_float());
+    }
+    data.scene = config["scene"].as_string();
+    data.buffer_size[0] = config["buffer_size"][0].as_int();
+    data.buffer_size[1] = config["buffer_size"][1].as_int();
+    data.max_path_depth = config["max_path_depth"].as_int();
+    data.max_samples = config["max_samples"].as_int();
+    data.environment_use = config["environment_use"].as_bool();
+    data.environment_auto = config["environment_auto"].as_bool();
+    data.environment_color = vec3_of(config["environment_color"]);
+    data.environment_intensity = config["environment_intensity"].as_float();
+    return data;
+}
+
+camera parse_camera(const std::string& path) {  // parser.cpp:65-79 (to_camera_data is applied by the caller)
+    printf("Parsing camera\n");
+    const Json config = Json::load(path);
+    const Json& cam = config["camera"];
+    camera c;
+    c.look_from = vec3_of(cam["look_from"]);
+    c.look_at = vec3_of(cam["look_at"]);
+    c.look_up = vec3_of(cam["look_up"]);
+    c.vertical_fov = cam["vertical_fov"].as_float();
+    return c;
+}
+
+std::vector<material_entry> parse_materials(const std::string& path) {  // parser.cpp:19-63
+    printf("Parsing materials\n");
+    const Json config = Json::load(path);
+    std::vector<material_entry> out;
+    const Json& mats = config["materials"];
+    for (size_t i = 0; i < mats.size(); ++i) {
+        const Json& m = mats[i];
+        material_entry e;
+        e.name = m["name"].as_string();
+        printf(" - \"%s\"\n", e.name.c_str());
+        e.data = default_material();
+        // superset of the reference: a missing "use_texture" counts as false
+        // (assets/sphere.json has none and would make the reference throw)
+        const bool use_texture = m.contains("use_texture") ? m["use_texture"].as_bool() : false;
+        if (use_texture) {
+            e.texture_file = e.name + "-textures/" + m["filename"].as_string();
+        } else {
+            e.data.base_color[0] = m["base_color"][0].as_float();
+            e.data.base_color[1] = m["base_color"][1].as_float();
+            e.data.base_color[2] = m["base_color"][2].as_float();
+        }
+        e.data.subsurface = m["subsurface"].as_float();
+        e.data.metallic = m["metallic"].as_float();
+        e.data.specular = m["specular"].as_float();
+        e.data.specular_tint = m["specular_tint"].as_float();
+        e.data.roughness = m["roughness"].as_float();
+        e.data.anisotropic = m["anisotropic"].as_float();
+        e.data.sheen = m["sheen"].as_float();
+        e.data.sheen_tint = m["sheen_tint"].as_float();
+        e.data.clearcoat = m["clearcoat"].as_float();
+        e.data.clearcoat_gloss = m["clearcoat_gloss"].as_float();
+        e.data.ior = m["ior"].as_float();
+        e.data.specular_transmission = m["specular_transmission"].as_float();
+        e.data.specular_transmission_roughness = m["specular_transmission_roughness"].as_float();
+        e.data.emission = m["emission"].as_float();
+        out.push_back(std::move(e));
+    }
+    return out;
+}
+
+// ------------------------------------------------------------------ OBJ reader
+// The subset of tinyobjloader's ObjReader the reference relies on (triangulate=false):
+// v / vn / vt / f / o / g; 1-based and negative indices; a shape is emitted for every
+// o/g block that has faces.  Everything else (mtllib, usemtl, s, ...) is ignored.
+namespace {
+struct obj_index {
+    int v = -1, vt = -1, vn = -1;
+};
+struct obj_shape {
+    std::string name;
+    std::vector<obj_index> indices;
+    std::vector<int> face_sizes;
+};
+struct obj_attrib {
+    std::vector<float> vertices, normals, texcoords;
+};
+
+inline int fix_index(int idx, int n) {
+    if (idx > 0) return idx - 1;
+    if (idx == 0) return -1;
+    return n + idx;
+}
+
+bool parse_obj(const std::string& path, obj_attrib& at, std::vector<obj_shape>& shapes, std::string& err) {
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) {
+        err = "Cannot open file [" + path + "]";
+        return false;
+    }
+    std::string data;
+    {
+        fseek(f, 0, SEEK_END);
+        long sz = ftell(f);
+        fseek(f, 0, SEEK_SET);
+        data.resize((size_t)sz);
+        if (sz > 0 && fread(&data[0], 1, (size_t)sz, f) != (size_t)sz) {
+            fclose(f);
+            err = "read error";
+            return false;
+        }
+        fclose(f);
+    }
+    obj_shape cur;
+    auto flush = [&]() {
+        if (!cur.face_sizes.empty()) shapes.push_back(cur);
+        cur.indices.clear();
+        cur.face_sizes.clear();
+    };
+    const char* p = data.c_str();
+    const char* end = p + data.size();
+    while (p < end) {
+        const char* eol = (const char*)memchr(p, '\n', (size_t)(end - p));
+        if (!eol) eol = end;
+        const char* q = p;
+        while (q < eol && (*q == ' ' || *q == '\t')) ++q;
+        auto is_sp = [](char c) { return c == ' ' || c == '\t'; };
+        if (q + 1 < eol && q[0] == 'v' && is_sp(q[1])) {
+            char* e;
+            q += 2;
+            for (int k = 0; k < 3; ++k) {
+                at.vertices.push_back((float)strtod(q, &e));
+                q = e;
+            }
+        } else if (q + 2 < eol && q[0] == 'v' && q[1] == 'n' && is_sp(q[2])) {
+            char* e;
+            q += 3;
+            for (int k = 0; k < 3; ++k) {
+                at.normals.push_back((float)strtod(q, &e));
+                q = e;
+            }
+        } else if (q + 2 < eol && q[0] == 'v' && q[1] == 't' && is_sp(q[2])) {
+            char* e;
+            q += 3;
+            for (int k = 0; k < 2; ++k) {
+                at.texcoords.push_back((float)strtod(q, &e));
+                q = e;
+            }
+        } else if (q + 1 < eol && q[0] == 'f' && is_sp(q[1])) {
+            q += 2;
+            int n = 0;
+            const int nv = (int)at.vertices.size() / 3, nn = (int)at.normals.size() / 3,
+                      nt = (int)at.texcoords.size() / 2;
+            while (q < eol) {
+                while (q < eol && (is_sp(*q) || *q == '\r')) ++q;
+                if (q >= eol) break;
+                obj_index ix;
+                char* e;
+                ix.v = fix_index((int)strtol(q, &e, 10), nv);
+                q = e;
+                if (q < eol && *q == '/') {
+                    ++q;
+                    if (q < eol && *q == '/') {
+                        ++q;
+                        ix.vn = fix_index((int)strtol(q, &e, 10), nn);
+                        q = e;
+                    } else {
+                        ix.vt = fix_index((int)strtol(q, &e, 10), nt);
+                        q = e;
+                        if (q < eol && *q == '/') {
+                            ++q;
+                            ix.vn = fix_index((int)strtol(q, &e, 10), nn);
+                            q = e;
+                        }
+                    }
+                }
+                cur.indices.push_back(ix);
+                ++n;
+            }
+            cur.face_sizes.push_back(n);
+        } else if (q + 1 < eol && (q[0] == 'o' || q[0] == 'g') && is_sp(q[1])) {
+            flush();
+            q += 2;
+            while (q < eol && is_sp(*q)) ++q;
+            const char* e = eol;
+            while (e > q && (e[-1] == '\r' || is_sp(e[-1]))) --e;
+            cur.name.assign(q, e);
+        }
+        p = eol + 1;
+    }
+    flush();
+    return true;
+}
+
+// create_mesh, mesh_loader.cpp:9-83: vertices are shared by POSITION index only; the
+// normal / uv stored for a local vertex is the one of the corner that first grew the
+// arrays past it.  Faces with more than 3 corners are fan-split
+// (the reference assumes triangles and would mis-index them).
+std::shared_ptr<mesh> create_mesh(const obj_shape& shape, const obj_attrib& at) {
+    auto m = std::make_shared<mesh>();
+    std::map<int32_t, int32_t> vertex_mapping;
+    size_t offset = 0;
+    auto corner = [&](const obj_index& ix) -> int32_t {
+        auto it = vertex_mapping.find(ix.v);
+        if (it == vertex_mapping.end()) {
+            it = vertex_mapping.insert({ix.v, (int32_t)(m->vertices.size() / 3)}).first;
+            for (int k = 0; k < 3; ++k) m->vertices.push_back(at.vertices[3 * (size_t)ix.v + k]);
+        }
+        if (ix.vn >= 0)
+            while (m->normals.size() < m->vertices.size())
+                for (int k = 0; k < 3; ++k) m->normals.push_back(at.normals[3 * (size_t)ix.vn + k]);
+        if (ix.vt >= 0)
+            while (m->texcoords.size() / 2 < m->vertices.size() / 3)
+                for (int k = 0; k < 2; ++k) m->texcoords.push_back(at.texcoords[2 * (size_t)ix.vt + k]);
+        return it->second;
+    };
+    for (int fs : shape.face_sizes) {
+        for (int t = 1; t + 1 < fs; ++t) {
+            const obj_index c[3] = {shape.indices[offset], shape.indices[offset + t], shape.indices[offset + t + 1]};
+            for (int k = 0; k < 3; ++k) {
+                if (c[k].v < 0 || 3 * (size_t)c[k].v + 2 >= at.vertices.size())
+                    throw std::runtime_error("obj: vertex index out of range");
+                m->indices.push_back(corner(c[k]));
+            }
+        }
+        offset += (size_t)fs;
+    }
+    return m;
+}
+}  // namespace
+
+std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::string& obj_file) {  // mesh_loader.cpp:85-121
+    obj_attrib at;
+    std::vector<obj_shape> shapes;
+    std::string err;
+    if (!parse_obj(obj_file, at, shapes, err)) throw std::runtime_error(err);
+    std::vector<std::pair<std::string, std::shared_ptr<mesh>>> out;
+    for (auto& s : shapes) out.emplace_back(s.name, create_mesh(s, at));
+    return out;
+}
+
+// ------------------------------------------------------------------ PNG
+static uint32_t be32(const unsigned char* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
+
+void write_png(const std::string& file_path, int w, int h, const uint32_t* rgba) {
+    std::vector<unsigned char> raw((size_t)h * (1 + (size_t)w * 4));
+    for (int y = 0; y < h; ++y) {
+        unsigned char* row = &raw[(size_t)y * (1 + (size_t)w * 4)];
+        row[0] = 0;
+        memcpy(row + 1, rgba + (size_t)y * w, (size_t)w * 4);
+    }
+    uLongf clen = compressBound((uLong)raw.size());
+    std::vector<unsigned char> comp(clen);
+    if (compress2(comp.data(), &clen, raw.data(), (uLong)raw.size(), 6) != Z_OK) throw std::runtime_error("png: deflate failed");
+    FILE* f = fopen(file_path.c_str(), "wb");
+    if (!f) throw std::runtime_error("png: cannot write " + file_path);
+    auto chunk = [&](const char* type, const unsigned char* d, uint32_t n) {
+        unsigned char len[4] = {(unsigned char)(n >> 24), (unsigned char)(n >> 16), (unsigned char)(n >> 8), (unsigned char)n};
+        fwrite(len, 1, 4, f);
+        fwrite(type, 1, 4, f);
+        if (n) fwrite(d, 1, n, f);
+        uLong c = crc32(0L, (const Bytef*)type, 4);
+        if (n) c = crc32(c, d, n);
+        unsigned char cb[4] = {(unsigned char)(c >> 24), (unsigned char)(c >> 16), (unsigned char)(c >> 8), (unsigned char)c};
+        fwrite(cb, 1, 4, f);
+    };
+    const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+    fwrite(sig, 1, 8, f);
+    unsigned char ihdr[13] = {(unsigned char)(w >> 24), (unsigned char)(w >> 16), (unsigned char)(w >> 8), (unsigned char)w,
+                              (unsigned char)(h >> 24), (unsigned char)(h >> 16), (unsigned char)(h >> 8), (unsigned char)h,
+                              8, 6, 0, 0, 0};
+    chunk("IHDR", ihdr, 13);
+    chunk("IDAT", comp.data(), (uint32_t)clen);
+    chunk("IEND", nullptr, 0);
+    fclose(f);
+}
+
+static bool read_png(const std::string& path, image_buffer& img) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) return false;
+    std::vector<unsigned char> d((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    if (d.size() < 8 || memcmp(d.data(), "\x89PNG\r\n\x1a\n", 8) != 0) return false;
+    size_t p = 8;
+    int w = 0, h = 0, depth = 0, ctype = 0, interlace = 0;
+    std::vector<unsigned char> idat, plte, trns;
+    while (p + 8 <= d.size()) {
+        uint32_t n = be32(&d[p]);
+        std::string type((const char*)&d[p + 4], 4);
+        const unsigned char* body = &d[p + 8];
+        if (p + 12 + n > d.size()) return false;
+        if (type == "IHDR") {
+            w = (int)be32(body);
+            h = (int)be32(body + 4);
+            depth = body[8];
+            ctype = body[9];
+            interlace = body[12];
+        } else if (type == "IDAT")
+            idat.insert(idat.end(), body, body + n);
+        else if (type == "PLTE")
+            plte.assign(body, body + n);
+        else if (type == "tRNS")
+            trns.assign(body, body + n);
+        else if (type == "IEND")
+            break;
+        p += 12 + n;
+    }
+    if (w <= 0 || h <= 0 || interlace != 0 || (depth != 8 && depth != 16)) return false;
+    const int channels = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
+    if (!channels || (ctype == 3 && depth != 8)) return false;
+    const size_t bpp = (size_t)channels * depth / 8, stride = (size_t)w * bpp;
+    std::vector<unsigned char> raw((size_t)h * (stride + 1));
+    uLongf rl = (uLongf)raw.size();
+    if (uncompress(raw.data(), &rl, idat.data(), (uLong)idat.size()) != Z_OK || rl != raw.size()) return false;
+    std::vector<unsigned char> px((size_t)h * stride);
+    for (int y = 0; y < h; ++y) {
+        const unsigned char* in = &raw[(size_t)y * (stride + 1)];
+        unsigned char* out = &px[(size_t)y * stride];
+        const unsigned char* up = y ? out - stride : nullptr;
+        const int ft = in[0];
+        for (size_t i = 0; i < stride; ++i) {
+            const int a = i >= bpp ? out[i - bpp] : 0, b = up ? up[i] : 0, c = (up && i >= bpp) ? up[i - bpp] : 0;
+            int v = in[1 + i];
+            switch (ft) {
+                case 1: v += a; break;
+                case 2: v += b; break;
+                case 3: v += (a + b) >> 1; break;
+                case 4: {
+                    const int pa = abs(b - c), pb = abs(a - c), pc = abs(a + b - 2 * c);
+                    v += (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+                    break;
+                }
+                default: break;
+            }
+            out[i] = (unsigned char)v;
+        }
+    }
+    img.width = w;
+    img.height = h;
+    img.pixels.resize((size_t)w * h);
+    const size_t step = depth / 8;
+    for (size_t i = 0; i < (size_t)w * h; ++i) {
+        const unsigned char* s = &px[i * bpp];
+        unsigned r, g, b, a = 255;
+        if (ctype == 0) { r = g = b = s[0]; }
+        else if (ctype == 2) { r = s[0]; g = s[step]; b = s[2 * step]; }
+        else if (ctype == 3) {
+            const unsigned k = s[0];
+            r = 3 * k + 2 < plte.size() ? plte[3 * k] : 0;
+            g = 3 * k + 2 < plte.size() ? plte[3 * k + 1] : 0;
+            b = 3 * k + 2 < plte.size() ? plte[3 * k + 2] : 0;
+            a = k < trns.size() ? trns[k] : 255;
+        } else if (ctype == 4) { r = g = b = s[0]; a = s[step]; }
+        else { r = s[0]; g = s[step]; b = s[2 * step]; a = s[3 * step]; }
+        img.pixels[i] = r | (g << 8) | (b << 16) | (a << 24);
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------ Radiance .hdr -> RGBA8
+// stbi_load(..., STBI_rgb_alpha) on an .hdr: decode RGBE to float (stb_image.h:7053-7078),
+// then stbi__hdr_to_ldr (stb_image.h:1864-1889): pow(x, 1/2.2)*255 + 0.5, truncated.
+static unsigned char hdr_channel_to_ldr(float v) {
+    float z = (float)pow((double)(v * 1.0f), (double)(1.0f / 2.2f)) * 255 + 0.5f;
+    if (z < 0) z = 0;
+    if (z > 255) z = 255;
+    return (unsigned char)(int)z;
+}
+
+image_buffer ldr_from_rgbe(int w, int h, const unsigned char* rgbe) {
+    image_buffer img;
+    img.width = w;
+    img.height = h;
+    img.pixels.resize((size_t)w * h);
+    for (size_t i = 0; i < (size_t)w * h; ++i) {
+        const unsigned char* e = &rgbe[i * 4];
+        float c[3] = {0, 0, 0};
+        if (e[3] != 0) {
+            const float f1 = (float)ldexp(1.0f, (int)e[3] - (int)(128 + 8));
+            c[0] = e[0] * f1;
+            c[1] = e[1] * f1;
+            c[2] = e[2] * f1;
+        }
+        img.pixels[i] = (uint32_t)hdr_channel_to_ldr(c[0]) | ((uint32_t)hdr_channel_to_ldr(c[1]) << 8) |
+                        ((uint32_t)hdr_channel_to_ldr(c[2]) << 16) | (255u << 24);
+    }
+    return img;
+}
+
+void rgbe_from_float(const float* c, unsigned char* o) {
+    float m = fmaxf(c[0], fmaxf(c[1], c[2]));
+    if (m < 1e-32f) {
+        o[0] = o[1] = o[2] = o[3] = 0;
+    } else {
+        int e;
+        float s = frexpf(m, &e) * 256.0f / m;
+        o[0] = (unsigned char)(c[0] * s);
+        o[1] = (unsigned char)(c[1] * s);
+        o[2] = (unsigned char)(c[2] * s);
+        o[3] = (unsigned char)(e + 128);
+    }
+}
+
+static bool read_hdr(const std::string& path, image_buffer& img) {
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return false;
+    char line[1024];
+    bool ok = false;
+    if (fgets(line, sizeof line, f) && (strncmp(line, "#?RADIANCE", 10) == 0 || strncmp(line, "#?RGBE", 6) == 0)) {
+        bool format = false;
+        while (fgets(line, sizeof line, f)) {
+            if (line[0] == '\n' || line[0] == '\r') break;
+            if (strncmp(line, "FORMAT=32-bit_rle_rgbe", 22) == 0) format = true;
+        }
+        int w = 0, h = 0;
+        if (format && fgets(line, sizeof line, f) && sscanf(line, "-Y %d +X %d", &h, &w) == 2 && w > 0 && h > 0) {
+            std::vector<unsigned char> rgbe((size_t)w * h * 4);
+            ok = true;
+            std::vector<unsigned char> scan((size_t)w * 4);
+            for (int y = 0; y < h && ok; ++y) {
+                unsigned char hd[4];
+                if (fread(hd, 1, 4, f) != 4) { ok = false; break; }
+                unsigned char* row = &rgbe[(size_t)y * w * 4];
+                if (w < 8 || w >= 32768 || hd[0] != 2 || hd[1] != 2 || (hd[2] & 0x80)) {
+                    // flat data: this scanline (and, as in stb, the rest of the file) is raw RGBE
+                    memcpy(row, hd, 4);
+                    size_t rest = ((size_t)w * (h - y) - 1) * 4;
+                    if (fread(row + 4, 1, rest, f) != rest) ok = false;
+                    break;
+                }
+                if (((hd[2] << 8) | hd[3]) != w) { ok = false; break; }
+                for (int k = 0; k < 4 && ok; ++k) {
+                    int i = 0;
+                    while (i < w) {
+                        int count = fgetc(f);
+                        if (count == EOF) { ok = false; break; }
+                        if (count > 128) {
+                            int value = fgetc(f);
+                            count -= 128;
+                            if (count > w - i) { ok = false; break; }
+                            for (int z = 0; z < count; ++z) scan[(size_t)(i++) * 4 + k] = (unsigned char)value;
+                        } else {
+                            if (count == 0 || count > w - i) { ok = false; break; }
+                            for (int z = 0; z < count; ++z) scan[(size_t)(i++) * 4 + k] = (unsigned char)fgetc(f);
+                        }
+                    }
+                }
+                if (ok) memcpy(row, scan.data(), (size_t)w * 4);
+            }
+            if (ok) img = ldr_from_rgbe(w, h, rgbe.data());
+        }
+    }
+    fclose(f);
+    return ok;
+}
+
+void write_hdr(const std::string& path, int w, int h, const float* rgb) {
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("hdr: cannot write " + path);
+    fprintf(f, "#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y %d +X %d\n", h, w);
+    if (w < 8 || w >= 32768) {
+        fclose(f);
+        throw std::runtime_error("hdr: width must be in [8, 32768)");
+    }
+    std::vector<unsigned char> row((size_t)w * 4);
+    for (int y = 0; y < h; ++y) {
+        for (int x = 0; x < w; ++x) {
+            rgbe_from_float(rgb + 3 * ((size_t)y * w + x), &row[(size_t)x * 4]);
+        }
+        // new-style RLE scanline made of literal runs only (valid, just not compressed)
+        const unsigned char hd[4] = {2, 2, (unsigned char)(w >> 8), (unsigned char)(w & 255)};
+        fwrite(hd, 1, 4, f);
+        for (int k = 0; k < 4; ++k) {
+            int i = 0;
+            while (i < w) {
+                const int n = (w - i) < 128 ? (w - i) : 128;
+                fputc(n, f);
+                for (int z = 0; z < n; ++z) fputc(row[(size_t)(i + z) * 4 + k], f);
+                i += n;
+            }
+        }
+    }
+    fclose(f);
+}
+
+void flip_rows(image_buffer& img) {  // image_buffer.cpp:50-55
+    for (int y = 0; y < img.height / 2; ++y) {
+        uint32_t* a = &img.pixels[(size_t)y * img.width];
+        uint32_t* b = &img.pixels[(size_t)(img.height - 1 - y) * img.width];
+        for (int x = 0; x < img.width; ++x) std::swap(a[x], b[x]);
+    }
+}
+
+image_buffer load_image(const std::string& name, const std::string& path) {  // image_buffer.cpp:36-59
+    const std::string file_path = path + "/" + name;
+    image_buffer img;
+    if (!std::filesystem::exists(file_path)) {
+        printf("Image file %s does not exist. Continue with empty.\n", file_path.c_str());
+        return img;
+    }
+    bool ok = false;
+    if (file_path.size() > 4 && file_path.substr(file_path.size() - 4) == ".hdr")
+        ok = read_hdr(file_path, img);
+    else
+        ok = read_png(file_path, img);
+    if (!ok) {
+        printf("Image file %s could not be decoded. Continue with empty.\n", file_path.c_str());
+        return image_buffer{};
+    }
+    flip_rows(img);
+    return img;
+}
+
+void write_image(const image_buffer& i, const std::string& name, const std::string& path) {  // image_buffer.cpp:25-34
+    if (i.pixels.empty()) throw std::runtime_error{"image buffer is null"};
+    const std::string file_path = path + "/" + name;
+    write_png(file_path, i.width, i.height, i.pixels.data());
+    printf("Image written to %s\n", std::filesystem::absolute(file_path).string().c_str());
+}
+
+}  // namespace host

@@ -1,0 +1,20 @@
+// loaders.hpp — see loaders.cpp
+#pragma once
+#include "scene.hpp"
+
+namespace host {
+
+camera_data to_camera_data(const camera& c, int width, int height);            // camera.cpp:3-22
+settings_data parse_settings(const std::string& path);                         // parser.cpp:81-117
+camera parse_camera(const std::string& path);                                  // parser.cpp:65-79
+std::vector<material_entry> parse_materials(const std::string& path);          // parser.cpp:19-63
+std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::string& obj_file);  // mesh_loader.cpp:85-121
+image_buffer load_image(const std::string& name, const std::string& path);     // image_buffer.cpp:36-59 (v-flipped)
+void write_image(const image_buffer& i, const std::string& name, const std::string& path);  // image_buffer.cpp:25-34
+void write_png(const std::string& file_path, int w, int h, const uint32_t* rgba);
+image_buffer ldr_from_rgbe(int w, int h, const unsigned char* rgbe);          // stb hdr -> 8 bit route
+void rgbe_from_float(const float* rgb, unsigned char* rgbe);
+void flip_rows(image_buffer& img);                                             // image_buffer.cpp:50-55
+void write_hdr(const std::string& path, int w, int h, const float* rgb);
+
+}  // namespace host

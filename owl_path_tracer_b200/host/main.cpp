@@ -1,0 +1,83 @@
+// main.cpp — the path_tracer executable (reference: path_tracer/Main.cpp:13-31).
+//
+// Without arguments it behaves like the reference: reads ./assets/settings.json, then
+// ./assets/<scene>.json + <scene>.obj.scene + environment.hdr, runs the settings' test
+// sweep and writes "<scene>_<test>_<attr>(<value>).png" files into the current
+// directory.  Optional flags (all default to the reference behaviour):
+//   --assets DIR  --scene NAME  --size W H  --spp N  --depth N  --env color|auto|map
+//   --env-intensity F  --detail N  --device K  --out DIR  --stats
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <filesystem>
+#include <string>
+
+#include "application.hpp"
+
+int main(int argc, char** argv) {
+    std::string assets_path = std::filesystem::current_path().string() + "/assets";
+    std::string out_dir = std::filesystem::current_path().string();
+    host::load_options opt;
+    int device = 0;
+    bool stats = false;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto need = [&](int n) {
+            if (i + n >= argc) {
+                fprintf(stderr, "missing value for %s\n", a.c_str());
+                exit(2);
+            }
+        };
+        if (a == "--assets") { need(1); assets_path = argv[++i]; }
+        else if (a == "--scene") { need(1); opt.scene_override = argv[++i]; }
+        else if (a == "--size") { need(2); opt.width = atoi(argv[++i]); opt.height = atoi(argv[++i]); }
+        else if (a == "--spp") { need(1); opt.max_samples = atoi(argv[++i]); }
+        else if (a == "--depth") { need(1); opt.max_path_depth = atoi(argv[++i]); }
+        else if (a == "--env") {
+            need(1);
+            const std::string m = argv[++i];
+            opt.env_mode = m == "map" ? 2 : (m == "auto" ? 1 : 0);
+        }
+        else if (a == "--env-intensity") { need(1); opt.env_intensity = (float)atof(argv[++i]); }
+        else if (a == "--detail") { need(1); opt.detail = atoi(argv[++i]); }
+        else if (a == "--device") { need(1); device = atoi(argv[++i]); }
+        else if (a == "--out") { need(1); out_dir = argv[++i]; }
+        else if (a == "--stats") stats = true;
+        else {
+            fprintf(stderr, "unknown argument %s\n", a.c_str());
+            return 2;
+        }
+    }
+    try {
+        host::program_data pdata;
+        host::test_data tdata;
+        host::init_program_data(pdata, tdata, assets_path, opt);
+        for (const std::string& n : pdata.notes) printf("NOTE: %s\n", n.c_str());
+
+        b200pt_config cfg{};
+        cfg.device_ordinal = device;
+        cfg.rank = 0;
+        cfg.world_size = 1;
+        b200pt_ctx* ctx = nullptr;
+        if (b200pt_create(&cfg, &ctx) != B200PT_OK) {
+            fprintf(stderr, "b200pt_create failed: %s\n", b200pt_last_error());
+            return 1;
+        }
+        host::bind_scene(pdata, ctx);
+        host::test_loop(ctx, pdata, tdata, out_dir);
+        if (stats) {
+            b200pt_stats st{};
+            b200pt_get_stats(ctx, &st);
+            printf("{\"render_ms\": %.3f, \"extend_ms\": %.3f, \"shade_ms\": %.3f, \"build_ms\": %.3f, \"rays\": %llu, "
+                   "\"paths\": %llu, \"mrays_per_s\": %.1f, \"bvh_nodes\": %u, \"bvh_tris\": %u}\n",
+                   st.render_ms, st.extend_ms, st.shade_ms, st.build_ms, (unsigned long long)st.rays,
+                   (unsigned long long)st.paths, st.render_ms > 0 ? st.rays / st.render_ms * 1e-3 : 0.0, st.bvh_nodes,
+                   st.bvh_tris);
+        }
+        b200pt_destroy(ctx);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "error: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}

@@ -1,0 +1,360 @@
+// emu.cpp — host emulation of the product's kernels.  TEST TOOL, never shipped, never
+// linked into libb200pt.so.  It compiles the very same per-element / per-lane functions
+// the CUDA kernels call (owl_path_tracer_b200/csrc/pt_*.h) with g++ and runs them in
+// plain loops, so that the builder, the 8-wide walk and the shade state machine can be
+// checked against the oracle in the CPU-only container (pytest -m "not gpu"), before any
+// GPU time is spent.  The GPU tests then only have to show that nvcc's code returns the
+// same bits.
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <numeric>
+#include <thread>
+#include <vector>
+
+#include "../../owl_path_tracer_b200/csrc/pt_build.h"
+#include "../../owl_path_tracer_b200/csrc/pt_integrator.h"
+
+using namespace pt;
+
+struct emu_scene {
+    std::vector<f4> pos, nrm;
+    std::vector<f2> uv;
+    std::vector<int32_t> idx4;
+    std::vector<MeshInfo> meshes;
+    std::vector<uint32_t> texels, env;
+    std::vector<Material> mats;
+    std::vector<Node8> nodes;
+    std::vector<Tri48> tris;
+    float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, max_abs = 0;
+    int levels = 0;
+    SceneView sv{};
+};
+
+static void refresh_view(emu_scene* s) {
+    s->sv.nodes = s->nodes.data();
+    s->sv.tris = s->tris.data();
+    s->sv.idx4 = s->idx4.data();
+    s->sv.vpos = s->pos.data();
+    s->sv.vnrm = s->nrm.data();
+    s->sv.vuv = s->uv.data();
+    s->sv.meshes = s->meshes.data();
+    s->sv.materials = s->mats.data();
+    s->sv.texels = s->texels.data();
+    s->sv.env = s->env.empty() ? nullptr : s->env.data();
+    s->sv.n_materials = (int)s->mats.size();
+}
+
+struct emu_hit {
+    int32_t mesh, prim;
+    float t, u, v;
+};
+static emu_hit to_rec(const emu_scene* s, const Hit& h, float tmax) {
+    if (h.tri == kNoHit) return emu_hit{-1, -1, tmax, 0, 0};
+    const int32_t mesh = s->idx4[4 * (size_t)h.tri + 3];
+    return emu_hit{mesh, (int32_t)h.tri - s->meshes[mesh].first_tri, h.t, h.u, h.v};
+}
+
+template <typename F>
+static void parallel_rows(int n, int nthreads, F&& f) {
+    std::atomic<int> next{0};
+    auto w = [&]() {
+        for (;;) {
+            int i = next.fetch_add(1);
+            if (i >= n) break;
+            f(i);
+        }
+    };
+    std::vector<std::thread> th;
+    for (int i = 1; i < nthreads; ++i) th.emplace_back(w);
+    w();
+    for (auto& t : th) t.join();
+}
+
+extern "C" {
+
+emu_scene* emu_create() { return new emu_scene(); }
+void emu_destroy(emu_scene* s) { delete s; }
+
+int emu_add_mesh(emu_scene* s, const float* verts, const float* normals, const float* uvs, int nv, const int32_t* idx,
+                 int nt, int material, const uint8_t* tex, int tw, int th) {
+    const int32_t vbase = (int32_t)s->pos.size(), tbase = (int32_t)(s->idx4.size() / 4), mesh = (int32_t)s->meshes.size();
+    for (int i = 0; i < nv; ++i) {
+        s->pos.push_back(f4{verts[3 * i], verts[3 * i + 1], verts[3 * i + 2], 0});
+        s->nrm.push_back(f4{normals[3 * i], normals[3 * i + 1], normals[3 * i + 2], 0});
+        s->uv.push_back(uvs ? f2{uvs[2 * i], uvs[2 * i + 1]} : f2{0, 0});
+        for (int a = 0; a < 3; ++a) {
+            s->lo[a] = fminf(s->lo[a], verts[3 * i + a]);
+            s->hi[a] = fmaxf(s->hi[a], verts[3 * i + a]);
+            s->max_abs = fmaxf(s->max_abs, fabsf(verts[3 * i + a]));
+        }
+    }
+    for (int t = 0; t < nt; ++t) {
+        for (int k = 0; k < 3; ++k) s->idx4.push_back(vbase + idx[3 * t + k]);
+        s->idx4.push_back(mesh);
+    }
+    MeshInfo mi{};
+    mi.first_tri = tbase;
+    mi.material = material;
+    mi.tex_offset = -1;
+    mi.has_uv = uvs ? 1 : 0;
+    if (tex) {
+        mi.tex_offset = (int32_t)s->texels.size();
+        mi.tex_w = tw;
+        mi.tex_h = th;
+        const uint32_t* px = (const uint32_t*)tex;
+        s->texels.insert(s->texels.end(), px, px + (size_t)tw * th);
+    }
+    s->meshes.push_back(mi);
+    return mesh;
+}
+
+void emu_set_materials(emu_scene* s, const float* m, int nm) {
+    s->mats.assign((size_t)nm, Material{});
+    for (int i = 0; i < nm; ++i) memcpy(&s->mats[i], m + 17 * i, 68);
+}
+void emu_set_environment(emu_scene* s, const uint8_t* rgba, int w, int h, int use, int auto_, const float* color,
+                         float intensity) {
+    s->env.clear();
+    if (rgba && w > 0 && h > 0) s->env.assign((const uint32_t*)rgba, (const uint32_t*)rgba + (size_t)w * h);
+    s->sv.env_w = s->env.empty() ? 0 : w;
+    s->sv.env_h = s->env.empty() ? 0 : h;
+    s->sv.env_use = use != 0;
+    s->sv.env_auto = auto_ != 0;
+    memcpy(s->sv.env_color, color, 12);
+    s->sv.env_intensity = intensity;
+}
+void emu_set_camera(emu_scene* s, const float* o, const float* llc, const float* h, const float* v) {
+    memcpy(s->sv.cam_origin, o, 12);
+    memcpy(s->sv.cam_llc, llc, 12);
+    memcpy(s->sv.cam_horizontal, h, 12);
+    memcpy(s->sv.cam_vertical, v, 12);
+}
+void emu_set_render(emu_scene* s, int w, int h, int spp, int depth) {
+    s->sv.width = w;
+    s->sv.height = h;
+    s->sv.max_samples = spp;
+    s->sv.max_depth = depth;
+}
+
+// same sequence as build_bvh_device (bvh_build.cu), element loops instead of kernels
+int emu_build(emu_scene* s) {
+    const uint32_t n = (uint32_t)(s->idx4.size() / 4);
+    if (n == 0) return -1;
+    const float pad = s->max_abs * 3.8146973e-6f + 1e-30f;
+    float slo[3], sinv[3];
+    for (int a = 0; a < 3; ++a) {
+        slo[a] = s->lo[a] - pad;
+        const float e = s->hi[a] - s->lo[a] + 2 * pad;
+        sinv[a] = e > 0 ? 1.0f / e : 0.0f;
+    }
+    std::vector<float> tri_lo(3 * (size_t)n), tri_hi(3 * (size_t)n);
+    std::vector<uint64_t> keys(n);
+    std::vector<uint32_t> order(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        float lo[3], hi[3];
+        tri_box(s->pos.data(), s->idx4.data(), i, pad, lo, hi);
+        for (int a = 0; a < 3; ++a) {
+            tri_lo[3 * (size_t)i + a] = lo[a];
+            tri_hi[3 * (size_t)i + a] = hi[a];
+        }
+        keys[i] = morton_key(lo, hi, slo, sinv);
+        order[i] = i;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+    std::vector<uint64_t> skeys(n);
+    for (uint32_t i = 0; i < n; ++i) skeys[i] = keys[order[i]];
+    std::vector<BinNode> bin(n);
+    std::vector<int32_t> leaf_parent(n, -1), flags(n, 0);
+    if (n >= 2) {
+        for (int i = 0; i < (int)n - 1; ++i) radix_tree_node(skeys.data(), (int)n, i, bin.data(), leaf_parent.data());
+        for (int k = 0; k < (int)n; ++k)
+            refit_from_leaf(k, leaf_parent.data(), bin.data(), flags.data(), order.data(), tri_lo.data(), tri_hi.data());
+    }
+    s->nodes.assign(n, Node8{});
+    s->tris.assign(n, Tri48{});
+    std::vector<CollapseItem> qa(n), qb(n);
+    uint32_t node_count = 1, tri_count = 0, n_items = 1;
+    qa[0] = CollapseItem{n >= 2 ? 0 : ~0, 0u};
+    s->levels = 0;
+    while (n_items) {
+        ++s->levels;
+        uint32_t next_count = 0;
+        for (uint32_t i = 0; i < n_items; ++i)
+            collapse_node(qa[i], bin.data(), order.data(), tri_lo.data(), tri_hi.data(), s->pos.data(), s->idx4.data(),
+                          s->nodes.data(), &node_count, s->tris.data(), &tri_count, qb.data(), &next_count, (int)n);
+        n_items = next_count;
+        std::swap(qa, qb);
+        if (s->levels > 4 * kStackSize) return -2;
+    }
+    if (tri_count != n) return -3;
+    if (s->levels > kStackSize) return -4;
+    s->nodes.resize(node_count);
+    return (int)node_count;
+}
+
+int emu_levels(emu_scene* s) { return s->levels; }
+uint32_t emu_export(emu_scene* s, void* nodes, void* tris) {
+    if (nodes) memcpy(nodes, s->nodes.data(), sizeof(Node8) * s->nodes.size());
+    if (tris) memcpy(tris, s->tris.data(), sizeof(Tri48) * s->tris.size());
+    return (uint32_t)s->nodes.size();
+}
+// walk a tree handed in from outside (e.g. exported from the GPU) instead of the emulated build
+void emu_import(emu_scene* s, const void* nodes, uint32_t n_nodes, const void* tris, uint32_t n_tris) {
+    s->nodes.assign((const Node8*)nodes, (const Node8*)nodes + n_nodes);
+    s->tris.assign((const Tri48*)tris, (const Tri48*)tris + n_tris);
+}
+
+void emu_trace(emu_scene* s, const float* o, const float* d, int n, float tmin, float tmax, emu_hit* out,
+               uint64_t* counters) {
+    refresh_view(s);
+    WalkCounters wc{0, 0};
+    uint64_t nodes = 0, tris = 0;
+    for (int i = 0; i < n; ++i) {
+        Hit h;
+        wc = WalkCounters{0, 0};
+        walk_closest<true>(s->nodes.data(), s->tris.data(), f3{o[3 * i], o[3 * i + 1], o[3 * i + 2]},
+                           f3{d[3 * i], d[3 * i + 1], d[3 * i + 2]}, tmin, tmax, h, &wc);
+        nodes += wc.nodes;
+        tris += wc.tris;
+        out[i] = to_rec(s, h, tmax);
+    }
+    if (counters) {
+        counters[0] = nodes;
+        counters[1] = tris;
+    }
+}
+
+void emu_primary_hits(emu_scene* s, int nthreads, emu_hit* out) {
+    refresh_view(s);
+    SceneView sv = s->sv;
+    parallel_rows(sv.height, nthreads, [&](int py) {
+        for (int px = 0; px < sv.width; ++px) {
+            uint32_t rng = rng_seed((uint32_t)px, (uint32_t)py);
+            f3 o, d;
+            camera_ray(sv, px, py, rng, o, d);
+            Hit h;
+            walk_closest<false>(sv.nodes, sv.tris, o, d, kTMin, kTMax, h, nullptr);
+            out[(size_t)px + (size_t)sv.width * py] = to_rec(s, h, kTMax);
+        }
+    });
+}
+
+// The wavefront of api.cu/wavefront.cu run lane by lane: init, then extend + shade until
+// the lane retires.  Lanes are independent, so running each to completion gives the same
+// per-lane sequence as the GPU's interleaving.  sum_out: W*H*4 floats indexed x + W*y.
+uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthreads, float* sum_out, float* mean_out,
+                    uint32_t* rgba_out) {
+    refresh_view(s);
+    SceneView sv = s->sv;
+    const int W = sv.width, H = sv.height, total_spp = sv.max_samples;
+    sv.row_first = 0;
+    sv.row_step = 1;
+    sv.seed_row_offset = 0;
+    sv.n_lanes = W * H;
+    if (world > 1) {
+        if (shard_mode == 1) {
+            sv.row_first = rank;
+            sv.row_step = world;
+            sv.n_lanes = W * (H > rank ? (H - rank + world - 1) / world : 0);
+        } else {
+            sv.max_samples = total_spp / world + (rank < total_spp % world ? 1 : 0);
+            sv.seed_row_offset = rank * H;
+        }
+    }
+    memset(sum_out, 0, sizeof(float) * 4 * (size_t)W * H);
+    std::atomic<uint64_t> rays{0};
+    const int rows = sv.n_lanes / W;
+    parallel_rows(rows, nthreads, [&](int row) {
+        uint64_t nr = 0;
+        for (int c = 0; c < W; ++c) {
+            const uint32_t lane = (uint32_t)row * W + c;
+            int px, py;
+            lane_pixel(sv, lane, px, py);
+            LaneState L{};
+            L.rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset));
+            camera_ray(sv, px, py, L.rng, L.o, L.d);
+            L.thr = mk3(1.0f);
+            L.sample = 0;
+            L.depth = 0;
+            L.lobe = LOBE_NONE;
+            f3 sum = mk3(0.0f);
+            if (sv.max_samples > 0 && sv.max_depth > 0) {
+                for (;;) {
+                    // state goes through the same packing as the device arrays
+                    const uint32_t ctl = pack_ctl(L.sample, L.depth, L.lobe);
+                    L.sample = ctl_sample(ctl);
+                    L.depth = ctl_depth(ctl);
+                    L.lobe = ctl_lobe(ctl);
+                    Hit h;
+                    walk_closest<false>(sv.nodes, sv.tris, L.o, L.d, kTMin, kTMax, h, nullptr);
+                    ++nr;
+                    const ShadeResult r = shade_lane(sv, L, h, px, py);
+                    if (L.sample_ended) sum = sum + L.contrib;
+                    if (r == LANE_DONE) break;
+                }
+            }
+            float* o = sum_out + 4 * ((size_t)px + (size_t)W * py);
+            o[0] = sum.x;
+            o[1] = sum.y;
+            o[2] = sum.z;
+        }
+        rays += nr;
+    });
+    if (mean_out || rgba_out) {
+        const float inv = 1.0f / static_cast<float>(total_spp);
+        for (int py = 0; py < H; ++py)
+            for (int px = 0; px < W; ++px) {
+                const float* sp = sum_out + 4 * ((size_t)px + (size_t)W * py);
+                const f3 c = f3{sp[0], sp[1], sp[2]} * inv;
+                const size_t ofs = (size_t)px + (size_t)W * (H - 1 - py);
+                if (rgba_out) rgba_out[ofs] = to_rgba(c);
+                if (mean_out) {
+                    mean_out[4 * ofs] = c.x;
+                    mean_out[4 * ofs + 1] = c.y;
+                    mean_out[4 * ofs + 2] = c.z;
+                    mean_out[4 * ofs + 3] = 1.0f;
+                }
+            }
+    }
+    return rays.load();
+}
+
+void emu_sample_disney(const float* mats, int n, const int32_t* material, const float* wo, const int32_t* lobe_in,
+                       const uint32_t* rng_in, float* f, float* wi, float* pdf, int32_t* lobe_out, uint32_t* rng_out) {
+    for (int i = 0; i < n; ++i) {
+        Material m{};
+        memcpy(&m, mats + 17 * material[i], 68);
+        uint32_t rng = rng_in[i];
+        int lobe = lobe_in[i];
+        BsdfSample s;
+        s.wi = mk3(0.0f);
+        s.pdf = 0.0f;
+        s.f = mk3(0.0f);
+        sample_disney(m, f3{wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]}, rng, lobe, s);
+        f[3 * i] = s.f.x; f[3 * i + 1] = s.f.y; f[3 * i + 2] = s.f.z;
+        wi[3 * i] = s.wi.x; wi[3 * i + 1] = s.wi.y; wi[3 * i + 2] = s.wi.z;
+        pdf[i] = s.pdf;
+        lobe_out[i] = lobe;
+        rng_out[i] = rng;
+    }
+}
+
+// detmath hook (fn ids as oracle_math)
+void emu_math(int fn, int n, const float* x, const float* y, float* out) {
+    for (int i = 0; i < n; ++i) {
+        switch (fn) {
+            case 0: out[i] = dm_sin(x[i]); break;
+            case 1: out[i] = dm_cos(x[i]); break;
+            case 2: out[i] = dm_tan(x[i]); break;
+            case 3: out[i] = dm_atan(x[i]); break;
+            case 4: out[i] = dm_asin(x[i]); break;
+            case 5: out[i] = dm_log(x[i]); break;
+            case 6: out[i] = dm_atan2(x[i], y[i]); break;
+            case 7: out[i] = dm_pow(x[i], y[i]); break;
+            default: out[i] = 0;
+        }
+    }
+}
+
+}  // extern "C"
