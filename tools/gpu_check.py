@@ -1,0 +1,50 @@
+"""Quick GPU-vs-oracle check + timing (development helper; the real gates are tests/ -m gpu)."""
+import sys, time, json
+from pathlib import Path
+R = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(R)); sys.path.insert(0, str(R / "tests"))
+import numpy as np
+import owl_path_tracer_b200 as pt
+from checkers import Oracle, rel_mse
+
+def bits(a): return np.ascontiguousarray(a).view(np.uint32)
+
+def check(scene, w, h, spp, depth, **kw):
+    sc = pt.Scene(scene=scene, width=w, height=h, spp=spp, depth=depth, **kw)
+    ctx = pt.Context(flags=pt.FLAG_COUNTERS)
+    ctx.bind(sc)
+    o = Oracle(det=True).load_scene(sc)
+    hg, ho = ctx.primary_hits(), o.primary_hits()
+    same = (hg['mesh']==ho['mesh'])&(hg['prim']==ho['prim'])&(bits(hg['t'])==bits(ho['t']))&(bits(hg['u'])==bits(ho['u']))&(bits(hg['v'])==bits(ho['v']))
+    ctx.render()
+    st = ctx.stats()
+    t=time.time(); ro = o.render(); to=time.time()-t
+    g = ctx.framebuffer_f32(); rg = ctx.framebuffer_rgba8()
+    print(json.dumps(dict(scene=scene, size=[w,h], spp=spp, tris=sc.n_triangles, primary_mismatch=int((~same).sum()),
+        mean_bit_mismatch=int((bits(g[...,:3])!=bits(ro['mean'][...,:3])).sum()), rgba_mismatch=int((rg!=ro['rgba']).sum()),
+        relmse=rel_mse(g, ro['mean']), rays_gpu=st['rays'], rays_oracle=ro['rays'], render_ms=st['render_ms'],
+        mrays=st['rays']/st['render_ms']*1e-3, oracle_s=to, nodes_per_ray=st['nodes_visited']/max(1,st['rays']),
+        tris_per_ray=st['tris_tested']/max(1,st['rays']), build_ms=st['build_ms'], bvh_nodes=st['bvh_nodes'], iters=st['iterations'])))
+    ctx.close()
+
+def timing(scene, w, h, spp, depth, flags=0, **kw):
+    sc = pt.Scene(scene=scene, width=w, height=h, spp=spp, depth=depth, **kw)
+    ctx = pt.Context(flags=flags)
+    ctx.bind(sc)
+    ctx.render(); ctx.render()
+    st = ctx.stats()
+    print(json.dumps(dict(scene=scene, size=[w,h], spp=spp, tris=sc.n_triangles, render_ms=st['render_ms'], extend_ms=st['extend_ms'], shade_ms=st['shade_ms'],
+        mrays=st['rays']/st['render_ms']*1e-3, rays=st['rays'], iters=st['iterations'], build_ms=st['build_ms'], bvh_nodes=st['bvh_nodes'], launches=st['kernel_launches'])))
+    ctx.close()
+
+if __name__ == "__main__":
+    check("cornell-box", 128, 128, 8, 8, env="color", env_intensity=0.0)
+    check("cube", 128, 128, 8, 8, env="auto", env_intensity=1.0)
+    check("sphere", 128, 128, 8, 8, env="map", env_intensity=1.0)
+    check("mitsuba", 160, 90, 4, 8, env="auto", env_intensity=1.0)
+    check("car", 160, 90, 4, 8, env="color", env_intensity=0.0)
+    check("dragon", 160, 90, 4, 8, env="color", env_intensity=0.0)
+    timing("cornell-box", 512, 512, 64, 8, env="color", env_intensity=0.0)
+    timing("cornell-box", 512, 512, 64, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
+    timing("dragon", 1920, 1080, 16, 8, env="color", env_intensity=0.0)
+    timing("dragon", 1920, 1080, 16, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
