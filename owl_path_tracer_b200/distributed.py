@@ -1,0 +1,47 @@
+"""Multi-GPU plumbing: one process per GPU, samples (or rows) sharded over ranks, ONE reduce of
+the float4 sum buffer to rank 0 per frame.  torch.distributed is only the carrier:
+NCCL over NVLink on the GPU box, gloo in the CPU tests."""
+from __future__ import annotations
+
+import numpy as np
+
+
+class _DevPtr:
+    """Expose a raw device pointer through __cuda_array_interface__ so torch can wrap it."""
+
+    def __init__(self, ptr, n_floats):
+        self.__cuda_array_interface__ = dict(shape=(int(n_floats),), typestr="<f4", data=(int(ptr), False), version=3,
+                                             strides=None)
+
+
+def accum_tensor(ctx):
+    """The context's float4 sum buffer as a torch CUDA tensor (no copy)."""
+    import torch
+    ptr, n = ctx.accum_buffer()
+    return torch.as_tensor(_DevPtr(ptr, n), device=f"cuda:{torch.cuda.current_device()}")
+
+
+def reduce_sum_to_rank0(tensor, group=None):
+    """The frame's single collective.  In place; only rank 0's result is meaningful."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.reduce(tensor, dst=0, op=dist.ReduceOp.SUM, group=group)
+    return tensor
+
+
+def render_frame(ctx, group=None):
+    """render this rank's share -> reduce -> rank 0 resolves (scale by 1/total spp, RGBA8 pack)."""
+    ctx.render()
+    if ctx.world_size > 1:
+        import torch
+        t = accum_tensor(ctx)
+        torch.cuda.current_stream().synchronize()
+        reduce_sum_to_rank0(t, group)
+        torch.cuda.current_stream().synchronize()
+        if ctx.rank == 0:
+            ctx.resolve()
+
+
+def shard_samples(total_spp: int, rank: int, world: int) -> int:
+    """Samples per pixel rank `rank` renders in SPP mode (same rule as api.cu rank_samples)."""
+    return total_spp // world + (1 if rank < total_spp % world else 0)

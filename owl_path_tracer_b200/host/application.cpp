@@ -88,7 +88,7 @@ void init_program_data(program_data& pdata, test_data& tdata, const std::string&
         if (file.empty()) continue;
         const mesh& m = *pdata.meshes[e.mesh_index].second;
         if (m.texcoords.size() / 2 != m.vertices.size() / 3) {
-            printf("Mesh %s has no texture coordinates; texture %s ignored.\n", pdata.meshes[e.mesh_index].first.c_str(),
+            host::say("Mesh %s has no texture coordinates; texture %s ignored.\n", pdata.meshes[e.mesh_index].first.c_str(),
                    file.c_str());
             continue;
         }
@@ -176,7 +176,7 @@ bool modify_material(program_data& pdata, const test_data& test, float value) { 
 // render_frame, application.cpp:363-371
 void render_frame(b200pt_ctx* ctx, const program_data& pdata, const test_data& tdata, const std::string& values,
                   const std::string& out_dir) {
-    printf("TRACING\n");
+    host::say("TRACING\n");
     check(b200pt_render(ctx), "render");
     const uint32_t* fb = nullptr;
     check(b200pt_framebuffer_rgba8(ctx, &fb), "framebuffer");

@@ -6,6 +6,8 @@
 #include <zlib.h>
 
 #include <cmath>
+#include <cstdarg>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <filesystem>
@@ -17,6 +19,15 @@
 #include "json.hpp"
 
 namespace host {
+
+void say(const char* fmt, ...) {
+    static const bool quiet = getenv("B200PT_QUIET") != nullptr;
+    if (quiet) return;
+    va_list ap;
+    va_start(ap, fmt);
+    vprintf(fmt, ap);
+    va_end(ap);
+}
 
 material_data default_material() {
     material_data m{};
@@ -69,7 +80,7 @@ camera_data to_camera_data(const camera& c, int width, int height) {
 static vec3 vec3_of(const Json& a) { return {a[0].as_float(), a[1].as_float(), a[2].as_float()}; }
 
 settings_data parse_settings(const std::string& path) {  // parser.cpp:81-117
-    printf("Parsing settings\n");
+    say("Parsing settings\n");
     const Json config = Json::load(path);
     settings_data data;
     const Json& test = config["test"];
@@ -98,7 +109,7 @@ settings_data parse_settings(const std::string& path) {  // parser.cpp:81-117
 }
 
 camera parse_camera(const std::string& path) {  // parser.cpp:65-79 (to_camera_data is applied by the caller)
-    printf("Parsing camera\n");
+    say("Parsing camera\n");
     const Json config = Json::load(path);
     const Json& cam = config["camera"];
     camera c;
@@ -110,7 +121,7 @@ camera parse_camera(const std::string& path) {  // parser.cpp:65-79 (to_camera_d
 }
 
 std::vector<material_entry> parse_materials(const std::string& path) {  // parser.cpp:19-63
-    printf("Parsing materials\n");
+    say("Parsing materials\n");
     const Json config = Json::load(path);
     std::vector<material_entry> out;
     const Json& mats = config["materials"];
@@ -118,7 +129,7 @@ std::vector<material_entry> parse_materials(const std::string& path) {  // parse
         const Json& m = mats[i];
         material_entry e;
         e.name = m["name"].as_string();
-        printf(" - \"%s\"\n", e.name.c_str());
+        say(" - \"%s\"\n", e.name.c_str());
         e.data = default_material();
         // superset of the reference: a missing "use_texture" counts as false
         // (assets/sphere.json has none and would make the reference throw)
@@ -574,7 +585,7 @@ image_buffer load_image(const std::string& name, const std::string& path) {  // 
     const std::string file_path = path + "/" + name;
     image_buffer img;
     if (!std::filesystem::exists(file_path)) {
-        printf("Image file %s does not exist. Continue with empty.\n", file_path.c_str());
+        say("Image file %s does not exist. Continue with empty.\n", file_path.c_str());
         return img;
     }
     bool ok = false;
@@ -583,7 +594,7 @@ image_buffer load_image(const std::string& name, const std::string& path) {  // 
     else
         ok = read_png(file_path, img);
     if (!ok) {
-        printf("Image file %s could not be decoded. Continue with empty.\n", file_path.c_str());
+        say("Image file %s could not be decoded. Continue with empty.\n", file_path.c_str());
         return image_buffer{};
     }
     flip_rows(img);
@@ -594,7 +605,7 @@ void write_image(const image_buffer& i, const std::string& name, const std::stri
     if (i.pixels.empty()) throw std::runtime_error{"image buffer is null"};
     const std::string file_path = path + "/" + name;
     write_png(file_path, i.width, i.height, i.pixels.data());
-    printf("Image written to %s\n", std::filesystem::absolute(file_path).string().c_str());
+    say("Image written to %s\n", std::filesystem::absolute(file_path).string().c_str());
 }
 
 }  // namespace host

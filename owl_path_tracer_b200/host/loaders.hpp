@@ -4,6 +4,9 @@
 
 namespace host {
 
+// console log of the stage banners (types.hpp:20-28 colours dropped); silent when B200PT_QUIET is set
+void say(const char* fmt, ...);
+
 camera_data to_camera_data(const camera& c, int width, int height);            // camera.cpp:3-22
 settings_data parse_settings(const std::string& path);                         // parser.cpp:81-117
 camera parse_camera(const std::string& path);                                  // parser.cpp:65-79
