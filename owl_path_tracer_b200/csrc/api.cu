@@ -26,6 +26,7 @@ struct b200pt_ctx {
     b200pt_config cfg{};
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    uint32_t* d_cursor = nullptr;  // ray-fetch cursor of the parity-hook kernels
     // host staging of the flattened scene (kept: parity hooks map triangle ids back)
     std::vector<f4> h_pos, h_nrm;
     std::vector<f2> h_uv;
@@ -64,7 +65,8 @@ struct b200pt_ctx {
 
 static void free_lanes(b200pt_ctx* c) {
     cudaFree(c->la.ray_o); cudaFree(c->la.ray_d); cudaFree(c->la.thr); cudaFree(c->la.sum); cudaFree(c->la.hit);
-    cudaFree(c->la.queue[0]); cudaFree(c->la.queue[1]); cudaFree(c->la.counts); cudaFree(c->la.walk_counters);
+    cudaFree(c->la.queue[0]); cudaFree(c->la.queue[1]); cudaFree(c->la.counts); cudaFree(c->la.cursor);
+    cudaFree(c->la.walk_counters);
     cudaFree(c->d_frame); cudaFree(c->d_rgba); cudaFree(c->d_mean);
     if (c->h_rgba) cudaFreeHost(c->h_rgba);
     if (c->h_mean) cudaFreeHost(c->h_mean);
@@ -149,6 +151,8 @@ extern "C" int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
+    CU(cudaMalloc(&c->d_cursor, sizeof(uint32_t)));
+    set_persistent_blocks(prop.multiProcessorCount);
     *out = c;
     return B200PT_OK;
 }
@@ -161,6 +165,7 @@ extern "C" int b200pt_destroy(b200pt_ctx* c) {
     free_scene(c);
     cudaFree(c->d_env);
     cudaFree(c->d_mats);
+    cudaFree(c->d_cursor);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
@@ -334,6 +339,7 @@ static int ensure_lanes(b200pt_ctx* c, const SceneView& sv) {
         CU(cudaMalloc(&c->la.queue[0], sizeof(uint32_t) * need));
         CU(cudaMalloc(&c->la.queue[1], sizeof(uint32_t) * need));
         CU(cudaMalloc(&c->la.counts, sizeof(uint32_t) * (kBatch + 1)));
+        CU(cudaMalloc(&c->la.cursor, sizeof(uint32_t) * kBatch));
         CU(cudaMalloc(&c->la.walk_counters, sizeof(unsigned long long) * 2));
         c->la.capacity = need;
         if (c->cfg.world_size > 1 && c->cfg.shard_mode == B200PT_SHARD_ROWS) CU(cudaMalloc(&c->d_frame, sizeof(f4) * px));
@@ -367,6 +373,7 @@ static int render_local(b200pt_ctx* c) {
 
     CU(cudaEventRecord(c->ev0, st));
     CU(cudaMemsetAsync(c->la.counts, 0, sizeof(uint32_t) * (kBatch + 1), st));
+    CU(cudaMemsetAsync(c->la.cursor, 0, sizeof(uint32_t) * kBatch, st));
     CU(cudaMemsetAsync(c->la.walk_counters, 0, sizeof(unsigned long long) * 2, st));
     uint32_t active = 0;
     if (sv.n_lanes > 0 && sv.max_samples > 0 && sv.max_depth > 0) {
@@ -399,6 +406,7 @@ static int render_local(b200pt_ctx* c) {
         // next batch starts from the last queue length; the other slots go back to zero
         CU(cudaMemcpyAsync(c->la.counts, c->la.counts + kBatch, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
         CU(cudaMemsetAsync(c->la.counts + 1, 0, sizeof(uint32_t) * kBatch, st));
+        CU(cudaMemsetAsync(c->la.cursor, 0, sizeof(uint32_t) * kBatch, st));
         CU(cudaStreamSynchronize(st));
         for (int k = 0; k < kBatch; ++k) {
             S.rays += h_counts[k];
@@ -521,7 +529,8 @@ extern "C" int b200pt_primary_hits(b200pt_ctx* c, b200pt_hit* out) {
     const size_t n = (size_t)c->width * c->height;
     f4* d_hits = nullptr;
     CU(cudaMalloc(&d_hits, sizeof(f4) * n));
-    launch_primary(full, d_hits, c->stream);
+    CU(cudaMemsetAsync(c->d_cursor, 0, sizeof(uint32_t), c->stream));
+    launch_primary(full, d_hits, c->d_cursor, c->stream);
     std::vector<f4> raw(n);
     cudaError_t e = cudaMemcpyAsync(raw.data(), d_hits, sizeof(f4) * n, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
@@ -548,7 +557,8 @@ extern "C" int b200pt_trace(b200pt_ctx* c, const float* origins, const float* di
     cudaError_t e = cudaMemcpyAsync(d_o, origins, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, c->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_d, dirs, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, c->stream);
     if (e == cudaSuccess) {
-        launch_trace(sv, d_o, d_d, n, tmin, tmax, d_hits, c->stream);
+        cudaMemsetAsync(c->d_cursor, 0, sizeof(uint32_t), c->stream);
+        launch_trace(sv, d_o, d_d, n, tmin, tmax, d_hits, c->d_cursor, c->stream);
         e = cudaMemcpyAsync(raw.data(), d_hits, sizeof(f4) * (size_t)n, cudaMemcpyDeviceToHost, c->stream);
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);

@@ -30,6 +30,7 @@ struct LaneArrays {
     f4* hit = nullptr;     // t, u, v, triangle id
     uint32_t* queue[2] = {nullptr, nullptr};
     uint32_t* counts = nullptr;   // kBatch + 1 queue lengths
+    uint32_t* cursor = nullptr;   // kBatch ray-fetch cursors of the persistent extend kernel
     unsigned long long* walk_counters = nullptr;  // nodes, tris (FLAG_COUNTERS)
     uint32_t capacity = 0;
 };
@@ -42,9 +43,10 @@ void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t ma
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st);
 void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStream_t st);
-void launch_primary(const SceneView& sv, f4* hits, cudaStream_t st);
+void launch_primary(const SceneView& sv, f4* hits, uint32_t* cursor, cudaStream_t st);
 void launch_trace(const SceneView& sv, const float* o, const float* d, int n, float tmin, float tmax, f4* hits,
-                  cudaStream_t st);
+                  uint32_t* cursor, cudaStream_t st);
+void set_persistent_blocks(int sm_count);
 void launch_sample_disney(const Material* mats, int n, const int32_t* material, const float* wo, const int32_t* lobe_in,
                           const uint32_t* rng_in, float* f, float* wi, float* pdf, int32_t* lobe_out, uint32_t* rng_out,
                           cudaStream_t st);

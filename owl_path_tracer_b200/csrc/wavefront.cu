@@ -8,7 +8,10 @@
 //   k_resolve     mean, RGBA8 pack, row flip                    (device.cu:246-253)
 // plus small parity-hook kernels.  Compiled with -fmad=false: the arithmetic must round
 // like the scalar oracle's (pt_defs.h); the slab test uses explicit fmaf.
+#include <algorithm>
+
 #include "device_ctx.h"
+#include "pt_walk_warp.cuh"
 
 namespace pt {
 
@@ -35,17 +38,37 @@ __global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays 
     la.queue[0][lane] = lane;
 }
 
+struct LaneRaySource {
+    const uint32_t* queue;
+    const f4* ray_o;
+    const f4* ray_d;
+    uint32_t* lane_of;  // unused
+    __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
+        const uint32_t lane = queue[i];
+        const f4 a = ld4(ray_o + lane), b = ld4(ray_d + lane);
+        o = f3{a.x, a.y, a.z};
+        d = f3{b.x, b.y, b.z};
+        tmin = kTMin;
+        tmax = kTMax;
+    }
+};
+struct LaneHitSink {
+    const uint32_t* queue;
+    f4* hit;
+    __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
+        st4(hit + queue[i], f4{h.t, h.u, h.v, u2f(h.tri)});
+    }
+};
+
+// persistent warps: every warp pulls rays of queue k until the queue is drained
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_extend(SceneView sv, LaneArrays la, int k) {
     const uint32_t n = la.counts[k];
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     WalkCounters wc{0, 0};
-    if (i < n) {
-        const uint32_t lane = la.queue[k & 1][i];
-        const f4 o = ld4(la.ray_o + lane), d = ld4(la.ray_d + lane);
-        Hit h;
-        walk_closest<COUNT>(sv.nodes, sv.tris, f3{o.x, o.y, o.z}, f3{d.x, d.y, d.z}, kTMin, kTMax, h, &wc);
-        st4(la.hit + lane, f4{h.t, h.u, h.v, u2f(h.tri)});
+    if (n) {
+        const uint32_t* q = la.queue[k & 1];
+        warp_walk<COUNT>(sv.nodes, sv.tris, n, la.cursor + k, LaneRaySource{q, la.ray_o, la.ray_d, nullptr},
+                         LaneHitSink{q, la.hit}, wc);
     }
     if (COUNT) {
         unsigned long long a = wc.nodes, b = wc.tris;
@@ -130,26 +153,40 @@ __global__ void __launch_bounds__(256) k_scatter_rows(SceneView sv, const f4* __
     st4(frame + ((size_t)px + (size_t)sv.width * (size_t)py), ld4(sum + lane));
 }
 
-__global__ void __launch_bounds__(kBlock) k_primary(SceneView sv, f4* hits) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (uint32_t)(sv.width * sv.height)) return;
-    const int px = (int)(i % (uint32_t)sv.width), py = (int)(i / (uint32_t)sv.width);
-    uint32_t rng = rng_seed((uint32_t)px, (uint32_t)py);
-    f3 o, d;
-    camera_ray(sv, px, py, rng, o, d);
-    Hit h;
-    walk_closest<false>(sv.nodes, sv.tris, o, d, kTMin, kTMax, h, nullptr);
-    st4(hits + i, f4{h.t, h.u, h.v, u2f(h.tri)});
+struct CameraRaySource {
+    SceneView sv;
+    __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
+        const int px = (int)(i % (uint32_t)sv.width), py = (int)(i / (uint32_t)sv.width);
+        uint32_t rng = rng_seed((uint32_t)px, (uint32_t)py);
+        camera_ray(sv, px, py, rng, o, d);
+        tmin = kTMin;
+        tmax = kTMax;
+    }
+};
+struct ArrayRaySource {
+    const float *o, *d;
+    float tmin, tmax;
+    __device__ __forceinline__ void load(uint32_t i, f3& oo, f3& dd, float& t0, float& t1) const {
+        oo = f3{o[3 * i], o[3 * i + 1], o[3 * i + 2]};
+        dd = f3{d[3 * i], d[3 * i + 1], d[3 * i + 2]};
+        t0 = tmin;
+        t1 = tmax;
+    }
+};
+struct ArrayHitSink {
+    f4* hits;
+    __device__ __forceinline__ void store(uint32_t i, const Hit& h) const { st4(hits + i, f4{h.t, h.u, h.v, u2f(h.tri)}); }
+};
+
+__global__ void __launch_bounds__(kBlock) k_primary(SceneView sv, f4* hits, uint32_t* cursor) {
+    WalkCounters wc{0, 0};
+    warp_walk<false>(sv.nodes, sv.tris, (uint32_t)(sv.width * sv.height), cursor, CameraRaySource{sv}, ArrayHitSink{hits}, wc);
 }
 
 __global__ void __launch_bounds__(kBlock) k_trace(SceneView sv, const float* __restrict__ o, const float* __restrict__ d,
-                                                  int n, float tmin, float tmax, f4* hits) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    Hit h;
-    walk_closest<false>(sv.nodes, sv.tris, f3{o[3 * i], o[3 * i + 1], o[3 * i + 2]},
-                        f3{d[3 * i], d[3 * i + 1], d[3 * i + 2]}, tmin, tmax, h, nullptr);
-    st4(hits + i, f4{h.t, h.u, h.v, u2f(h.tri)});
+                                                  int n, float tmin, float tmax, f4* hits, uint32_t* cursor) {
+    WalkCounters wc{0, 0};
+    warp_walk<false>(sv.nodes, sv.tris, (uint32_t)n, cursor, ArrayRaySource{o, d, tmin, tmax}, ArrayHitSink{hits}, wc);
 }
 
 __global__ void k_sample_disney(const Material* __restrict__ mats, int n, const int32_t* material, const float* wo,
@@ -177,15 +214,18 @@ __global__ void k_sample_disney(const Material* __restrict__ mats, int n, const 
 }
 
 static inline unsigned blocks(uint32_t n, int b) { return n ? (n + b - 1) / b : 1; }
+static int g_persistent_blocks = 148 * 8;
+void set_persistent_blocks(int sm_count) { g_persistent_blocks = sm_count * 8; }
+static inline unsigned pblocks(uint32_t n) { return std::min<unsigned>(blocks(n, kBlock), (unsigned)g_persistent_blocks); }
 
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, cudaStream_t st) {
     k_init_lanes<<<blocks(sv.n_lanes, kBlock), kBlock, 0, st>>>(sv, la);
 }
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st) {
     if (count)
-        k_extend<true><<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
+        k_extend<true><<<pblocks(max_count), kBlock, 0, st>>>(sv, la, k);
     else
-        k_extend<false><<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
+        k_extend<false><<<pblocks(max_count), kBlock, 0, st>>>(sv, la, k);
 }
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st) {
     k_shade<<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
@@ -196,12 +236,12 @@ void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t*
 void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStream_t st) {
     k_scatter_rows<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, frame);
 }
-void launch_primary(const SceneView& sv, f4* hits, cudaStream_t st) {
-    k_primary<<<blocks(sv.width * sv.height, kBlock), kBlock, 0, st>>>(sv, hits);
+void launch_primary(const SceneView& sv, f4* hits, uint32_t* cursor, cudaStream_t st) {
+    k_primary<<<pblocks(sv.width * sv.height), kBlock, 0, st>>>(sv, hits, cursor);
 }
 void launch_trace(const SceneView& sv, const float* o, const float* d, int n, float tmin, float tmax, f4* hits,
-                  cudaStream_t st) {
-    k_trace<<<blocks(n, kBlock), kBlock, 0, st>>>(sv, o, d, n, tmin, tmax, hits);
+                  uint32_t* cursor, cudaStream_t st) {
+    k_trace<<<pblocks(n), kBlock, 0, st>>>(sv, o, d, n, tmin, tmax, hits, cursor);
 }
 void launch_sample_disney(const Material* mats, int n, const int32_t* material, const float* wo, const int32_t* lobe_in,
                           const uint32_t* rng_in, float* f, float* wi, float* pdf, int32_t* lobe_out, uint32_t* rng_out,

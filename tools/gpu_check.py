@@ -38,6 +38,13 @@ def timing(scene, w, h, spp, depth, flags=0, **kw):
     ctx.close()
 
 if __name__ == "__main__":
+    import os
+    os.environ.setdefault("B200PT_QUIET", "1")
+    if len(sys.argv) > 1 and sys.argv[1] == "timing":
+        timing("cornell-box", 512, 512, 64, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
+        timing("dragon", 1920, 1080, 16, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
+        timing("car", 1920, 1080, 16, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
+        sys.exit(0)
     check("cornell-box", 128, 128, 8, 8, env="color", env_intensity=0.0)
     check("cube", 128, 128, 8, 8, env="auto", env_intensity=1.0)
     check("sphere", 128, 128, 8, 8, env="map", env_intensity=1.0)
