@@ -94,7 +94,7 @@ def run_reference(args):
     if rank != 0:
         return
     cores = host_cores()
-    spp = 1
+    spp = 4   # bounded sample: ~4 s per step on 16 cores, so steps+warmup stay within minutes
     rate, sec, rays = cpu_oracle_rate(spp, cores, steps=args.steps, warmup=args.warmup)
     sample = f"full 1920x1080 dragon frame at {spp} spp per step ({rays} rays), oracle with glibc math, {cores} threads"
     line = dict(impl="reference", metric="Mrays/s", value=rate, unit="Mrays/s", n_gpus=args.gpus, steps=args.steps,
@@ -236,9 +236,10 @@ def main():
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         cores = host_cores()
-        rate, sec, rays = cpu_oracle_rate(1, cores)
+        cpu_spp = max(1, min(32, int(round(16 * 16 / cores))))     # ~15 s of CPU work on a 16-core box
+        rate, sec, rays = cpu_oracle_rate(cpu_spp, cores)
         cpu = dict(value=rate, unit="Mrays/s", cores=cores, kind="port",
-                   sample=f"full 1920x1080 dragon frame at 1 spp ({rays} rays, {sec:.1f} s), oracle/oracle.cpp with glibc math")
+                   sample=f"full 1920x1080 dragon frame at {cpu_spp} spp ({rays} rays, {sec:.1f} s), oracle/oracle.cpp with glibc math")
 
     if rank == 0:
         total_spp = wl["spp"]
