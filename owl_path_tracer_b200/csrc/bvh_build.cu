@@ -2,6 +2,7 @@
 // Replaces optixAccelBuild (reference: application.cpp:131-140 via OWL).  Not on the
 // per-frame path: runs once per b200pt_build_accel.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 
 #include <string>
@@ -28,6 +29,43 @@ __global__ void k_tri_prepare(const f4* __restrict__ pos, const int32_t* __restr
     vals[i] = i;
 }
 
+__global__ void k_ploc_init(uint32_t n, const uint32_t* __restrict__ sorted_tri, const float* __restrict__ tri_lo,
+                            const float* __restrict__ tri_hi, int32_t* __restrict__ cid, Box6* __restrict__ cbox) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    cid[i] = ~(int32_t)i;
+    const uint32_t t = sorted_tri[i];
+    Box6 b;
+    for (int a = 0; a < 3; ++a) {
+        b.lo[a] = tri_lo[3 * (size_t)t + a];
+        b.hi[a] = tri_hi[3 * (size_t)t + a];
+    }
+    cbox[i] = b;
+}
+
+__global__ void k_ploc_nearest(int m, const Box6* __restrict__ cbox, int32_t* __restrict__ nn) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    ploc_nearest(i, m, cbox, nn);
+}
+
+__global__ void k_ploc_flags(int m, const int32_t* __restrict__ nn, unsigned long long* __restrict__ flags) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    flags[i] = ploc_flags(i, nn);
+}
+
+__global__ void k_ploc_emit(int m, const int32_t* __restrict__ nn, const unsigned long long* __restrict__ incl,
+                            const int32_t* __restrict__ cid, const Box6* __restrict__ cbox, int32_t* __restrict__ out_cid,
+                            Box6* __restrict__ out_cbox, BinNode* bin, CollapsePlan* plans, uint32_t node_base,
+                            const uint32_t* __restrict__ sorted_tri, const float* __restrict__ tri_lo,
+                            const float* __restrict__ tri_hi) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const uint64_t excl = incl[i] - ploc_flags(i, nn);
+    ploc_emit(i, nn, excl, cid, cbox, out_cid, out_cbox, bin, plans, node_base, sorted_tri, tri_lo, tri_hi);
+}
+
 __global__ void k_radix_tree(const uint64_t* __restrict__ keys, int n, BinNode* nodes, int32_t* leaf_parent) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
@@ -36,21 +74,22 @@ __global__ void k_radix_tree(const uint64_t* __restrict__ keys, int n, BinNode* 
 
 __global__ void k_refit(int n, const int32_t* __restrict__ leaf_parent, BinNode* nodes, int32_t* flags,
                         const uint32_t* __restrict__ sorted_tri, const float* __restrict__ tri_lo,
-                        const float* __restrict__ tri_hi) {
+                        const float* __restrict__ tri_hi, CollapsePlan* plans) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
-    refit_from_leaf(k, leaf_parent, nodes, flags, sorted_tri, tri_lo, tri_hi);
+    refit_from_leaf(k, leaf_parent, nodes, flags, sorted_tri, tri_lo, tri_hi, plans);
 }
 
 __global__ void k_collapse(const CollapseItem* __restrict__ items, uint32_t n_items, const BinNode* __restrict__ bin,
                            const uint32_t* __restrict__ sorted_tri, const float* __restrict__ tri_lo,
                            const float* __restrict__ tri_hi, const f4* __restrict__ pos,
                            const int32_t* __restrict__ idx4, Node8* nodes_out, uint32_t* node_count, Tri48* tris_out,
-                           uint32_t* tri_count, CollapseItem* next, uint32_t* next_count, int n_tris) {
+                           uint32_t* tri_count, CollapseItem* next, uint32_t* next_count, int n_tris,
+                           const CollapsePlan* __restrict__ plans) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_items) return;
     collapse_node(items[i], bin, sorted_tri, tri_lo, tri_hi, pos, idx4, nodes_out, node_count, tris_out, tri_count, next,
-                  next_count, n_tris);
+                  next_count, n_tris, plans);
 }
 
 #define CK(x)                                                                                   \
@@ -68,7 +107,13 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
     uint64_t *keys = nullptr, *keys2 = nullptr;
     uint32_t *vals = nullptr, *vals2 = nullptr, *counters = nullptr;
     BinNode* bin = nullptr;
-    int32_t *leaf_parent = nullptr, *flags = nullptr;
+    int32_t *cid = nullptr, *cid2 = nullptr, *nn = nullptr;
+    Box6 *cbox = nullptr, *cbox2 = nullptr;
+    unsigned long long *pflags = nullptr, *pscan = nullptr;
+    CollapsePlan* plans = nullptr;
+    void* tmp2 = nullptr;
+    size_t tmp2_bytes = 0;
+    int32_t root = ~0;
     CollapseItem *qa = nullptr, *qb = nullptr;
     Node8* nodes = nullptr;
     Tri48* tris = nullptr;
@@ -97,55 +142,103 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
     CK(cudaMalloc(&vals, sizeof(uint32_t) * (size_t)n));
     CK(cudaMalloc(&vals2, sizeof(uint32_t) * (size_t)n));
     CK(cudaMalloc(&bin, sizeof(BinNode) * (size_t)n));
-    CK(cudaMalloc(&leaf_parent, sizeof(int32_t) * (size_t)n));
-    CK(cudaMalloc(&flags, sizeof(int32_t) * (size_t)n));
+    CK(cudaMalloc(&cid, sizeof(int32_t) * (size_t)n));
+    CK(cudaMalloc(&cid2, sizeof(int32_t) * (size_t)n));
+    CK(cudaMalloc(&nn, sizeof(int32_t) * (size_t)n));
+    CK(cudaMalloc(&cbox, sizeof(Box6) * (size_t)n));
+    CK(cudaMalloc(&cbox2, sizeof(Box6) * (size_t)n));
+    CK(cudaMalloc(&pflags, sizeof(unsigned long long) * (size_t)n));
+    CK(cudaMalloc(&pscan, sizeof(unsigned long long) * (size_t)n));
+    CK(cudaMalloc(&plans, sizeof(CollapsePlan) * (size_t)n));
     CK(cudaMalloc(&qa, sizeof(CollapseItem) * (size_t)n));
     CK(cudaMalloc(&qb, sizeof(CollapseItem) * (size_t)n));
     CK(cudaMalloc(&nodes, sizeof(Node8) * (size_t)n));
     CK(cudaMalloc(&tris, sizeof(Tri48) * (size_t)n));
     CK(cudaMalloc(&counters, sizeof(uint32_t) * 4));
-    CK(cudaMemsetAsync(flags, 0, sizeof(int32_t) * (size_t)n, st));
-    CK(cudaMemsetAsync(leaf_parent, 0xFF, sizeof(int32_t) * (size_t)n, st));
 
     k_tri_prepare<<<nb, B, 0, st>>>(d_pos, d_idx4, n, pad, slo, sinv, tri_lo, tri_hi, keys, vals);
     CK(cudaGetLastError());
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, (int)n, 0, 63, st));
     CK(cudaMalloc(&tmp, tmp_bytes));
     CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, (int)n, 0, 63, st));
-    if (n >= 2) {
-        k_radix_tree<<<nb, B, 0, st>>>(keys2, (int)n, bin, leaf_parent);
-        CK(cudaGetLastError());
-        k_refit<<<nb, B, 0, st>>>((int)n, leaf_parent, bin, flags, vals2, tri_lo, tri_hi);
-        CK(cudaGetLastError());
-    }
-    // collapse, level by level.  counters: [0] wide nodes, [1] triangles, [2] next queue
-    h_counters[0] = 1;
-    h_counters[1] = 0;
-    h_counters[2] = 0;
-    h_counters[3] = 0;
-    CK(cudaMemcpyAsync(counters, h_counters, sizeof h_counters, cudaMemcpyHostToDevice, st));
-    {
-        CollapseItem root{n >= 2 ? 0 : ~0, 0u};
-        CK(cudaMemcpyAsync(qa, &root, sizeof root, cudaMemcpyHostToDevice, st));
-    }
-    while (n_items > 0) {
-        ++levels;
-        k_collapse<<<(n_items + 63) / 64, 64, 0, st>>>(qa, n_items, bin, vals2, tri_lo, tri_hi, d_pos, d_idx4, nodes,
-                                                       counters + 0, tris, counters + 1, qb, counters + 2, (int)n);
-        CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(h_counters, counters, sizeof h_counters, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        n_items = h_counters[2];
-        CK(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), st));
-        std::swap(qa, qb);
-        if (levels > 4 * kStackSize) {
-            err = "bvh collapse did not terminate";
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        if (n >= 2 && attempt == 0) {
+            // parallel locally-ordered clustering: rounds of nearest neighbour / flags / scan / emit
+            CK(cub::DeviceScan::InclusiveSum(nullptr, tmp2_bytes, pflags, pscan, (int)n, st));
+            CK(cudaMalloc(&tmp2, tmp2_bytes));
+            k_ploc_init<<<nb, B, 0, st>>>(n, vals2, tri_lo, tri_hi, cid, cbox);
+            CK(cudaGetLastError());
+            uint32_t m = n, node_base = 0;
+            int rounds = 0;
+            while (m > 1) {
+                const uint32_t mb = (m + B - 1) / B;
+                k_ploc_nearest<<<mb, B, 0, st>>>((int)m, cbox, nn);
+                k_ploc_flags<<<mb, B, 0, st>>>((int)m, nn, pflags);
+                CK(cub::DeviceScan::InclusiveSum(tmp2, tmp2_bytes, pflags, pscan, (int)m, st));
+                k_ploc_emit<<<mb, B, 0, st>>>((int)m, nn, pscan, cid, cbox, cid2, cbox2, bin, plans, node_base, vals2, tri_lo,
+                                             tri_hi);
+                CK(cudaGetLastError());
+                unsigned long long total = 0;
+                CK(cudaMemcpyAsync(&total, pscan + (m - 1), sizeof total, cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+                const uint32_t merged = (uint32_t)(total >> 32);
+                if (merged == 0 || ++rounds > 4096) {
+                    err = "ploc made no progress";
+                    goto fail;
+                }
+                m = (uint32_t)(total & 0xFFFFFFFFull);
+                node_base += merged;
+                std::swap(cid, cid2);
+                std::swap(cbox, cbox2);
+            }
+            CK(cudaMemcpyAsync(&root, cid, sizeof root, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+        }
+        if (n >= 2 && attempt == 1) {
+            // fallback: binary radix tree over the Morton keys (Karras 2012), depth bounded by the key
+            // length; used when the clustering produced a tree deeper than the traversal stack
+            int32_t *leaf_parent = cid, *arrive_flags = cid2;
+            CK(cudaMemsetAsync(arrive_flags, 0, sizeof(int32_t) * (size_t)n, st));
+            CK(cudaMemsetAsync(leaf_parent, 0xFF, sizeof(int32_t) * (size_t)n, st));
+            k_radix_tree<<<nb, B, 0, st>>>(keys2, (int)n, bin, leaf_parent);
+            CK(cudaGetLastError());
+            k_refit<<<nb, B, 0, st>>>((int)n, leaf_parent, bin, arrive_flags, vals2, tri_lo, tri_hi, plans);
+            CK(cudaGetLastError());
+            root = 0;
+        }
+        // collapse, level by level.  counters: [0] wide nodes, [1] triangles, [2] next queue
+        h_counters[0] = 1;
+        h_counters[1] = 0;
+        h_counters[2] = 0;
+        h_counters[3] = 0;
+        CK(cudaMemcpyAsync(counters, h_counters, sizeof h_counters, cudaMemcpyHostToDevice, st));
+        {
+            CollapseItem root_item{root, 0u};
+            CK(cudaMemcpyAsync(qa, &root_item, sizeof root_item, cudaMemcpyHostToDevice, st));
+            CK(cudaStreamSynchronize(st));
+        }
+        levels = 0;
+        n_items = 1;
+        while (n_items > 0) {
+            ++levels;
+            k_collapse<<<(n_items + 63) / 64, 64, 0, st>>>(qa, n_items, bin, vals2, tri_lo, tri_hi, d_pos, d_idx4, nodes,
+                                                           counters + 0, tris, counters + 1, qb, counters + 2, (int)n, plans);
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(h_counters, counters, sizeof h_counters, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            n_items = h_counters[2];
+            CK(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), st));
+            std::swap(qa, qb);
+            if (levels > 4 * kStackSize) {
+                err = "bvh collapse did not terminate";
+                goto fail;
+            }
+        }
+        if (levels <= kStackSize) break;
+        if (attempt == 1) {
+            err = "bvh deeper than the traversal stack (" + std::to_string(levels) + " levels)";
             goto fail;
         }
-    }
-    if (levels > kStackSize) {
-        err = "bvh deeper than the traversal stack (" + std::to_string(levels) + " levels)";
-        goto fail;
     }
     if (h_counters[1] != n) {
         err = "bvh collapse lost triangles: " + std::to_string(h_counters[1]) + " of " + std::to_string(n);
@@ -160,12 +253,14 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
     tris = nullptr;
     CK(cudaStreamSynchronize(st));
     cudaFree(tri_lo); cudaFree(tri_hi); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
-    cudaFree(bin); cudaFree(leaf_parent); cudaFree(flags); cudaFree(qa); cudaFree(qb); cudaFree(nodes);
+    cudaFree(bin); cudaFree(cid); cudaFree(cid2); cudaFree(nn); cudaFree(cbox); cudaFree(cbox2); cudaFree(pflags);
+    cudaFree(pscan); cudaFree(plans); cudaFree(tmp2); cudaFree(qa); cudaFree(qb); cudaFree(nodes);
     cudaFree(counters); cudaFree(tmp);
     return true;
 fail:
     cudaFree(tri_lo); cudaFree(tri_hi); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
-    cudaFree(bin); cudaFree(leaf_parent); cudaFree(flags); cudaFree(qa); cudaFree(qb); cudaFree(nodes);
+    cudaFree(bin); cudaFree(cid); cudaFree(cid2); cudaFree(nn); cudaFree(cbox); cudaFree(cbox2); cudaFree(pflags);
+    cudaFree(pscan); cudaFree(plans); cudaFree(tmp2); cudaFree(qa); cudaFree(qb); cudaFree(nodes);
     cudaFree(tris); cudaFree(counters); cudaFree(tmp);
     return false;
 }

@@ -5,11 +5,16 @@
 //   1. triangle boxes + scene box          (tri_prepare, one thread per triangle)
 //   2. 63-bit Morton key of the centroid   (same pass)
 //   3. radix sort of (key, triangle)       (cub::DeviceRadixSort in bvh_build.cu)
-//   4. binary radix tree, Karras 2012      (radix_tree_node, one thread per inner node)
-//   5. bottom-up boxes with arrival flags  (refit_from_leaf, one thread per leaf)
-//   6. top-down collapse to 8-wide nodes, greedy by surface area, subtrees of <= 3
-//      triangles become leaves; octant-ordered slot assignment; 8-bit quantisation;
+//   4. binary tree by parallel locally-ordered clustering over the Morton order
+//      (ploc_nearest / ploc_flags / scan / ploc_emit, rounds until one cluster is left);
+//      every new node gets its box, triangle count and collapse plan when it is created
+//   5. cost-optimal collapse plan per binary node (plan_node, dynamic programme over
+//      "subtree in at most i slots", Ylitie et al. 2017)
+//   6. top-down collapse to 8-wide nodes following the plan, subtrees of <= 3
+//      triangles may become leaves; octant-ordered slot assignment; 8-bit quantisation;
 //      triangles re-emitted in node order   (collapse_node, level by level)
+//   (radix_tree_node / refit_from_leaf build the plain LBVH tree instead; kept for the
+//    builder comparison in tools/bvh_quality.py)
 // Each step is a PT_HD function of the element index so that tests/emu can run the
 // very same code sequentially on the host.
 #pragma once
@@ -147,10 +152,103 @@ PT_HD void fence() {
 #endif
 }
 
+
+// ---- cost-optimal collapse plan (Ylitie, Karras, Laine 2017, section 3.1) ------------------
+// For every binary node n: c[i-1] = smallest SAH cost of representing the subtree of n with at
+// most i child slots of a wide node (i = 1..7), and the decisions that reach it:
+//   dec[0]    1 = as ONE slot the subtree is a leaf (<= kMaxLeafTris triangles), 0 = an inner
+//             wide node whose 8 slots are distributed over the two children by dec[7]
+//   dec[j-1]  (j = 2..8) how `j` slots are used: 0 = no better than j-1 slots, k > 0 = left child
+//             gets k slots, right child gets j-k
+// Costs: kCostNode per wide-node visit, kCostTri per triangle test, both weighted by the box
+// half-area.  The numbers follow the measured instruction cost of the two phases of the walker
+// (about 300 vs 70 issued instructions, profiles/r01_ncu_summary.md).
+constexpr int kMaxLeafTris = 3;
+constexpr float kCostNode = 1.0f;
+#ifndef PT_COST_TRI
+#define PT_COST_TRI 0.3f
+#endif
+constexpr float kCostTri = PT_COST_TRI;
+
+struct CollapsePlan {
+    float c[7];
+    uint8_t dec[8];
+    uint32_t pad;
+};
+static_assert(sizeof(CollapsePlan) == 40, "CollapsePlan is 40 bytes");
+
+PT_HD float half_area(const float* lo, const float* hi) {
+    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// plan of inner binary node `cur` from the finished plans of its children (leaves of the binary
+// tree are single triangles: cost area * kCostTri for any number of slots)
+PT_HD void plan_node(int cur, BinNode* nodes, CollapsePlan* plans, const uint32_t* sorted_tri, const float* tri_lo,
+                     const float* tri_hi) {
+    const BinNode& nd = nodes[cur];
+    float cc[2][7];
+    for (int side = 0; side < 2; ++side) {
+        const int32_t c = side == 0 ? nd.left : nd.right;
+        if (c < 0) {
+            const uint32_t t = sorted_tri[~c];
+            float lo[3], hi[3];
+            for (int a = 0; a < 3; ++a) {
+                lo[a] = load_cg(tri_lo + 3 * (size_t)t + a);
+                hi[a] = load_cg(tri_hi + 3 * (size_t)t + a);
+            }
+            const float v = half_area(lo, hi) * kCostTri;
+            for (int i = 0; i < 7; ++i) cc[side][i] = v;
+        } else {
+            for (int i = 0; i < 7; ++i) cc[side][i] = load_cg(&plans[c].c[i]);
+        }
+    }
+    const float area = half_area(nd.lo, nd.hi);
+    CollapsePlan p;
+    p.pad = 0;
+    float dist[9];  // dist[j]: best cost using exactly-at-most j slots split over both children
+    uint8_t split[9];
+    for (int j = 2; j <= 8; ++j) {
+        float best = 3.4e38f;
+        int bk = 1;
+        for (int k = 1; k < j; ++k) {
+            if (k > 7 || j - k > 7) continue;
+            const float v = cc[0][k - 1] + cc[1][j - k - 1];
+            if (v < best) {
+                best = v;
+                bk = k;
+            }
+        }
+        dist[j] = best;
+        split[j] = (uint8_t)bk;
+    }
+    const float c_leaf = nd.count <= kMaxLeafTris ? area * (float)nd.count * kCostTri : 3.4e38f;
+    const float c_inner = dist[8] + area * kCostNode;
+    p.dec[7] = split[8];
+    if (c_leaf <= c_inner) {
+        p.c[0] = c_leaf;
+        p.dec[0] = 1;
+    } else {
+        p.c[0] = c_inner;
+        p.dec[0] = 0;
+    }
+    for (int j = 2; j <= 7; ++j) {
+        if (dist[j] < p.c[j - 2]) {
+            p.c[j - 1] = dist[j];
+            p.dec[j - 1] = split[j];
+        } else {
+            p.c[j - 1] = p.c[j - 2];
+            p.dec[j - 1] = 0;
+        }
+    }
+    plans[cur] = p;
+}
+
 // leaf at sorted position k walks up; the second thread to reach a node merges the
 // two child boxes (boxes of leaves come from tri_lo/tri_hi via the sorted order).
 PT_HD void refit_from_leaf(int k, const int32_t* leaf_parent, BinNode* nodes, int32_t* flags,
-                           const uint32_t* sorted_tri, const float* tri_lo, const float* tri_hi) {
+                           const uint32_t* sorted_tri, const float* tri_lo, const float* tri_hi,
+                           CollapsePlan* plans) {
     int cur = leaf_parent[k];
     while (cur >= 0) {
         fence();
@@ -180,21 +278,122 @@ PT_HD void refit_from_leaf(int k, const int32_t* leaf_parent, BinNode* nodes, in
             nd.lo[a] = lo[a];
             nd.hi[a] = hi[a];
         }
+        plan_node(cur, nodes, plans, sorted_tri, tri_lo, tri_hi);
         cur = nd.parent;
     }
 }
 
-PT_HD float half_area(const float* lo, const float* hi) {
-    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+
+// sorted positions of the triangles under binary node n (count <= kMaxLeafTris), left to right
+PT_HD int leaf_positions(const BinNode* bin, int32_t n, int* out) {
+    int32_t st[2 * kMaxLeafTris];
+    int sp = 0, cnt = 0;
+    st[sp++] = n;
+    while (sp > 0) {
+        const int32_t c = st[--sp];
+        if (c < 0) {
+            if (cnt < kMaxLeafTris) out[cnt] = ~c;
+            ++cnt;
+        } else {
+            st[sp++] = bin[c].right;
+            st[sp++] = bin[c].left;
+        }
+    }
+    return cnt < kMaxLeafTris ? cnt : kMaxLeafTris;
+}
+
+// ---- binary tree by parallel locally-ordered clustering (Meister & Bittner, TVCG 2018) -------
+// Clusters start as the Morton-sorted triangles.  Every round each cluster looks kPlocRadius
+// positions to both sides for the neighbour giving the smallest merged box (ploc_nearest),
+// mutual nearest neighbours merge into a new inner node (ploc_flags + an exclusive scan decide
+// the node index and the compacted position, ploc_emit writes both), until one cluster is left.
+// Ties go to the buddy position i^1, then to the smaller position, so the result is the same
+// whatever the thread order and at least one pair merges every round.
+// The new node's box, triangle count and collapse plan are complete when it is created: no
+// separate refit pass.  Cluster ids: >= 0 inner node, < 0 ~(sorted position) of a triangle.
+#ifndef PT_PLOC_RADIUS
+#define PT_PLOC_RADIUS 8
+#endif
+constexpr int kPlocRadius = PT_PLOC_RADIUS;
+
+struct Box6 {
+    float lo[3], hi[3];
+};
+
+PT_HD float merged_half_area(const Box6& a, const Box6& b) {
+    const float dx = fmaxf(a.hi[0], b.hi[0]) - fminf(a.lo[0], b.lo[0]);
+    const float dy = fmaxf(a.hi[1], b.hi[1]) - fminf(a.lo[1], b.lo[1]);
+    const float dz = fmaxf(a.hi[2], b.hi[2]) - fminf(a.lo[2], b.lo[2]);
     return dx * dy + dy * dz + dz * dx;
+}
+
+PT_HD void ploc_nearest(int i, int m, const Box6* cbox, int32_t* nn) {
+    const Box6 me = cbox[i];
+    const int j0 = i - kPlocRadius < 0 ? 0 : i - kPlocRadius;
+    const int j1 = i + kPlocRadius > m - 1 ? m - 1 : i + kPlocRadius;
+    float best = 3.4e38f;
+    int bj = -1;
+    for (int j = j0; j <= j1; ++j) {
+        if (j == i) continue;
+        const float d = merged_half_area(me, cbox[j]);
+        // equal cost: the buddy position i^1 wins, then the smaller position (identical boxes
+        // — duplicated triangles — then pair up (2k, 2k+1) and the tree stays balanced)
+        if (d < best || (d == best && j == (i ^ 1))) {
+            best = d;
+            bj = j;
+        }
+    }
+    nn[i] = bj;
+}
+
+// low 32 bits: 1 when position i survives the round, high 32 bits: 1 when it creates a node
+PT_HD uint64_t ploc_flags(int i, const int32_t* nn) {
+    const int j = nn[i];
+    const bool mutual = j >= 0 && nn[j] == i;
+    if (!mutual) return 1ull;
+    return i < j ? (1ull | (1ull << 32)) : 0ull;
+}
+
+PT_HD void ploc_emit(int i, const int32_t* nn, uint64_t excl, const int32_t* cid, const Box6* cbox,
+                     int32_t* out_cid, Box6* out_cbox, BinNode* bin, CollapsePlan* plans, uint32_t node_base,
+                     const uint32_t* sorted_tri, const float* tri_lo, const float* tri_hi) {
+    const int j = nn[i];
+    const bool mutual = j >= 0 && nn[j] == i;
+    if (mutual && i > j) return;
+    const uint32_t pos = (uint32_t)(excl & 0xFFFFFFFFull);  // exclusive scan of ploc_flags at i
+    if (!mutual) {
+        out_cid[pos] = cid[i];
+        out_cbox[pos] = cbox[i];
+        return;
+    }
+    const int32_t id = (int32_t)(node_base + (uint32_t)(excl >> 32));
+    const Box6 a = cbox[i], b = cbox[j];
+    BinNode nd;
+    for (int k = 0; k < 3; ++k) {
+        nd.lo[k] = fminf(a.lo[k], b.lo[k]);
+        nd.hi[k] = fmaxf(a.hi[k], b.hi[k]);
+    }
+    nd.left = cid[i];
+    nd.right = cid[j];
+    nd.first = 0;
+    nd.count = (nd.left < 0 ? 1 : bin[nd.left].count) + (nd.right < 0 ? 1 : bin[nd.right].count);
+    nd.parent = -1;
+    nd.pad = 0;
+    bin[id] = nd;
+    plan_node(id, bin, plans, sorted_tri, tri_lo, tri_hi);
+    out_cid[pos] = id;
+    Box6 u;
+    for (int k = 0; k < 3; ++k) {
+        u.lo[k] = nd.lo[k];
+        u.hi[k] = nd.hi[k];
+    }
+    out_cbox[pos] = u;
 }
 
 struct CollapseItem {
     int32_t bin;    // binary node to turn into a wide node (>= 0), or ~leafpos for a 1-triangle scene
     uint32_t wide;  // index of the wide node to write
 };
-
-constexpr int kMaxLeafTris = 3;
 
 // smallest exponent byte eb such that 255 * 2^(eb-127) >= ext (with room for the
 // outward rounding of quantise())
@@ -215,7 +414,7 @@ PT_HD uint32_t quant_exponent(float ext) {
 PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* sorted_tri,
                          const float* tri_lo, const float* tri_hi, const f4* pos, const int32_t* idx4,
                          Node8* nodes_out, uint32_t* node_count, Tri48* tris_out, uint32_t* tri_count,
-                         CollapseItem* next, uint32_t* next_count, int n_tris) {
+                         CollapseItem* next, uint32_t* next_count, int n_tris, const CollapsePlan* plans) {
     // children under construction: inner binary node (>=0) or single leaf (~pos)
     int32_t ch[8];
     int nch = 0;
@@ -236,26 +435,34 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
         if (b.count <= kMaxLeafTris) {
             ch[nch++] = item.bin;  // whole subtree is one leaf
         } else {
-            ch[nch++] = b.left;
-            ch[nch++] = b.right;
-            // greedy: open the inner child with the largest box until 8 children
-            while (nch < 8) {
-                int best = -1;
-                float best_area = -1.0f;
-                for (int i = 0; i < nch; ++i) {
-                    if (ch[i] < 0) continue;
-                    const BinNode& c = bin[ch[i]];
-                    if (c.count <= kMaxLeafTris) continue;
-                    const float ar = half_area(c.lo, c.hi);
-                    if (ar > best_area) {
-                        best_area = ar;
-                        best = i;
-                    }
+            // follow the cost-optimal plan: 8 slots distributed over the two subtrees
+            int32_t st_n[16];
+            int st_j[16];
+            int sp = 0;
+            const int k0 = plans[item.bin].dec[7];
+            st_n[sp] = b.right;
+            st_j[sp++] = 8 - k0;
+            st_n[sp] = b.left;
+            st_j[sp++] = k0;
+            while (sp > 0) {
+                --sp;
+                const int32_t n = st_n[sp];
+                int j = st_j[sp];
+                if (n < 0) {
+                    ch[nch++] = n;
+                    continue;
                 }
-                if (best < 0) break;
-                const BinNode& c = bin[ch[best]];
-                ch[best] = c.left;
-                ch[nch++] = c.right;
+                const CollapsePlan& p = plans[n];
+                while (j > 1 && p.dec[j - 1] == 0) --j;
+                if (j == 1) {
+                    ch[nch++] = n;
+                    continue;
+                }
+                const int k = p.dec[j - 1];
+                st_n[sp] = bin[n].right;
+                st_j[sp++] = j - k;
+                st_n[sp] = bin[n].left;
+                st_j[sp++] = k;
             }
         }
     }
@@ -263,7 +470,8 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
     // child boxes, kinds
     float clo[8][3], chi[8][3];
     bool inner[8];
-    int first[8], cnt[8];
+    int cnt[8];
+    int lpos[8][kMaxLeafTris];  // sorted positions of a leaf child's triangles
     for (int i = 0; i < nch; ++i) {
         if (ch[i] < 0) {
             const int posn = ~ch[i];
@@ -273,7 +481,7 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
                 chi[i][a] = tri_hi[3 * (size_t)t + a];
             }
             inner[i] = false;
-            first[i] = posn;
+            lpos[i][0] = posn;
             cnt[i] = 1;
         } else {
             const BinNode& c = bin[ch[i]];
@@ -281,9 +489,9 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
                 clo[i][a] = c.lo[a];
                 chi[i][a] = c.hi[a];
             }
-            inner[i] = c.count > kMaxLeafTris;
-            first[i] = c.first;
+            inner[i] = c.count > kMaxLeafTris && plans[ch[i]].dec[0] == 0;
             cnt[i] = c.count;
+            if (!inner[i]) cnt[i] = leaf_positions(bin, ch[i], lpos[i]);
         }
     }
 
@@ -362,7 +570,7 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
             const uint32_t unary = cnt[i] == 1 ? 1u : (cnt[i] == 2 ? 3u : 7u);
             meta[s] = (uint8_t)((unary << 5) | (uint32_t)tri_off);
             for (int k = 0; k < cnt[i]; ++k) {
-                const uint32_t t = sorted_tri[first[i] + k];
+                const uint32_t t = sorted_tri[lpos[i][k]];
                 const f4 a = pos[idx4[4 * (size_t)t + 0]], b = pos[idx4[4 * (size_t)t + 1]],
                          c = pos[idx4[4 * (size_t)t + 2]];
                 Tri48 o;

@@ -207,6 +207,8 @@ class Emu(_SceneChecker):
         L.emu_set_render.argtypes = [P, C.c_int, C.c_int, C.c_int, C.c_int]
         L.emu_build.argtypes = [P]
         L.emu_levels.argtypes = [P]
+        L.emu_walk_counters.argtypes = [P, P]
+        L.emu_force_lbvh.argtypes = [P, C.c_int]
         L.emu_export.argtypes = [P, P, P]
         L.emu_export.restype = C.c_uint32
         L.emu_import.argtypes = [P, P, C.c_uint32, P, C.c_uint32]
@@ -240,7 +242,9 @@ class Emu(_SceneChecker):
         mean = np.zeros((H, W, 4), np.float32)
         rgba = np.zeros((H, W), np.uint32)
         rays = self.L.emu_render(self.h, rank, world, shard_mode, threads, _p(s), _p(mean), _p(rgba))
-        return dict(sum=s, mean=mean, rgba=rgba, rays=int(rays))
+        wc = np.zeros(2, np.uint64)
+        self.L.emu_walk_counters(self.h, _p(wc))
+        return dict(sum=s, mean=mean, rgba=rgba, rays=int(rays), nodes_visited=int(wc[0]), tris_tested=int(wc[1]))
 
     def primary_hits(self, threads=NCPU):
         out = np.empty((self.height, self.width), HIT_DTYPE)

@@ -28,6 +28,9 @@ struct emu_scene {
     std::vector<Tri48> tris;
     float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, max_abs = 0;
     int levels = 0;
+    int ploc_rounds = 0;
+    int force_lbvh = 0;  // tools/bvh_quality.py: build the fallback tree on purpose
+    uint64_t walk_nodes = 0, walk_tris = 0;  // node fetches / triangle tests of the last emu_render
     SceneView sv{};
 };
 
@@ -165,27 +168,69 @@ int emu_build(emu_scene* s) {
     std::vector<uint64_t> skeys(n);
     for (uint32_t i = 0; i < n; ++i) skeys[i] = keys[order[i]];
     std::vector<BinNode> bin(n);
-    std::vector<int32_t> leaf_parent(n, -1), flags(n, 0);
-    if (n >= 2) {
+    std::vector<CollapsePlan> plans(n);
+    uint32_t node_count = 1, tri_count = 0;
+    for (int attempt = (s->force_lbvh ? 1 : 0); attempt < 2; ++attempt) {
+    int32_t root = ~0;
+    if (n >= 2 && attempt == 0) {
+        // same rounds as build_bvh_device: nearest neighbour, flags, exclusive scan, emit
+        std::vector<int32_t> cid(n), cid2(n), nn(n);
+        std::vector<Box6> cbox(n), cbox2(n);
+        std::vector<uint64_t> scan(n);
+        for (uint32_t i = 0; i < n; ++i) {
+            cid[i] = ~(int32_t)i;
+            const uint32_t t = order[i];
+            for (int a = 0; a < 3; ++a) {
+                cbox[i].lo[a] = tri_lo[3 * (size_t)t + a];
+                cbox[i].hi[a] = tri_hi[3 * (size_t)t + a];
+            }
+        }
+        uint32_t m = n, node_base = 0;
+        while (m > 1) {
+            for (uint32_t i = 0; i < m; ++i) ploc_nearest((int)i, (int)m, cbox.data(), nn.data());
+            uint64_t acc = 0;
+            for (uint32_t i = 0; i < m; ++i) {
+                scan[i] = acc;
+                acc += ploc_flags((int)i, nn.data());
+            }
+            for (uint32_t i = 0; i < m; ++i)
+                ploc_emit((int)i, nn.data(), scan[i], cid.data(), cbox.data(), cid2.data(), cbox2.data(), bin.data(),
+                          plans.data(), node_base, order.data(), tri_lo.data(), tri_hi.data());
+            m = (uint32_t)(acc & 0xFFFFFFFFull);
+            node_base += (uint32_t)(acc >> 32);
+            std::swap(cid, cid2);
+            std::swap(cbox, cbox2);
+            ++s->ploc_rounds;
+        }
+        root = cid[0];
+    }
+    if (n >= 2 && attempt == 1) {  // fallback of build_bvh_device: binary radix tree + refit
+        std::vector<int32_t> leaf_parent(n, -1), flags(n, 0);
         for (int i = 0; i < (int)n - 1; ++i) radix_tree_node(skeys.data(), (int)n, i, bin.data(), leaf_parent.data());
         for (int k = 0; k < (int)n; ++k)
-            refit_from_leaf(k, leaf_parent.data(), bin.data(), flags.data(), order.data(), tri_lo.data(), tri_hi.data());
+            refit_from_leaf(k, leaf_parent.data(), bin.data(), flags.data(), order.data(), tri_lo.data(), tri_hi.data(),
+                            plans.data());
+        root = 0;
     }
     s->nodes.assign(n, Node8{});
     s->tris.assign(n, Tri48{});
     std::vector<CollapseItem> qa(n), qb(n);
-    uint32_t node_count = 1, tri_count = 0, n_items = 1;
-    qa[0] = CollapseItem{n >= 2 ? 0 : ~0, 0u};
+    uint32_t n_items = 1;
+    node_count = 1;
+    tri_count = 0;
+    qa[0] = CollapseItem{root, 0u};
     s->levels = 0;
     while (n_items) {
         ++s->levels;
         uint32_t next_count = 0;
         for (uint32_t i = 0; i < n_items; ++i)
             collapse_node(qa[i], bin.data(), order.data(), tri_lo.data(), tri_hi.data(), s->pos.data(), s->idx4.data(),
-                          s->nodes.data(), &node_count, s->tris.data(), &tri_count, qb.data(), &next_count, (int)n);
+                          s->nodes.data(), &node_count, s->tris.data(), &tri_count, qb.data(), &next_count, (int)n, plans.data());
         n_items = next_count;
         std::swap(qa, qb);
         if (s->levels > 4 * kStackSize) return -2;
+    }
+    if (s->levels <= kStackSize) break;
     }
     if (tri_count != n) return -3;
     if (s->levels > kStackSize) return -4;
@@ -194,6 +239,11 @@ int emu_build(emu_scene* s) {
 }
 
 int emu_levels(emu_scene* s) { return s->levels; }
+void emu_force_lbvh(emu_scene* s, int on) { s->force_lbvh = on; }
+void emu_walk_counters(emu_scene* s, uint64_t* out) {
+    out[0] = s->walk_nodes;
+    out[1] = s->walk_tris;
+}
 uint32_t emu_export(emu_scene* s, void* nodes, void* tris) {
     if (nodes) memcpy(nodes, s->nodes.data(), sizeof(Node8) * s->nodes.size());
     if (tris) memcpy(tris, s->tris.data(), sizeof(Tri48) * s->tris.size());
@@ -264,9 +314,12 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
     }
     memset(sum_out, 0, sizeof(float) * 4 * (size_t)W * H);
     std::atomic<uint64_t> rays{0};
+    std::atomic<uint64_t> cnt_nodes{0}, cnt_tris{0};
     const int rows = sv.n_lanes / W;
     parallel_rows(rows, nthreads, [&](int row) {
         uint64_t nr = 0;
+        WalkCounters wc{0, 0};
+        uint64_t wn = 0, wt = 0;
         for (int c = 0; c < W; ++c) {
             const uint32_t lane = (uint32_t)row * W + c;
             int px, py;
@@ -287,7 +340,10 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
                     L.depth = ctl_depth(ctl);
                     L.lobe = ctl_lobe(ctl);
                     Hit h;
-                    walk_closest<false>(sv.nodes, sv.tris, L.o, L.d, kTMin, kTMax, h, nullptr);
+                    wc = WalkCounters{0, 0};
+                    walk_closest<true>(sv.nodes, sv.tris, L.o, L.d, kTMin, kTMax, h, &wc);
+                    wn += wc.nodes;
+                    wt += wc.tris;
                     ++nr;
                     const ShadeResult r = shade_lane(sv, L, h, px, py);
                     if (L.sample_ended) sum = sum + L.contrib;
@@ -300,7 +356,11 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
             o[2] = sum.z;
         }
         rays += nr;
+        cnt_nodes += wn;
+        cnt_tris += wt;
     });
+    s->walk_nodes = cnt_nodes.load();
+    s->walk_tris = cnt_tris.load();
     if (mean_out || rgba_out) {
         const float inv = 1.0f / static_cast<float>(total_spp);
         for (int py = 0; py < H; ++py)

@@ -115,6 +115,21 @@ def test_triangle_soups_and_edge_counts(n, degenerate):
     assert same_hits(o.trace(org, d, brute=True), e.trace(org, d)).all()
 
 
+def test_fallback_radix_tree_builder():
+    """The builder falls back to the Morton radix tree when the clustered tree is deeper than the
+    traversal stack; force that path and check it against brute force too."""
+    verts, normals, idx = make_soup(3000, 77, True)
+    mats = np.zeros(1, pt.MATERIAL_DTYPE)
+    o, e = Oracle(det=True), Emu()
+    e.L.emu_force_lbvh(e.h, 1)
+    for c in (o, e):
+        c.add_mesh(verts, normals, idx, 0)
+        c.set_materials(mats)
+        c.build()
+    org, d = random_rays(800, 5, [0, 0, 0], 1.5)
+    assert same_hits(o.trace(org, d, brute=True), e.trace(org, d)).all()
+
+
 def decode_nodes(nodes):
     """80-byte nodes -> origin, scales, imask, child_base, tri_base, meta, lo[3][8], hi[3][8]"""
     p = nodes[:, 0:12].view(np.float32)
