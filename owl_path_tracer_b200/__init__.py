@@ -88,6 +88,8 @@ _libs = {}
 def _load(name: str) -> C.CDLL:
     if name not in _libs:
         path = LIB_DIR / name
+        if name == "libb200pt.so" and os.environ.get("B200PT_LIB"):   # A/B builds (tools/build_variants.sh)
+            path = Path(os.environ["B200PT_LIB"])
         if not path.exists():
             raise B200ptError(f"{path} is missing: run `make product` (or __graft_entry__.build()); "
                               "there is no CPU fallback for the render path")

@@ -118,6 +118,7 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     sv.row_step = 1;
     sv.seed_row_offset = 0;
     sv.n_lanes = c->width * c->height;
+    sv.plane_magic = 0x3F800000u;
     if (!full_frame && c->cfg.world_size > 1) {
         if (c->cfg.shard_mode == B200PT_SHARD_ROWS) {
             sv.row_first = c->cfg.rank;
@@ -548,6 +549,7 @@ extern "C" int b200pt_trace(b200pt_ctx* c, const float* origins, const float* di
     SceneView sv{};
     sv.nodes = c->bvh.nodes;
     sv.tris = c->bvh.tris;
+    sv.plane_magic = 0x3F800000u;
     float *d_o = nullptr, *d_d = nullptr;
     f4* d_hits = nullptr;
     CU(cudaMalloc(&d_o, sizeof(float) * 3 * (size_t)n));

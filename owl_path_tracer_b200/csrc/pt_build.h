@@ -404,7 +404,7 @@ PT_HD uint32_t quant_exponent(float ext) {
     uint32_t eb = (bits >> 23) & 0xFFu;
     if (bits & 0x7FFFFFu) eb += 1;  // round up to the next power of two
     if (eb < 1) eb = 1;
-    if (eb > 250) eb = 250;
+    if (eb > 230) eb = 230;  // the walk adds 15 to the exponent byte (slab_axis)
     return eb;
 }
 
@@ -534,9 +534,16 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
     const uint32_t tri_base = n_leaf_tris ? grab(tri_count, (uint32_t)n_leaf_tris) : 0u;
     const uint32_t next_base = n_inner ? grab(next_count, (uint32_t)n_inner) : 0u;
 
-    const uint32_t ex = quant_exponent(nhi[0] - nlo[0]), ey = quant_exponent(nhi[1] - nlo[1]),
-                   ez = quant_exponent(nhi[2] - nlo[2]);
+    // Quantisation grid: the scale is chosen for 1.01 x the extent, and the grid origin sits 1/8 of a
+    // step below the node box.  That leaves room on both sides, so the 1/64-step outward slack of
+    // every child plane is never lost to the clamp at 0 / 255 — the slab test of the walker
+    // (plane_q, pt_bvh8.h) has a rounding error of up to 2^-9 step and relies on that slack.
+    const uint32_t ex = quant_exponent((nhi[0] - nlo[0]) * 1.01f), ey = quant_exponent((nhi[1] - nlo[1]) * 1.01f),
+                   ez = quant_exponent((nhi[2] - nlo[2]) * 1.01f);
     const float isx = u2f((254u - ex) << 23), isy = u2f((254u - ey) << 23), isz = u2f((254u - ez) << 23);
+    nlo[0] = nlo[0] - 0.125f * u2f(ex << 23);
+    nlo[1] = nlo[1] - 0.125f * u2f(ey << 23);
+    nlo[2] = nlo[2] - 0.125f * u2f(ez << 23);
 
     uint8_t meta[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     uint8_t q[6][8];

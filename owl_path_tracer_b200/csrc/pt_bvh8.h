@@ -115,6 +115,37 @@ PT_HD float safe_rcp_dir(float d) {
     return 1.0f / a;
 }
 
+// Quantised plane byte j of a packed word as the float 1 + q * 2^-15, built by ONE byte permute
+// (0x3F80'qq'00) instead of an int->float conversion: on sm_100 the conversion I2F.U8 runs on the
+// quarter-rate XU pipe and 48 of them per node made that pipe the busiest one of the walker
+// (profiles/r01_ncu_summary.md).  The slab test then evaluates
+//     t = fma(1 + q 2^-15, 2^15 a, b - 2^15 a)  =  q a + b  (+ rounding of the constant term,
+// at most 2^-9 of a quantisation step, covered by the builder's 1/64-step outward slack).
+// `magic` must hold 0x3F800000; device callers fetch it through plane_magic() so that it lives in
+// a register and the permute selector can be the instruction's immediate (with both as
+// constants ptxas re-materialises the selector in front of every PRMT).
+PT_HD uint32_t plane_magic() {
+#if defined(__CUDA_ARCH__)
+    uint32_t m;
+    asm("mov.b32 %0, 0x3F800000;" : "=r"(m));
+    return m;
+#else
+    return 0x3F800000u;
+#endif
+}
+PT_HD float plane_q(uint32_t word, int j, uint32_t magic) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(word, magic, 0x7604u | ((uint32_t)j << 4)));
+#else
+    return u2f(magic | (((word >> (8 * j)) & 0xFFu) << 8));
+#endif
+}
+// per axis: a2 = 2^15 * scale / d,  b2 = (p - o) / d - a2
+PT_HD void slab_axis(uint32_t exp_byte, float p, float o, float inv_d, float& a2, float& b2) {
+    a2 = u2f((exp_byte + 15u) << 23) * inv_d;
+    b2 = (p - o) * inv_d - a2;
+}
+
 struct WalkCounters {
     uint32_t nodes, tris;
 };
@@ -131,6 +162,7 @@ PT_HD void walk_closest(const Node8* __restrict__ nodes, const Tri48* __restrict
     const float idx = safe_rcp_dir(d.x), idy = safe_rcp_dir(d.y), idz = safe_rcp_dir(d.z);
     const uint32_t octinv = (d.x < 0.0f ? 0u : 4u) | (d.y < 0.0f ? 0u : 2u) | (d.z < 0.0f ? 0u : 1u);
 
+    const uint32_t magic = plane_magic();
     uint32_t stack_base[kStackSize];
     uint32_t stack_mask[kStackSize];
     int sp = 0;
@@ -155,23 +187,19 @@ PT_HD void walk_closest(const Node8* __restrict__ nodes, const Tri48* __restrict
             if (COUNT) wc->nodes++;
 
             const uint32_t e = w0.w;
-            const float sx = u2f((e & 0xFFu) << 23), sy = u2f(((e >> 8) & 0xFFu) << 23),
-                        sz = u2f(((e >> 16) & 0xFFu) << 23);
-            const float aix = sx * idx, aiy = sy * idy, aiz = sz * idz;
-            const float aox = (u2f(w0.x) - o.x) * idx, aoy = (u2f(w0.y) - o.y) * idy,
-                        aoz = (u2f(w0.z) - o.z) * idz;
+            float aix, aiy, aiz, aox, aoy, aoz;
+            slab_axis(e & 0xFFu, u2f(w0.x), o.x, idx, aix, aox);
+            slab_axis((e >> 8) & 0xFFu, u2f(w0.y), o.y, idy, aiy, aoy);
+            slab_axis((e >> 16) & 0xFFu, u2f(w0.z), o.z, idz, aiz, aoz);
             uint32_t hitmask = 0;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int sh = (i & 3) * 8;
+                const int j = i & 3, sh = j * 8;
                 const uint32_t meta = ((i < 4 ? w1.z : w1.w) >> sh) & 0xFFu;
                 if (meta == 0) continue;
-                const float lox = (float)(((i < 4 ? w2.x : w2.y) >> sh) & 0xFFu);
-                const float loy = (float)(((i < 4 ? w2.z : w2.w) >> sh) & 0xFFu);
-                const float loz = (float)(((i < 4 ? w3.x : w3.y) >> sh) & 0xFFu);
-                const float hix = (float)(((i < 4 ? w3.z : w3.w) >> sh) & 0xFFu);
-                const float hiy = (float)(((i < 4 ? w4.x : w4.y) >> sh) & 0xFFu);
-                const float hiz = (float)(((i < 4 ? w4.z : w4.w) >> sh) & 0xFFu);
+                const float lox = plane_q(i < 4 ? w2.x : w2.y, j, magic), loy = plane_q(i < 4 ? w2.z : w2.w, j, magic);
+                const float loz = plane_q(i < 4 ? w3.x : w3.y, j, magic), hix = plane_q(i < 4 ? w3.z : w3.w, j, magic);
+                const float hiy = plane_q(i < 4 ? w4.x : w4.y, j, magic), hiz = plane_q(i < 4 ? w4.z : w4.w, j, magic);
                 const float nx = d.x < 0.0f ? hix : lox, fx = d.x < 0.0f ? lox : hix;
                 const float ny = d.y < 0.0f ? hiy : loy, fy = d.y < 0.0f ? loy : hiy;
                 const float nz = d.z < 0.0f ? hiz : loz, fz = d.z < 0.0f ? loz : hiz;

@@ -44,6 +44,7 @@ struct SceneView {
     int32_t row_first, row_step;
     int32_t seed_row_offset;   // added to y when seeding (per-rank streams: rank * height)
     int32_t n_lanes;
+    uint32_t plane_magic;      // 0x3F800000, see plane_q (pt_bvh8.h): a runtime value on purpose
 };
 
 // packed per-lane control word: sample index (20 bits) | depth (8 bits) | lobe+1 (3 bits)

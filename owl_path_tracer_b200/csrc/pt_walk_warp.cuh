@@ -17,7 +17,20 @@
 
 namespace pt {
 
-constexpr int kRefill = 6;        // refill when at least this many lanes are idle
+// Tunables (compile-time; tools/build_variants.sh builds A/B libraries from them).
+#ifndef PT_REFILL
+#define PT_REFILL 6          // refill when at least this many lanes are idle
+#endif
+#ifndef PT_TRI_VOTE
+#define PT_TRI_VOTE 3        // triangle phase when PT_TRI_VOTE * (lanes with triangles) >= working lanes
+#endif
+#ifndef PT_PREFETCH_TRI
+#define PT_PREFETCH_TRI 0    // prefetch.global.L1 of the first leaf triangle at the end of a node step
+#endif
+#ifndef PT_PREFETCH_NODE
+#define PT_PREFETCH_NODE 0   // prefetch.global.L1 of the next child node at the end of a node step
+#endif
+constexpr int kRefill = PT_REFILL;
 constexpr int kWalkStack = 2 * kStackSize;  // per tree level at most one node group + one postponed triangle group
 
 __device__ __forceinline__ u4 ldg4(const u4* p) {
@@ -29,11 +42,13 @@ __device__ __forceinline__ f4 ldg4f(const f4* p) {
     return f4{v.x, v.y, v.z, v.w};
 }
 
+// magic: 0x3F800000 handed in as a RUNTIME value (SceneView::plane_magic, a kernel parameter), so that
+//        it sits in a register and the byte-permute selector of plane_q is the immediate.
 // Src:  bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax)   (i < n)
 // Sink: void store(uint32_t i, const Hit& h)
 template <bool COUNT, class Src, class Sink>
 __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const Tri48* __restrict__ tris, uint32_t n,
-                                          uint32_t* cursor, Src src, Sink sink, WalkCounters& wc) {
+                                          uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic) {
     const unsigned FULL = 0xffffffffu;
     const int lid = threadIdx.x & 31;
 
@@ -45,7 +60,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
     uint32_t octinv4 = 0;
     Hit hit{0, 0, 0, kNoHit};
     uint32_t ng_base = 0, ng_mask = 0, tg_base = 0, tg_mask = 0;
-    uint32_t stack_base[kWalkStack], stack_mask[kWalkStack];
+    uint2 stack[kWalkStack];  // (base, mask) pairs: one 8-byte local store / load per push / pop
     int sp = 0;
 
     for (;;) {
@@ -83,7 +98,8 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
                 has_ray = false;
             } else {
                 --sp;
-                const uint32_t b = stack_base[sp], m = stack_mask[sp];
+                const uint2 top = stack[sp];
+                const uint32_t b = top.x, m = top.y;
                 if (m > 0x00FFFFFFu) {
                     ng_base = b;
                     ng_mask = m;
@@ -103,7 +119,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         const bool can_node = has_ray && ng_mask > 0x00FFFFFFu;
         const int n_tri = __popc(__ballot_sync(FULL, want_tri));
         const int n_node = __popc(__ballot_sync(FULL, can_node));
-        const bool tri_phase = n_tri > 0 && (3 * n_tri >= __popc(act) || n_node == 0);
+        const bool tri_phase = n_tri > 0 && (PT_TRI_VOTE * n_tri >= __popc(act) || n_node == 0);
 
         if (tri_phase) {
             if (want_tri) {
@@ -134,8 +150,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
             }
         } else if (can_node) {
             if (tg_mask != 0) {  // lost the vote: keep the leaf triangles for later
-                stack_base[sp] = tg_base;
-                stack_mask[sp] = tg_mask;
+                stack[sp] = make_uint2(tg_base, tg_mask);
                 ++sp;
                 tg_mask = 0;
             }
@@ -143,8 +158,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
             const uint32_t imask = ng_mask & 0xFFu;
             ng_mask &= ~(1u << bit);
             if (ng_mask > 0x00FFFFFFu) {
-                stack_base[sp] = ng_base;
-                stack_mask[sp] = ng_mask;
+                stack[sp] = make_uint2(ng_base, ng_mask);
                 ++sp;
             }
             const uint32_t slot = (uint32_t)(bit - 24) ^ (octinv4 & 0xFFu);
@@ -154,9 +168,10 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
                      w4 = ldg4(&np->w[4]);
             if (COUNT) wc.nodes++;
             const uint32_t e = w0.w;
-            const float aix = u2f((e & 0xFFu) << 23) * idx, aiy = u2f(((e >> 8) & 0xFFu) << 23) * idy,
-                        aiz = u2f(((e >> 16) & 0xFFu) << 23) * idz;
-            const float aox = (u2f(w0.x) - o.x) * idx, aoy = (u2f(w0.y) - o.y) * idy, aoz = (u2f(w0.z) - o.z) * idz;
+            float aix, aiy, aiz, aox, aoy, aoz;
+            slab_axis(e & 0xFFu, u2f(w0.x), o.x, idx, aix, aox);
+            slab_axis((e >> 8) & 0xFFu, u2f(w0.y), o.y, idy, aiy, aoy);
+            slab_axis((e >> 16) & 0xFFu, u2f(w0.z), o.z, idz, aiz, aoz);
             const bool nx = d.x < 0.0f, ny = d.y < 0.0f, nz = d.z < 0.0f;
             uint32_t hitmask = 0;
 #pragma unroll
@@ -174,12 +189,12 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int sh = 8 * j;
-                    const float tnx = fmaf((float)((nearx >> sh) & 0xFFu), aix, aox);
-                    const float tny = fmaf((float)((neary >> sh) & 0xFFu), aiy, aoy);
-                    const float tnz = fmaf((float)((nearz >> sh) & 0xFFu), aiz, aoz);
-                    const float tfx = fmaf((float)((farx >> sh) & 0xFFu), aix, aox);
-                    const float tfy = fmaf((float)((fary >> sh) & 0xFFu), aiy, aoy);
-                    const float tfz = fmaf((float)((farz >> sh) & 0xFFu), aiz, aoz);
+                    const float tnx = fmaf(plane_q(nearx, j, magic), aix, aox);
+                    const float tny = fmaf(plane_q(neary, j, magic), aiy, aoy);
+                    const float tnz = fmaf(plane_q(nearz, j, magic), aiz, aoz);
+                    const float tfx = fmaf(plane_q(farx, j, magic), aix, aox);
+                    const float tfy = fmaf(plane_q(fary, j, magic), aiy, aoy);
+                    const float tfz = fmaf(plane_q(farz, j, magic), aiz, aoz);
                     const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
                     const float tf = fminf(fminf(tfx, tfy), fminf(tfz, hit.t));
                     const uint32_t cb = (child_bits4 >> sh) & 0xFFu;
@@ -191,6 +206,22 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
             ng_mask = (hitmask & 0xFF000000u) | (e >> 24);
             tg_base = w1.y;
             tg_mask = hitmask & 0x00FFFFFFu;
+#if PT_PREFETCH_TRI
+            if (tg_mask != 0) {
+                const char* tp = reinterpret_cast<const char*>(tris + (tg_base + (uint32_t)(31 - __clz(tg_mask))));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(tp));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 32));
+            }
+#endif
+#if PT_PREFETCH_NODE
+            if (ng_mask > 0x00FFFFFFu) {
+                const uint32_t nslot = (uint32_t)(31 - __clz(ng_mask) - 24) ^ (octinv4 & 0xFFu);
+                const uint32_t nrel = (uint32_t)__popc((ng_mask & 0xFFu) & ~(0xFFFFFFFFu << nslot));
+                const char* np2 = reinterpret_cast<const char*>(nodes + (ng_base + nrel));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(np2));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(np2 + 64));
+            }
+#endif
         }
     }
 }

@@ -15,6 +15,12 @@
 
 namespace pt {
 
+#ifndef PT_BLOCKS_PER_SM
+#define PT_BLOCKS_PER_SM 8     // persistent blocks of 128 threads per SM for the walker kernels
+#endif
+#ifndef PT_SHADE_MIN_BLOCKS
+#define PT_SHADE_MIN_BLOCKS 4   // register cap of k_shade: 65536 / (128 * blocks)
+#endif
 constexpr int kBlock = 128;
 
 __device__ __forceinline__ f4 ld4(const f4* p) {
@@ -66,9 +72,9 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneView sv, LaneArrays la, 
     const uint32_t n = la.counts[k];
     WalkCounters wc{0, 0};
     if (n) {
-        const uint32_t* q = la.queue[k & 1];
+        const uint32_t* q = (k & 1) ? la.queue[1] : la.queue[0];  // no dynamic index into the parameter struct
         warp_walk<COUNT>(sv.nodes, sv.tris, n, la.cursor + k, LaneRaySource{q, la.ray_o, la.ray_d, nullptr},
-                         LaneHitSink{q, la.hit}, wc);
+                         LaneHitSink{q, la.hit}, wc, sv.plane_magic);
     }
     if (COUNT) {
         unsigned long long a = wc.nodes, b = wc.tris;
@@ -83,13 +89,13 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneView sv, LaneArrays la, 
     }
 }
 
-__global__ void __launch_bounds__(kBlock) k_shade(SceneView sv, LaneArrays la, int k) {
+__global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView sv, LaneArrays la, int k) {
     const uint32_t n = la.counts[k];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     bool keep = false;
     uint32_t lane = 0;
     if (i < n) {
-        lane = la.queue[k & 1][i];
+        lane = ((k & 1) ? la.queue[1] : la.queue[0])[i];
         const f4 d = ld4(la.ray_d + lane), t = ld4(la.thr + lane), hv = ld4(la.hit + lane);
         LaneState L;
         L.o = mk3(0.0f);  // only written: the old origin is never needed again
@@ -126,7 +132,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(SceneView sv, LaneArrays la, i
         uint32_t base = 0;
         if (lid == leader) base = atomicAdd(la.counts + k + 1, (uint32_t)__popc(m));
         base = __shfl_sync(0xffffffffu, base, leader);
-        if (keep) la.queue[(k + 1) & 1][base + __popc(m & ((1u << lid) - 1u))] = lane;
+        if (keep) ((k & 1) ? la.queue[0] : la.queue[1])[base + __popc(m & ((1u << lid) - 1u))] = lane;
     }
 }
 
@@ -180,13 +186,15 @@ struct ArrayHitSink {
 
 __global__ void __launch_bounds__(kBlock) k_primary(SceneView sv, f4* hits, uint32_t* cursor) {
     WalkCounters wc{0, 0};
-    warp_walk<false>(sv.nodes, sv.tris, (uint32_t)(sv.width * sv.height), cursor, CameraRaySource{sv}, ArrayHitSink{hits}, wc);
+    warp_walk<false>(sv.nodes, sv.tris, (uint32_t)(sv.width * sv.height), cursor, CameraRaySource{sv}, ArrayHitSink{hits}, wc,
+                     sv.plane_magic);
 }
 
 __global__ void __launch_bounds__(kBlock) k_trace(SceneView sv, const float* __restrict__ o, const float* __restrict__ d,
                                                   int n, float tmin, float tmax, f4* hits, uint32_t* cursor) {
     WalkCounters wc{0, 0};
-    warp_walk<false>(sv.nodes, sv.tris, (uint32_t)n, cursor, ArrayRaySource{o, d, tmin, tmax}, ArrayHitSink{hits}, wc);
+    warp_walk<false>(sv.nodes, sv.tris, (uint32_t)n, cursor, ArrayRaySource{o, d, tmin, tmax}, ArrayHitSink{hits}, wc,
+                     sv.plane_magic);
 }
 
 __global__ void k_sample_disney(const Material* __restrict__ mats, int n, const int32_t* material, const float* wo,
@@ -214,8 +222,8 @@ __global__ void k_sample_disney(const Material* __restrict__ mats, int n, const 
 }
 
 static inline unsigned blocks(uint32_t n, int b) { return n ? (n + b - 1) / b : 1; }
-static int g_persistent_blocks = 148 * 8;
-void set_persistent_blocks(int sm_count) { g_persistent_blocks = sm_count * 8; }
+static int g_persistent_blocks = 148 * PT_BLOCKS_PER_SM;
+void set_persistent_blocks(int sm_count) { g_persistent_blocks = sm_count * PT_BLOCKS_PER_SM; }
 static inline unsigned pblocks(uint32_t n) { return std::min<unsigned>(blocks(n, kBlock), (unsigned)g_persistent_blocks); }
 
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, cudaStream_t st) {

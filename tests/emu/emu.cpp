@@ -7,6 +7,7 @@
 // same bits.
 #include <algorithm>
 #include <atomic>
+#include <cstdio>
 #include <cstring>
 #include <numeric>
 #include <thread>
@@ -29,6 +30,7 @@ struct emu_scene {
     float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, max_abs = 0;
     int levels = 0;
     int ploc_rounds = 0;
+    int debug_px = -1, debug_py = -1;  // print every ray of this pixel (debugging aid)
     int force_lbvh = 0;  // tools/bvh_quality.py: build the fallback tree on purpose
     uint64_t walk_nodes = 0, walk_tris = 0;  // node fetches / triangle tests of the last emu_render
     SceneView sv{};
@@ -240,6 +242,10 @@ int emu_build(emu_scene* s) {
 
 int emu_levels(emu_scene* s) { return s->levels; }
 void emu_force_lbvh(emu_scene* s, int on) { s->force_lbvh = on; }
+void emu_debug_pixel(emu_scene* s, int px, int py) {
+    s->debug_px = px;
+    s->debug_py = py;
+}
 void emu_walk_counters(emu_scene* s, uint64_t* out) {
     out[0] = s->walk_nodes;
     out[1] = s->walk_tris;
@@ -345,6 +351,8 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
                     wn += wc.nodes;
                     wt += wc.tris;
                     ++nr;
+                    if (s->debug_px == px && s->debug_py == py)
+                        printf("DBG %.9g %.9g %.9g %.9g %.9g %.9g %.9g %u\n", L.o.x, L.o.y, L.o.z, L.d.x, L.d.y, L.d.z, h.t, h.tri);
                     const ShadeResult r = shade_lane(sv, L, h, px, py);
                     if (L.sample_ended) sum = sum + L.contrib;
                     if (r == LANE_DONE) break;

@@ -143,6 +143,27 @@ def test_incoherent_rays_and_tie_rule():
     ctx2.close()
 
 
+@pytest.mark.parametrize("name", ["cornell-box", "sphere", "car"])
+def test_surface_rays_warp_walker_equals_scalar_walk(name):
+    """Bounce-like rays (origins on the geometry; random, grazing and zero-component directions)
+    through b200pt_trace: the warp-cooperative walker must return exactly what the scalar walk of
+    the same tree returns on the host (tests/test_emu_parity.py checks that one against brute
+    force), and — cornell-box 128x128 at 8 spp is the frame that once exposed a culled hit at
+    t ~ t_min — the full frame must equal the oracle bit for bit."""
+    from test_emu_parity import surface_rays
+    sc = pt.Scene(scene=name, width=128, height=128, spp=8, depth=8, **SCENES[name])
+    ctx, e = gpu_for(sc), Emu().load_scene(sc)
+    P, D = surface_rays(sc, 60000, 3)
+    assert same_hits(ctx.trace(P, D), e.trace(P, D)).all()
+    if name == "cornell-box":
+        o = Oracle(det=True).load_scene(sc)
+        ctx.render()
+        ro = o.render()
+        assert ctx.stats()["rays"] == ro["rays"]
+        assert (bits(ctx.framebuffer_f32()[..., :3]) == bits(ro["mean"][..., :3])).all()
+    ctx.close()
+
+
 def test_device_built_tree_equals_host_emulation_and_is_complete():
     """The tree built by the kernels is the tree the emulated builder produces (same per-element
     functions): identical node and triangle arrays."""

@@ -40,6 +40,10 @@ def timing(scene, w, h, spp, depth, flags=0, **kw):
 if __name__ == "__main__":
     import os
     os.environ.setdefault("B200PT_QUIET", "1")
+    if len(sys.argv) > 1 and sys.argv[1] == "ab":
+        timing("dragon", 1920, 1080, 32, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
+        timing("car", 1920, 1080, 32, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "timing":
         timing("cornell-box", 512, 512, 64, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
         timing("dragon", 1920, 1080, 16, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
