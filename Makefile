@@ -15,7 +15,7 @@ NVFLAGS = -std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad
           -Xcompiler -fPIC -Xcompiler -ffp-contract=off --expt-relaxed-constexpr -cudart static
 CXXFLAGS = -std=c++17 -O2 -fPIC -Wall -Wno-unused-function
 
-CUHDR = $(wildcard $(CSRC)/*.h) include/b200pt.h
+CUHDR = $(wildcard $(CSRC)/*.h) $(wildcard $(CSRC)/*.cuh) include/b200pt.h
 HOSTHDR = $(wildcard $(HOST)/*.hpp) include/b200pt.h include/b200pt_host.h
 
 all: product oracle emu
