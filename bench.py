@@ -236,7 +236,8 @@ def main():
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         cores = host_cores()
-        cpu_spp = max(1, min(32, int(round(16 * 16 / cores))))     # ~15 s of CPU work on a 16-core box
+        _, sec1, _ = cpu_oracle_rate(1, cores)                       # probe: one sample per pixel
+        cpu_spp = max(2, min(64, int(round(15.0 / max(sec1, 0.05)))))   # then ~15 s of CPU work
         rate, sec, rays = cpu_oracle_rate(cpu_spp, cores)
         cpu = dict(value=rate, unit="Mrays/s", cores=cores, kind="port",
                    sample=f"full 1920x1080 dragon frame at {cpu_spp} spp ({rays} rays, {sec:.1f} s), oracle/oracle.cpp with glibc math")

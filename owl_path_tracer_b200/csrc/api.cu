@@ -43,6 +43,10 @@ struct b200pt_ctx {
     uint32_t *d_texels = nullptr, *d_env = nullptr;
     Material* d_mats = nullptr;
     int n_mats = 0;
+    std::vector<Material> h_mats;      // host copy: the per-mesh material array is rebuilt from it
+    Material* d_mesh_mats = nullptr;   // materials[meshes[m].material] for every mesh (SceneView::mesh_materials)
+    size_t mesh_mats_capacity = 0;
+    bool mesh_mats_dirty = true;
     DeviceBVH bvh;
     bool built = false;
     // settings
@@ -64,7 +68,10 @@ struct b200pt_ctx {
 };
 
 static void free_lanes(b200pt_ctx* c) {
-    cudaFree(c->la.ray_o); cudaFree(c->la.ray_d); cudaFree(c->la.thr); cudaFree(c->la.sum); cudaFree(c->la.hit);
+    for (int b = 0; b < 2; ++b) {
+        cudaFree(c->la.ray_o[b]); cudaFree(c->la.ray_d[b]); cudaFree(c->la.thr[b]);
+    }
+    cudaFree(c->la.sum); cudaFree(c->la.hit);
     cudaFree(c->la.queue[0]); cudaFree(c->la.queue[1]); cudaFree(c->la.counts); cudaFree(c->la.cursor);
     cudaFree(c->la.walk_counters);
     cudaFree(c->d_frame); cudaFree(c->d_rgba); cudaFree(c->d_mean);
@@ -97,6 +104,7 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     sv.vuv = c->d_uv;
     sv.meshes = c->d_meshes;
     sv.materials = c->d_mats;
+    sv.mesh_materials = c->d_mesh_mats;
     sv.texels = c->d_texels;
     sv.env = c->d_env;
     sv.env_w = c->env_w;
@@ -166,6 +174,7 @@ extern "C" int b200pt_destroy(b200pt_ctx* c) {
     free_scene(c);
     cudaFree(c->d_env);
     cudaFree(c->d_mats);
+    cudaFree(c->d_mesh_mats);
     cudaFree(c->d_cursor);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
@@ -218,6 +227,7 @@ extern "C" int b200pt_add_mesh(b200pt_ctx* c, const float* verts, const float* n
     }
     c->h_meshes.push_back(mi);
     c->built = false;
+    c->mesh_mats_dirty = true;
     if (mesh_index) *mesh_index = mesh;
     return B200PT_OK;
 }
@@ -277,6 +287,8 @@ extern "C" int b200pt_set_materials(b200pt_ctx* c, const b200pt_material* m, int
     }
     CU(cudaMemcpyAsync(c->d_mats, tmp.data(), sizeof(Material) * (size_t)nm, cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));  // tmp goes out of scope
+    c->h_mats.swap(tmp);
+    c->mesh_mats_dirty = true;
     return B200PT_OK;
 }
 
@@ -326,19 +338,46 @@ extern "C" int b200pt_set_render(b200pt_ctx* c, int32_t width, int32_t height, i
 }
 
 // ---------------------------------------------------------------------------- render
+// per-mesh copy of the material each mesh is bound to: the shade kernel then needs the mesh index
+// only (one dependent load less than entity -> material_index -> material_buffer, device.cu:150-154)
+static int sync_mesh_materials(b200pt_ctx* c) {
+    if (!c->mesh_mats_dirty) return B200PT_OK;
+    const size_t nm = c->h_meshes.size();
+    std::vector<Material> tmp(nm);
+    for (size_t i = 0; i < nm; ++i) {
+        const int32_t mi = c->h_meshes[i].material;
+        if (mi < 0 || mi >= (int32_t)c->h_mats.size()) return fail(B200PT_ERR_BOUNDS, "a mesh refers to material " + std::to_string(mi));
+        tmp[i] = c->h_mats[(size_t)mi];
+    }
+    if (nm > c->mesh_mats_capacity) {
+        CU(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_mesh_mats);
+        c->d_mesh_mats = nullptr;
+        CU(cudaMalloc(&c->d_mesh_mats, sizeof(Material) * nm));
+        c->mesh_mats_capacity = nm;
+    }
+    CU(cudaMemcpyAsync(c->d_mesh_mats, tmp.data(), sizeof(Material) * nm, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->mesh_mats_dirty = false;
+    return B200PT_OK;
+}
+
 static int ensure_lanes(b200pt_ctx* c, const SceneView& sv) {
     const size_t px = (size_t)c->width * c->height;
     const uint32_t need = (uint32_t)std::max(sv.n_lanes, 1);
     if (c->la.capacity < need || c->fb_pixels != px) {
         CU(cudaStreamSynchronize(c->stream));
         free_lanes(c);
-        CU(cudaMalloc(&c->la.ray_o, sizeof(f4) * need));
-        CU(cudaMalloc(&c->la.ray_d, sizeof(f4) * need));
-        CU(cudaMalloc(&c->la.thr, sizeof(f4) * need));
-        CU(cudaMalloc(&c->la.sum, sizeof(f4) * need));
-        CU(cudaMalloc(&c->la.hit, sizeof(f4) * need));
-        CU(cudaMalloc(&c->la.queue[0], sizeof(uint32_t) * need));
-        CU(cudaMalloc(&c->la.queue[1], sizeof(uint32_t) * need));
+        const size_t padded = (size_t)need + 256;  // k_shade loads entry i before it knows the queue length
+        for (int b = 0; b < 2; ++b) {
+            CU(cudaMalloc(&c->la.ray_o[b], sizeof(f4) * padded));
+            CU(cudaMalloc(&c->la.ray_d[b], sizeof(f4) * padded));
+            CU(cudaMalloc(&c->la.thr[b], sizeof(f4) * padded));
+            CU(cudaMalloc(&c->la.queue[b], sizeof(uint32_t) * padded));
+            CU(cudaMemsetAsync(c->la.queue[b], 0, sizeof(uint32_t) * padded, c->stream));
+        }
+        CU(cudaMalloc(&c->la.sum, sizeof(f4) * padded));
+        CU(cudaMalloc(&c->la.hit, sizeof(f4) * padded));
         CU(cudaMalloc(&c->la.counts, sizeof(uint32_t) * (kBatch + 1)));
         CU(cudaMalloc(&c->la.cursor, sizeof(uint32_t) * kBatch));
         CU(cudaMalloc(&c->la.walk_counters, sizeof(unsigned long long) * 2));
@@ -363,6 +402,7 @@ static int check_ready(b200pt_ctx* c, const char* who) {
 
 static int render_local(b200pt_ctx* c) {
     CU(cudaSetDevice(c->cfg.device_ordinal));
+    if (int r = sync_mesh_materials(c)) return r;
     const SceneView sv = make_view(c, false);
     if (int r = ensure_lanes(c, sv)) return r;
     const bool count = (c->cfg.flags & B200PT_FLAG_COUNTERS) != 0;

@@ -21,21 +21,25 @@ struct DeviceBVH {
 bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const float scene_lo[3],
                       const float scene_hi[3], float max_abs, DeviceBVH* out, cudaStream_t st, std::string& err);
 
-// per-lane state, structure of arrays, 16-byte elements (one LDG.128 / STG.128 each)
+// Path state, structure of arrays with 16-byte elements (one LDG.128 / STG.128 each).
+// The state of the paths in flight is kept COMPACT: entry i of set (k & 1) belongs to the i-th
+// queued path of wavefront iteration k; k_shade writes the survivors to consecutive entries of the
+// other set.  Both kernels therefore read and write the state with coalesced accesses and without
+// going through the queue; only the per-pixel sum is addressed by lane (= pixel).
 struct LaneArrays {
-    f4* ray_o = nullptr;   // origin.xyz, -
-    f4* ray_d = nullptr;   // direction.xyz, control word (pack_ctl)
-    f4* thr = nullptr;     // throughput.xyz, RNG state
-    f4* sum = nullptr;     // sum of finished samples .xyz, -   (this is the accumulation buffer)
-    f4* hit = nullptr;     // t, u, v, triangle id
-    uint32_t* queue[2] = {nullptr, nullptr};
+    f4* ray_o[2] = {nullptr, nullptr};   // origin.xyz, -
+    f4* ray_d[2] = {nullptr, nullptr};   // direction.xyz, control word (pack_ctl)
+    f4* thr[2] = {nullptr, nullptr};     // throughput.xyz, RNG state
+    f4* hit = nullptr;                   // t, u, v, triangle id   (written by k_extend, same index)
+    uint32_t* queue[2] = {nullptr, nullptr};  // lane (pixel) id of entry i
+    f4* sum = nullptr;     // per lane: sum of finished samples .xyz, -   (this is the accumulation buffer)
     uint32_t* counts = nullptr;   // kBatch + 1 queue lengths
     uint32_t* cursor = nullptr;   // kBatch ray-fetch cursors of the persistent extend kernel
     unsigned long long* walk_counters = nullptr;  // nodes, tris (FLAG_COUNTERS)
     uint32_t capacity = 0;
 };
 
-constexpr int kBatch = 32;  // wavefront iterations between host checks (even)
+constexpr int kBatch = 32;  // wavefront iterations between host checks (even: the state sets alternate with k)
 
 // launch wrappers (wavefront.cu)
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, cudaStream_t st);

@@ -71,7 +71,7 @@ PT_HD f3 lerp3(f3 a, f3 b, float t) { return a + (b - a) * t; }
 PT_HD float clampf(float x, float lo, float hi) { return fminf(hi, fmaxf(lo, x)); }
 
 // material_data, device_global.hpp:19-36, padded to 20 floats (5 x 16 B) on the device
-struct Material {
+struct alignas(16) Material {
     float base_color[3];
     float subsurface;
     float metallic;

@@ -11,7 +11,28 @@
 
 namespace pt {
 
-struct MeshInfo {
+// read-only 16-byte-granular struct fetch: LDG.128s through the non-coherent path on the device
+// (a plain struct copy compiles to one 4-byte load per member)
+template <class T>
+PT_HD T load_ro(const T* p) {
+#if defined(__CUDA_ARCH__)
+    static_assert(sizeof(T) % 16 == 0, "load_ro: size must be a multiple of 16 bytes");
+    T r;
+    const uint4* src = reinterpret_cast<const uint4*>(p);
+    uint4* dst = reinterpret_cast<uint4*>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); ++i) dst[i] = __ldg(src + i);
+    return r;
+#else
+    return *p;
+#endif
+}
+
+struct alignas(16) TriIdx {   // per global triangle: 3 global vertex ids + mesh index
+    int32_t i0, i1, i2, mesh;
+};
+
+struct alignas(16) MeshInfo {
     int32_t first_tri;    // global id of this mesh's primitive 0
     int32_t material;     // material_index (entity_data, device_global.hpp:38-44)
     int32_t tex_offset;   // first texel in the texture pool, -1 = no texture
@@ -29,6 +50,7 @@ struct SceneView {
     const f2* vuv;
     const MeshInfo* meshes;
     const Material* materials;
+    const Material* mesh_materials;  // materials[meshes[m].material] per mesh: one dependent load less in shade
     const uint32_t* texels;    // RGBA8 pool (mesh textures)
     const uint32_t* env;       // RGBA8 environment map or nullptr
     int32_t env_w, env_h;
@@ -139,10 +161,15 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
         const f3 rad = miss_radiance(sv, L.d);
         return end_sample(sv, L, px, py, rad * L.thr);
     }
-    const int32_t* ix = sv.idx4 + 4 * (size_t)hit.tri;
-    const int i0 = ix[0], i1 = ix[1], i2 = ix[2], mesh = ix[3];
-    const MeshInfo mi = sv.meshes[mesh];
-    Material m = sv.materials[mi.material];
+    const TriIdx ix = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + hit.tri);
+    const int i0 = ix.i0, i1 = ix.i1, i2 = ix.i2, mesh = ix.mesh;
+    // everything below depends on idx4 only: mesh record, its material and the six vertex
+    // attributes are fetched side by side (entity_data + material_buffer[material_index],
+    // device.cu:150-154)
+    const MeshInfo mi = load_ro(sv.meshes + mesh);
+    Material m = load_ro(sv.mesh_materials + mesh);
+    const f4 p0 = load_ro(sv.vpos + i0), p1 = load_ro(sv.vpos + i1), p2 = load_ro(sv.vpos + i2);
+    const f4 n0 = load_ro(sv.vnrm + i0), n1 = load_ro(sv.vnrm + i1), n2 = load_ro(sv.vnrm + i2);
 
     if (m.emission > 0.0f) {  // device.cu:157-161: radiance = emission (overwrites)
         return end_sample(sv, L, px, py, mk3(m.emission) * L.thr);
@@ -150,9 +177,7 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
 
     const float bu = hit.u, bv = hit.v;
     const float bw = 1.0f - bu - bv;
-    const f4 p0 = sv.vpos[i0], p1 = sv.vpos[i1], p2 = sv.vpos[i2];
     const f3 vp = bw * f3{p0.x, p0.y, p0.z} + bu * f3{p1.x, p1.y, p1.z} + bv * f3{p2.x, p2.y, p2.z};
-    const f4 n0 = sv.vnrm[i0], n1 = sv.vnrm[i1], n2 = sv.vnrm[i2];
     const f3 vn = normalize(bw * f3{n0.x, n0.y, n0.z} + bu * f3{n1.x, n1.y, n1.z} + bv * f3{n2.x, n2.y, n2.z});
     if (mi.tex_offset >= 0) {  // device.cu:75-94
         const f2 t0 = sv.vuv[i0], t1 = sv.vuv[i1], t2 = sv.vuv[i2];

@@ -37,21 +37,18 @@ __global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays 
     uint32_t rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset));  // device.cu:226
     f3 o, d;
     camera_ray(sv, px, py, rng, o, d);
-    st4(la.ray_o + lane, f4{o.x, o.y, o.z, 0.0f});
-    st4(la.ray_d + lane, f4{d.x, d.y, d.z, u2f(pack_ctl(0, 0, LOBE_NONE))});
-    st4(la.thr + lane, f4{1.0f, 1.0f, 1.0f, u2f(rng)});
+    st4(la.ray_o[0] + lane, f4{o.x, o.y, o.z, 0.0f});
+    st4(la.ray_d[0] + lane, f4{d.x, d.y, d.z, u2f(pack_ctl(0, 0, LOBE_NONE))});
+    st4(la.thr[0] + lane, f4{1.0f, 1.0f, 1.0f, u2f(rng)});
     st4(la.sum + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
     la.queue[0][lane] = lane;
 }
 
-struct LaneRaySource {
-    const uint32_t* queue;
+struct LaneRaySource {   // entry i of the current state set
     const f4* ray_o;
     const f4* ray_d;
-    uint32_t* lane_of;  // unused
     __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
-        const uint32_t lane = queue[i];
-        const f4 a = ld4(ray_o + lane), b = ld4(ray_d + lane);
+        const f4 a = ld4(ray_o + i), b = ld4(ray_d + i);
         o = f3{a.x, a.y, a.z};
         d = f3{b.x, b.y, b.z};
         tmin = kTMin;
@@ -59,11 +56,8 @@ struct LaneRaySource {
     }
 };
 struct LaneHitSink {
-    const uint32_t* queue;
     f4* hit;
-    __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
-        st4(hit + queue[i], f4{h.t, h.u, h.v, u2f(h.tri)});
-    }
+    __device__ __forceinline__ void store(uint32_t i, const Hit& h) const { st4(hit + i, f4{h.t, h.u, h.v, u2f(h.tri)}); }
 };
 
 // persistent warps: every warp pulls rays of queue k until the queue is drained
@@ -72,9 +66,10 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneView sv, LaneArrays la, 
     const uint32_t n = la.counts[k];
     WalkCounters wc{0, 0};
     if (n) {
-        const uint32_t* q = (k & 1) ? la.queue[1] : la.queue[0];  // no dynamic index into the parameter struct
-        warp_walk<COUNT>(sv.nodes, sv.tris, n, la.cursor + k, LaneRaySource{q, la.ray_o, la.ray_d, nullptr},
-                         LaneHitSink{q, la.hit}, wc, sv.plane_magic);
+        // (k & 1) selects the state set; written out so that the parameter struct is never indexed dynamically
+        warp_walk<COUNT>(sv.nodes, sv.tris, n, la.cursor + k,
+                         LaneRaySource{(k & 1) ? la.ray_o[1] : la.ray_o[0], (k & 1) ? la.ray_d[1] : la.ray_d[0]},
+                         LaneHitSink{la.hit}, wc, sv.plane_magic);
     }
     if (COUNT) {
         unsigned long long a = wc.nodes, b = wc.tris;
@@ -90,14 +85,22 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneView sv, LaneArrays la, 
 }
 
 __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView sv, LaneArrays la, int k) {
-    const uint32_t n = la.counts[k];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool odd = (k & 1) != 0;
+    const f4 *in_d = odd ? la.ray_d[1] : la.ray_d[0], *in_t = odd ? la.thr[1] : la.thr[0];
+    f4 *out_o = odd ? la.ray_o[0] : la.ray_o[1], *out_d = odd ? la.ray_d[0] : la.ray_d[1], *out_t = odd ? la.thr[0] : la.thr[1];
+    const uint32_t* in_q = odd ? la.queue[1] : la.queue[0];
+    uint32_t* out_q = odd ? la.queue[0] : la.queue[1];
+    // everything entry i needs is fetched before the queue length is known (the arrays are padded):
+    // queue length, lane id, ray, throughput and hit are five independent loads, the lane's sum
+    // follows the lane id
+    const uint32_t n = la.counts[k];
+    const uint32_t lane = in_q[i];
+    const f4 d = ld4(in_d + i), t = ld4(in_t + i), hv = ld4(la.hit + i);
     bool keep = false;
-    uint32_t lane = 0;
+    LaneState L;
     if (i < n) {
-        lane = ((k & 1) ? la.queue[1] : la.queue[0])[i];
-        const f4 d = ld4(la.ray_d + lane), t = ld4(la.thr + lane), hv = ld4(la.hit + lane);
-        LaneState L;
+        f4 s = ld4(la.sum + lane);
         L.o = mk3(0.0f);  // only written: the old origin is never needed again
         L.d = f3{d.x, d.y, d.z};
         L.thr = f3{t.x, t.y, t.z};
@@ -111,20 +114,14 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
         lane_pixel(sv, lane, px, py);
         const ShadeResult r = shade_lane(sv, L, h, px, py);
         if (L.sample_ended) {  // color += trace_path(...), in sample order
-            f4 s = ld4(la.sum + lane);
             s.x += L.contrib.x;
             s.y += L.contrib.y;
             s.z += L.contrib.z;
             st4(la.sum + lane, s);
         }
         keep = r == LANE_CONTINUE;
-        if (keep) {
-            st4(la.ray_o + lane, f4{L.o.x, L.o.y, L.o.z, 0.0f});
-            st4(la.ray_d + lane, f4{L.d.x, L.d.y, L.d.z, u2f(pack_ctl(L.sample, L.depth, L.lobe))});
-            st4(la.thr + lane, f4{L.thr.x, L.thr.y, L.thr.z, u2f(L.rng)});
-        }
     }
-    // warp-aggregated append to the next queue
+    // warp-aggregated append of the survivors to the other state set
     const unsigned m = __ballot_sync(0xffffffffu, keep);
     if (m) {
         const int lid = threadIdx.x & 31;
@@ -132,7 +129,13 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
         uint32_t base = 0;
         if (lid == leader) base = atomicAdd(la.counts + k + 1, (uint32_t)__popc(m));
         base = __shfl_sync(0xffffffffu, base, leader);
-        if (keep) ((k & 1) ? la.queue[0] : la.queue[1])[base + __popc(m & ((1u << lid) - 1u))] = lane;
+        if (keep) {
+            const uint32_t pos = base + __popc(m & ((1u << lid) - 1u));
+            st4(out_o + pos, f4{L.o.x, L.o.y, L.o.z, 0.0f});
+            st4(out_d + pos, f4{L.d.x, L.d.y, L.d.z, u2f(pack_ctl(L.sample, L.depth, L.lobe))});
+            st4(out_t + pos, f4{L.thr.x, L.thr.y, L.thr.z, u2f(L.rng)});
+            out_q[pos] = lane;
+        }
     }
 }
 

@@ -24,7 +24,7 @@ struct emu_scene {
     std::vector<int32_t> idx4;
     std::vector<MeshInfo> meshes;
     std::vector<uint32_t> texels, env;
-    std::vector<Material> mats;
+    std::vector<Material> mats, mesh_mats;
     std::vector<Node8> nodes;
     std::vector<Tri48> tris;
     float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, max_abs = 0;
@@ -45,6 +45,10 @@ static void refresh_view(emu_scene* s) {
     s->sv.vuv = s->uv.data();
     s->sv.meshes = s->meshes.data();
     s->sv.materials = s->mats.data();
+    s->mesh_mats.resize(s->meshes.size());
+    for (size_t i = 0; i < s->meshes.size(); ++i)
+        if (s->meshes[i].material >= 0 && (size_t)s->meshes[i].material < s->mats.size()) s->mesh_mats[i] = s->mats[s->meshes[i].material];
+    s->sv.mesh_materials = s->mesh_mats.data();
     s->sv.texels = s->texels.data();
     s->sv.env = s->env.empty() ? nullptr : s->env.data();
     s->sv.n_materials = (int)s->mats.size();
