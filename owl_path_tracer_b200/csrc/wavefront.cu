@@ -18,6 +18,9 @@ namespace pt {
 #ifndef PT_BLOCKS_PER_SM
 #define PT_BLOCKS_PER_SM 8     // persistent blocks of 128 threads per SM for the walker kernels
 #endif
+#ifndef PT_EXTEND_MIN_BLOCKS
+#define PT_EXTEND_MIN_BLOCKS 8  // register cap of the walker kernels: 65536 / (128 * blocks) = 64
+#endif
 #ifndef PT_SHADE_MIN_BLOCKS
 #define PT_SHADE_MIN_BLOCKS 4   // register cap of k_shade: 65536 / (128 * blocks)
 #endif
@@ -62,7 +65,7 @@ struct LaneHitSink {
 
 // persistent warps: every warp pulls rays of queue k until the queue is drained
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock) k_extend(SceneView sv, LaneArrays la, int k) {
+__global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_extend(SceneView sv, LaneArrays la, int k) {
     const uint32_t n = la.counts[k];
     WalkCounters wc{0, 0};
     if (n) {
@@ -187,13 +190,13 @@ struct ArrayHitSink {
     __device__ __forceinline__ void store(uint32_t i, const Hit& h) const { st4(hits + i, f4{h.t, h.u, h.v, u2f(h.tri)}); }
 };
 
-__global__ void __launch_bounds__(kBlock) k_primary(SceneView sv, f4* hits, uint32_t* cursor) {
+__global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_primary(SceneView sv, f4* hits, uint32_t* cursor) {
     WalkCounters wc{0, 0};
     warp_walk<false>(sv.nodes, sv.tris, (uint32_t)(sv.width * sv.height), cursor, CameraRaySource{sv}, ArrayHitSink{hits}, wc,
                      sv.plane_magic);
 }
 
-__global__ void __launch_bounds__(kBlock) k_trace(SceneView sv, const float* __restrict__ o, const float* __restrict__ d,
+__global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_trace(SceneView sv, const float* __restrict__ o, const float* __restrict__ d,
                                                   int n, float tmin, float tmax, f4* hits, uint32_t* cursor) {
     WalkCounters wc{0, 0};
     warp_walk<false>(sv.nodes, sv.tris, (uint32_t)n, cursor, ArrayRaySource{o, d, tmin, tmax}, ArrayHitSink{hits}, wc,
