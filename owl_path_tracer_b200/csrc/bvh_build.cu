@@ -119,6 +119,7 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
     Tri48* tris = nullptr;
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
+    char* arena = nullptr;
     const int B = 256;
     const uint32_t nb = (n + B - 1) / B;
     // absolute box padding: covers the rounding of the slab test for rays whose origin
@@ -135,37 +136,57 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
     int levels = 0;
     uint32_t n_items = 1;
 
-    CK(cudaMalloc(&tri_lo, sizeof(float) * 3 * (size_t)n));
-    CK(cudaMalloc(&tri_hi, sizeof(float) * 3 * (size_t)n));
-    CK(cudaMalloc(&keys, sizeof(uint64_t) * (size_t)n));
-    CK(cudaMalloc(&keys2, sizeof(uint64_t) * (size_t)n));
-    CK(cudaMalloc(&vals, sizeof(uint32_t) * (size_t)n));
-    CK(cudaMalloc(&vals2, sizeof(uint32_t) * (size_t)n));
-    CK(cudaMalloc(&bin, sizeof(BinNode) * (size_t)n));
-    CK(cudaMalloc(&cid, sizeof(int32_t) * (size_t)n));
-    CK(cudaMalloc(&cid2, sizeof(int32_t) * (size_t)n));
-    CK(cudaMalloc(&nn, sizeof(int32_t) * (size_t)n));
-    CK(cudaMalloc(&cbox, sizeof(Box6) * (size_t)n));
-    CK(cudaMalloc(&cbox2, sizeof(Box6) * (size_t)n));
-    CK(cudaMalloc(&pflags, sizeof(unsigned long long) * (size_t)n));
-    CK(cudaMalloc(&pscan, sizeof(unsigned long long) * (size_t)n));
-    CK(cudaMalloc(&plans, sizeof(CollapsePlan) * (size_t)n));
-    CK(cudaMalloc(&qa, sizeof(CollapseItem) * (size_t)n));
-    CK(cudaMalloc(&qb, sizeof(CollapseItem) * (size_t)n));
-    CK(cudaMalloc(&nodes, sizeof(Node8) * (size_t)n));
+    // one arena for every temporary (a dozen cudaMalloc/cudaFree pairs per build cost more host time
+    // than the build itself); the triangles of the finished tree get their own allocation
+    {
+        size_t off = 0;
+        auto carve = [&](size_t bytes) {
+            const size_t at = off;
+            off += (bytes + 255) & ~(size_t)255;
+            return at;
+        };
+        const size_t N = (size_t)n;
+        const size_t o_tri_lo = carve(sizeof(float) * 3 * N), o_tri_hi = carve(sizeof(float) * 3 * N);
+        const size_t o_keys = carve(sizeof(uint64_t) * N), o_keys2 = carve(sizeof(uint64_t) * N);
+        const size_t o_vals = carve(sizeof(uint32_t) * N), o_vals2 = carve(sizeof(uint32_t) * N);
+        const size_t o_bin = carve(sizeof(BinNode) * N);
+        const size_t o_cid = carve(sizeof(int32_t) * N), o_cid2 = carve(sizeof(int32_t) * N), o_nn = carve(sizeof(int32_t) * N);
+        const size_t o_cbox = carve(sizeof(Box6) * N), o_cbox2 = carve(sizeof(Box6) * N);
+        const size_t o_pflags = carve(sizeof(unsigned long long) * N), o_pscan = carve(sizeof(unsigned long long) * N);
+        const size_t o_plans = carve(sizeof(CollapsePlan) * N);
+        const size_t o_qa = carve(sizeof(CollapseItem) * N), o_qb = carve(sizeof(CollapseItem) * N);
+        const size_t o_nodes = carve(sizeof(Node8) * N);
+        const size_t o_counters = carve(sizeof(uint32_t) * 4);
+        size_t sort_bytes = 0, scan_bytes = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (uint64_t*)nullptr, (uint64_t*)nullptr, (uint32_t*)nullptr,
+                                           (uint32_t*)nullptr, (int)n, 0, 63, st));
+        CK(cub::DeviceScan::InclusiveSum(nullptr, scan_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)n, st));
+        tmp_bytes = sort_bytes;
+        tmp2_bytes = scan_bytes;
+        const size_t o_tmp = carve(sort_bytes), o_tmp2 = carve(scan_bytes);
+        CK(cudaMalloc(&arena, off));
+        tri_lo = (float*)(arena + o_tri_lo); tri_hi = (float*)(arena + o_tri_hi);
+        keys = (uint64_t*)(arena + o_keys); keys2 = (uint64_t*)(arena + o_keys2);
+        vals = (uint32_t*)(arena + o_vals); vals2 = (uint32_t*)(arena + o_vals2);
+        bin = (BinNode*)(arena + o_bin);
+        cid = (int32_t*)(arena + o_cid); cid2 = (int32_t*)(arena + o_cid2); nn = (int32_t*)(arena + o_nn);
+        cbox = (Box6*)(arena + o_cbox); cbox2 = (Box6*)(arena + o_cbox2);
+        pflags = (unsigned long long*)(arena + o_pflags); pscan = (unsigned long long*)(arena + o_pscan);
+        plans = (CollapsePlan*)(arena + o_plans);
+        qa = (CollapseItem*)(arena + o_qa); qb = (CollapseItem*)(arena + o_qb);
+        nodes = (Node8*)(arena + o_nodes);
+        counters = (uint32_t*)(arena + o_counters);
+        tmp = arena + o_tmp;
+        tmp2 = arena + o_tmp2;
+    }
     CK(cudaMalloc(&tris, sizeof(Tri48) * (size_t)n));
-    CK(cudaMalloc(&counters, sizeof(uint32_t) * 4));
 
     k_tri_prepare<<<nb, B, 0, st>>>(d_pos, d_idx4, n, pad, slo, sinv, tri_lo, tri_hi, keys, vals);
     CK(cudaGetLastError());
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, (int)n, 0, 63, st));
-    CK(cudaMalloc(&tmp, tmp_bytes));
     CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, (int)n, 0, 63, st));
     for (int attempt = 0; attempt < 2; ++attempt) {
         if (n >= 2 && attempt == 0) {
             // parallel locally-ordered clustering: rounds of nearest neighbour / flags / scan / emit
-            CK(cub::DeviceScan::InclusiveSum(nullptr, tmp2_bytes, pflags, pscan, (int)n, st));
-            CK(cudaMalloc(&tmp2, tmp2_bytes));
             k_ploc_init<<<nb, B, 0, st>>>(n, vals2, tri_lo, tri_hi, cid, cbox);
             CK(cudaGetLastError());
             uint32_t m = n, node_base = 0;
@@ -252,16 +273,11 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
     out->tris = tris;
     tris = nullptr;
     CK(cudaStreamSynchronize(st));
-    cudaFree(tri_lo); cudaFree(tri_hi); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
-    cudaFree(bin); cudaFree(cid); cudaFree(cid2); cudaFree(nn); cudaFree(cbox); cudaFree(cbox2); cudaFree(pflags);
-    cudaFree(pscan); cudaFree(plans); cudaFree(tmp2); cudaFree(qa); cudaFree(qb); cudaFree(nodes);
-    cudaFree(counters); cudaFree(tmp);
+    cudaFree(arena);
     return true;
 fail:
-    cudaFree(tri_lo); cudaFree(tri_hi); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
-    cudaFree(bin); cudaFree(cid); cudaFree(cid2); cudaFree(nn); cudaFree(cbox); cudaFree(cbox2); cudaFree(pflags);
-    cudaFree(pscan); cudaFree(plans); cudaFree(tmp2); cudaFree(qa); cudaFree(qb); cudaFree(nodes);
-    cudaFree(tris); cudaFree(counters); cudaFree(tmp);
+    cudaFree(arena);
+    cudaFree(tris);
     return false;
 }
 
