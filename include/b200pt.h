@@ -61,6 +61,11 @@ typedef struct b200pt_config {
 #define B200PT_FLAG_COUNTERS   1  /* count nodes/triangles visited (slower; for the
                                      roofline's algorithmic bytes)                 */
 #define B200PT_FLAG_HOST_BVH   2  /* reserved                                       */
+#define B200PT_FLAG_NEE        8  /* next-event estimation: light sampling of the emissive triangles with a
+                                     shadow any-hit ray per path vertex, combined with the BSDF-sampled
+                                     emitter hits by the power heuristic.  NOT the reference's estimator
+                                     (its light sampling, lights.hpp + visibiliy_test device.cu:97-110, is
+                                     dead code): an opt-in mode with the same mode in the oracle.      */
 #define B200PT_FLAG_TIMING     4  /* CUDA events around every extend / shade launch
                                      (fills extend_ms / shade_ms in b200pt_stats)   */
 
@@ -105,6 +110,10 @@ typedef struct b200pt_stats {
     uint32_t bvh_nodes;       /* 8-wide nodes in the tree                          */
     uint32_t bvh_tris;        /* triangles referenced by the tree                  */
     uint64_t bvh_bytes;       /* nodes*80 + tris*48                                */
+    uint64_t shadow_rays;     /* shadow (any-hit) rays traced (B200PT_FLAG_NEE)    */
+    double shadow_ms;         /* share spent in the shadow kernel (FLAG_TIMING)    */
+    uint32_t n_lights;        /* emissive triangles in the light table (FLAG_NEE)  */
+    uint32_t reserved;
 } b200pt_stats;
 
 typedef struct b200pt_ctx b200pt_ctx;

@@ -383,6 +383,78 @@ V3 eval_sheen(const Mat& m, V3 wo, V3 wi) {
     return scale(scale(lerp(v3(1.0f), tint, m.sheen_tint), m.sheen), schlick_weight(cos_d));
 }
 
+// ---------------------------------------------------------------- next-event estimation support
+// Not part of the reference's integrator (its light sampling code is dead); an optional
+// mode assembled from the reference's own eval_* functions and lights.hpp.  Mirrors
+// owl_path_tracer_b200/csrc/pt_disney.h eval_mixture; see DESIGN.md "NEE mode" for the estimator.
+V3 eval_diffuse(const Mat& m, V3 wo, V3 wi, float& pdf) {                                 // disney_diffuse.cuh:26-55
+    float fo = schlick_weight(cos_theta(wo));
+    float fi = schlick_weight(cos_theta(wi));
+    V3 lambert = scale(base_of(m), inv_pi);
+    float fd = (1.0f - 0.5f * fo) * (1.0f - 0.5f * fi);
+    float rr = m.roughness * (dot(wo, wi) + 1.0f);
+    float fr = rr * (fi + fo + fo * fi * (rr - 1.0f));
+    pdf = fabsf(cos_theta(wi)) * inv_pi;
+    return scale(lambert, fd + fr);
+}
+V3 eval_clearcoat(const Mat& m, V3 wo, V3 wh, V3 wi, float& pdf) {                       // disney_clearcoat.cuh:13-20,45-59
+    float a = lerp(0.1f, .001f, m.clearcoat_gloss);
+    float a2 = sqr(a);
+    float d;
+    if (a >= 1)
+        d = inv_pi;
+    else
+        d = (a2 - 1.0f) / (pi * m_log(a2) * (1.0f + (a2 - 1.0f) * sqr(cos_theta(wh))));
+    float f = lerp(1.0f, schlick_weight(cos_theta(wi)), 0.04f);
+    float g = g2_separable(wo, wi, .25f, .25f);
+    pdf = d / (4.0f * dot(wh, wi));
+    return v3(d * g * f / (4.0f * fabsf(cos_theta(wo)) * fabsf(cos_theta(wi))));
+}
+// f_eff = sum_l p_l (f_l + sheen), pdf_eff = sum_l p_l pdf_l over metal, clearcoat, diffuse
+void eval_mixture(const Mat& m, V3 wo, V3 wi, V3& f_eff, float& pdf_eff) {
+    float diffuse_w = (1.0f - m.specular_transmission) * (1.0f - m.metallic);
+    float metallic_w = m.metallic;
+    float clearcoat_w = .25f * m.clearcoat;
+    float glass_w = (1.0f - m.metallic) * m.specular_transmission;
+    float factor = 1.0f / (metallic_w + glass_w + diffuse_w + clearcoat_w);
+    float p_metallic = metallic_w * factor;
+    float p_diffuse = diffuse_w * factor;
+    float p_clearcoat = clearcoat_w * factor;
+    f_eff = v3(0.0f);
+    pdf_eff = 0.0f;
+    V3 wh = add(wo, wi);
+    const bool has_wh = !(wh.x == 0.0f && wh.y == 0.0f && wh.z == 0.0f);
+    if (has_wh) wh = normalize(wh);
+    const V3 sheen = eval_sheen(m, wo, wi);
+    if (p_metallic > 0.0f && has_wh && cos_theta(wi) > 0.0f) {
+        float pdf;
+        V3 f = eval_specular_brdf(m, wo, wh, wi, pdf);
+        f_eff = add(f_eff, scale(p_metallic, add(f, sheen)));
+        pdf_eff = pdf_eff + p_metallic * pdf;
+    }
+    if (p_clearcoat > 0.0f && has_wh && same_hemisphere(wo, wi)) {
+        float pdf;
+        V3 f = eval_clearcoat(m, wo, wh, wi, pdf);
+        f_eff = add(f_eff, scale(p_clearcoat, add(f, sheen)));
+        pdf_eff = pdf_eff + p_clearcoat * pdf;
+    }
+    if (p_diffuse > 0.0f && cos_theta(wi) > 0.0f) {
+        float pdf;
+        V3 f = eval_diffuse(m, wo, wi, pdf);
+        f_eff = add(f_eff, scale(p_diffuse, add(f, sheen)));
+        pdf_eff = pdf_eff + p_diffuse * pdf;
+    }
+}
+inline float power_heuristic(float pdf_f, float pdf_g) {                                  // lights.hpp:56-61, n_f = n_g = 1
+    float f = pdf_f, g = pdf_g;
+    return (f * f) / (f * f + g * g);
+}
+inline float pdf_area_to_solid_angle(float pdf_area, float dist_sqr, float cos_t) {     // lights.hpp:23-28
+    float a = fabsf(cos_t);
+    if (a < 1e-4f) return 0.0f;
+    return pdf_area * dist_sqr / a;
+}
+
 // ---------------------------------------------------------------- disney.cuh:15-66
 V3 sample_disney(const Mat& m, V3 wo, Rng& rng, V3& wi, float& pdf, int& sampled_lobe) {
     float diffuse_w = (1.0f - m.specular_transmission) * (1.0f - m.metallic);
@@ -453,7 +525,17 @@ struct Scene {
     std::vector<TriRef> tris_flat;  // id order
     std::vector<BNode> nodes;
     std::vector<int32_t> tri_mesh;  // global id -> mesh
+    // next-event estimation mode (oracle_set_nee): emissive triangles, chosen by area * emission
+    bool nee = false;
+    struct Light {
+        int mesh, prim;
+        float area, prob, emission;
+    };
+    std::vector<Light> lights;
+    std::vector<float> light_cdf;
+    std::vector<int> mesh_light_first;
     std::atomic<uint64_t> rays{0};
+    std::atomic<uint64_t> shadow_rays{0};  // of the last render (NEE mode)
 };
 
 // Moller-Trumbore.  This expression order is the parity contract with the GPU
@@ -644,12 +726,52 @@ V3 sample_environment(const Scene& sc, V3 dir) {                                
 
 typedef Closest (*Finder)(const Scene&, V3, V3, float, float);
 
+// light table of the NEE mode: every triangle of every mesh whose material emits, in mesh order;
+// weight = triangle_area (lights.hpp:15-20) * emission, cdf accumulated in binary64
+void build_lights(Scene& sc) {
+    sc.lights.clear();
+    sc.light_cdf.clear();
+    sc.mesh_light_first.assign(sc.meshes.size(), -1);
+    if (!sc.nee) return;
+    std::vector<double> acc;
+    double total = 0.0;
+    for (size_t mi = 0; mi < sc.meshes.size(); ++mi) {
+        const MeshRec& mesh = sc.meshes[mi];
+        const float emission = sc.mats[mesh.material].emission;
+        if (!(emission > 0.0f)) continue;
+        sc.mesh_light_first[mi] = (int)sc.lights.size();
+        for (int prim = 0; prim < (int)(mesh.idx.size() / 3); ++prim) {
+            const V3 a = mesh.verts[mesh.idx[3 * prim]], b = mesh.verts[mesh.idx[3 * prim + 1]], c = mesh.verts[mesh.idx[3 * prim + 2]];
+            const V3 n = cross(sub(b, a), sub(c, a));
+            const float area = 0.5f * sqrtf(dot(n, n));
+            const float w = area * emission;
+            total += (double)w;
+            acc.push_back(total);
+            sc.lights.push_back(Scene::Light{(int)mi, prim, area, 0.0f, emission});
+        }
+    }
+    if (!(total > 0.0)) {
+        sc.lights.clear();
+        sc.mesh_light_first.assign(sc.meshes.size(), -1);
+        return;
+    }
+    sc.light_cdf.resize(sc.lights.size());
+    for (size_t i = 0; i < sc.lights.size(); ++i) sc.light_cdf[i] = (float)(acc[i] / total);
+    sc.light_cdf.back() = 1.0f;
+    for (size_t i = 0; i < sc.lights.size(); ++i) sc.lights[i].prob = sc.light_cdf[i] - (i ? sc.light_cdf[i - 1] : 0.0f);
+}
+
 // ---------------------------------------------------------------- device.cu:113-218
-V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays) {
+V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays, uint64_t& nshadow) {
     V3 radiance = v3(0.0f);
     V3 throughput = v3(1.0f);
     int sampled_lobe = LOBE_NONE;
     int nan_retries = 0;
+    // next-event estimation mode: light-sampled radiance gathered along the path, and the density
+    // with which the BSDF generated the current ray (<= 0: an emitter it reaches counts fully)
+    const bool nee = sc.nee && !sc.lights.empty();
+    V3 gathered = v3(0.0f);
+    float prev_pdf = -1.0f;
     for (int depth = 0; depth < sc.max_depth; ++depth) {
         Closest h = find(sc, org, dir, t_min, t_max);
         ++nrays;
@@ -667,13 +789,20 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays)
         const MeshRec& mesh = sc.meshes[mesh_index];
         const int prim = (int)h.id - mesh.first_tri;
         Mat material = sc.mats[mesh.material];                                            // :150-154
-        if (material.emission > 0.0f) {                                                   // :157-161
-            radiance = v3(material.emission);
-            break;
-        }
         const int i0 = mesh.idx[3 * prim], i1 = mesh.idx[3 * prim + 1], i2 = mesh.idx[3 * prim + 2];
         const float bx = h.u, by = h.v;
         const float bw = 1 - bx - by;
+        if (material.emission > 0.0f) {                                                   // :157-161
+            if (nee && prev_pdf > 0.0f && sc.mesh_light_first[mesh_index] >= 0) {
+                const Scene::Light& lt = sc.lights[sc.mesh_light_first[mesh_index] + prim];
+                V3 nl = add(add(scale(bw, mesh.normals[i0]), scale(bx, mesh.normals[i1])), scale(by, mesh.normals[i2]));
+                float pdf_light = lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, h.t * h.t, dot(neg(dir), nl));
+                radiance = v3(material.emission * power_heuristic(prev_pdf, pdf_light));
+            } else {
+                radiance = v3(material.emission);
+            }
+            break;
+        }
         V3 v_p = add(add(scale(bw, mesh.verts[i0]), scale(bx, mesh.verts[i1])), scale(by, mesh.verts[i2]));  // :59
         V3 v_n = normalize(add(add(scale(bw, mesh.normals[i0]), scale(bx, mesh.normals[i1])), scale(by, mesh.normals[i2])));  // :72
         if (!mesh.tex.empty()) {                                                          // :75-94
@@ -689,6 +818,46 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays)
         V3 T, B;
         onb(v_n, T, B);
         V3 local_wo = to_local(T, B, v_n, wo);
+        if (nee && nan_retries == 0) {
+            // one emissive triangle by power, one point on it by area (lights.hpp:30-48), a shadow
+            // ray over (t_min, distance - t_min) (visibiliy_test, device.cu:97-110)
+            const float us = rng.next(), u0 = rng.next(), u1 = rng.next();
+            int lo = 0, hi = (int)sc.lights.size() - 1;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (us <= sc.light_cdf[mid]) hi = mid;
+                else lo = mid + 1;
+            }
+            const Scene::Light& lt = sc.lights[lo];
+            const MeshRec& lm = sc.meshes[lt.mesh];
+            const int j0 = lm.idx[3 * lt.prim], j1 = lm.idx[3 * lt.prim + 1], j2 = lm.idx[3 * lt.prim + 2];
+            const float su0 = sqrtf(u0);                                                  // sample_methods.hpp:82-86
+            const float cx = 1.0f - su0, cy = u1 * su0;
+            const float cz = 1.0f - cx - cy;
+            V3 pos = add(add(scale(cz, lm.verts[j0]), scale(cx, lm.verts[j1])), scale(cy, lm.verts[j2]));
+            V3 nl = add(add(scale(cz, lm.normals[j0]), scale(cx, lm.normals[j1])), scale(cy, lm.normals[j2]));
+            V3 ldir = sub(pos, v_p);
+            const float dist2 = dot(ldir, ldir);
+            const float dist = sqrtf(dist2);
+            ldir = divs(ldir, dist);
+            const float pdf_light = lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, dist2, dot(neg(ldir), nl));
+            if (pdf_light > 0.0f && dist > 2.0f * t_min) {
+                V3 lwi = normalize(V3{dot(ldir, T), dot(ldir, B), dot(ldir, v_n)});
+                V3 f_eff;
+                float pdf_eff;
+                eval_mixture(material, local_wo, lwi, f_eff, pdf_eff);
+                if (pdf_eff > 0.0f) {
+                    const float w = power_heuristic(pdf_light, pdf_eff);
+                    V3 c = mul(throughput, scale(f_eff, fabsf(cos_theta(lwi)) * lt.emission * w / pdf_light));
+                    const bool bad = isinf(c.x) || isinf(c.y) || isinf(c.z) || isnan(c.x) || isnan(c.y) || isnan(c.z);
+                    if (!bad && (c.x != 0.0f || c.y != 0.0f || c.z != 0.0f)) {
+                        Closest blocker = find(sc, v_p, ldir, t_min, dist - t_min);
+                        ++nshadow;
+                        if (blocker.id == 0xFFFFFFFFu) gathered = add(gathered, c);
+                    }
+                }
+            }
+        }
         V3 local_wi = v3(0.0f);
         float pdf = 0.0f;
         V3 f = sample_disney(material, local_wo, rng, local_wi, pdf, sampled_lobe);
@@ -704,12 +873,19 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays)
         throughput = mul(throughput, divs(scale(f, fabsf(cos_theta(local_wi))), pdf));    // :204
         org = v_p;
         dir = wi;
+        if (nee) {
+            V3 fe;
+            float pe;
+            eval_mixture(material, local_wo, local_wi, fe, pe);
+            prev_pdf = sampled_lobe == LOBE_GLASS ? -1.0f : pe;
+        }
         float beta_max = fmaxf(throughput.x, fmaxf(throughput.y, throughput.z));
         if (sampled_lobe != LOBE_GLASS && depth > 3) {                                    // :209-214
             float q = fmaxf(.05f, 1 - beta_max);
             if (rng.next() > q) break;
         }
     }
+    if (nee) return add(gathered, mul(radiance, throughput));
     return mul(radiance, throughput);
 }
 
@@ -722,7 +898,7 @@ uint32_t quantise8(float f) {  // owl_device.h:79-82; NaN -> 0 as on the device
 }
 
 // device.cu:220-254 for one pixel; returns the SUM over samples (caller scales)
-V3 render_pixel(Scene& sc, int x, int y, int seed_row_offset, int nsamples, Finder find, uint64_t& nrays) {
+V3 render_pixel(Scene& sc, int x, int y, int seed_row_offset, int nsamples, Finder find, uint64_t& nrays, uint64_t& nshadow) {
     Rng rng;
     rng.seed((uint32_t)x, (uint32_t)(y + seed_row_offset));
     V3 color = v3(0.0f);
@@ -732,7 +908,7 @@ V3 render_pixel(Scene& sc, int x, int y, int seed_row_offset, int nsamples, Find
         float su = ((float)x + rx) / (float)sc.width;
         float sv = ((float)y + ry) / (float)sc.height;
         V3 dir = normalize(sub(add(add(sc.cam_llc, scale(su, sc.cam_h)), scale(sv, sc.cam_v)), sc.cam_origin));
-        color = add(color, trace_path(sc, sc.cam_origin, dir, rng, find, nrays));
+        color = add(color, trace_path(sc, sc.cam_origin, dir, rng, find, nrays, nshadow));
     }
     return color;
 }
@@ -815,6 +991,9 @@ void oracle_set_render(oracle_scene* o, int w, int h, int spp, int depth) {
     o->s.max_depth = depth;
 }
 void oracle_build(oracle_scene* o) { build_bvh(o->s); }
+// next-event estimation mode on/off (see trace_path); shadow rays of the last render
+void oracle_set_nee(oracle_scene* o, int on) { o->s.nee = on != 0; }
+uint64_t oracle_shadow_rays(oracle_scene* o) { return o->s.shadow_rays.load(); }
 
 // camera.cpp:3-22.  out: origin, llc, horizontal, vertical (12 floats)
 void oracle_camera(const float* from, const float* at, const float* up, float vfov, int w, int h, float* out) {
@@ -857,16 +1036,18 @@ uint64_t oracle_render(oracle_scene* o, int rank, int world, int shard_mode, int
         }
     }
     if (nthreads < 1) nthreads = 1;
+    build_lights(sc);
+    sc.shadow_rays = 0;
     std::atomic<int> next_row{y0};
     std::atomic<uint64_t> total{0};
     auto worker = [&]() {
-        uint64_t nr = 0;
+        uint64_t nr = 0, ns = 0;
         for (;;) {
             int y = next_row.fetch_add(1);
             if (y >= y1) break;
             if (y < row_first || (y - row_first) % row_step != 0) continue;
             for (int x = x0; x < x1; ++x) {
-                V3 c = render_pixel(sc, x, y, seed_off, nsamples, find, nr);
+                V3 c = render_pixel(sc, x, y, seed_off, nsamples, find, nr, ns);
                 float* d = sum_out + 4 * ((size_t)x + (size_t)W * y);
                 d[0] = c.x;
                 d[1] = c.y;
@@ -875,6 +1056,7 @@ uint64_t oracle_render(oracle_scene* o, int rank, int world, int shard_mode, int
             }
         }
         total += nr;
+        sc.shadow_rays += ns;
     };
     std::vector<std::thread> th;
     for (int i = 1; i < nthreads; ++i) th.emplace_back(worker);

@@ -26,7 +26,7 @@ LIB_DIR = PKG_DIR / "lib"
 ASSETS_DIR = REPO_DIR / "assets"
 
 SHARD_SPP, SHARD_ROWS = 0, 1
-FLAG_COUNTERS, FLAG_TIMING = 1, 4
+FLAG_COUNTERS, FLAG_TIMING, FLAG_NEE = 1, 4, 8
 
 
 class B200ptError(RuntimeError):
@@ -53,7 +53,8 @@ class Stats(C.Structure):
                 ("other_ms", C.c_double), ("build_ms", C.c_double), ("rays", C.c_uint64),
                 ("paths", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("iterations", C.c_uint64), ("bvh_nodes", C.c_uint32),
-                ("bvh_tris", C.c_uint32), ("bvh_bytes", C.c_uint64)]
+                ("bvh_tris", C.c_uint32), ("bvh_bytes", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("shadow_ms", C.c_double), ("n_lights", C.c_uint32), ("reserved", C.c_uint32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -172,4 +173,4 @@ from ._scene import Scene  # noqa: E402
 from ._context import Context  # noqa: E402
 
 __all__ = ["Scene", "Context", "Config", "Stats", "B200ptError", "MATERIAL_DTYPE", "HIT_DTYPE",
-           "SHARD_SPP", "SHARD_ROWS", "FLAG_COUNTERS", "FLAG_TIMING", "lib", "host_lib", "ASSETS_DIR"]
+           "SHARD_SPP", "SHARD_ROWS", "FLAG_COUNTERS", "FLAG_TIMING", "FLAG_NEE", "lib", "host_lib", "ASSETS_DIR"]

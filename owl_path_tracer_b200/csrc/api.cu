@@ -5,6 +5,7 @@
 #include <cstring>
 
 #include "device_ctx.h"
+#include "pt_lights.h"
 
 using namespace pt;
 
@@ -47,6 +48,12 @@ struct b200pt_ctx {
     Material* d_mesh_mats = nullptr;   // materials[meshes[m].material] for every mesh (SceneView::mesh_materials)
     size_t mesh_mats_capacity = 0;
     bool mesh_mats_dirty = true;
+    // light table of the NEE mode (rebuilt with the per-mesh materials: emission is a material attribute)
+    std::vector<LightTri> h_lights;
+    std::vector<float> h_light_cdf;
+    LightTri* d_lights = nullptr;
+    float* d_light_cdf = nullptr;
+    size_t lights_capacity = 0;
     DeviceBVH bvh;
     bool built = false;
     // settings
@@ -72,6 +79,8 @@ static void free_lanes(b200pt_ctx* c) {
         cudaFree(c->la.ray_o[b]); cudaFree(c->la.ray_d[b]); cudaFree(c->la.thr[b]);
     }
     cudaFree(c->la.sum); cudaFree(c->la.hit);
+    cudaFree(c->la.rad); cudaFree(c->la.sh_o); cudaFree(c->la.sh_d); cudaFree(c->la.sh_c); cudaFree(c->la.sh_f);
+    cudaFree(c->la.sh_counts); cudaFree(c->la.sh_cursor);
     cudaFree(c->la.queue[0]); cudaFree(c->la.queue[1]); cudaFree(c->la.counts); cudaFree(c->la.cursor);
     cudaFree(c->la.walk_counters);
     cudaFree(c->d_frame); cudaFree(c->d_rgba); cudaFree(c->d_mean);
@@ -105,6 +114,10 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     sv.meshes = c->d_meshes;
     sv.materials = c->d_mats;
     sv.mesh_materials = c->d_mesh_mats;
+    sv.lights = c->d_lights;
+    sv.light_cdf = c->d_light_cdf;
+    sv.n_lights = (c->cfg.flags & B200PT_FLAG_NEE) ? (int32_t)c->h_lights.size() : 0;
+    sv.nee = (c->cfg.flags & B200PT_FLAG_NEE) ? 1 : 0;
     sv.texels = c->d_texels;
     sv.env = c->d_env;
     sv.env_w = c->env_w;
@@ -175,6 +188,8 @@ extern "C" int b200pt_destroy(b200pt_ctx* c) {
     cudaFree(c->d_env);
     cudaFree(c->d_mats);
     cudaFree(c->d_mesh_mats);
+    cudaFree(c->d_lights);
+    cudaFree(c->d_light_cdf);
     cudaFree(c->d_cursor);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
@@ -217,6 +232,7 @@ extern "C" int b200pt_add_mesh(b200pt_ctx* c, const float* verts, const float* n
     mi.first_tri = tbase;
     mi.material = material_index;
     mi.tex_offset = -1;
+    mi.light_first = -1;
     mi.has_uv = uvs ? 1 : 0;
     if (tex_rgba) {
         mi.tex_offset = (int32_t)c->h_texels.size();
@@ -357,6 +373,28 @@ static int sync_mesh_materials(b200pt_ctx* c) {
         c->mesh_mats_capacity = nm;
     }
     CU(cudaMemcpyAsync(c->d_mesh_mats, tmp.data(), sizeof(Material) * nm, cudaMemcpyHostToDevice, c->stream));
+    if (c->cfg.flags & B200PT_FLAG_NEE) {
+        // emissive triangles, their selection probabilities, and light_first of every mesh
+        build_light_table(c->h_pos, c->h_idx4, c->h_meshes, c->h_mats, c->h_lights, c->h_light_cdf);
+        const size_t nl = c->h_lights.size();
+        if (nl > c->lights_capacity) {
+            CU(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_lights);
+            cudaFree(c->d_light_cdf);
+            c->d_lights = nullptr;
+            c->d_light_cdf = nullptr;
+            CU(cudaMalloc(&c->d_lights, sizeof(LightTri) * nl));
+            CU(cudaMalloc(&c->d_light_cdf, sizeof(float) * nl));
+            c->lights_capacity = nl;
+        }
+        if (nl) {
+            CU(cudaMemcpyAsync(c->d_lights, c->h_lights.data(), sizeof(LightTri) * nl, cudaMemcpyHostToDevice, c->stream));
+            CU(cudaMemcpyAsync(c->d_light_cdf, c->h_light_cdf.data(), sizeof(float) * nl, cudaMemcpyHostToDevice, c->stream));
+        }
+        if (c->d_meshes)
+            CU(cudaMemcpyAsync(c->d_meshes, c->h_meshes.data(), sizeof(MeshInfo) * nm, cudaMemcpyHostToDevice, c->stream));
+        c->stats.n_lights = (uint32_t)nl;
+    }
     CU(cudaStreamSynchronize(c->stream));
     c->mesh_mats_dirty = false;
     return B200PT_OK;
@@ -378,6 +416,15 @@ static int ensure_lanes(b200pt_ctx* c, const SceneView& sv) {
         }
         CU(cudaMalloc(&c->la.sum, sizeof(f4) * padded));
         CU(cudaMalloc(&c->la.hit, sizeof(f4) * padded));
+        if (c->cfg.flags & B200PT_FLAG_NEE) {
+            CU(cudaMalloc(&c->la.rad, sizeof(f4) * padded));
+            CU(cudaMalloc(&c->la.sh_o, sizeof(f4) * padded));
+            CU(cudaMalloc(&c->la.sh_d, sizeof(f4) * padded));
+            CU(cudaMalloc(&c->la.sh_c, sizeof(f4) * padded));
+            CU(cudaMalloc(&c->la.sh_f, sizeof(f4) * padded));
+            CU(cudaMalloc(&c->la.sh_counts, sizeof(uint32_t) * kBatch));
+            CU(cudaMalloc(&c->la.sh_cursor, sizeof(uint32_t) * kBatch));
+        }
         CU(cudaMalloc(&c->la.counts, sizeof(uint32_t) * (kBatch + 1)));
         CU(cudaMalloc(&c->la.cursor, sizeof(uint32_t) * kBatch));
         CU(cudaMalloc(&c->la.walk_counters, sizeof(unsigned long long) * 2));
@@ -406,16 +453,24 @@ static int render_local(b200pt_ctx* c) {
     const SceneView sv = make_view(c, false);
     if (int r = ensure_lanes(c, sv)) return r;
     const bool count = (c->cfg.flags & B200PT_FLAG_COUNTERS) != 0;
-    const bool timing = (c->cfg.flags & 4) != 0;
+    const bool timing = (c->cfg.flags & B200PT_FLAG_TIMING) != 0;
+    const bool nee = sv.nee != 0;
+    const int ev_per_iter = nee ? 3 : 2;  // extend | shade [| shadow]
     cudaStream_t st = c->stream;
     b200pt_stats& S = c->stats;
     S.render_ms = S.extend_ms = S.shade_ms = S.other_ms = 0;
     S.rays = S.paths = S.nodes_visited = S.tris_tested = S.kernel_launches = S.iterations = 0;
+    S.shadow_rays = 0;
+    S.shadow_ms = 0;
 
     CU(cudaEventRecord(c->ev0, st));
     CU(cudaMemsetAsync(c->la.counts, 0, sizeof(uint32_t) * (kBatch + 1), st));
     CU(cudaMemsetAsync(c->la.cursor, 0, sizeof(uint32_t) * kBatch, st));
     CU(cudaMemsetAsync(c->la.walk_counters, 0, sizeof(unsigned long long) * 2, st));
+    if (nee) {
+        CU(cudaMemsetAsync(c->la.sh_counts, 0, sizeof(uint32_t) * kBatch, st));
+        CU(cudaMemsetAsync(c->la.sh_cursor, 0, sizeof(uint32_t) * kBatch, st));
+    }
     uint32_t active = 0;
     if (sv.n_lanes > 0 && sv.max_samples > 0 && sv.max_depth > 0) {
         launch_init_lanes(sv, c->la, st);
@@ -425,25 +480,36 @@ static int render_local(b200pt_ctx* c) {
     } else {
         CU(cudaMemsetAsync(c->la.sum, 0, sizeof(f4) * c->la.capacity, st));
     }
-    if (timing && c->ev_pool.size() < (size_t)(2 * kBatch + 1)) {
-        while (c->ev_pool.size() < (size_t)(2 * kBatch + 1)) {
+    if (timing) {
+        while (c->ev_pool.size() < (size_t)(3 * kBatch + 1)) {
             cudaEvent_t e;
             CU(cudaEventCreate(&e));
             c->ev_pool.push_back(e);
         }
     }
     uint32_t h_counts[kBatch + 1];
+    uint32_t h_shadow[kBatch] = {};
     while (active > 0) {
         for (int k = 0; k < kBatch; ++k) {
-            if (timing) CU(cudaEventRecord(c->ev_pool[2 * k], st));
+            if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k], st));
             launch_extend(sv, c->la, k, active, count, st);
-            if (timing) CU(cudaEventRecord(c->ev_pool[2 * k + 1], st));
+            if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 1], st));
             launch_shade(sv, c->la, k, active, st);
+            if (nee) {
+                // the shadow rays this iteration's vertices asked for: any-hit walk, then the gated add
+                if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 2], st));
+                launch_shadow(sv, c->la, k, active, st);
+            }
         }
-        if (timing) CU(cudaEventRecord(c->ev_pool[2 * kBatch], st));
-        S.kernel_launches += 2 * kBatch;
+        if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * kBatch], st));
+        S.kernel_launches += (uint64_t)ev_per_iter * kBatch;
         CU(cudaGetLastError());
         CU(cudaMemcpyAsync(h_counts, c->la.counts, sizeof h_counts, cudaMemcpyDeviceToHost, st));
+        if (nee) {
+            CU(cudaMemcpyAsync(h_shadow, c->la.sh_counts, sizeof h_shadow, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemsetAsync(c->la.sh_counts, 0, sizeof(uint32_t) * kBatch, st));
+            CU(cudaMemsetAsync(c->la.sh_cursor, 0, sizeof(uint32_t) * kBatch, st));
+        }
         // next batch starts from the last queue length; the other slots go back to zero
         CU(cudaMemcpyAsync(c->la.counts, c->la.counts + kBatch, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
         CU(cudaMemsetAsync(c->la.counts + 1, 0, sizeof(uint32_t) * kBatch, st));
@@ -451,15 +517,18 @@ static int render_local(b200pt_ctx* c) {
         CU(cudaStreamSynchronize(st));
         for (int k = 0; k < kBatch; ++k) {
             S.rays += h_counts[k];
+            S.shadow_rays += h_shadow[k];
             if (h_counts[k]) S.iterations++;
         }
         if (timing) {
             for (int k = 0; k < kBatch; ++k) {
-                float a = 0, b = 0;
-                cudaEventElapsedTime(&a, c->ev_pool[2 * k], c->ev_pool[2 * k + 1]);
-                cudaEventElapsedTime(&b, c->ev_pool[2 * k + 1], c->ev_pool[2 * k + 2]);
+                float a = 0, b = 0, s = 0;
+                cudaEventElapsedTime(&a, c->ev_pool[ev_per_iter * k], c->ev_pool[ev_per_iter * k + 1]);
+                cudaEventElapsedTime(&b, c->ev_pool[ev_per_iter * k + 1], c->ev_pool[ev_per_iter * k + 2]);
+                if (nee) cudaEventElapsedTime(&s, c->ev_pool[ev_per_iter * k + 2], c->ev_pool[ev_per_iter * k + 3]);
                 S.extend_ms += a;
                 S.shade_ms += b;
+                S.shadow_ms += s;
             }
         }
         active = h_counts[kBatch];
@@ -475,7 +544,7 @@ static int render_local(b200pt_ctx* c) {
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     S.render_ms = ms;
-    S.other_ms = timing ? ms - S.extend_ms - S.shade_ms : 0;
+    S.other_ms = timing ? ms - S.extend_ms - S.shade_ms - S.shadow_ms : 0;
     S.paths = (uint64_t)std::max(sv.n_lanes, 0) * (uint64_t)sv.max_samples;
     if (count) {
         unsigned long long wc[2];

@@ -33,6 +33,14 @@ struct LaneArrays {
     f4* hit = nullptr;                   // t, u, v, triangle id   (written by k_extend, same index)
     uint32_t* queue[2] = {nullptr, nullptr};  // lane (pixel) id of entry i
     f4* sum = nullptr;     // per lane: sum of finished samples .xyz, -   (this is the accumulation buffer)
+    // next-event estimation mode (B200PT_FLAG_NEE) only
+    f4* rad = nullptr;     // per lane: light-sampled radiance of the sample in flight .xyz
+    f4* sh_o = nullptr;    // shadow requests of the current iteration: origin.xyz, tmax
+    f4* sh_d = nullptr;    //   direction.xyz, lane id
+    f4* sh_c = nullptr;    //   contribution if unoccluded .xyz, flags (1 = the sample ends with this request)
+    f4* sh_f = nullptr;    //   last term of the ending sample .xyz
+    uint32_t* sh_counts = nullptr;  // kBatch request counts
+    uint32_t* sh_cursor = nullptr;  // kBatch fetch cursors of k_shadow
     uint32_t* counts = nullptr;   // kBatch + 1 queue lengths
     uint32_t* cursor = nullptr;   // kBatch ray-fetch cursors of the persistent extend kernel
     unsigned long long* walk_counters = nullptr;  // nodes, tris (FLAG_COUNTERS)
@@ -45,6 +53,7 @@ constexpr int kBatch = 32;  // wavefront iterations between host checks (even: t
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, cudaStream_t st);
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st);
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
+void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st);
 void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStream_t st);
 void launch_primary(const SceneView& sv, f4* hits, uint32_t* cursor, cudaStream_t st);

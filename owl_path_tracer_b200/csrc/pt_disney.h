@@ -104,7 +104,19 @@ struct BsdfSample {
     float pdf;
 };
 
-// disney_diffuse.cuh:26-62 with sample_methods.hpp:19-57
+// eval_disney_diffuse, disney_diffuse.cuh:26-55 (pdf_cosine_hemisphere, sample_methods.hpp:59-62)
+PT_HD f3 eval_diffuse(const Material& m, f3 wo, f3 wi, float& pdf) {
+    float fo = schlick_w(wo.z);
+    float fi = schlick_w(wi.z);
+    f3 lambert = f3{m.base_color[0], m.base_color[1], m.base_color[2]} * kInvPi;
+    float fd = (1.0f - 0.5f * fo) * (1.0f - 0.5f * fi);
+    float rr = m.roughness * (dot(wo, wi) + 1.0f);
+    float fr = rr * (fi + fo + fo * fi * (rr - 1.0f));
+    pdf = fabsf(wi.z) * kInvPi;
+    return lambert * (fd + fr);
+}
+
+// disney_diffuse.cuh:57-62 with sample_methods.hpp:19-57
 PT_HD void lobe_diffuse(const Material& m, f3 wo, uint32_t& rng, BsdfSample& s) {
     float ux = rng_next(rng);
     float uy = rng_next(rng);
@@ -124,18 +136,25 @@ PT_HD void lobe_diffuse(const Material& m, f3 wo, uint32_t& rng, BsdfSample& s) 
         py = r * dm_sin(phi);
     }
     f3 wi{px, py, sqrtf(fmaxf(0.0f, 1.0f - sqr(px) - sqr(py)))};
-    float fo = schlick_w(wo.z);
-    float fi = schlick_w(wi.z);
-    f3 lambert = f3{m.base_color[0], m.base_color[1], m.base_color[2]} * kInvPi;
-    float fd = (1.0f - 0.5f * fo) * (1.0f - 0.5f * fi);
-    float rr = m.roughness * (dot(wo, wi) + 1.0f);
-    float fr = rr * (fi + fo + fo * fi * (rr - 1.0f));
     s.wi = wi;
-    s.pdf = fabsf(wi.z) * kInvPi;
-    s.f = lambert * (fd + fr);
+    s.f = eval_diffuse(m, wo, wi, s.pdf);
 }
 
-// disney_specular.cuh:125-170
+// eval_disney_specular_brdf, disney_specular.cuh:125-149
+PT_HD f3 eval_metal(const Material& m, f3 wo, f3 wh, f3 wi, float& pdf) {
+    f2 a = alpha_aniso(m.roughness, m.anisotropic);
+    f3 base{m.base_color[0], m.base_color[1], m.base_color[2]};
+    float lum = lum709(base);
+    f3 tint = lum > 0.0f ? base / lum : mk3(1.0f);
+    f3 cspec = lerp3(.08f * m.specular * lerp3(mk3(1.0f), tint, m.specular_tint), base, m.metallic);
+    float d = ggx_d(wh, a.x, a.y);
+    float g = 1.0f / (1.0f + smith_lambda(wo, a.x, a.y) + smith_lambda(wi, a.x, a.y));
+    f3 fr = lerp3(cspec, mk3(1.0f), schlick_w(dot(wi, wh)));
+    pdf = d * smith_g1(wo, a.x, a.y) * fmaxf(0.0f, dot(wo, wh)) / (4.0f * wo.z);
+    return d * g * fr / (4.0f * fabsf(wo.z));
+}
+
+// disney_specular.cuh:151-170
 PT_HD void lobe_metal(const Material& m, f3 wo, uint32_t& rng, BsdfSample& s) {
     f2 a = alpha_aniso(m.roughness, m.anisotropic);
     float u0 = rng_next(rng);
@@ -149,18 +168,25 @@ PT_HD void lobe_metal(const Material& m, f3 wo, uint32_t& rng, BsdfSample& s) {
         s.f = mk3(0.0f);
         return;
     }
-    f3 base{m.base_color[0], m.base_color[1], m.base_color[2]};
-    float lum = lum709(base);
-    f3 tint = lum > 0.0f ? base / lum : mk3(1.0f);
-    f3 cspec = lerp3(.08f * m.specular * lerp3(mk3(1.0f), tint, m.specular_tint), base, m.metallic);
-    float d = ggx_d(wh, a.x, a.y);
-    float g = 1.0f / (1.0f + smith_lambda(wo, a.x, a.y) + smith_lambda(wi, a.x, a.y));
-    f3 fr = lerp3(cspec, mk3(1.0f), schlick_w(dot(wi, wh)));
-    s.pdf = d * smith_g1(wo, a.x, a.y) * fmaxf(0.0f, dot(wo, wh)) / (4.0f * wo.z);
-    s.f = d * g * fr / (4.0f * fabsf(wo.z));
+    s.f = eval_metal(m, wo, wh, wi, s.pdf);
 }
 
-// disney_clearcoat.cuh:13-78
+// eval_disney_clearcoat (m.clearcoat > 0 checked by the caller), disney_clearcoat.cuh:13-20,45-59
+PT_HD f3 eval_clearcoat(const Material& m, f3 wo, f3 wh, f3 wi, float& pdf) {
+    float a = lerpf(0.1f, .001f, m.clearcoat_gloss);
+    float a2 = sqr(a);
+    float d;
+    if (a >= 1)
+        d = kInvPi;
+    else
+        d = (a2 - 1.0f) / (kPi * dm_log(a2) * (1.0f + (a2 - 1.0f) * sqr(wh.z)));
+    float fr = lerpf(1.0f, schlick_w(wi.z), 0.04f);
+    float g = smith_g1(wo, .25f, .25f) * smith_g1(wi, .25f, .25f);
+    pdf = d / (4.0f * dot(wh, wi));
+    return mk3(d * g * fr / (4.0f * fabsf(wo.z) * fabsf(wi.z)));
+}
+
+// disney_clearcoat.cuh:22-35,61-78
 PT_HD void lobe_clearcoat(const Material& m, f3 wo, uint32_t& rng, BsdfSample& s) {
     float a = lerpf(0.1f, .001f, m.clearcoat_gloss);
     float u0 = rng_next(rng);
@@ -180,15 +206,7 @@ PT_HD void lobe_clearcoat(const Material& m, f3 wo, uint32_t& rng, BsdfSample& s
         s.f = mk3(0.0f);
         return;
     }
-    float d;
-    if (a >= 1)
-        d = kInvPi;
-    else
-        d = (a2 - 1.0f) / (kPi * dm_log(a2) * (1.0f + (a2 - 1.0f) * sqr(wh.z)));
-    float fr = lerpf(1.0f, schlick_w(wi.z), 0.04f);
-    float g = smith_g1(wo, .25f, .25f) * smith_g1(wi, .25f, .25f);
-    s.pdf = d / (4.0f * dot(wh, wi));
-    s.f = mk3(d * g * fr / (4.0f * fabsf(wo.z) * fabsf(wi.z)));
+    s.f = eval_clearcoat(m, wo, wh, wi, s.pdf);
 }
 
 // disney_specular.cuh:175-244
@@ -274,6 +292,56 @@ PT_HD void sample_disney(const Material& m, f3 wo, uint32_t& rng, int& lobe, Bsd
         lobe = LOBE_GLASS;
     }
     s.f = s.f + sheen_term(m, wo, s.wi);
+}
+
+// ---- next-event estimation support (B200PT_FLAG_NEE; no counterpart in the reference's integrator,
+// built from its eval_* functions).  The reference's estimator picks ONE lobe l with probability
+// p_l and weights (f_l + sheen) / pdf_l, so in expectation it integrates
+//     f_eff(wo, wi) = sum_l p_l (f_l(wo, wi) + sheen(wo, wi))
+// and generates directions with density pdf_eff = sum_l p_l pdf_l.  eval_mixture returns both for a
+// GIVEN wi over the three lobes a light sample can reach (metal, clearcoat, diffuse); the glass lobe
+// reports a probability instead of a density (disney_specular.cuh:204-213) and is treated as
+// specular: it is left out here and emitters found through it count fully.
+// The hemisphere conditions are those under which each sampler returns a non-zero sample.
+PT_HD void eval_mixture(const Material& m, f3 wo, f3 wi, f3& f_eff, float& pdf_eff) {
+    float dw = (1.0f - m.specular_transmission) * (1.0f - m.metallic);
+    float mw = m.metallic;
+    float cw = .25f * m.clearcoat;
+    float gw = (1.0f - m.metallic) * m.specular_transmission;
+    float factor = 1.0f / (mw + gw + dw + cw);
+    float pm = mw * factor;
+    float pd = dw * factor;
+    float pc = cw * factor;
+    f_eff = mk3(0.0f);
+    pdf_eff = 0.0f;
+    f3 wh = wo + wi;
+    const bool has_wh = !(wh.x == 0.0f && wh.y == 0.0f && wh.z == 0.0f);
+    if (has_wh) wh = normalize(wh);
+    const f3 sheen = sheen_term(m, wo, wi);
+    if (pm > 0.0f && has_wh && wi.z > 0.0f) {          // lobe_metal: rejects cos(wi) <= 0
+        float pdf;
+        f3 f = eval_metal(m, wo, wh, wi, pdf);
+        f_eff = f_eff + pm * (f + sheen);
+        pdf_eff = pdf_eff + pm * pdf;
+    }
+    if (pc > 0.0f && has_wh && same_side(wo, wi)) {    // lobe_clearcoat: rejects the other hemisphere
+        float pdf;
+        f3 f = eval_clearcoat(m, wo, wh, wi, pdf);
+        f_eff = f_eff + pc * (f + sheen);
+        pdf_eff = pdf_eff + pc * pdf;
+    }
+    if (pd > 0.0f && wi.z > 0.0f) {                    // cosine hemisphere: only generates cos(wi) >= 0
+        float pdf;
+        f3 f = eval_diffuse(m, wo, wi, pdf);
+        f_eff = f_eff + pd * (f + sheen);
+        pdf_eff = pdf_eff + pd * pdf;
+    }
+}
+
+// power_heuristic(1, a, 1, b), lights.hpp:56-61
+PT_HD float power_heuristic(float pdf_f, float pdf_g) {
+    float f = pdf_f, g = pdf_g;
+    return (f * f) / (f * f + g * g);
 }
 
 }  // namespace pt

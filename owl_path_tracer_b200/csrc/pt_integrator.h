@@ -38,7 +38,17 @@ struct alignas(16) MeshInfo {
     int32_t tex_offset;   // first texel in the texture pool, -1 = no texture
     int32_t tex_w, tex_h;
     int32_t has_uv;
-    int32_t pad0, pad1;
+    int32_t light_first;  // index of this mesh's primitive 0 in SceneView::lights, -1 = not an emitter
+    int32_t pad1;
+};
+
+// one emissive triangle of the light table (next-event estimation mode): chosen with probability
+// `prob` (proportional to area * emission), sampled uniformly by area (lights.hpp:30-48)
+struct alignas(16) LightTri {
+    uint32_t tri;      // global triangle id
+    float area;        // triangle_area, lights.hpp:15-20
+    float prob;        // cdf[i] - cdf[i-1]
+    float emission;    // material_data::emission of its mesh
 };
 
 struct SceneView {
@@ -66,6 +76,11 @@ struct SceneView {
     int32_t row_first, row_step;
     int32_t seed_row_offset;   // added to y when seeding (per-rank streams: rank * height)
     int32_t n_lanes;
+    // next-event estimation (B200PT_FLAG_NEE); n_lights == 0 or nee == 0: the reference's estimator verbatim
+    const LightTri* lights;
+    const float* light_cdf;    // n_lights ascending values, last = 1
+    int32_t n_lights;
+    int32_t nee;
     uint32_t plane_magic;      // 0x3F800000, see plane_q (pt_bvh8.h): a runtime value on purpose
 };
 
@@ -132,6 +147,12 @@ struct LaneState {
     uint32_t sample;  // index of the sample in flight
     uint32_t depth;   // loop counter of trace_path
     int lobe;         // sampled_lobe, persists across bounces (device.cu:127)
+    // next-event estimation mode only
+    float prev_pdf;   // density with which the BSDF generated the current ray; <= 0: count an emitter fully
+    int sh_valid;     // a shadow ray is requested: from sh_o along sh_d up to sh_tmax; if nothing is hit,
+    f3 sh_o, sh_d;    //   sh_c is added to the radiance of the sample this vertex belongs to
+    float sh_tmax;
+    f3 sh_c;
 };
 
 enum ShadeResult { LANE_CONTINUE = 0, LANE_DONE = 1 };
@@ -150,13 +171,24 @@ PT_HD ShadeResult end_sample(const SceneView& sv, LaneState& L, int px, int py, 
     L.thr = mk3(1.0f);
     L.depth = 0;
     L.lobe = LOBE_NONE;
+    L.prev_pdf = -1.0f;
     return LANE_CONTINUE;
+}
+
+// pdf_area_to_solid_angle, lights.hpp:23-28
+PT_HD float pdf_area_to_solid_angle(float pdf_area, float dist_sqr, float cos_theta) {
+    const float a = fabsf(cos_theta);
+    if (a < 1e-4f) return 0.0f;
+    return pdf_area * dist_sqr / a;
 }
 
 // One iteration of the loop body of trace_path (device.cu:130-215) for a lane whose
 // ray has just been traced.  Returns LANE_DONE when the pixel's last sample ended.
+template <bool NEE>
 PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, int px, int py) {
     L.sample_ended = false;
+    L.sh_valid = 0;
+    const bool nee = NEE && sv.n_lights > 0;  // NEE: compiled for B200PT_FLAG_NEE contexts only
     if (hit.tri == kNoHit) {
         const f3 rad = miss_radiance(sv, L.d);
         return end_sample(sv, L, px, py, rad * L.thr);
@@ -172,6 +204,16 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
     const f4 n0 = load_ro(sv.vnrm + i0), n1 = load_ro(sv.vnrm + i1), n2 = load_ro(sv.vnrm + i2);
 
     if (m.emission > 0.0f) {  // device.cu:157-161: radiance = emission (overwrites)
+        if (nee && L.prev_pdf > 0.0f && mi.light_first >= 0) {
+            // the same emitter could have been reached by light sampling at the previous vertex:
+            // power heuristic between the BSDF density and the light density of this very point
+            const LightTri lt = load_ro(sv.lights + (mi.light_first + ((int)hit.tri - mi.first_tri)));
+            const float lw = 1.0f - hit.u - hit.v;
+            const f3 nl = lw * f3{n0.x, n0.y, n0.z} + hit.u * f3{n1.x, n1.y, n1.z} + hit.v * f3{n2.x, n2.y, n2.z};
+            const float pdf_light = lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, hit.t * hit.t, dot(-L.d, nl));
+            const float w = power_heuristic(L.prev_pdf, pdf_light);
+            return end_sample(sv, L, px, py, mk3(m.emission * w) * L.thr);
+        }
         return end_sample(sv, L, px, py, mk3(m.emission) * L.thr);
     }
 
@@ -200,6 +242,49 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
     const f3 B = cross(vn, T);
     const f3 lwo = normalize(f3{dot(wo, T), dot(wo, B), dot(wo, vn)});
 
+    if (nee) {
+        // next-event estimation: one emissive triangle by power, one point on it by area
+        // (sample_triangle, lights.hpp:30-48; uniform_sample_triangle, sample_methods.hpp:82-86)
+        const float us = rng_next(L.rng), u0 = rng_next(L.rng), u1 = rng_next(L.rng);
+        int lo = 0, hi = sv.n_lights - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (us <= sv.light_cdf[mid]) hi = mid;
+            else lo = mid + 1;
+        }
+        const LightTri lt = load_ro(sv.lights + lo);
+        const TriIdx lx = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + lt.tri);
+        const f4 q0 = load_ro(sv.vpos + lx.i0), q1 = load_ro(sv.vpos + lx.i1), q2 = load_ro(sv.vpos + lx.i2);
+        const f4 m0 = load_ro(sv.vnrm + lx.i0), m1 = load_ro(sv.vnrm + lx.i1), m2 = load_ro(sv.vnrm + lx.i2);
+        const float su0 = sqrtf(u0);
+        const float bx = 1.0f - su0, by = u1 * su0;
+        const float bz = 1.0f - bx - by;
+        const f3 pos = bz * f3{q0.x, q0.y, q0.z} + bx * f3{q1.x, q1.y, q1.z} + by * f3{q2.x, q2.y, q2.z};
+        const f3 nl = bz * f3{m0.x, m0.y, m0.z} + bx * f3{m1.x, m1.y, m1.z} + by * f3{m2.x, m2.y, m2.z};
+        f3 dir = pos - vp;
+        const float dist2 = dot(dir, dir);
+        const float dist = sqrtf(dist2);
+        dir = dir / dist;
+        const float pdf_light = lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, dist2, dot(-dir, nl));
+        if (pdf_light > 0.0f && dist > 2.0f * kTMin) {
+            const f3 lwi = normalize(f3{dot(dir, T), dot(dir, B), dot(dir, vn)});
+            f3 f_eff;
+            float pdf_eff;
+            eval_mixture(m, lwo, lwi, f_eff, pdf_eff);
+            if (pdf_eff > 0.0f) {
+                const float w = power_heuristic(pdf_light, pdf_eff);
+                const f3 c = L.thr * (f_eff * (fabsf(lwi.z) * lt.emission * w / pdf_light));
+                if (!bad3(c) && (c.x != 0.0f || c.y != 0.0f || c.z != 0.0f)) {
+                    L.sh_valid = 1;
+                    L.sh_o = vp;
+                    L.sh_d = dir;
+                    L.sh_tmax = dist - kTMin;   // visibiliy_test, device.cu:97-110
+                    L.sh_c = c;
+                }
+            }
+        }
+    }
+
     // The reference re-traces the same ray when f is inf/nan (--depth; continue,
     // device.cu:196-201).  The trace is deterministic, so the retry only redraws the
     // BSDF sample; we loop here instead of going round the wavefront again.
@@ -215,6 +300,12 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
         L.thr = L.thr * (s.f * fabsf(s.wi.z) / s.pdf);
         L.o = vp;
         L.d = wi;
+        if (nee) {  // density of this direction under BSDF sampling, for the emitter it may reach
+            f3 fe;
+            float pe;
+            eval_mixture(m, lwo, s.wi, fe, pe);
+            L.prev_pdf = L.lobe == LOBE_GLASS ? -1.0f : pe;
+        }
         const float bmax = fmaxf(L.thr.x, fmaxf(L.thr.y, L.thr.z));
         if (L.lobe != LOBE_GLASS && L.depth > 3) {  // inverted, uncompensated RR (Q14)
             const float q = fmaxf(.05f, 1.0f - bmax);

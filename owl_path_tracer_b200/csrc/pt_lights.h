@@ -1,0 +1,54 @@
+// pt_lights.h — host-side light table of the next-event estimation mode (B200PT_FLAG_NEE).
+//
+// The reference samples no lights (its lights.hpp is dead code); this mode is assembled
+// from those helpers.  Every triangle of every mesh whose material has emission > 0 becomes one entry,
+// in mesh order; an entry is chosen with probability proportional to triangle_area * emission
+// (lights.hpp:8-20: power = L_emit * area * pi).  The cdf is accumulated in binary64 and rounded once, so
+// the scalar oracle (oracle/oracle.cpp build_lights) arrives at the same bits independently.
+// Used by api.cu (upload) and tests/emu (host emulation of the kernels).
+#pragma once
+#include <vector>
+
+#include "pt_integrator.h"
+
+namespace pt {
+
+// meshes[].light_first is rewritten; lights/cdf are empty when nothing emits.
+inline void build_light_table(const std::vector<f4>& pos, const std::vector<int32_t>& idx4, std::vector<MeshInfo>& meshes,
+                              const std::vector<Material>& mats, std::vector<LightTri>& lights, std::vector<float>& cdf) {
+    lights.clear();
+    cdf.clear();
+    std::vector<double> acc;
+    double total = 0.0;
+    const size_t n_tris = idx4.size() / 4;
+    for (size_t mi = 0; mi < meshes.size(); ++mi) {
+        meshes[mi].light_first = -1;
+        const int32_t mat = meshes[mi].material;
+        if (mat < 0 || (size_t)mat >= mats.size()) continue;
+        const float emission = mats[(size_t)mat].emission;
+        if (!(emission > 0.0f)) continue;
+        const size_t first = (size_t)meshes[mi].first_tri;
+        const size_t last = mi + 1 < meshes.size() ? (size_t)meshes[mi + 1].first_tri : n_tris;
+        meshes[mi].light_first = (int32_t)lights.size();
+        for (size_t t = first; t < last; ++t) {
+            const f4 a = pos[(size_t)idx4[4 * t]], b = pos[(size_t)idx4[4 * t + 1]], c = pos[(size_t)idx4[4 * t + 2]];
+            const f3 n = cross(f3{b.x, b.y, b.z} - f3{a.x, a.y, a.z}, f3{c.x, c.y, c.z} - f3{a.x, a.y, a.z});
+            const float area = 0.5f * sqrtf(dot(n, n));
+            const float w = area * emission;
+            total += (double)w;
+            acc.push_back(total);
+            lights.push_back(LightTri{(uint32_t)t, area, 0.0f, emission});
+        }
+    }
+    if (!(total > 0.0)) {
+        lights.clear();
+        for (MeshInfo& m : meshes) m.light_first = -1;
+        return;
+    }
+    cdf.resize(lights.size());
+    for (size_t i = 0; i < lights.size(); ++i) cdf[i] = (float)(acc[i] / total);
+    cdf.back() = 1.0f;
+    for (size_t i = 0; i < lights.size(); ++i) lights[i].prob = cdf[i] - (i ? cdf[i - 1] : 0.0f);
+}
+
+}  // namespace pt

@@ -44,9 +44,11 @@ __device__ __forceinline__ f4 ldg4f(const f4* p) {
 
 // magic: 0x3F800000 handed in as a RUNTIME value (SceneView::plane_magic, a kernel parameter), so that
 //        it sits in a register and the byte-permute selector of plane_q is the immediate.
+// ANY:  shadow rays — the first accepted triangle ends the ray (any hit in (tmin, tmax)); the hit record then
+//       only says whether something was hit.
 // Src:  bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax)   (i < n)
 // Sink: void store(uint32_t i, const Hit& h)
-template <bool COUNT, class Src, class Sink>
+template <bool COUNT, bool ANY, class Src, class Sink>
 __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const Tri48* __restrict__ tris, uint32_t n,
                                           uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic) {
     const unsigned FULL = 0xffffffffu;
@@ -163,6 +165,11 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
                     hit.u = uu;
                     hit.v = vv;
                     hit.tri = id;
+                    if (ANY) {  // occluded: drop the rest of the traversal
+                        ng_mask = 0;
+                        tg_mask = 0;
+                        sp = 0;
+                    }
                 }
             }
         } else if (can_node) {

@@ -40,7 +40,8 @@ __global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays 
     uint32_t rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset));  // device.cu:226
     f3 o, d;
     camera_ray(sv, px, py, rng, o, d);
-    st4(la.ray_o[0] + lane, f4{o.x, o.y, o.z, 0.0f});
+    st4(la.ray_o[0] + lane, f4{o.x, o.y, o.z, -1.0f});  // .w: prev_pdf of the NEE mode (camera ray: count emitters fully)
+    if (la.rad) st4(la.rad + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
     st4(la.ray_d[0] + lane, f4{d.x, d.y, d.z, u2f(pack_ctl(0, 0, LOBE_NONE))});
     st4(la.thr[0] + lane, f4{1.0f, 1.0f, 1.0f, u2f(rng)});
     st4(la.sum + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
@@ -70,7 +71,7 @@ __global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_extend(SceneVi
     WalkCounters wc{0, 0};
     if (n) {
         // (k & 1) selects the state set; written out so that the parameter struct is never indexed dynamically
-        warp_walk<COUNT>(sv.nodes, sv.tris, n, la.cursor + k,
+        warp_walk<COUNT, false>(sv.nodes, sv.tris, n, la.cursor + k,
                          LaneRaySource{(k & 1) ? la.ray_o[1] : la.ray_o[0], (k & 1) ? la.ray_d[1] : la.ray_d[0]},
                          LaneHitSink{la.hit}, wc, sv.plane_magic);
     }
@@ -87,10 +88,11 @@ __global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_extend(SceneVi
     }
 }
 
+template <bool NEE>
 __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView sv, LaneArrays la, int k) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool odd = (k & 1) != 0;
-    const f4 *in_d = odd ? la.ray_d[1] : la.ray_d[0], *in_t = odd ? la.thr[1] : la.thr[0];
+    const f4 *in_o = odd ? la.ray_o[1] : la.ray_o[0], *in_d = odd ? la.ray_d[1] : la.ray_d[0], *in_t = odd ? la.thr[1] : la.thr[0];
     f4 *out_o = odd ? la.ray_o[0] : la.ray_o[1], *out_d = odd ? la.ray_d[0] : la.ray_d[1], *out_t = odd ? la.thr[0] : la.thr[1];
     const uint32_t* in_q = odd ? la.queue[1] : la.queue[0];
     uint32_t* out_q = odd ? la.queue[0] : la.queue[1];
@@ -100,10 +102,13 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
     const uint32_t n = la.counts[k];
     const uint32_t lane = in_q[i];
     const f4 d = ld4(in_d + i), t = ld4(in_t + i), hv = ld4(la.hit + i);
-    bool keep = false;
+    bool keep = false, shadow = false;
     LaneState L;
+    f3 last_term = mk3(0.0f);
+    uint32_t shadow_flags = 0;
     if (i < n) {
         f4 s = ld4(la.sum + lane);
+        if (NEE) L.prev_pdf = in_o[i].w;  // density of the current ray under BSDF sampling (ray_o.w)
         L.o = mk3(0.0f);  // only written: the old origin is never needed again
         L.d = f3{d.x, d.y, d.z};
         L.thr = f3{t.x, t.y, t.z};
@@ -115,8 +120,25 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
         Hit h{hv.x, hv.y, hv.z, f2u(hv.w)};
         int px, py;
         lane_pixel(sv, lane, px, py);
-        const ShadeResult r = shade_lane(sv, L, h, px, py);
-        if (L.sample_ended) {  // color += trace_path(...), in sample order
+        const ShadeResult r = shade_lane<NEE>(sv, L, h, px, py);
+        if (NEE) {
+            // sample value = light-sampled radiance gathered along the path + last term.  When this very
+            // vertex asked for a shadow ray the sample is finished by k_shadow instead (flag 1).
+            shadow = L.sh_valid != 0;
+            if (L.sample_ended) {
+                if (shadow) {
+                    shadow_flags = 1u;
+                    last_term = L.contrib;
+                } else {
+                    const f4 g = ld4(la.rad + lane);
+                    s.x += g.x + L.contrib.x;
+                    s.y += g.y + L.contrib.y;
+                    s.z += g.z + L.contrib.z;
+                    st4(la.sum + lane, s);
+                    st4(la.rad + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
+                }
+            }
+        } else if (L.sample_ended) {  // color += trace_path(...), in sample order
             s.x += L.contrib.x;
             s.y += L.contrib.y;
             s.z += L.contrib.z;
@@ -134,12 +156,79 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
         base = __shfl_sync(0xffffffffu, base, leader);
         if (keep) {
             const uint32_t pos = base + __popc(m & ((1u << lid) - 1u));
-            st4(out_o + pos, f4{L.o.x, L.o.y, L.o.z, 0.0f});
+            st4(out_o + pos, f4{L.o.x, L.o.y, L.o.z, NEE ? L.prev_pdf : 0.0f});
             st4(out_d + pos, f4{L.d.x, L.d.y, L.d.z, u2f(pack_ctl(L.sample, L.depth, L.lobe))});
             st4(out_t + pos, f4{L.thr.x, L.thr.y, L.thr.z, u2f(L.rng)});
             out_q[pos] = lane;
         }
     }
+    if (NEE) {  // warp-aggregated append of the shadow requests of this iteration
+        const unsigned ms = __ballot_sync(0xffffffffu, shadow);
+        if (ms) {
+            const int lid = threadIdx.x & 31;
+            const int leader = __ffs(ms) - 1;
+            uint32_t base = 0;
+            if (lid == leader) base = atomicAdd(la.sh_counts + k, (uint32_t)__popc(ms));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (shadow) {
+                const uint32_t pos = base + __popc(ms & ((1u << lid) - 1u));
+                st4(la.sh_o + pos, f4{L.sh_o.x, L.sh_o.y, L.sh_o.z, L.sh_tmax});
+                st4(la.sh_d + pos, f4{L.sh_d.x, L.sh_d.y, L.sh_d.z, u2f(lane)});
+                st4(la.sh_c + pos, f4{L.sh_c.x, L.sh_c.y, L.sh_c.z, u2f(shadow_flags)});
+                st4(la.sh_f + pos, f4{last_term.x, last_term.y, last_term.z, 0.0f});
+            }
+        }
+    }
+}
+
+// ---- k_shadow: any-hit walk of the shadow requests k_shade<true> queued in iteration k (the
+// reference's unused visibiliy_test, device.cu:97-110).  An unoccluded request adds its contribution to
+// the lane's gathered radiance; a request flagged 1 also finishes the lane's sample.
+struct ShadowRaySource {
+    const f4* sh_o;
+    const f4* sh_d;
+    __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
+        const f4 a = ld4(sh_o + i), b = ld4(sh_d + i);
+        o = f3{a.x, a.y, a.z};
+        d = f3{b.x, b.y, b.z};
+        tmin = kTMin;
+        tmax = a.w;
+    }
+};
+struct ShadowSink {
+    const f4* sh_d;
+    const f4* sh_c;
+    const f4* sh_f;
+    f4* rad;
+    f4* sum;
+    __device__ __forceinline__ void store(uint32_t i, const Hit& h) const {
+        const uint32_t lane = f2u(sh_d[i].w);
+        const f4 c = ld4(sh_c + i);
+        f4 g = ld4(rad + lane);
+        if (h.tri == kNoHit) {
+            g.x += c.x;
+            g.y += c.y;
+            g.z += c.z;
+        }
+        if (f2u(c.w) & 1u) {
+            const f4 f = ld4(sh_f + i);
+            f4 s = ld4(sum + lane);
+            s.x += g.x + f.x;
+            s.y += g.y + f.y;
+            s.z += g.z + f.z;
+            st4(sum + lane, s);
+            g = f4{0.0f, 0.0f, 0.0f, 0.0f};
+        }
+        st4(rad + lane, g);
+    }
+};
+
+__global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_shadow(SceneView sv, LaneArrays la, int k) {
+    const uint32_t n = la.sh_counts[k];
+    WalkCounters wc{0, 0};
+    if (n)
+        warp_walk<false, true>(sv.nodes, sv.tris, n, la.sh_cursor + k, ShadowRaySource{la.sh_o, la.sh_d},
+                               ShadowSink{la.sh_d, la.sh_c, la.sh_f, la.rad, la.sum}, wc, sv.plane_magic);
 }
 
 // device.cu:246-253.  sum is indexed by lane; the frame is written row-flipped.
@@ -192,14 +281,14 @@ struct ArrayHitSink {
 
 __global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_primary(SceneView sv, f4* hits, uint32_t* cursor) {
     WalkCounters wc{0, 0};
-    warp_walk<false>(sv.nodes, sv.tris, (uint32_t)(sv.width * sv.height), cursor, CameraRaySource{sv}, ArrayHitSink{hits}, wc,
+    warp_walk<false, false>(sv.nodes, sv.tris, (uint32_t)(sv.width * sv.height), cursor, CameraRaySource{sv}, ArrayHitSink{hits}, wc,
                      sv.plane_magic);
 }
 
 __global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_trace(SceneView sv, const float* __restrict__ o, const float* __restrict__ d,
                                                   int n, float tmin, float tmax, f4* hits, uint32_t* cursor) {
     WalkCounters wc{0, 0};
-    warp_walk<false>(sv.nodes, sv.tris, (uint32_t)n, cursor, ArrayRaySource{o, d, tmin, tmax}, ArrayHitSink{hits}, wc,
+    warp_walk<false, false>(sv.nodes, sv.tris, (uint32_t)n, cursor, ArrayRaySource{o, d, tmin, tmax}, ArrayHitSink{hits}, wc,
                      sv.plane_magic);
 }
 
@@ -242,7 +331,13 @@ void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t ma
         k_extend<false><<<pblocks(max_count), kBlock, 0, st>>>(sv, la, k);
 }
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st) {
-    k_shade<<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
+    if (sv.nee)
+        k_shade<true><<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
+    else
+        k_shade<false><<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
+}
+void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st) {
+    k_shadow<<<pblocks(max_count), kBlock, 0, st>>>(sv, la, k);
 }
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st) {
     k_resolve<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, inv_spp, rgba, mean);

@@ -106,6 +106,9 @@ class Oracle(_SceneChecker):
         L.oracle_set_camera.argtypes = [P, P, P, P, P]
         L.oracle_set_render.argtypes = [P, C.c_int, C.c_int, C.c_int, C.c_int]
         L.oracle_build.argtypes = [P]
+        L.oracle_set_nee.argtypes = [P, C.c_int]
+        L.oracle_shadow_rays.argtypes = [P]
+        L.oracle_shadow_rays.restype = C.c_uint64
         L.oracle_camera.argtypes = [P, P, P, C.c_float, C.c_int, C.c_int, P]
         L.oracle_render.argtypes = [P] + [C.c_int] * 9 + [P, P, P]
         L.oracle_render.restype = C.c_uint64
@@ -133,7 +136,12 @@ class Oracle(_SceneChecker):
         rgba = np.zeros((H, W), np.uint32)
         rays = self.L.oracle_render(self.h, rank, world, shard_mode, x0, y0, x1, y1, int(brute), threads, _p(s),
                                     _p(mean), _p(rgba))
-        return dict(sum=s, mean=mean, rgba=rgba, rays=int(rays))
+        return dict(sum=s, mean=mean, rgba=rgba, rays=int(rays), shadow_rays=int(self.L.oracle_shadow_rays(self.h)))
+
+    def set_nee(self, on=True):
+        """Next-event estimation mode (light sampling + MIS); off = the reference's estimator."""
+        self.L.oracle_set_nee(self.h, int(on))
+        return self
 
     def primary_hits(self, brute=False, threads=NCPU):
         out = np.empty((self.height, self.width), HIT_DTYPE)
@@ -209,6 +217,9 @@ class Emu(_SceneChecker):
         L.emu_levels.argtypes = [P]
         L.emu_walk_counters.argtypes = [P, P]
         L.emu_force_lbvh.argtypes = [P, C.c_int]
+        L.emu_set_nee.argtypes = [P, C.c_int]
+        L.emu_shadow_rays.argtypes = [P]
+        L.emu_shadow_rays.restype = C.c_uint64
         L.emu_export.argtypes = [P, P, P]
         L.emu_export.restype = C.c_uint32
         L.emu_import.argtypes = [P, P, C.c_uint32, P, C.c_uint32]
@@ -244,7 +255,12 @@ class Emu(_SceneChecker):
         rays = self.L.emu_render(self.h, rank, world, shard_mode, threads, _p(s), _p(mean), _p(rgba))
         wc = np.zeros(2, np.uint64)
         self.L.emu_walk_counters(self.h, _p(wc))
-        return dict(sum=s, mean=mean, rgba=rgba, rays=int(rays), nodes_visited=int(wc[0]), tris_tested=int(wc[1]))
+        return dict(sum=s, mean=mean, rgba=rgba, rays=int(rays), nodes_visited=int(wc[0]), tris_tested=int(wc[1]),
+                    shadow_rays=int(self.L.emu_shadow_rays(self.h)))
+
+    def set_nee(self, on=True):
+        self.L.emu_set_nee(self.h, int(on))
+        return self
 
     def primary_hits(self, threads=NCPU):
         out = np.empty((self.height, self.width), HIT_DTYPE)

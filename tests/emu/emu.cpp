@@ -15,6 +15,7 @@
 
 #include "../../owl_path_tracer_b200/csrc/pt_build.h"
 #include "../../owl_path_tracer_b200/csrc/pt_integrator.h"
+#include "../../owl_path_tracer_b200/csrc/pt_lights.h"
 
 using namespace pt;
 
@@ -25,6 +26,10 @@ struct emu_scene {
     std::vector<MeshInfo> meshes;
     std::vector<uint32_t> texels, env;
     std::vector<Material> mats, mesh_mats;
+    std::vector<LightTri> lights;
+    std::vector<float> light_cdf;
+    int nee = 0;
+    uint64_t shadow_rays = 0;
     std::vector<Node8> nodes;
     std::vector<Tri48> tris;
     float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, max_abs = 0;
@@ -49,6 +54,15 @@ static void refresh_view(emu_scene* s) {
     for (size_t i = 0; i < s->meshes.size(); ++i)
         if (s->meshes[i].material >= 0 && (size_t)s->meshes[i].material < s->mats.size()) s->mesh_mats[i] = s->mats[s->meshes[i].material];
     s->sv.mesh_materials = s->mesh_mats.data();
+    // next-event estimation mode: same table builder as api.cu
+    s->lights.clear();
+    s->light_cdf.clear();
+    for (MeshInfo& mi : s->meshes) mi.light_first = -1;
+    if (s->nee) build_light_table(s->pos, s->idx4, s->meshes, s->mats, s->lights, s->light_cdf);
+    s->sv.lights = s->lights.data();
+    s->sv.light_cdf = s->light_cdf.data();
+    s->sv.n_lights = (int)s->lights.size();
+    s->sv.nee = s->nee;
     s->sv.texels = s->texels.data();
     s->sv.env = s->env.empty() ? nullptr : s->env.data();
     s->sv.n_materials = (int)s->mats.size();
@@ -246,6 +260,8 @@ int emu_build(emu_scene* s) {
 
 int emu_levels(emu_scene* s) { return s->levels; }
 void emu_force_lbvh(emu_scene* s, int on) { s->force_lbvh = on; }
+void emu_set_nee(emu_scene* s, int on) { s->nee = on; }
+uint64_t emu_shadow_rays(emu_scene* s) { return s->shadow_rays; }
 void emu_debug_pixel(emu_scene* s, int px, int py) {
     s->debug_px = px;
     s->debug_py = py;
@@ -324,10 +340,10 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
     }
     memset(sum_out, 0, sizeof(float) * 4 * (size_t)W * H);
     std::atomic<uint64_t> rays{0};
-    std::atomic<uint64_t> cnt_nodes{0}, cnt_tris{0};
+    std::atomic<uint64_t> cnt_nodes{0}, cnt_tris{0}, cnt_shadow{0};
     const int rows = sv.n_lanes / W;
     parallel_rows(rows, nthreads, [&](int row) {
-        uint64_t nr = 0;
+        uint64_t nr = 0, nsh = 0;
         WalkCounters wc{0, 0};
         uint64_t wn = 0, wt = 0;
         for (int c = 0; c < W; ++c) {
@@ -341,7 +357,8 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
             L.sample = 0;
             L.depth = 0;
             L.lobe = LOBE_NONE;
-            f3 sum = mk3(0.0f);
+            f3 sum = mk3(0.0f), gathered = mk3(0.0f);
+            L.prev_pdf = -1.0f;
             if (sv.max_samples > 0 && sv.max_depth > 0) {
                 for (;;) {
                     // state goes through the same packing as the device arrays
@@ -357,8 +374,23 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
                     ++nr;
                     if (s->debug_px == px && s->debug_py == py)
                         printf("DBG %.9g %.9g %.9g %.9g %.9g %.9g %.9g %u\n", L.o.x, L.o.y, L.o.z, L.d.x, L.d.y, L.d.z, h.t, h.tri);
-                    const ShadeResult r = shade_lane(sv, L, h, px, py);
-                    if (L.sample_ended) sum = sum + L.contrib;
+                    const ShadeResult r = sv.nee ? shade_lane<true>(sv, L, h, px, py) : shade_lane<false>(sv, L, h, px, py);
+                    if (sv.nee) {
+                        // k_shadow: the light sample counts when nothing lies between the vertex and the
+                        // light; k_shade / k_shadow: a finished sample is gathered radiance + last term
+                        if (L.sh_valid) {
+                            Hit blocker;
+                            walk_closest<false>(sv.nodes, sv.tris, L.sh_o, L.sh_d, kTMin, L.sh_tmax, blocker, nullptr);
+                            ++nsh;
+                            if (blocker.tri == kNoHit) gathered = gathered + L.sh_c;
+                        }
+                        if (L.sample_ended) {
+                            sum = sum + (gathered + L.contrib);
+                            gathered = mk3(0.0f);
+                        }
+                    } else if (L.sample_ended) {
+                        sum = sum + L.contrib;
+                    }
                     if (r == LANE_DONE) break;
                 }
             }
@@ -368,9 +400,11 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
             o[2] = sum.z;
         }
         rays += nr;
+        cnt_shadow += nsh;
         cnt_nodes += wn;
         cnt_tris += wt;
     });
+    s->shadow_rays = cnt_shadow.load();
     s->walk_nodes = cnt_nodes.load();
     s->walk_tris = cnt_tris.load();
     if (mean_out || rgba_out) {

@@ -44,6 +44,26 @@ if __name__ == "__main__":
         timing("dragon", 1920, 1080, 32, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
         timing("car", 1920, 1080, 32, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "nee":
+        # NEE mode: throughput with the shadow kernel, and error at equal spp / equal time against a long render
+        for scene, w, h, spp in (("cornell-box", 512, 512, 64), ("car", 1920, 1080, 32), ("dragon", 1920, 1080, 32)):
+            sc = pt.Scene(scene=scene, width=w, height=h, spp=spp, depth=8, env="color", env_intensity=0.0)
+            res = {}
+            for tag, fl in (("ref", pt.FLAG_TIMING), ("nee", pt.FLAG_TIMING | pt.FLAG_NEE)):
+                ctx = pt.Context(flags=fl); ctx.bind(sc); ctx.render(); ctx.render()
+                st = ctx.stats(); res[tag] = (st, ctx.framebuffer_f32()[..., :3].copy()); ctx.close()
+            scl = pt.Scene(scene=scene, width=w, height=h, spp=spp * 16, depth=8, env="color", env_intensity=0.0)
+            ctx = pt.Context(flags=pt.FLAG_NEE); ctx.bind(scl); ctx.render(); truth = ctx.framebuffer_f32()[..., :3].copy(); ctx.close()
+            out = dict(scene=scene, size=[w, h], spp=spp)
+            for tag in ("ref", "nee"):
+                st, img = res[tag]
+                out[tag] = dict(render_ms=st['render_ms'], extend_ms=st['extend_ms'], shade_ms=st['shade_ms'], shadow_ms=st['shadow_ms'],
+                                rays=st['rays'], shadow_rays=st['shadow_rays'], n_lights=st['n_lights'],
+                                mrays_incl_shadow=(st['rays'] + st['shadow_rays']) / st['render_ms'] * 1e-3,
+                                relmse_vs_16x_nee=rel_mse(img, truth), mean=float(img.mean()))
+            out["truth_mean"] = float(truth.mean())
+            print(json.dumps(out), flush=True)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "timing":
         timing("cornell-box", 512, 512, 64, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
         timing("dragon", 1920, 1080, 16, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
