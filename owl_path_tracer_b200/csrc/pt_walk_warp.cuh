@@ -24,6 +24,9 @@ namespace pt {
 #ifndef PT_TRI_VOTE
 #define PT_TRI_VOTE 3        // triangle phase when PT_TRI_VOTE * (lanes with triangles) >= working lanes
 #endif
+#ifndef PT_TRI_LOOP
+#define PT_TRI_LOOP 1        // stay in the triangle phase while the vote still holds (skips the loop head per triangle)
+#endif
 #ifndef PT_PREFETCH_TRI
 #define PT_PREFETCH_TRI 0    // prefetch.global.L1 of the first leaf triangle at the end of a node step
 #endif
@@ -141,7 +144,12 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         const bool tri_phase = PT_TRI_VOTE * n_tri >= __popc(act);
 
         if (tri_phase) {
-            if (want_tri) {
+#if PT_TRI_LOOP
+            const int n_act = __popc(act);
+            bool again;
+            do {
+#endif
+            if (has_ray && tg_mask != 0) {
                 const int bit = 31 - __clz(tg_mask);
                 tg_mask &= ~(1u << bit);
                 const Tri48* tp = tris + (tg_base + (uint32_t)bit);
@@ -172,6 +180,11 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
                     }
                 }
             }
+#if PT_TRI_LOOP
+            // same vote as above, without the trip through the loop head (no lane gains work in here)
+            again = PT_TRI_VOTE * __popc(__ballot_sync(FULL, has_ray && tg_mask != 0)) >= n_act;
+            } while (again);
+#endif
         } else if (can_node) {
             if (tg_mask != 0) {  // lost the vote: keep the leaf triangles for later
                 PT_PUSH(tg_base, tg_mask);
