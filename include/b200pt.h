@@ -67,7 +67,11 @@ typedef struct b200pt_config {
                                      (its light sampling, lights.hpp + visibiliy_test device.cu:97-110, is
                                      dead code): an opt-in mode with the same mode in the oracle.      */
 #define B200PT_FLAG_TIMING     4  /* CUDA events around every extend / shade launch
-                                     (fills extend_ms / shade_ms in b200pt_stats)   */
+                                     (fills extend_ms / shade_ms in b200pt_stats).  Also keeps
+                                     the frame on ONE stream: without this flag frames of
+                                     >= 2^18 lanes are rendered as two interleaved sub-frames
+                                     on two streams (same result bit for bit, ~1-6 % faster),
+                                     whose kernels overlap and cannot be timed one by one. */
 
 /* material_data, device_global.hpp:19-36 — 17 floats, 68 bytes, same order. */
 typedef struct b200pt_material {

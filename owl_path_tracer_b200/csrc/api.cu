@@ -27,6 +27,13 @@ struct b200pt_ctx {
     b200pt_config cfg{};
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // parts of the frame walked concurrently (render_local); part 0 runs on `stream`
+    cudaStream_t part_stream[kMaxParts] = {};
+    cudaEvent_t part_done[kMaxParts] = {};
+    LaneArrays part[kMaxParts];
+    int n_parts = 0;              // parts the lane arrays are currently laid out for
+    int lanes_width = 0;          // frame width they were sized for
+    uint32_t* h_counts = nullptr; // pinned: kMaxParts x (kBatch + 1 queue lengths, kBatch shadow counts)
     uint32_t* d_cursor = nullptr;  // ray-fetch cursor of the parity-hook kernels
     // host staging of the flattened scene (kept: parity hooks map triangle ids back)
     std::vector<f4> h_pos, h_nrm;
@@ -75,18 +82,23 @@ struct b200pt_ctx {
 };
 
 static void free_lanes(b200pt_ctx* c) {
-    for (int b = 0; b < 2; ++b) {
-        cudaFree(c->la.ray_o[b]); cudaFree(c->la.ray_d[b]); cudaFree(c->la.thr[b]);
+    for (int p = 0; p < kMaxParts; ++p) {
+        LaneArrays& L = c->part[p];
+        for (int b = 0; b < 2; ++b) {
+            cudaFree(L.ray_o[b]); cudaFree(L.ray_d[b]); cudaFree(L.thr[b]); cudaFree(L.queue[b]);
+        }
+        cudaFree(L.hit);
+        cudaFree(L.sh_o); cudaFree(L.sh_d); cudaFree(L.sh_c); cudaFree(L.sh_f);
+        cudaFree(L.sh_counts); cudaFree(L.sh_cursor);
+        cudaFree(L.counts); cudaFree(L.cursor);
+        L = LaneArrays{};  // sum, rad, walk_counters are aliases of c->la's
     }
-    cudaFree(c->la.sum); cudaFree(c->la.hit);
-    cudaFree(c->la.rad); cudaFree(c->la.sh_o); cudaFree(c->la.sh_d); cudaFree(c->la.sh_c); cudaFree(c->la.sh_f);
-    cudaFree(c->la.sh_counts); cudaFree(c->la.sh_cursor);
-    cudaFree(c->la.queue[0]); cudaFree(c->la.queue[1]); cudaFree(c->la.counts); cudaFree(c->la.cursor);
-    cudaFree(c->la.walk_counters);
+    cudaFree(c->la.sum); cudaFree(c->la.rad); cudaFree(c->la.walk_counters);
     cudaFree(c->d_frame); cudaFree(c->d_rgba); cudaFree(c->d_mean);
     if (c->h_rgba) cudaFreeHost(c->h_rgba);
     if (c->h_mean) cudaFreeHost(c->h_mean);
     c->la = LaneArrays{};
+    c->n_parts = 0;
     c->d_frame = nullptr; c->d_rgba = nullptr; c->d_mean = nullptr; c->h_rgba = nullptr; c->h_mean = nullptr;
     c->fb_pixels = 0;
 }
@@ -174,6 +186,10 @@ extern "C" int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
     CU(cudaMalloc(&c->d_cursor, sizeof(uint32_t)));
+    c->part_stream[0] = c->stream;
+    for (int p = 1; p < kMaxParts; ++p) CU(cudaStreamCreateWithFlags(&c->part_stream[p], cudaStreamNonBlocking));
+    for (int p = 0; p < kMaxParts; ++p) CU(cudaEventCreateWithFlags(&c->part_done[p], cudaEventDisableTiming));
+    CU(cudaMallocHost(&c->h_counts, sizeof(uint32_t) * kMaxParts * (2 * kBatch + 1)));
     set_persistent_blocks(prop.multiProcessorCount);
     *out = c;
     return B200PT_OK;
@@ -182,7 +198,7 @@ extern "C" int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
 extern "C" int b200pt_destroy(b200pt_ctx* c) {
     if (!c) return B200PT_OK;
     cudaSetDevice(c->cfg.device_ordinal);
-    cudaStreamSynchronize(c->stream);
+    cudaDeviceSynchronize();
     free_lanes(c);
     free_scene(c);
     cudaFree(c->d_env);
@@ -194,6 +210,9 @@ extern "C" int b200pt_destroy(b200pt_ctx* c) {
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
+    for (int p = 1; p < kMaxParts; ++p) cudaStreamDestroy(c->part_stream[p]);
+    for (int p = 0; p < kMaxParts; ++p) cudaEventDestroy(c->part_done[p]);
+    cudaFreeHost(c->h_counts);
     cudaStreamDestroy(c->stream);
     delete c;
     return B200PT_OK;
@@ -400,41 +419,72 @@ static int sync_mesh_materials(b200pt_ctx* c) {
     return B200PT_OK;
 }
 
-static int ensure_lanes(b200pt_ctx* c, const SceneView& sv) {
+// Parts: the rank's lanes are split into `parts` interleaved sub-frames (rows r = p mod parts), each with its
+// own compact state, queues and stream.  Every launch of the persistent walker ends with a tail in which a few
+// long rays keep a few warps busy (sm__cycles_active was 91 % of elapsed with one stream); with two independent
+// sub-frames the other part's kernels fill the SMs the tail leaves idle.  B200PT_FLAG_TIMING keeps one part so
+// that the per-kernel event times stay clean; B200PT_PARTS overrides (development).
+static int choose_parts(const b200pt_ctx* c, const SceneView& sv) {
+    int parts = 2;
+    if (const char* e = getenv("B200PT_PARTS")) parts = atoi(e);
+    else if (c->cfg.flags & B200PT_FLAG_TIMING) parts = 1;
+    const int rows = sv.width > 0 ? sv.n_lanes / sv.width : 0;
+    if (sv.n_lanes < (1 << 18)) parts = getenv("B200PT_PARTS") ? parts : 1;  // small frames: launch-bound already
+    return std::max(1, std::min({parts, kMaxParts, std::max(rows, 1)}));
+}
+static uint32_t part_lanes(const SceneView& sv, int p, int parts) {
+    const int rows = sv.width > 0 ? sv.n_lanes / sv.width : 0;
+    const int mine = rows > p ? (rows - p + parts - 1) / parts : 0;
+    return (uint32_t)mine * (uint32_t)sv.width;
+}
+
+static int ensure_lanes(b200pt_ctx* c, const SceneView& sv, int parts) {
     const size_t px = (size_t)c->width * c->height;
     const uint32_t need = (uint32_t)std::max(sv.n_lanes, 1);
-    if (c->la.capacity < need || c->fb_pixels != px) {
-        CU(cudaStreamSynchronize(c->stream));
+    if (c->la.capacity < need || c->fb_pixels != px || c->n_parts != parts || c->lanes_width != c->width) {
+        CU(cudaDeviceSynchronize());
         free_lanes(c);
-        const size_t padded = (size_t)need + 256;  // k_shade loads entry i before it knows the queue length
-        for (int b = 0; b < 2; ++b) {
-            CU(cudaMalloc(&c->la.ray_o[b], sizeof(f4) * padded));
-            CU(cudaMalloc(&c->la.ray_d[b], sizeof(f4) * padded));
-            CU(cudaMalloc(&c->la.thr[b], sizeof(f4) * padded));
-            CU(cudaMalloc(&c->la.queue[b], sizeof(uint32_t) * padded));
-            CU(cudaMemsetAsync(c->la.queue[b], 0, sizeof(uint32_t) * padded, c->stream));
-        }
-        CU(cudaMalloc(&c->la.sum, sizeof(f4) * padded));
-        CU(cudaMalloc(&c->la.hit, sizeof(f4) * padded));
-        if (c->cfg.flags & B200PT_FLAG_NEE) {
-            CU(cudaMalloc(&c->la.rad, sizeof(f4) * padded));
-            CU(cudaMalloc(&c->la.sh_o, sizeof(f4) * padded));
-            CU(cudaMalloc(&c->la.sh_d, sizeof(f4) * padded));
-            CU(cudaMalloc(&c->la.sh_c, sizeof(f4) * padded));
-            CU(cudaMalloc(&c->la.sh_f, sizeof(f4) * padded));
-            CU(cudaMalloc(&c->la.sh_counts, sizeof(uint32_t) * kBatch));
-            CU(cudaMalloc(&c->la.sh_cursor, sizeof(uint32_t) * kBatch));
-        }
-        CU(cudaMalloc(&c->la.counts, sizeof(uint32_t) * (kBatch + 1)));
-        CU(cudaMalloc(&c->la.cursor, sizeof(uint32_t) * kBatch));
+        const bool nee = (c->cfg.flags & B200PT_FLAG_NEE) != 0;
+        CU(cudaMalloc(&c->la.sum, sizeof(f4) * need));
+        if (nee) CU(cudaMalloc(&c->la.rad, sizeof(f4) * need));
         CU(cudaMalloc(&c->la.walk_counters, sizeof(unsigned long long) * 2));
+        for (int p = 0; p < parts; ++p) {
+            LaneArrays& L = c->part[p];
+            // + 256: k_shade loads entry i before it knows the queue length
+            const size_t padded = (size_t)(need + parts - 1) / parts + (size_t)c->width + 256;
+            for (int b = 0; b < 2; ++b) {
+                CU(cudaMalloc(&L.ray_o[b], sizeof(f4) * padded));
+                CU(cudaMalloc(&L.ray_d[b], sizeof(f4) * padded));
+                CU(cudaMalloc(&L.thr[b], sizeof(f4) * padded));
+                CU(cudaMalloc(&L.queue[b], sizeof(uint32_t) * padded));
+                CU(cudaMemsetAsync(L.queue[b], 0, sizeof(uint32_t) * padded, c->stream));
+            }
+            CU(cudaMalloc(&L.hit, sizeof(f4) * padded));
+            if (nee) {
+                CU(cudaMalloc(&L.sh_o, sizeof(f4) * padded));
+                CU(cudaMalloc(&L.sh_d, sizeof(f4) * padded));
+                CU(cudaMalloc(&L.sh_c, sizeof(f4) * padded));
+                CU(cudaMalloc(&L.sh_f, sizeof(f4) * padded));
+                CU(cudaMalloc(&L.sh_counts, sizeof(uint32_t) * kBatch));
+                CU(cudaMalloc(&L.sh_cursor, sizeof(uint32_t) * kBatch));
+            }
+            CU(cudaMalloc(&L.counts, sizeof(uint32_t) * (kBatch + 1)));
+            CU(cudaMalloc(&L.cursor, sizeof(uint32_t) * kBatch));
+            L.sum = c->la.sum;
+            L.rad = c->la.rad;
+            L.walk_counters = c->la.walk_counters;
+            L.capacity = (uint32_t)padded;
+        }
         c->la.capacity = need;
+        c->n_parts = parts;
+        c->lanes_width = c->width;
         if (c->cfg.world_size > 1 && c->cfg.shard_mode == B200PT_SHARD_ROWS) CU(cudaMalloc(&c->d_frame, sizeof(f4) * px));
         CU(cudaMalloc(&c->d_rgba, sizeof(uint32_t) * px));
         CU(cudaMalloc(&c->d_mean, sizeof(f4) * px));
         CU(cudaMallocHost(&c->h_rgba, sizeof(uint32_t) * px));
         CU(cudaMallocHost(&c->h_mean, sizeof(float) * 4 * px));
         c->fb_pixels = px;
+        CU(cudaStreamSynchronize(c->stream));
     }
     return B200PT_OK;
 }
@@ -451,9 +501,10 @@ static int render_local(b200pt_ctx* c) {
     CU(cudaSetDevice(c->cfg.device_ordinal));
     if (int r = sync_mesh_materials(c)) return r;
     const SceneView sv = make_view(c, false);
-    if (int r = ensure_lanes(c, sv)) return r;
+    const int parts = choose_parts(c, sv);
+    if (int r = ensure_lanes(c, sv, parts)) return r;
     const bool count = (c->cfg.flags & B200PT_FLAG_COUNTERS) != 0;
-    const bool timing = (c->cfg.flags & B200PT_FLAG_TIMING) != 0;
+    const bool timing = (c->cfg.flags & B200PT_FLAG_TIMING) != 0 && parts == 1;
     const bool nee = sv.nee != 0;
     const int ev_per_iter = nee ? 3 : 2;  // extend | shade [| shadow]
     cudaStream_t st = c->stream;
@@ -463,22 +514,29 @@ static int render_local(b200pt_ctx* c) {
     S.shadow_rays = 0;
     S.shadow_ms = 0;
 
-    CU(cudaEventRecord(c->ev0, st));
-    CU(cudaMemsetAsync(c->la.counts, 0, sizeof(uint32_t) * (kBatch + 1), st));
-    CU(cudaMemsetAsync(c->la.cursor, 0, sizeof(uint32_t) * kBatch, st));
     CU(cudaMemsetAsync(c->la.walk_counters, 0, sizeof(unsigned long long) * 2, st));
-    if (nee) {
-        CU(cudaMemsetAsync(c->la.sh_counts, 0, sizeof(uint32_t) * kBatch, st));
-        CU(cudaMemsetAsync(c->la.sh_cursor, 0, sizeof(uint32_t) * kBatch, st));
-    }
-    uint32_t active = 0;
-    if (sv.n_lanes > 0 && sv.max_samples > 0 && sv.max_depth > 0) {
-        launch_init_lanes(sv, c->la, st);
-        S.kernel_launches++;
-        active = (uint32_t)sv.n_lanes;
-        CU(cudaMemcpyAsync(c->la.counts, &active, sizeof active, cudaMemcpyHostToDevice, st));
-    } else {
-        CU(cudaMemsetAsync(c->la.sum, 0, sizeof(f4) * c->la.capacity, st));
+    CU(cudaEventRecord(c->ev0, st));  // the other parts' streams start behind this point
+    uint32_t active[kMaxParts] = {};
+    const bool any_work = sv.n_lanes > 0 && sv.max_samples > 0 && sv.max_depth > 0;
+    if (!any_work) CU(cudaMemsetAsync(c->la.sum, 0, sizeof(f4) * c->la.capacity, st));
+    for (int p = 1; p < parts; ++p) CU(cudaStreamWaitEvent(c->part_stream[p], c->ev0, 0));
+    for (int p = 0; p < parts; ++p) {
+        const LaneArrays& L = c->part[p];
+        cudaStream_t ps = c->part_stream[p];
+        CU(cudaMemsetAsync(L.counts, 0, sizeof(uint32_t) * (kBatch + 1), ps));
+        CU(cudaMemsetAsync(L.cursor, 0, sizeof(uint32_t) * kBatch, ps));
+        if (nee) {
+            CU(cudaMemsetAsync(L.sh_counts, 0, sizeof(uint32_t) * kBatch, ps));
+            CU(cudaMemsetAsync(L.sh_cursor, 0, sizeof(uint32_t) * kBatch, ps));
+        }
+        const uint32_t n_part = any_work ? part_lanes(sv, p, parts) : 0;
+        if (n_part) {
+            launch_init_lanes(sv, L, p, parts, n_part, ps);
+            S.kernel_launches++;
+            active[p] = n_part;
+            c->h_counts[p * (2 * kBatch + 1)] = n_part;  // pinned: stays valid until the copy ran
+            CU(cudaMemcpyAsync(L.counts, &c->h_counts[p * (2 * kBatch + 1)], sizeof(uint32_t), cudaMemcpyHostToDevice, ps));
+        }
     }
     if (timing) {
         while (c->ev_pool.size() < (size_t)(3 * kBatch + 1)) {
@@ -487,38 +545,58 @@ static int render_local(b200pt_ctx* c) {
             c->ev_pool.push_back(e);
         }
     }
-    uint32_t h_counts[kBatch + 1];
-    uint32_t h_shadow[kBatch] = {};
-    while (active > 0) {
+    auto any_active = [&] {
+        for (int p = 0; p < parts; ++p)
+            if (active[p]) return true;
+        return false;
+    };
+    while (any_active()) {
+        // the parts' launches are interleaved so that neither stream runs ahead of the other in the queue
         for (int k = 0; k < kBatch; ++k) {
-            if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k], st));
-            launch_extend(sv, c->la, k, active, count, st);
-            if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 1], st));
-            launch_shade(sv, c->la, k, active, st);
-            if (nee) {
-                // the shadow rays this iteration's vertices asked for: any-hit walk, then the gated add
-                if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 2], st));
-                launch_shadow(sv, c->la, k, active, st);
+            for (int p = 0; p < parts; ++p) {
+                if (!active[p]) continue;
+                const LaneArrays& L = c->part[p];
+                cudaStream_t ps = c->part_stream[p];
+                if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k], ps));
+                launch_extend(sv, L, k, active[p], count, ps);
+                if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 1], ps));
+                launch_shade(sv, L, k, active[p], ps);
+                if (nee) {
+                    // the shadow rays this iteration's vertices asked for: any-hit walk, then the gated add
+                    if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 2], ps));
+                    launch_shadow(sv, L, k, active[p], ps);
+                }
+                S.kernel_launches += (uint64_t)ev_per_iter;
             }
         }
         if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * kBatch], st));
-        S.kernel_launches += (uint64_t)ev_per_iter * kBatch;
         CU(cudaGetLastError());
-        CU(cudaMemcpyAsync(h_counts, c->la.counts, sizeof h_counts, cudaMemcpyDeviceToHost, st));
-        if (nee) {
-            CU(cudaMemcpyAsync(h_shadow, c->la.sh_counts, sizeof h_shadow, cudaMemcpyDeviceToHost, st));
-            CU(cudaMemsetAsync(c->la.sh_counts, 0, sizeof(uint32_t) * kBatch, st));
-            CU(cudaMemsetAsync(c->la.sh_cursor, 0, sizeof(uint32_t) * kBatch, st));
+        for (int p = 0; p < parts; ++p) {
+            if (!active[p]) continue;
+            const LaneArrays& L = c->part[p];
+            cudaStream_t ps = c->part_stream[p];
+            uint32_t* hc = c->h_counts + p * (2 * kBatch + 1);
+            CU(cudaMemcpyAsync(hc, L.counts, sizeof(uint32_t) * (kBatch + 1), cudaMemcpyDeviceToHost, ps));
+            // next batch starts from the last queue length; the other slots go back to zero
+            CU(cudaMemcpyAsync(L.counts, L.counts + kBatch, sizeof(uint32_t), cudaMemcpyDeviceToDevice, ps));
+            CU(cudaMemsetAsync(L.counts + 1, 0, sizeof(uint32_t) * kBatch, ps));
+            CU(cudaMemsetAsync(L.cursor, 0, sizeof(uint32_t) * kBatch, ps));
+            if (nee) {
+                CU(cudaMemcpyAsync(hc + kBatch + 1, L.sh_counts, sizeof(uint32_t) * kBatch, cudaMemcpyDeviceToHost, ps));
+                CU(cudaMemsetAsync(L.sh_counts, 0, sizeof(uint32_t) * kBatch, ps));
+                CU(cudaMemsetAsync(L.sh_cursor, 0, sizeof(uint32_t) * kBatch, ps));
+            }
         }
-        // next batch starts from the last queue length; the other slots go back to zero
-        CU(cudaMemcpyAsync(c->la.counts, c->la.counts + kBatch, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
-        CU(cudaMemsetAsync(c->la.counts + 1, 0, sizeof(uint32_t) * kBatch, st));
-        CU(cudaMemsetAsync(c->la.cursor, 0, sizeof(uint32_t) * kBatch, st));
-        CU(cudaStreamSynchronize(st));
-        for (int k = 0; k < kBatch; ++k) {
-            S.rays += h_counts[k];
-            S.shadow_rays += h_shadow[k];
-            if (h_counts[k]) S.iterations++;
+        for (int p = 0; p < parts; ++p) {
+            if (!active[p]) continue;
+            CU(cudaStreamSynchronize(c->part_stream[p]));
+            const uint32_t* hc = c->h_counts + p * (2 * kBatch + 1);
+            for (int k = 0; k < kBatch; ++k) {
+                S.rays += hc[k];
+                if (nee) S.shadow_rays += hc[kBatch + 1 + k];
+                if (p == 0 && hc[k]) S.iterations++;
+            }
+            active[p] = hc[kBatch];
         }
         if (timing) {
             for (int k = 0; k < kBatch; ++k) {
@@ -531,7 +609,10 @@ static int render_local(b200pt_ctx* c) {
                 S.shadow_ms += s;
             }
         }
-        active = h_counts[kBatch];
+    }
+    for (int p = 1; p < parts; ++p) {  // the frame is complete on `stream` once every part is
+        CU(cudaEventRecord(c->part_done[p], c->part_stream[p]));
+        CU(cudaStreamWaitEvent(st, c->part_done[p], 0));
     }
     if (c->d_frame) {  // ROWS sharding: lane sums -> full frame, zeros elsewhere
         CU(cudaMemsetAsync(c->d_frame, 0, sizeof(f4) * c->fb_pixels, st));

@@ -47,10 +47,11 @@ struct LaneArrays {
     uint32_t capacity = 0;
 };
 
+constexpr int kMaxParts = 4;  // interleaved sub-frames walked on separate streams (api.cu: render_local)
 constexpr int kBatch = 32;  // wavefront iterations between host checks (even: the state sets alternate with k)
 
 // launch wrappers (wavefront.cu)
-void launch_init_lanes(const SceneView& sv, const LaneArrays& la, cudaStream_t st);
+void launch_init_lanes(const SceneView& sv, const LaneArrays& la, int part, int parts, uint32_t n_part, cudaStream_t st);
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st);
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);

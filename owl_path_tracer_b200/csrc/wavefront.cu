@@ -32,20 +32,26 @@ __device__ __forceinline__ f4 ld4(const f4* p) {
 }
 __device__ __forceinline__ void st4(f4* p, f4 v) { *reinterpret_cast<float4*>(p) = make_float4(v.x, v.y, v.z, v.w); }
 
-__global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays la) {
-    const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
-    if (lane >= (uint32_t)sv.n_lanes) return;
+// Part `part` of `parts` owns the rows r = part (mod parts) of the rank's lanes; its state arrays are indexed
+// by the position inside the part.  (parts > 1: the frame is walked as independent interleaved sub-frames on
+// separate streams so that the tail of one part's kernel overlaps the other part's work; `sum` / `rad` are
+// shared and addressed by lane.)
+__global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays la, int part, int parts, uint32_t n_part) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_part) return;
+    const uint32_t w = (uint32_t)sv.width;
+    const uint32_t lane = ((i / w) * (uint32_t)parts + (uint32_t)part) * w + i % w;
     int px, py;
     lane_pixel(sv, lane, px, py);
     uint32_t rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset));  // device.cu:226
     f3 o, d;
     camera_ray(sv, px, py, rng, o, d);
-    st4(la.ray_o[0] + lane, f4{o.x, o.y, o.z, -1.0f});  // .w: prev_pdf of the NEE mode (camera ray: count emitters fully)
+    st4(la.ray_o[0] + i, f4{o.x, o.y, o.z, -1.0f});  // .w: prev_pdf of the NEE mode (camera ray: count emitters fully)
     if (la.rad) st4(la.rad + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
-    st4(la.ray_d[0] + lane, f4{d.x, d.y, d.z, u2f(pack_ctl(0, 0, LOBE_NONE))});
-    st4(la.thr[0] + lane, f4{1.0f, 1.0f, 1.0f, u2f(rng)});
+    st4(la.ray_d[0] + i, f4{d.x, d.y, d.z, u2f(pack_ctl(0, 0, LOBE_NONE))});
+    st4(la.thr[0] + i, f4{1.0f, 1.0f, 1.0f, u2f(rng)});
     st4(la.sum + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
-    la.queue[0][lane] = lane;
+    la.queue[0][i] = lane;
 }
 
 struct LaneRaySource {   // entry i of the current state set
@@ -321,8 +327,8 @@ static int g_persistent_blocks = 148 * PT_BLOCKS_PER_SM;
 void set_persistent_blocks(int sm_count) { g_persistent_blocks = sm_count * PT_BLOCKS_PER_SM; }
 static inline unsigned pblocks(uint32_t n) { return std::min<unsigned>(blocks(n, kBlock), (unsigned)g_persistent_blocks); }
 
-void launch_init_lanes(const SceneView& sv, const LaneArrays& la, cudaStream_t st) {
-    k_init_lanes<<<blocks(sv.n_lanes, kBlock), kBlock, 0, st>>>(sv, la);
+void launch_init_lanes(const SceneView& sv, const LaneArrays& la, int part, int parts, uint32_t n_part, cudaStream_t st) {
+    k_init_lanes<<<blocks(n_part, kBlock), kBlock, 0, st>>>(sv, la, part, parts, n_part);
 }
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st) {
     if (count)

@@ -44,6 +44,19 @@ if __name__ == "__main__":
         timing("dragon", 1920, 1080, 32, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
         timing("car", 1920, 1080, 32, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "parts":
+        # concurrent sub-frames: frame time without per-kernel events, for B200PT_PARTS = 1..4
+        for scene, spp in (("dragon", 32), ("car", 32), ("dragon", 128)):
+            for parts in ("1", "2", "3", "4"):
+                os.environ["B200PT_PARTS"] = parts
+                sc = pt.Scene(scene=scene, width=1920, height=1080, spp=spp, depth=8, env="color", env_intensity=0.0)
+                ctx = pt.Context(flags=0); ctx.bind(sc); ctx.render(); ctx.render()
+                st = ctx.stats()
+                print(json.dumps(dict(scene=scene, spp=spp, parts=int(parts), render_ms=st['render_ms'],
+                                      mrays=st['rays'] / st['render_ms'] * 1e-3, rays=st['rays'], launches=st['kernel_launches'])), flush=True)
+                ctx.close()
+        os.environ.pop("B200PT_PARTS", None)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "nee":
         # NEE mode: throughput with the shadow kernel, and error at equal spp / equal time against a long render
         for scene, w, h, spp in (("cornell-box", 512, 512, 64), ("car", 1920, 1080, 32), ("dragon", 1920, 1080, 32)):
