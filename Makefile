@@ -41,7 +41,7 @@ oracle:
 
 emu: tests/emu/libemu.so
 tests/emu/libemu.so: tests/emu/emu.cpp $(CUHDR)
-	$(CXX) -std=c++17 -O2 -fPIC -shared -ffp-contract=off -fno-fast-math -Wall -Wno-unused-function -Wno-unknown-pragmas -pthread -o $@ $<
+	$(CXX) -std=c++17 -O2 -fPIC -shared -ffp-contract=off -mfma -fno-fast-math -Wall -Wno-unused-function -Wno-unknown-pragmas -pthread -o $@ $<
 
 clean:
 	rm -rf $(LIB) $(BIN) tests/emu/libemu.so

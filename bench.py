@@ -237,7 +237,9 @@ def main():
         traffic = None
         tf = REPO / "profiles" / "extend_traffic.json"
         if tf.exists():
-            traffic = json.loads(tf.read_text()).get("dram_bytes_per_launch")
+            # ncu's capture is a full-queue launch; scaled per ray to the average launch of the timing pass
+            per_ray = json.loads(tf.read_text()).get("dram_bytes_per_ray")
+            traffic = per_ray * rank0_rays / max(1, launches_extend) if per_ray else None
         roof = dict(bound="hbm", kernel="k_extend", achieved=achieved, peak=peak, unit="GB/s", frac=(achieved / peak) if achieved else None,
                     traffic=traffic, peak_source=peak_src, bytes_per_ray=bytes_per_ray, nodes_per_ray=npr, tris_per_ray=tpr,
                     avg_launch_ms=kt["extend_ms"] / max(1, launches_extend), launches=launches_extend,

@@ -539,19 +539,24 @@ struct Scene {
 };
 
 // Moller-Trumbore.  This expression order is the parity contract with the GPU
-// (owl_path_tracer_b200/csrc/pt_bvh8.h ray_triangle).
+// (owl_path_tracer_b200/csrc/pt_bvh8.h ray_triangle): products accumulated with explicit fused
+// multiply-adds, one IEEE rounding each (std::fmaf is exact on every host, with or without FMA hardware).
+inline float dot_fma(V3 a, V3 b) { return std::fmaf(a.z, b.z, std::fmaf(a.y, b.y, a.x * b.x)); }
+inline V3 cross_fma(V3 a, V3 b) {
+    return V3{std::fmaf(a.y, b.z, -(a.z * b.y)), std::fmaf(a.z, b.x, -(a.x * b.z)), std::fmaf(a.x, b.y, -(a.y * b.x))};
+}
 inline bool ray_triangle(V3 o, V3 d, const TriRef& tr, float tmin, float tmax, float& t, float& u, float& v) {
-    V3 p = cross(d, tr.e2);
-    float det = dot(tr.e1, p);
+    V3 p = cross_fma(d, tr.e2);
+    float det = dot_fma(tr.e1, p);
     if (!(det != 0.0f)) return false;
     float inv = 1.0f / det;
     V3 s = sub(o, tr.v0);
-    float uu = dot(s, p) * inv;
+    float uu = dot_fma(s, p) * inv;
     if (!(uu >= 0.0f && uu <= 1.0f)) return false;
-    V3 q = cross(s, tr.e1);
-    float vv = dot(d, q) * inv;
+    V3 q = cross_fma(s, tr.e1);
+    float vv = dot_fma(d, q) * inv;
     if (!(vv >= 0.0f && uu + vv <= 1.0f)) return false;
-    float tt = dot(tr.e2, q) * inv;
+    float tt = dot_fma(tr.e2, q) * inv;
     if (!(tt > tmin && tt < tmax)) return false;
     t = tt;
     u = uu;

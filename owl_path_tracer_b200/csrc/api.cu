@@ -750,10 +750,18 @@ extern "C" int b200pt_trace(b200pt_ctx* c, const float* origins, const float* di
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_d, dirs, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, c->stream);
     if (e == cudaSuccess) {
         cudaMemsetAsync(c->d_cursor, 0, sizeof(uint32_t), c->stream);
+        cudaEventRecord(c->ev0, c->stream);
         launch_trace(sv, d_o, d_d, n, tmin, tmax, d_hits, c->d_cursor, c->stream);
+        cudaEventRecord(c->ev1, c->stream);
         e = cudaMemcpyAsync(raw.data(), d_hits, sizeof(f4) * (size_t)n, cudaMemcpyDeviceToHost, c->stream);
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) {  // stats: device time of the walk kernel alone, rays = n
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+        c->stats.render_ms = ms;
+        c->stats.rays = (uint64_t)n;
+    }
     cudaFree(d_o); cudaFree(d_d); cudaFree(d_hits);
     if (e != cudaSuccess) return fail(B200PT_ERR_CUDA, std::string("trace: ") + cudaGetErrorString(e));
     hits_to_records(c, raw, tmax, out);

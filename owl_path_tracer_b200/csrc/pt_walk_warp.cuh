@@ -157,14 +157,14 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
                 if (COUNT) wc.tris++;
                 // ray_triangle of pt_bvh8.h, same expression order, conditions evaluated together
                 const f3 v0{a.x, a.y, a.z}, e1{b.x, b.y, b.z}, e2{c.x, c.y, c.z};
-                const f3 p = cross(d, e2);
-                const float det = dot(e1, p);
+                const f3 p = cross_fma(d, e2);
+                const float det = dot_fma(e1, p);
                 const float inv = 1.0f / det;
                 const f3 s = o - v0;
-                const float uu = dot(s, p) * inv;
-                const f3 q = cross(s, e1);
-                const float vv = dot(d, q) * inv;
-                const float tt = dot(e2, q) * inv;
+                const float uu = dot_fma(s, p) * inv;
+                const f3 q = cross_fma(s, e1);
+                const float vv = dot_fma(d, q) * inv;
+                const float tt = dot_fma(e2, q) * inv;
                 const bool ok = (det != 0.0f) && (uu >= 0.0f && uu <= 1.0f) && (vv >= 0.0f && uu + vv <= 1.0f) &&
                                 (tt > tmin && tt < tmax);
                 const uint32_t id = f2u(a.w);
