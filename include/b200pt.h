@@ -61,9 +61,10 @@ typedef struct b200pt_config {
 #define B200PT_FLAG_COUNTERS   1  /* count nodes/triangles visited (slower; for the
                                      roofline's algorithmic bytes)                 */
 #define B200PT_FLAG_HOST_BVH   2  /* reserved                                       */
-#define B200PT_FLAG_NEE        8  /* next-event estimation: light sampling of the emissive triangles with a
-                                     shadow any-hit ray per path vertex, combined with the BSDF-sampled
-                                     emitter hits by the power heuristic.  NOT the reference's estimator
+#define B200PT_FLAG_NEE        8  /* next-event estimation: light sampling of the emissive triangles (by power)
+                                     and of the environment map when one is in use (texels by luminance) with
+                                     a shadow any-hit ray per path vertex, combined with the BSDF-sampled
+                                     emitter hits / misses by the power heuristic.  NOT the reference's estimator
                                      (its light sampling, lights.hpp + visibiliy_test device.cu:97-110, is
                                      dead code): an opt-in mode with the same mode in the oracle.      */
 #define B200PT_FLAG_TIMING     4  /* CUDA events around every extend / shade launch

@@ -534,6 +534,7 @@ struct Scene {
     std::vector<Light> lights;
     std::vector<float> light_cdf;
     std::vector<int> mesh_light_first;
+    std::vector<float> env_cdf_rows, env_cdf_cols;  // NEE mode, environment map in use: luminance cdfs (rows, then columns per row)
     std::atomic<uint64_t> rays{0};
     std::atomic<uint64_t> shadow_rays{0};  // of the last render (NEE mode)
 };
@@ -729,6 +730,65 @@ V3 sample_environment(const Scene& sc, V3 dir) {                                
     return fetch_rgba8(sc.env.data(), sc.env_w, sc.env_h, u, v);
 }
 
+// --- NEE mode, importance sampling of the environment map -------------------------------------
+// P(texel) ~ Rec.709 luminance of the RGBA8 texel; sums in binary64, rounded once per entry.
+void build_env_table(Scene& sc) {
+    sc.env_cdf_rows.clear();
+    sc.env_cdf_cols.clear();
+    if (!sc.nee || !sc.env_use || sc.env.empty()) return;
+    const int w = sc.env_w, h = sc.env_h;
+    sc.env_cdf_rows.resize((size_t)h);
+    sc.env_cdf_cols.resize((size_t)w * (size_t)h);
+    std::vector<double> row_acc((size_t)h), col_acc((size_t)w);
+    double total = 0.0;
+    for (int j = 0; j < h; ++j) {
+        double acc = 0.0;
+        for (int i = 0; i < w; ++i) {
+            const uint32_t p = sc.env[(size_t)j * (size_t)w + (size_t)i];
+            const float r = (float)(p & 0xFFu) / 255.0f, g = (float)((p >> 8) & 0xFFu) / 255.0f, b = (float)((p >> 16) & 0xFFu) / 255.0f;
+            const float lum = 0.2126f * r + 0.7152f * g + 0.0722f * b;
+            acc += (double)lum;
+            col_acc[(size_t)i] = acc;
+        }
+        float* row = sc.env_cdf_cols.data() + (size_t)j * (size_t)w;
+        for (int i = 0; i < w; ++i) row[i] = acc > 0.0 ? (float)(col_acc[(size_t)i] / acc) : (float)(i + 1) / (float)w;
+        row[w - 1] = 1.0f;
+        total += acc;
+        row_acc[(size_t)j] = total;
+    }
+    if (!(total > 0.0)) {
+        sc.env_cdf_rows.clear();
+        sc.env_cdf_cols.clear();
+        return;
+    }
+    for (int j = 0; j < h; ++j) sc.env_cdf_rows[(size_t)j] = (float)(row_acc[(size_t)j] / total);
+    sc.env_cdf_rows[(size_t)h - 1] = 1.0f;
+}
+// density (per solid angle) with which the map sampler produces `dir`: probability of the texel the miss
+// branch reads for dir, over the texel's solid angle (du dv = dlon dlat / 2 pi^2, d omega = cos(lat) dlon dlat)
+float env_pdf(const Scene& sc, V3 dir) {
+    const float u = 0.5f + m_atan2(dir.x, dir.z) / (2.0f * pi);
+    const float v = 0.5f + m_asin(dir.y) / pi;
+    const float fx = floorf(u * (float)sc.env_w), fy = floorf(v * (float)sc.env_h);
+    const int ix = (fx >= 0.0f) ? (fx < (float)sc.env_w ? (int)fx : sc.env_w - 1) : 0;
+    const int iy = (fy >= 0.0f) ? (fy < (float)sc.env_h ? (int)fy : sc.env_h - 1) : 0;
+    const float prow = sc.env_cdf_rows[iy] - (iy ? sc.env_cdf_rows[iy - 1] : 0.0f);
+    const float* row = sc.env_cdf_cols.data() + (size_t)iy * (size_t)sc.env_w;
+    const float pcol = row[ix] - (ix ? row[ix - 1] : 0.0f);
+    const float cl = sqrtf(fmaxf(0.0f, 1.0f - dir.y * dir.y));
+    if (cl < 1e-4f) return 0.0f;
+    return prow * pcol * ((float)sc.env_w * (float)sc.env_h) / (2.0f * pi * pi * cl);
+}
+int cdf_find(const float* cdf, int n, float u) {  // first entry with cdf >= u
+    int lo = 0, hi = n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (u <= cdf[mid]) hi = mid;
+        else lo = mid + 1;
+    }
+    return lo;
+}
+
 typedef Closest (*Finder)(const Scene&, V3, V3, float, float);
 
 // light table of the NEE mode: every triangle of every mesh whose material emits, in mesh order;
@@ -774,7 +834,11 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays,
     int nan_retries = 0;
     // next-event estimation mode: light-sampled radiance gathered along the path, and the density
     // with which the BSDF generated the current ray (<= 0: an emitter it reaches counts fully)
-    const bool nee = sc.nee && !sc.lights.empty();
+    // light sampling draws from the emissive triangles, from the environment map, or (one extra draw) from
+    // either with probability 1/2 when the scene has both
+    const bool tri_l = sc.nee && !sc.lights.empty(), env_l = sc.nee && !sc.env_cdf_rows.empty();
+    const bool nee = tri_l || env_l;
+    const float p_sel = (tri_l && env_l) ? 0.5f : 1.0f;
     V3 gathered = v3(0.0f);
     float prev_pdf = -1.0f;
     for (int depth = 0; depth < sc.max_depth; ++depth) {
@@ -788,6 +852,7 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays,
             else
                 radiance = add(radiance, sc.env_color);
             radiance = scale(radiance, sc.env_intensity);
+            if (env_l && prev_pdf > 0.0f) radiance = scale(radiance, power_heuristic(prev_pdf, p_sel * env_pdf(sc, dir)));
             break;
         }
         const int mesh_index = sc.tri_mesh[h.id];
@@ -798,10 +863,10 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays,
         const float bx = h.u, by = h.v;
         const float bw = 1 - bx - by;
         if (material.emission > 0.0f) {                                                   // :157-161
-            if (nee && prev_pdf > 0.0f && sc.mesh_light_first[mesh_index] >= 0) {
+            if (tri_l && prev_pdf > 0.0f && sc.mesh_light_first[mesh_index] >= 0) {
                 const Scene::Light& lt = sc.lights[sc.mesh_light_first[mesh_index] + prim];
                 V3 nl = add(add(scale(bw, mesh.normals[i0]), scale(bx, mesh.normals[i1])), scale(by, mesh.normals[i2]));
-                float pdf_light = lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, h.t * h.t, dot(neg(dir), nl));
+                float pdf_light = p_sel * (lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, h.t * h.t, dot(neg(dir), nl)));
                 radiance = v3(material.emission * power_heuristic(prev_pdf, pdf_light));
             } else {
                 radiance = v3(material.emission);
@@ -824,39 +889,56 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays,
         onb(v_n, T, B);
         V3 local_wo = to_local(T, B, v_n, wo);
         if (nee && nan_retries == 0) {
-            // one emissive triangle by power, one point on it by area (lights.hpp:30-48), a shadow
-            // ray over (t_min, distance - t_min) (visibiliy_test, device.cu:97-110)
-            const float us = rng.next(), u0 = rng.next(), u1 = rng.next();
-            int lo = 0, hi = (int)sc.lights.size() - 1;
-            while (lo < hi) {
-                const int mid = (lo + hi) >> 1;
-                if (us <= sc.light_cdf[mid]) hi = mid;
-                else lo = mid + 1;
+            bool use_env = env_l;
+            if (tri_l && env_l) use_env = rng.next() < 0.5f;
+            V3 ldir = v3(0.0f), emitted = v3(0.0f);
+            float pdf_light = 0.0f, tmax = 0.0f;
+            if (use_env) {
+                // one texel by luminance, a uniform point in it; density and radiance re-read through the
+                // direction -> texel mapping of the miss branch
+                const float u0 = rng.next(), u1 = rng.next(), u2 = rng.next(), u3 = rng.next();
+                const int iy = cdf_find(sc.env_cdf_rows.data(), sc.env_h, u0);
+                const int ix = cdf_find(sc.env_cdf_cols.data() + (size_t)iy * (size_t)sc.env_w, sc.env_w, u1);
+                const float lon = (((float)ix + u2) / (float)sc.env_w - 0.5f) * (2.0f * pi);
+                const float lat = (((float)iy + u3) / (float)sc.env_h - 0.5f) * pi;
+                const float cl = m_cos(lat);
+                ldir = normalize(V3{m_sin(lon) * cl, m_sin(lat), m_cos(lon) * cl});
+                pdf_light = p_sel * env_pdf(sc, ldir);
+                emitted = scale(add(v3(0.0f), sample_environment(sc, ldir)), sc.env_intensity);
+                tmax = t_max;
+            } else {
+                // one emissive triangle by power, one point on it by area (lights.hpp:30-48), a shadow
+                // ray over (t_min, distance - t_min) (visibiliy_test, device.cu:97-110)
+                const float us = rng.next(), u0 = rng.next(), u1 = rng.next();
+                const int lo = cdf_find(sc.light_cdf.data(), (int)sc.lights.size(), us);
+                const Scene::Light& lt = sc.lights[lo];
+                const MeshRec& lm = sc.meshes[lt.mesh];
+                const int j0 = lm.idx[3 * lt.prim], j1 = lm.idx[3 * lt.prim + 1], j2 = lm.idx[3 * lt.prim + 2];
+                const float su0 = sqrtf(u0);                                              // sample_methods.hpp:82-86
+                const float cx = 1.0f - su0, cy = u1 * su0;
+                const float cz = 1.0f - cx - cy;
+                V3 pos = add(add(scale(cz, lm.verts[j0]), scale(cx, lm.verts[j1])), scale(cy, lm.verts[j2]));
+                V3 nl = add(add(scale(cz, lm.normals[j0]), scale(cx, lm.normals[j1])), scale(cy, lm.normals[j2]));
+                ldir = sub(pos, v_p);
+                const float dist2 = dot(ldir, ldir);
+                const float dist = sqrtf(dist2);
+                ldir = divs(ldir, dist);
+                pdf_light = p_sel * (lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, dist2, dot(neg(ldir), nl)));
+                if (!(dist > 2.0f * t_min)) pdf_light = 0.0f;
+                emitted = v3(lt.emission);
+                tmax = dist - t_min;
             }
-            const Scene::Light& lt = sc.lights[lo];
-            const MeshRec& lm = sc.meshes[lt.mesh];
-            const int j0 = lm.idx[3 * lt.prim], j1 = lm.idx[3 * lt.prim + 1], j2 = lm.idx[3 * lt.prim + 2];
-            const float su0 = sqrtf(u0);                                                  // sample_methods.hpp:82-86
-            const float cx = 1.0f - su0, cy = u1 * su0;
-            const float cz = 1.0f - cx - cy;
-            V3 pos = add(add(scale(cz, lm.verts[j0]), scale(cx, lm.verts[j1])), scale(cy, lm.verts[j2]));
-            V3 nl = add(add(scale(cz, lm.normals[j0]), scale(cx, lm.normals[j1])), scale(cy, lm.normals[j2]));
-            V3 ldir = sub(pos, v_p);
-            const float dist2 = dot(ldir, ldir);
-            const float dist = sqrtf(dist2);
-            ldir = divs(ldir, dist);
-            const float pdf_light = lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, dist2, dot(neg(ldir), nl));
-            if (pdf_light > 0.0f && dist > 2.0f * t_min) {
+            if (pdf_light > 0.0f) {
                 V3 lwi = normalize(V3{dot(ldir, T), dot(ldir, B), dot(ldir, v_n)});
                 V3 f_eff;
                 float pdf_eff;
                 eval_mixture(material, local_wo, lwi, f_eff, pdf_eff);
                 if (pdf_eff > 0.0f) {
                     const float w = power_heuristic(pdf_light, pdf_eff);
-                    V3 c = mul(throughput, scale(f_eff, fabsf(cos_theta(lwi)) * lt.emission * w / pdf_light));
+                    V3 c = mul(throughput, mul(f_eff, scale(emitted, fabsf(cos_theta(lwi)) * w / pdf_light)));
                     const bool bad = isinf(c.x) || isinf(c.y) || isinf(c.z) || isnan(c.x) || isnan(c.y) || isnan(c.z);
                     if (!bad && (c.x != 0.0f || c.y != 0.0f || c.z != 0.0f)) {
-                        Closest blocker = find(sc, v_p, ldir, t_min, dist - t_min);
+                        Closest blocker = find(sc, v_p, ldir, t_min, tmax);
                         ++nshadow;
                         if (blocker.id == 0xFFFFFFFFu) gathered = add(gathered, c);
                     }
@@ -1042,6 +1124,7 @@ uint64_t oracle_render(oracle_scene* o, int rank, int world, int shard_mode, int
     }
     if (nthreads < 1) nthreads = 1;
     build_lights(sc);
+    build_env_table(sc);
     sc.shadow_rays = 0;
     std::atomic<int> next_row{y0};
     std::atomic<uint64_t> total{0};

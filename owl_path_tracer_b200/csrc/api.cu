@@ -49,6 +49,7 @@ struct b200pt_ctx {
     int32_t* d_idx4 = nullptr;
     MeshInfo* d_meshes = nullptr;
     uint32_t *d_texels = nullptr, *d_env = nullptr;
+    float *d_env_rows = nullptr, *d_env_cols = nullptr;  // NEE mode: luminance cdfs of the map (pt_lights.h)
     Material* d_mats = nullptr;
     int n_mats = 0;
     std::vector<Material> h_mats;      // host copy: the per-mesh material array is rebuilt from it
@@ -130,6 +131,9 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     sv.light_cdf = c->d_light_cdf;
     sv.n_lights = (c->cfg.flags & B200PT_FLAG_NEE) ? (int32_t)c->h_lights.size() : 0;
     sv.nee = (c->cfg.flags & B200PT_FLAG_NEE) ? 1 : 0;
+    sv.env_cdf_rows = c->d_env_rows;
+    sv.env_cdf_cols = c->d_env_cols;
+    sv.env_nee = (sv.nee && c->env_use && c->d_env && c->d_env_rows) ? 1 : 0;
     sv.texels = c->d_texels;
     sv.env = c->d_env;
     sv.env_w = c->env_w;
@@ -202,6 +206,8 @@ extern "C" int b200pt_destroy(b200pt_ctx* c) {
     free_lanes(c);
     free_scene(c);
     cudaFree(c->d_env);
+    cudaFree(c->d_env_rows);
+    cudaFree(c->d_env_cols);
     cudaFree(c->d_mats);
     cudaFree(c->d_mesh_mats);
     cudaFree(c->d_lights);
@@ -333,13 +339,27 @@ extern "C" int b200pt_set_environment(b200pt_ctx* c, const uint8_t* rgba, int32_
     CU(cudaSetDevice(c->cfg.device_ordinal));
     CU(cudaStreamSynchronize(c->stream));
     cudaFree(c->d_env);
+    cudaFree(c->d_env_rows);
+    cudaFree(c->d_env_cols);
     c->d_env = nullptr;
+    c->d_env_rows = c->d_env_cols = nullptr;
     c->env_w = c->env_h = 0;
     if (rgba && w > 0 && h > 0) {
         CU(cudaMalloc(&c->d_env, (size_t)w * h * 4));
         CU(cudaMemcpy(c->d_env, rgba, (size_t)w * h * 4, cudaMemcpyHostToDevice));
         c->env_w = w;
         c->env_h = h;
+        if ((c->cfg.flags & B200PT_FLAG_NEE) && use) {  // importance sampling of the map
+            std::vector<float> rows, cols;
+            std::vector<uint32_t> texels((size_t)w * h);
+            memcpy(texels.data(), rgba, texels.size() * 4);
+            if (build_env_table(texels.data(), w, h, rows, cols)) {
+                CU(cudaMalloc(&c->d_env_rows, sizeof(float) * rows.size()));
+                CU(cudaMalloc(&c->d_env_cols, sizeof(float) * cols.size()));
+                CU(cudaMemcpy(c->d_env_rows, rows.data(), sizeof(float) * rows.size(), cudaMemcpyHostToDevice));
+                CU(cudaMemcpy(c->d_env_cols, cols.data(), sizeof(float) * cols.size(), cudaMemcpyHostToDevice));
+            }
+        }
     }
     c->env_use = use != 0;
     c->env_auto = auto_ != 0;

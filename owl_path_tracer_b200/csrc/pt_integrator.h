@@ -81,6 +81,11 @@ struct SceneView {
     const float* light_cdf;    // n_lights ascending values, last = 1
     int32_t n_lights;
     int32_t nee;
+    // importance sampling of the environment map in the NEE mode (pt_lights.h build_env_table): the texel is
+    // chosen with probability proportional to its luminance, rows first (marginal), then the column of the row
+    const float* env_cdf_rows;  // env_h ascending values, last = 1
+    const float* env_cdf_cols;  // env_h x env_w, each row ascending, last = 1
+    int32_t env_nee;            // 1: NEE mode, map in use, tables present
     uint32_t plane_magic;      // 0x3F800000, see plane_q (pt_bvh8.h): a runtime value on purpose
 };
 
@@ -137,6 +142,36 @@ PT_HD f3 miss_radiance(const SceneView& sv, f3 dir) {
     return rad * sv.env_intensity;
 }
 
+// NEE mode, environment map: texel (ix, iy) that miss_radiance reads for `dir`
+PT_HD void env_texel(const SceneView& sv, f3 dir, int& ix, int& iy) {
+    const float u = 0.5f + dm_atan2(dir.x, dir.z) / (2.0f * kPi);
+    const float v = 0.5f + dm_asin(dir.y) / kPi;
+    const float fx = floorf(u * (float)sv.env_w), fy = floorf(v * (float)sv.env_h);  // fetch_rgba8's addressing
+    ix = (fx >= 0.0f) ? (fx < (float)sv.env_w ? (int)fx : sv.env_w - 1) : 0;
+    iy = (fy >= 0.0f) ? (fy < (float)sv.env_h ? (int)fy : sv.env_h - 1) : 0;
+}
+// solid-angle density with which the environment sampler produces `dir`: the texel's probability spread over
+// the texel's solid angle  (du dv = dlon dlat / 2 pi^2,  d omega = cos(lat) dlon dlat,  cos(lat) = sqrt(1 - y^2))
+PT_HD float env_pdf(const SceneView& sv, f3 dir) {
+    int ix, iy;
+    env_texel(sv, dir, ix, iy);
+    const float prow = sv.env_cdf_rows[iy] - (iy ? sv.env_cdf_rows[iy - 1] : 0.0f);
+    const float* row = sv.env_cdf_cols + (size_t)iy * (size_t)sv.env_w;
+    const float pcol = row[ix] - (ix ? row[ix - 1] : 0.0f);
+    const float cl = sqrtf(fmaxf(0.0f, 1.0f - dir.y * dir.y));
+    if (cl < 1e-4f) return 0.0f;
+    return prow * pcol * ((float)sv.env_w * (float)sv.env_h) / (2.0f * kPi * kPi * cl);
+}
+PT_HD int cdf_find(const float* cdf, int n, float u) {  // first entry with cdf >= u
+    int lo = 0, hi = n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (u <= cdf[mid]) hi = mid;
+        else lo = mid + 1;
+    }
+    return lo;
+}
+
 // state of one lane as the shade step sees it
 struct LaneState {
     f3 o, d;          // current ray
@@ -188,9 +223,15 @@ template <bool NEE>
 PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, int px, int py) {
     L.sample_ended = false;
     L.sh_valid = 0;
-    const bool nee = NEE && sv.n_lights > 0;  // NEE: compiled for B200PT_FLAG_NEE contexts only
+    // NEE: compiled for B200PT_FLAG_NEE contexts only.  Light sampling draws from the emissive triangles, from
+    // the environment map, or (one extra draw) from either with probability 1/2 when the scene has both.
+    const bool tri_l = NEE && sv.n_lights > 0, env_l = NEE && sv.env_nee != 0;
+    const bool nee = tri_l || env_l;
+    const float p_sel = (tri_l && env_l) ? 0.5f : 1.0f;
     if (hit.tri == kNoHit) {
-        const f3 rad = miss_radiance(sv, L.d);
+        f3 rad = miss_radiance(sv, L.d);
+        if (env_l && L.prev_pdf > 0.0f)   // the map could have been reached by light sampling at the previous vertex
+            rad = rad * power_heuristic(L.prev_pdf, p_sel * env_pdf(sv, L.d));
         return end_sample(sv, L, px, py, rad * L.thr);
     }
     const TriIdx ix = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + hit.tri);
@@ -204,13 +245,13 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
     const f4 n0 = load_ro(sv.vnrm + i0), n1 = load_ro(sv.vnrm + i1), n2 = load_ro(sv.vnrm + i2);
 
     if (m.emission > 0.0f) {  // device.cu:157-161: radiance = emission (overwrites)
-        if (nee && L.prev_pdf > 0.0f && mi.light_first >= 0) {
+        if (tri_l && L.prev_pdf > 0.0f && mi.light_first >= 0) {
             // the same emitter could have been reached by light sampling at the previous vertex:
             // power heuristic between the BSDF density and the light density of this very point
             const LightTri lt = load_ro(sv.lights + (mi.light_first + ((int)hit.tri - mi.first_tri)));
             const float lw = 1.0f - hit.u - hit.v;
             const f3 nl = lw * f3{n0.x, n0.y, n0.z} + hit.u * f3{n1.x, n1.y, n1.z} + hit.v * f3{n2.x, n2.y, n2.z};
-            const float pdf_light = lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, hit.t * hit.t, dot(-L.d, nl));
+            const float pdf_light = p_sel * (lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, hit.t * hit.t, dot(-L.d, nl)));
             const float w = power_heuristic(L.prev_pdf, pdf_light);
             return end_sample(sv, L, px, py, mk3(m.emission * w) * L.thr);
         }
@@ -243,42 +284,59 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
     const f3 lwo = normalize(f3{dot(wo, T), dot(wo, B), dot(wo, vn)});
 
     if (nee) {
-        // next-event estimation: one emissive triangle by power, one point on it by area
-        // (sample_triangle, lights.hpp:30-48; uniform_sample_triangle, sample_methods.hpp:82-86)
-        const float us = rng_next(L.rng), u0 = rng_next(L.rng), u1 = rng_next(L.rng);
-        int lo = 0, hi = sv.n_lights - 1;
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            if (us <= sv.light_cdf[mid]) hi = mid;
-            else lo = mid + 1;
+        bool use_env = env_l;
+        if (tri_l && env_l) use_env = rng_next(L.rng) < 0.5f;
+        f3 dir = mk3(0.0f), emitted = mk3(0.0f);
+        float pdf_light = 0.0f, tmax = 0.0f;
+        if (use_env) {
+            // one texel of the map by luminance, a uniform point in it; density and radiance are re-read through
+            // the direction -> texel mapping of the miss branch, so both strategies see the same function
+            const float u0 = rng_next(L.rng), u1 = rng_next(L.rng), u2 = rng_next(L.rng), u3 = rng_next(L.rng);
+            const int iy = cdf_find(sv.env_cdf_rows, sv.env_h, u0);
+            const int ix = cdf_find(sv.env_cdf_cols + (size_t)iy * (size_t)sv.env_w, sv.env_w, u1);
+            const float lon = (((float)ix + u2) / (float)sv.env_w - 0.5f) * (2.0f * kPi);
+            const float lat = (((float)iy + u3) / (float)sv.env_h - 0.5f) * kPi;
+            const float cl = dm_cos(lat);
+            dir = normalize(f3{dm_sin(lon) * cl, dm_sin(lat), dm_cos(lon) * cl});
+            pdf_light = p_sel * env_pdf(sv, dir);
+            emitted = miss_radiance(sv, dir);
+            tmax = kTMax;
+        } else {
+            // one emissive triangle by power, one point on it by area
+            // (sample_triangle, lights.hpp:30-48; uniform_sample_triangle, sample_methods.hpp:82-86)
+            const float us = rng_next(L.rng), u0 = rng_next(L.rng), u1 = rng_next(L.rng);
+            const int lo = cdf_find(sv.light_cdf, sv.n_lights, us);
+            const LightTri lt = load_ro(sv.lights + lo);
+            const TriIdx lx = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + lt.tri);
+            const f4 q0 = load_ro(sv.vpos + lx.i0), q1 = load_ro(sv.vpos + lx.i1), q2 = load_ro(sv.vpos + lx.i2);
+            const f4 m0 = load_ro(sv.vnrm + lx.i0), m1 = load_ro(sv.vnrm + lx.i1), m2 = load_ro(sv.vnrm + lx.i2);
+            const float su0 = sqrtf(u0);
+            const float bx = 1.0f - su0, by = u1 * su0;
+            const float bz = 1.0f - bx - by;
+            const f3 pos = bz * f3{q0.x, q0.y, q0.z} + bx * f3{q1.x, q1.y, q1.z} + by * f3{q2.x, q2.y, q2.z};
+            const f3 nl = bz * f3{m0.x, m0.y, m0.z} + bx * f3{m1.x, m1.y, m1.z} + by * f3{m2.x, m2.y, m2.z};
+            dir = pos - vp;
+            const float dist2 = dot(dir, dir);
+            const float dist = sqrtf(dist2);
+            dir = dir / dist;
+            pdf_light = p_sel * (lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, dist2, dot(-dir, nl)));
+            if (!(dist > 2.0f * kTMin)) pdf_light = 0.0f;
+            emitted = mk3(lt.emission);
+            tmax = dist - kTMin;   // visibiliy_test, device.cu:97-110
         }
-        const LightTri lt = load_ro(sv.lights + lo);
-        const TriIdx lx = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + lt.tri);
-        const f4 q0 = load_ro(sv.vpos + lx.i0), q1 = load_ro(sv.vpos + lx.i1), q2 = load_ro(sv.vpos + lx.i2);
-        const f4 m0 = load_ro(sv.vnrm + lx.i0), m1 = load_ro(sv.vnrm + lx.i1), m2 = load_ro(sv.vnrm + lx.i2);
-        const float su0 = sqrtf(u0);
-        const float bx = 1.0f - su0, by = u1 * su0;
-        const float bz = 1.0f - bx - by;
-        const f3 pos = bz * f3{q0.x, q0.y, q0.z} + bx * f3{q1.x, q1.y, q1.z} + by * f3{q2.x, q2.y, q2.z};
-        const f3 nl = bz * f3{m0.x, m0.y, m0.z} + bx * f3{m1.x, m1.y, m1.z} + by * f3{m2.x, m2.y, m2.z};
-        f3 dir = pos - vp;
-        const float dist2 = dot(dir, dir);
-        const float dist = sqrtf(dist2);
-        dir = dir / dist;
-        const float pdf_light = lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, dist2, dot(-dir, nl));
-        if (pdf_light > 0.0f && dist > 2.0f * kTMin) {
+        if (pdf_light > 0.0f) {
             const f3 lwi = normalize(f3{dot(dir, T), dot(dir, B), dot(dir, vn)});
             f3 f_eff;
             float pdf_eff;
             eval_mixture(m, lwo, lwi, f_eff, pdf_eff);
             if (pdf_eff > 0.0f) {
                 const float w = power_heuristic(pdf_light, pdf_eff);
-                const f3 c = L.thr * (f_eff * (fabsf(lwi.z) * lt.emission * w / pdf_light));
+                const f3 c = L.thr * (f_eff * (emitted * (fabsf(lwi.z) * w / pdf_light)));
                 if (!bad3(c) && (c.x != 0.0f || c.y != 0.0f || c.z != 0.0f)) {
                     L.sh_valid = 1;
                     L.sh_o = vp;
                     L.sh_d = dir;
-                    L.sh_tmax = dist - kTMin;   // visibiliy_test, device.cu:97-110
+                    L.sh_tmax = tmax;
                     L.sh_c = c;
                 }
             }

@@ -51,4 +51,41 @@ inline void build_light_table(const std::vector<f4>& pos, const std::vector<int3
     for (size_t i = 0; i < lights.size(); ++i) lights[i].prob = cdf[i] - (i ? cdf[i - 1] : 0.0f);
 }
 
+// Environment map of the NEE mode: P(texel) proportional to the Rec.709 luminance of the RGBA8 texel (the
+// map is LDR by the reference's loading route).  rows: marginal cdf over the h rows; cols: cdf of
+// every row over its w texels (a black row gets a uniform cdf; it is never selected).  Sums in binary64,
+// rounded once per entry.  Returns false (tables empty) when the whole map is black.
+inline bool build_env_table(const uint32_t* rgba, int w, int h, std::vector<float>& rows, std::vector<float>& cols) {
+    rows.clear();
+    cols.clear();
+    if (!rgba || w <= 0 || h <= 0) return false;
+    rows.resize((size_t)h);
+    cols.resize((size_t)w * (size_t)h);
+    std::vector<double> row_acc((size_t)h), col_acc((size_t)w);
+    double total = 0.0;
+    for (int j = 0; j < h; ++j) {
+        double acc = 0.0;
+        for (int i = 0; i < w; ++i) {
+            const uint32_t p = rgba[(size_t)j * (size_t)w + (size_t)i];
+            const float r = (float)(p & 0xFFu) / 255.0f, g = (float)((p >> 8) & 0xFFu) / 255.0f, b = (float)((p >> 16) & 0xFFu) / 255.0f;
+            const float lum = 0.2126f * r + 0.7152f * g + 0.0722f * b;
+            acc += (double)lum;
+            col_acc[(size_t)i] = acc;
+        }
+        float* row = cols.data() + (size_t)j * (size_t)w;
+        for (int i = 0; i < w; ++i) row[i] = acc > 0.0 ? (float)(col_acc[(size_t)i] / acc) : (float)(i + 1) / (float)w;
+        row[w - 1] = 1.0f;
+        total += acc;
+        row_acc[(size_t)j] = total;
+    }
+    if (!(total > 0.0)) {
+        rows.clear();
+        cols.clear();
+        return false;
+    }
+    for (int j = 0; j < h; ++j) rows[(size_t)j] = (float)(row_acc[(size_t)j] / total);
+    rows[(size_t)h - 1] = 1.0f;
+    return true;
+}
+
 }  // namespace pt

@@ -25,6 +25,7 @@ struct emu_scene {
     std::vector<int32_t> idx4;
     std::vector<MeshInfo> meshes;
     std::vector<uint32_t> texels, env;
+    std::vector<float> env_rows, env_cols;
     std::vector<Material> mats, mesh_mats;
     std::vector<LightTri> lights;
     std::vector<float> light_cdf;
@@ -65,6 +66,12 @@ static void refresh_view(emu_scene* s) {
     s->sv.nee = s->nee;
     s->sv.texels = s->texels.data();
     s->sv.env = s->env.empty() ? nullptr : s->env.data();
+    s->env_rows.clear();
+    s->env_cols.clear();
+    if (s->nee && s->sv.env_use && !s->env.empty()) build_env_table(s->env.data(), s->sv.env_w, s->sv.env_h, s->env_rows, s->env_cols);
+    s->sv.env_cdf_rows = s->env_rows.data();
+    s->sv.env_cdf_cols = s->env_cols.data();
+    s->sv.env_nee = (s->nee && s->sv.env_use && !s->env_rows.empty()) ? 1 : 0;
     s->sv.n_materials = (int)s->mats.size();
 }
 

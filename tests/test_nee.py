@@ -1,6 +1,7 @@
 """Next-event estimation mode (B200PT_FLAG_NEE): light sampling of the emissive
 triangles + shadow any-hit ray + power-heuristic MIS.
 
+Lights are the emissive triangles and, when an environment map is in use, the map (texels by luminance).
 The reference holds the ingredients but never calls them (lights.hpp sample_light / power_heuristic,
 visibiliy_test device.cu:97-110), so there is no reference image of this mode: the oracle carries the
 same opt-in estimator (oracle_set_nee) and parity is product == oracle, bit for bit, as for the
@@ -14,8 +15,8 @@ from checkers import Emu, Oracle, rel_mse
 
 SCENES = {
     "cornell-box": dict(env="color", env_intensity=0.0),
-    "sphere": dict(env="map", env_intensity=1.0),          # no emissive triangle: empty light table
-    "mitsuba": dict(env="auto", env_intensity=1.0),        # no emissive triangle either
+    "sphere": dict(env="map", env_intensity=1.0),          # no emissive triangle: the environment map is the light
+    "mitsuba": dict(env="auto", env_intensity=1.0),        # analytic sky, no emissive triangle: nothing to sample
     "car": dict(env="color", env_intensity=0.0, detail=1),
 }
 
@@ -32,7 +33,7 @@ def test_nee_emulation_bit_equals_oracle(name):
     assert ro["rays"] == re["rays"] and ro["shadow_rays"] == re["shadow_rays"]
     assert (bits(ro["sum"]) == bits(re["sum"])).all()
     assert (ro["rgba"] == re["rgba"]).all()
-    if name in ("sphere", "mitsuba"):      # lit by the environment only: empty light table
+    if name == "mitsuba":
         assert ro["shadow_rays"] == 0
     else:
         assert ro["shadow_rays"] > 0
@@ -63,6 +64,24 @@ def test_nee_same_expectation_lower_variance():
     assert e_nee < 0.5 * e_ref, (e_nee, e_ref)
 
 
+def test_nee_map_and_triangles_together():
+    """A scene with an emissive quad AND an environment map in use: one extra draw picks the strategy."""
+    sc = pt.Scene(scene="cornell-box", width=40, height=30, spp=4, depth=6, env="map", env_intensity=1.0)
+    assert sc.environment["rgba"].size > 0 and sc.environment["use"]
+    ro = Oracle(det=True).load_scene(sc).set_nee().render()
+    re = Emu().load_scene(sc).set_nee().render()
+    assert ro["rays"] == re["rays"] and ro["shadow_rays"] == re["shadow_rays"] and ro["shadow_rays"] > 0
+    assert (bits(ro["sum"]) == bits(re["sum"])).all()
+
+
+def test_nee_environment_map_same_expectation():
+    kw = dict(scene="sphere", width=48, height=36, depth=8, env="map", env_intensity=1.0)
+    ref = Oracle(det=False).load_scene(pt.Scene(spp=256, **kw)).render()["mean"][..., :3]
+    nee = Oracle(det=False).load_scene(pt.Scene(spp=256, **kw)).set_nee().render()["mean"][..., :3]
+    assert abs(ref.mean() - nee.mean()) <= 0.01 * ref.mean()
+    assert rel_mse(nee, ref) < 2e-3          # two independent 256-spp estimates of the same image
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ["cornell-box", "sphere", "mitsuba", "car", "dragon"])
 def test_nee_gpu_bit_equals_oracle(name):
@@ -79,6 +98,19 @@ def test_nee_gpu_bit_equals_oracle(name):
     assert (ctx.framebuffer_rgba8() == ro["rgba"]).all()
     # a second frame on the same context starts from clean state
     ctx.render()
+    assert (bits(ctx.framebuffer_f32()[..., :3]) == bits(ro["mean"][..., :3])).all()
+    ctx.close()
+
+
+@pytest.mark.gpu
+def test_nee_gpu_map_and_triangles_together():
+    sc = pt.Scene(scene="cornell-box", width=160, height=120, spp=4, depth=8, env="map", env_intensity=1.0)
+    ro = Oracle(det=True).load_scene(sc).set_nee().render()
+    ctx = pt.Context(flags=pt.FLAG_NEE)
+    ctx.bind(sc)
+    ctx.render()
+    st = ctx.stats()
+    assert st["rays"] == ro["rays"] and st["shadow_rays"] == ro["shadow_rays"] and st["shadow_rays"] > 0
     assert (bits(ctx.framebuffer_f32()[..., :3]) == bits(ro["mean"][..., :3])).all()
     ctx.close()
 
