@@ -230,7 +230,9 @@ def main():
         s2 = c2.stats()
         npr, tpr = s2["nodes_visited"] / s2["rays"], s2["tris_tested"] / s2["rays"]
         c2.close()
-        bytes_per_ray = 4 + 32 + 16 + 80.0 * npr + 48.0 * tpr   # queue id + ray (2x16) + hit (16) + nodes + triangles
+        # ray read 32 + hit write 32 + 80 B per node visited + triangle bytes; a tested triangle is
+        # half of an 80-byte two-triangle block (pt_bvh8.h TriPair) -> 40 B (SURVEY's 48 B was the one-triangle record)
+        bytes_per_ray = 32 + 32 + 80.0 * npr + 40.0 * tpr
         rank0_rays = kt["rays"]
         launches_extend = kt["iterations"]
         achieved = rank0_rays * bytes_per_ray / (kt["extend_ms"] * 1e-3) * 1e-9 if kt["extend_ms"] > 0 else None

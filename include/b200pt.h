@@ -114,7 +114,7 @@ typedef struct b200pt_stats {
     uint64_t iterations;      /* wavefront iterations of the last render           */
     uint32_t bvh_nodes;       /* 8-wide nodes in the tree                          */
     uint32_t bvh_tris;        /* triangles referenced by the tree                  */
-    uint64_t bvh_bytes;       /* nodes*80 + tris*48                                */
+    uint64_t bvh_bytes;       /* nodes*80 + triangle-pair blocks*80                */
     uint64_t shadow_rays;     /* shadow (any-hit) rays traced (B200PT_FLAG_NEE)    */
     double shadow_ms;         /* share spent in the shadow kernel (FLAG_TIMING)    */
     uint32_t n_lights;        /* emissive triangles in the light table (FLAG_NEE)  */
@@ -205,7 +205,7 @@ int b200pt_sample_disney(b200pt_ctx* ctx, int32_t n, const int32_t* material, co
  * triangles) so the oracle-side checker can walk the same topology and count
  * node/triangle visits for the roofline.  Call with NULL pointers to get sizes. */
 int b200pt_export_bvh(b200pt_ctx* ctx, void* nodes, uint32_t* n_nodes, void* tris,
-                      uint32_t* n_tris);
+                      uint32_t* n_tris);   /* tris: 80-byte blocks of two triangles (pt_bvh8.h TriPair), n_tris = blocks */
 
 #ifdef __cplusplus
 }

@@ -139,6 +139,6 @@ class Context:
         nn, nt = C.c_uint32(), C.c_uint32()
         self._ck(self._L.b200pt_export_bvh(self._h, None, C.byref(nn), None, C.byref(nt)), "export_bvh")
         nodes = np.empty((nn.value, 80), np.uint8)
-        tris = np.empty((nt.value, 12), np.float32)
+        tris = np.empty((nt.value, 20), np.float32)   # 80-byte blocks of two triangles (pt_bvh8.h TriPair)
         self._ck(self._L.b200pt_export_bvh(self._h, _ptr(nodes), C.byref(nn), _ptr(tris), C.byref(nt)), "export_bvh")
         return nodes, tris

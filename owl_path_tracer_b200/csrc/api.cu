@@ -303,8 +303,8 @@ extern "C" int b200pt_build_accel(b200pt_ctx* c) {
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     c->stats.build_ms = ms;
     c->stats.bvh_nodes = c->bvh.n_nodes;
-    c->stats.bvh_tris = c->bvh.n_tris;
-    c->stats.bvh_bytes = (uint64_t)c->bvh.n_nodes * sizeof(Node8) + (uint64_t)c->bvh.n_tris * sizeof(Tri48);
+    c->stats.bvh_tris = (uint32_t)nt;
+    c->stats.bvh_bytes = (uint64_t)c->bvh.n_nodes * sizeof(Node8) + (uint64_t)c->bvh.n_tris * sizeof(TriPair);
     c->built = true;
     return B200PT_OK;
 }
@@ -834,6 +834,6 @@ extern "C" int b200pt_export_bvh(b200pt_ctx* c, void* nodes, uint32_t* n_nodes, 
     if (n_nodes) *n_nodes = c->bvh.n_nodes;
     if (n_tris) *n_tris = c->bvh.n_tris;
     if (nodes) CU(cudaMemcpy(nodes, c->bvh.nodes, sizeof(Node8) * (size_t)c->bvh.n_nodes, cudaMemcpyDeviceToHost));
-    if (tris) CU(cudaMemcpy(tris, c->bvh.tris, sizeof(Tri48) * (size_t)c->bvh.n_tris, cudaMemcpyDeviceToHost));
+    if (tris) CU(cudaMemcpy(tris, c->bvh.tris, sizeof(TriPair) * (size_t)c->bvh.n_tris, cudaMemcpyDeviceToHost));
     return B200PT_OK;
 }

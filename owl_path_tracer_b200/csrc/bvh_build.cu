@@ -83,7 +83,7 @@ __global__ void k_refit(int n, const int32_t* __restrict__ leaf_parent, BinNode*
 __global__ void k_collapse(const CollapseItem* __restrict__ items, uint32_t n_items, const BinNode* __restrict__ bin,
                            const uint32_t* __restrict__ sorted_tri, const float* __restrict__ tri_lo,
                            const float* __restrict__ tri_hi, const f4* __restrict__ pos,
-                           const int32_t* __restrict__ idx4, Node8* nodes_out, uint32_t* node_count, Tri48* tris_out,
+                           const int32_t* __restrict__ idx4, Node8* nodes_out, uint32_t* node_count, TriPair* tris_out,
                            uint32_t* tri_count, CollapseItem* next, uint32_t* next_count, int n_tris,
                            const CollapsePlan* __restrict__ plans) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -116,7 +116,7 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
     int32_t root = ~0;
     CollapseItem *qa = nullptr, *qb = nullptr;
     Node8* nodes = nullptr;
-    Tri48* tris = nullptr;
+    TriPair* tris = nullptr;
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
     char* arena = nullptr;
@@ -179,7 +179,7 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
         tmp = arena + o_tmp;
         tmp2 = arena + o_tmp2;
     }
-    CK(cudaMalloc(&tris, sizeof(Tri48) * (size_t)n));
+    CK(cudaMalloc(&tris, sizeof(TriPair) * (size_t)n));
 
     k_tri_prepare<<<nb, B, 0, st>>>(d_pos, d_idx4, n, pad, slo, sinv, tri_lo, tri_hi, keys, vals);
     CK(cudaGetLastError());
@@ -261,8 +261,9 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
             goto fail;
         }
     }
-    if (h_counters[1] != n) {
-        err = "bvh collapse lost triangles: " + std::to_string(h_counters[1]) + " of " + std::to_string(n);
+    // h_counters[1] counts triangle-pair blocks: every leaf of k triangles takes ceil(k/2) of them
+    if (h_counters[1] < (n + 1) / 2 || h_counters[1] > n) {
+        err = "bvh collapse lost triangles: " + std::to_string(h_counters[1]) + " pair blocks for " + std::to_string(n) + " triangles";
         goto fail;
     }
     out->n_nodes = h_counters[0];

@@ -13,7 +13,7 @@ namespace pt {
 
 struct DeviceBVH {
     Node8* nodes = nullptr;
-    Tri48* tris = nullptr;
+    TriPair* tris = nullptr;
     uint32_t n_nodes = 0, n_tris = 0;
     int levels = 0;
 };

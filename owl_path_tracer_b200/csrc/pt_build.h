@@ -156,19 +156,24 @@ PT_HD void fence() {
 // ---- cost-optimal collapse plan (Ylitie, Karras, Laine 2017, section 3.1) ------------------
 // For every binary node n: c[i-1] = smallest SAH cost of representing the subtree of n with at
 // most i child slots of a wide node (i = 1..7), and the decisions that reach it:
-//   dec[0]    1 = as ONE slot the subtree is a leaf (<= kMaxLeafTris triangles), 0 = an inner
+//   dec[0]    1 = as ONE slot the subtree is a leaf (<= kMaxLeafTris triangles = 3 pair blocks), 0 = an inner
 //             wide node whose 8 slots are distributed over the two children by dec[7]
 //   dec[j-1]  (j = 2..8) how `j` slots are used: 0 = no better than j-1 slots, k > 0 = left child
 //             gets k slots, right child gets j-k
-// Costs: kCostNode per wide-node visit, kCostTri per triangle test, both weighted by the box
-// half-area.  The numbers follow the measured instruction cost of the two phases of the walker
-// (about 300 vs 70 issued instructions, profiles/r01_ncu_summary.md).
-constexpr int kMaxLeafTris = 3;
+// Costs: kCostNode per wide-node visit, kCostTri per triangle-pair BLOCK test (pt_bvh8.h TriPair: two
+// triangles are tested for the price of one), both weighted by the box half-area.  The frame time is
+// nearly flat in kCostTri (0.3 .. 2.0 measured, 0.8 best by 1-3 %): node steps and block tests trade evenly.
+#ifndef PT_MAX_LEAF_TRIS
+#define PT_MAX_LEAF_TRIS 6
+#endif
+constexpr int kMaxLeafTris = PT_MAX_LEAF_TRIS;  // <= 6: a leaf slot addresses at most 3 blocks (3 unary bits)
+static_assert(kMaxLeafTris >= 1 && kMaxLeafTris <= 6, "leaf slots hold 1..3 pair blocks");
 constexpr float kCostNode = 1.0f;
 #ifndef PT_COST_TRI
-#define PT_COST_TRI 0.3f
+#define PT_COST_TRI 0.8f
 #endif
 constexpr float kCostTri = PT_COST_TRI;
+PT_HD int leaf_blocks(int count) { return (count + 1) >> 1; }
 
 struct CollapsePlan {
     float c[7];
@@ -222,7 +227,7 @@ PT_HD void plan_node(int cur, BinNode* nodes, CollapsePlan* plans, const uint32_
         dist[j] = best;
         split[j] = (uint8_t)bk;
     }
-    const float c_leaf = nd.count <= kMaxLeafTris ? area * (float)nd.count * kCostTri : 3.4e38f;
+    const float c_leaf = nd.count <= kMaxLeafTris ? area * (float)leaf_blocks(nd.count) * kCostTri : 3.4e38f;
     const float c_inner = dist[8] + area * kCostNode;
     p.dec[7] = split[8];
     if (c_leaf <= c_inner) {
@@ -413,7 +418,7 @@ PT_HD uint32_t quant_exponent(float ext) {
 // for the inner children into next[]/next_count.
 PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* sorted_tri,
                          const float* tri_lo, const float* tri_hi, const f4* pos, const int32_t* idx4,
-                         Node8* nodes_out, uint32_t* node_count, Tri48* tris_out, uint32_t* tri_count,
+                         Node8* nodes_out, uint32_t* node_count, TriPair* tris_out, uint32_t* tri_count,
                          CollapseItem* next, uint32_t* next_count, int n_tris, const CollapsePlan* plans) {
     // children under construction: inner binary node (>=0) or single leaf (~pos)
     int32_t ch[8];
@@ -525,13 +530,13 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
     }
 
     // counts, allocation
-    int n_inner = 0, n_leaf_tris = 0;
+    int n_inner = 0, n_leaf_blocks = 0;
     for (int i = 0; i < nch; ++i) {
         if (inner[i]) ++n_inner;
-        else n_leaf_tris += cnt[i];
+        else n_leaf_blocks += leaf_blocks(cnt[i]);
     }
     const uint32_t child_base = n_inner ? grab(node_count, (uint32_t)n_inner) : 0u;
-    const uint32_t tri_base = n_leaf_tris ? grab(tri_count, (uint32_t)n_leaf_tris) : 0u;
+    const uint32_t tri_base = n_leaf_blocks ? grab(tri_count, (uint32_t)n_leaf_blocks) : 0u;  // tri_count counts BLOCKS
     const uint32_t next_base = n_inner ? grab(next_count, (uint32_t)n_inner) : 0u;
 
     // Quantisation grid: the scale is chosen for 1.01 x the extent, and the grid origin sits 1/8 of a
@@ -574,19 +579,36 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
             next[next_base + inner_rank] = CollapseItem{ch[i], child_base + (uint32_t)inner_rank};
             ++inner_rank;
         } else {
-            const uint32_t unary = cnt[i] == 1 ? 1u : (cnt[i] == 2 ? 3u : 7u);
+            const int nb = leaf_blocks(cnt[i]);
+            const uint32_t unary = nb == 1 ? 1u : (nb == 2 ? 3u : 7u);
             meta[s] = (uint8_t)((unary << 5) | (uint32_t)tri_off);
-            for (int k = 0; k < cnt[i]; ++k) {
-                const uint32_t t = sorted_tri[lpos[i][k]];
-                const f4 a = pos[idx4[4 * (size_t)t + 0]], b = pos[idx4[4 * (size_t)t + 1]],
-                         c = pos[idx4[4 * (size_t)t + 2]];
-                Tri48 o;
-                o.a = f4{a.x, a.y, a.z, u2f(t)};
-                o.b = f4{b.x - a.x, b.y - a.y, b.z - a.z, 0.0f};
-                o.c = f4{c.x - a.x, c.y - a.y, c.z - a.z, 0.0f};
-                tris_out[tri_base + (uint32_t)tri_off + (uint32_t)k] = o;
+            for (int blk = 0; blk < nb; ++blk) {
+                float v[2][9];
+                uint32_t id[2];
+                for (int half = 0; half < 2; ++half) {
+                    const int k = 2 * blk + half;
+                    if (k < cnt[i]) {
+                        const uint32_t t = sorted_tri[lpos[i][k]];
+                        const f4 a = pos[idx4[4 * (size_t)t + 0]], b = pos[idx4[4 * (size_t)t + 1]],
+                                 c = pos[idx4[4 * (size_t)t + 2]];
+                        v[half][0] = a.x; v[half][1] = a.y; v[half][2] = a.z;
+                        v[half][3] = b.x - a.x; v[half][4] = b.y - a.y; v[half][5] = b.z - a.z;
+                        v[half][6] = c.x - a.x; v[half][7] = c.y - a.y; v[half][8] = c.z - a.z;
+                        id[half] = t;
+                    } else {  // odd leaf: empty half, never accepted (det = 0)
+                        for (int q2 = 0; q2 < 9; ++q2) v[half][q2] = 0.0f;
+                        id[half] = 0xFFFFFFFFu;
+                    }
+                }
+                TriPair o;
+                o.w[0] = f4{v[0][0], v[1][0], v[0][1], v[1][1]};
+                o.w[1] = f4{v[0][2], v[1][2], v[0][3], v[1][3]};
+                o.w[2] = f4{v[0][4], v[1][4], v[0][5], v[1][5]};
+                o.w[3] = f4{v[0][6], v[1][6], v[0][7], v[1][7]};
+                o.w[4] = f4{v[0][8], v[1][8], u2f(id[0]), u2f(id[1])};
+                tris_out[tri_base + (uint32_t)tri_off + (uint32_t)blk] = o;
             }
-            tri_off += cnt[i];
+            tri_off += nb;
         }
     }
 

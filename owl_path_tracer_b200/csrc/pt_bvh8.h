@@ -64,19 +64,24 @@ PT_HD int msb32(uint32_t v) {  // index of highest set bit, v != 0
 //  w2: qlo_x[0..7], qlo_y[0..7]
 //  w3: qlo_z[0..7], qhi_x[0..7]
 //  w4: qhi_y[0..7], qhi_z[0..7]
-// meta[i]: 0 = empty; internal child: (1<<5) | (24+i); leaf: (unary tri count << 5) |
-// offset of its first triangle from tri_base (1..3 triangles -> 001, 011, 111).
+// meta[i]: 0 = empty; internal child: (1<<5) | (24+i); leaf: (unary block count << 5) |
+// offset of its first triangle-pair block from tri_base (1..3 blocks = 1..6 triangles -> 001, 011, 111).
 struct Node8 {
     u4 w[5];
 };
 static_assert(sizeof(Node8) == 80, "Node8 is 80 bytes");
 
-// 48-byte triangle: v0 + edges, prepared once so the walk does no index chasing.
-//  a: v0.xyz, global triangle id (bits)   b: e1.xyz, 0   c: e2.xyz, 0
-struct Tri48 {
-    f4 a, b, c;
+// 80-byte block of TWO triangles A, B (v0 + edges, prepared once so the walk does no index chasing), stored
+// component-interleaved: every 16-byte word holds (A, B) pairs that the warp walker feeds to the packed
+// fp32x2 instructions of sm_100 (FMUL2 / FFMA2 / FADD2) — one block test costs about what one triangle cost:
+//  w0: v0.x_A v0.x_B v0.y_A v0.y_B     w1: v0.z_A v0.z_B e1.x_A e1.x_B     w2: e1.y_A e1.y_B e1.z_A e1.z_B
+//  w3: e2.x_A e2.x_B e2.y_A e2.y_B     w4: e2.z_A e2.z_B id_A   id_B       (global triangle ids as bits)
+// A leaf of n triangles owns ceil(n/2) consecutive blocks; the unused half of its last block has id = kNoHit
+// and all-zero geometry (det = 0: never accepted).
+struct TriPair {
+    f4 w[5];
 };
-static_assert(sizeof(Tri48) == 48, "Tri48 is 48 bytes");
+static_assert(sizeof(TriPair) == 80, "TriPair is 80 bytes");
 
 struct Hit {
     float t, u, v;
@@ -160,7 +165,7 @@ struct WalkCounters {
 
 // Closest-hit walk.  COUNT=true also counts node fetches and triangle tests.
 template <bool COUNT>
-PT_HD void walk_closest(const Node8* __restrict__ nodes, const Tri48* __restrict__ tris, f3 o, f3 d,
+PT_HD void walk_closest(const Node8* __restrict__ nodes, const TriPair* __restrict__ tris, f3 o, f3 d,
                         float tmin, float tmax, Hit& hit, WalkCounters* wc) {
     hit.t = tmax;
     hit.u = 0.0f;
@@ -235,18 +240,25 @@ PT_HD void walk_closest(const Node8* __restrict__ nodes, const Tri48* __restrict
         while (tg_mask != 0) {
             const int bit = msb32(tg_mask);
             tg_mask &= ~(1u << bit);
-            const Tri48* tp = tris + (tg_base + (uint32_t)bit);
-            const f4 a = tp->a, b = tp->b, c = tp->c;
-            if (COUNT) wc->tris++;
-            float t, u, v;
-            if (ray_triangle(o, d, f3{a.x, a.y, a.z}, f3{b.x, b.y, b.z}, f3{c.x, c.y, c.z}, tmin, tmax, t,
-                             u, v)) {
-                const uint32_t id = f2u(a.w);
-                if (t < hit.t || (t == hit.t && id < hit.tri)) {
-                    hit.t = t;
-                    hit.u = u;
-                    hit.v = v;
-                    hit.tri = id;
+            const TriPair* tp = tris + (tg_base + (uint32_t)bit);
+            const f4 w0 = tp->w[0], w1 = tp->w[1], w2 = tp->w[2], w3 = tp->w[3], w4 = tp->w[4];
+            // the two triangles of the block one after the other (the warp walker does both at once with
+            // packed instructions: same IEEE operations per triangle, same bits)
+            for (int half = 0; half < 2; ++half) {
+                const uint32_t id = f2u(half ? w4.w : w4.z);
+                if (id == kNoHit) continue;
+                if (COUNT) wc->tris++;
+                const f3 v0 = half ? f3{w0.y, w0.w, w1.y} : f3{w0.x, w0.z, w1.x};
+                const f3 e1 = half ? f3{w1.w, w2.y, w2.w} : f3{w1.z, w2.x, w2.z};
+                const f3 e2 = half ? f3{w3.y, w3.w, w4.y} : f3{w3.x, w3.z, w4.x};
+                float t, u, v;
+                if (ray_triangle(o, d, v0, e1, e2, tmin, tmax, t, u, v)) {
+                    if (t < hit.t || (t == hit.t && id < hit.tri)) {
+                        hit.t = t;
+                        hit.u = u;
+                        hit.v = v;
+                        hit.tri = id;
+                    }
                 }
             }
         }

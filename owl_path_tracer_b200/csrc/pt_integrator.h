@@ -53,7 +53,7 @@ struct alignas(16) LightTri {
 
 struct SceneView {
     const Node8* nodes;
-    const Tri48* tris;
+    const TriPair* tris;
     const int32_t* idx4;       // per global triangle: 3 global vertex ids + mesh index
     const f4* vpos;            // per global vertex
     const f4* vnrm;

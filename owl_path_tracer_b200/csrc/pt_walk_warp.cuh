@@ -52,7 +52,7 @@ __device__ __forceinline__ f4 ldg4f(const f4* p) {
 // Src:  bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax)   (i < n)
 // Sink: void store(uint32_t i, const Hit& h)
 template <bool COUNT, bool ANY, class Src, class Sink>
-__device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const Tri48* __restrict__ tris, uint32_t n,
+__device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const TriPair* __restrict__ tris, uint32_t n,
                                           uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic) {
     const unsigned FULL = 0xffffffffu;
     const int lid = threadIdx.x & 31;
@@ -152,32 +152,57 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
             if (has_ray && tg_mask != 0) {
                 const int bit = 31 - __clz(tg_mask);
                 tg_mask &= ~(1u << bit);
-                const Tri48* tp = tris + (tg_base + (uint32_t)bit);
-                const f4 a = ldg4f(&tp->a), b = ldg4f(&tp->b), c = ldg4f(&tp->c);
-                if (COUNT) wc.tris++;
-                // ray_triangle of pt_bvh8.h, same expression order, conditions evaluated together
-                const f3 v0{a.x, a.y, a.z}, e1{b.x, b.y, b.z}, e2{c.x, c.y, c.z};
-                const f3 p = cross_fma(d, e2);
-                const float det = dot_fma(e1, p);
-                const float inv = 1.0f / det;
-                const f3 s = o - v0;
-                const float uu = dot_fma(s, p) * inv;
-                const f3 q = cross_fma(s, e1);
-                const float vv = dot_fma(d, q) * inv;
-                const float tt = dot_fma(e2, q) * inv;
-                const bool ok = (det != 0.0f) && (uu >= 0.0f && uu <= 1.0f) && (vv >= 0.0f && uu + vv <= 1.0f) &&
-                                (tt > tmin && tt < tmax);
-                const uint32_t id = f2u(a.w);
-                if (ok && (tt < hit.t || (tt == hit.t && id < hit.tri))) {
-                    hit.t = tt;
-                    hit.u = uu;
-                    hit.v = vv;
-                    hit.tri = id;
-                    if (ANY) {  // occluded: drop the rest of the traversal
-                        ng_mask = 0;
-                        tg_mask = 0;
-                        sp = 0;
-                    }
+                const TriPair* tp = tris + (tg_base + (uint32_t)bit);
+                const f4 w0 = ldg4f(&tp->w[0]), w1 = ldg4f(&tp->w[1]), w2 = ldg4f(&tp->w[2]), w3 = ldg4f(&tp->w[3]),
+                         w4 = ldg4f(&tp->w[4]);
+                // Both triangles of the block at once: every float2 holds (triangle A, triangle B) and every
+                // operation is the packed form of the scalar one in ray_triangle (pt_bvh8.h) — fma.rn.f32x2 /
+                // mul.rn.f32x2 / add.rn.f32x2 round each half like the scalar instruction, so the bits are
+                // those of two scalar tests (conditions evaluated together, no early outs).
+                const float2 v0x = make_float2(w0.x, w0.y), v0y = make_float2(w0.z, w0.w), v0z = make_float2(w1.x, w1.y);
+                const float2 e1x = make_float2(w1.z, w1.w), e1y = make_float2(w2.x, w2.y), e1z = make_float2(w2.z, w2.w);
+                const float2 e2x = make_float2(w3.x, w3.y), e2y = make_float2(w3.z, w3.w), e2z = make_float2(w4.x, w4.y);
+                const float2 dx = make_float2(d.x, d.x), dy = make_float2(d.y, d.y), dz = make_float2(d.z, d.z);
+                const float2 ndx = make_float2(-d.x, -d.x), ndy = make_float2(-d.y, -d.y), ndz = make_float2(-d.z, -d.z);
+                // p = d x e2        (a x b).x = fma(a.y, b.z, -(a.z b.y)),  -(a.z b.y) = (-a.z) b.y exactly
+                const float2 px = __ffma2_rn(dy, e2z, __fmul2_rn(ndz, e2y));
+                const float2 py = __ffma2_rn(dz, e2x, __fmul2_rn(ndx, e2z));
+                const float2 pz = __ffma2_rn(dx, e2y, __fmul2_rn(ndy, e2x));
+                const float2 det = __ffma2_rn(e1z, pz, __ffma2_rn(e1y, py, __fmul2_rn(e1x, px)));
+                const float2 inv = make_float2(1.0f / det.x, 1.0f / det.y);
+                // s = o - v0
+                const float2 sx = __fadd2_rn(make_float2(o.x, o.x), make_float2(-v0x.x, -v0x.y));
+                const float2 sy = __fadd2_rn(make_float2(o.y, o.y), make_float2(-v0y.x, -v0y.y));
+                const float2 sz = __fadd2_rn(make_float2(o.z, o.z), make_float2(-v0z.x, -v0z.y));
+                const float2 uu = __fmul2_rn(__ffma2_rn(sz, pz, __ffma2_rn(sy, py, __fmul2_rn(sx, px))), inv);
+                // q = s x e1
+                const float2 qx = __ffma2_rn(sy, e1z, __fmul2_rn(make_float2(-sz.x, -sz.y), e1y));
+                const float2 qy = __ffma2_rn(sz, e1x, __fmul2_rn(make_float2(-sx.x, -sx.y), e1z));
+                const float2 qz = __ffma2_rn(sx, e1y, __fmul2_rn(make_float2(-sy.x, -sy.y), e1x));
+                const float2 vv = __fmul2_rn(__ffma2_rn(dz, qz, __ffma2_rn(dy, qy, __fmul2_rn(dx, qx))), inv);
+                const float2 tt = __fmul2_rn(__ffma2_rn(e2z, qz, __ffma2_rn(e2y, qy, __fmul2_rn(e2x, qx))), inv);
+                const uint32_t idA = f2u(w4.z), idB = f2u(w4.w);
+                if (COUNT) wc.tris += 1u + (idB != kNoHit ? 1u : 0u);
+                const bool okA = (det.x != 0.0f) && (uu.x >= 0.0f && uu.x <= 1.0f) && (vv.x >= 0.0f && uu.x + vv.x <= 1.0f) &&
+                                 (tt.x > tmin && tt.x < tmax);
+                const bool okB = (det.y != 0.0f) && (uu.y >= 0.0f && uu.y <= 1.0f) && (vv.y >= 0.0f && uu.y + vv.y <= 1.0f) &&
+                                 (tt.y > tmin && tt.y < tmax);
+                if (okA && (tt.x < hit.t || (tt.x == hit.t && idA < hit.tri))) {
+                    hit.t = tt.x;
+                    hit.u = uu.x;
+                    hit.v = vv.x;
+                    hit.tri = idA;
+                }
+                if (okB && (tt.y < hit.t || (tt.y == hit.t && idB < hit.tri))) {
+                    hit.t = tt.y;
+                    hit.u = uu.y;
+                    hit.v = vv.y;
+                    hit.tri = idB;
+                }
+                if (ANY && hit.tri != kNoHit) {  // occluded: drop the rest of the traversal
+                    ng_mask = 0;
+                    tg_mask = 0;
+                    sp = 0;
                 }
             }
 #if PT_TRI_LOOP

@@ -16,10 +16,11 @@
 namespace pt {
 
 #ifndef PT_BLOCKS_PER_SM
-#define PT_BLOCKS_PER_SM 8     // persistent blocks of 128 threads per SM for the walker kernels
+#define PT_BLOCKS_PER_SM 7     // persistent blocks of 128 threads per SM for the walker kernels
 #endif
 #ifndef PT_EXTEND_MIN_BLOCKS
-#define PT_EXTEND_MIN_BLOCKS 8  // register cap of the walker kernels: 65536 / (128 * blocks) = 64
+#define PT_EXTEND_MIN_BLOCKS 7  // register cap of the walker kernels: 65536 / (128 * blocks) -> 72 (the packed
+                                // two-triangle test spills at 64: 8 blocks/SM measured 10 % slower)
 #endif
 #ifndef PT_SHADE_MIN_BLOCKS
 #define PT_SHADE_MIN_BLOCKS 4   // register cap of k_shade: 65536 / (128 * blocks)

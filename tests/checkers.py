@@ -198,6 +198,19 @@ def _sample_disney(f, mats, material, wo, lobe_in, rng_in):
     return dict(f=fo, wi=wi, pdf=pdf, lobe=lobe, rng=rng)
 
 
+def unpack_pairs(blocks):
+    """(n_blocks, 20) float32 TriPair blocks (pt_bvh8.h) -> per-triangle arrays of the non-empty halves,
+    in block order: ids (uint32), v0, e1, e2 (float32 x 3), block index."""
+    b = np.ascontiguousarray(blocks, np.float32).reshape(-1, 20)
+    ids = b[:, 18:20].view(np.uint32)                         # (n, 2)
+    comp = b[:, :18].reshape(-1, 9, 2)                        # component k of triangle A/B
+    tri = np.transpose(comp, (0, 2, 1)).reshape(-1, 9)        # (2n, 9): A0, B0, A1, B1, ...
+    idf = ids.reshape(-1)
+    keep = idf != 0xFFFFFFFF
+    blk = np.repeat(np.arange(b.shape[0]), 2)
+    return idf[keep], tri[keep, 0:3], tri[keep, 3:6], tri[keep, 6:9], blk[keep]
+
+
 class Emu(_SceneChecker):
     prefix = "emu_"
 
@@ -222,6 +235,8 @@ class Emu(_SceneChecker):
         L.emu_shadow_rays.restype = C.c_uint64
         L.emu_export.argtypes = [P, P, P]
         L.emu_export.restype = C.c_uint32
+        L.emu_n_pairs.argtypes = [P]
+        L.emu_n_pairs.restype = C.c_uint32
         L.emu_import.argtypes = [P, P, C.c_uint32, P, C.c_uint32]
         L.emu_trace.argtypes = [P, P, P, C.c_int, C.c_float, C.c_float, P, P]
         L.emu_primary_hits.argtypes = [P, C.c_int, P]
@@ -261,6 +276,13 @@ class Emu(_SceneChecker):
     def set_nee(self, on=True):
         self.L.emu_set_nee(self.h, int(on))
         return self
+
+    def export(self):
+        """nodes (n, 80) uint8 and triangle-pair blocks (n_blocks, 20) float32 of the emulated build"""
+        nodes = np.zeros((self.n_nodes, 80), np.uint8)
+        tris = np.zeros((int(self.L.emu_n_pairs(self.h)), 20), np.float32)
+        self.L.emu_export(self.h, nodes.ctypes.data, tris.ctypes.data)
+        return nodes, tris
 
     def primary_hits(self, threads=NCPU):
         out = np.empty((self.height, self.width), HIT_DTYPE)

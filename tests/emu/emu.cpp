@@ -32,7 +32,7 @@ struct emu_scene {
     int nee = 0;
     uint64_t shadow_rays = 0;
     std::vector<Node8> nodes;
-    std::vector<Tri48> tris;
+    std::vector<TriPair> tris;
     float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, max_abs = 0;
     int levels = 0;
     int ploc_rounds = 0;
@@ -240,7 +240,7 @@ int emu_build(emu_scene* s) {
         root = 0;
     }
     s->nodes.assign(n, Node8{});
-    s->tris.assign(n, Tri48{});
+    s->tris.assign(n, TriPair{});
     std::vector<CollapseItem> qa(n), qb(n);
     uint32_t n_items = 1;
     node_count = 1;
@@ -259,13 +259,15 @@ int emu_build(emu_scene* s) {
     }
     if (s->levels <= kStackSize) break;
     }
-    if (tri_count != n) return -3;
+    if (tri_count < (n + 1) / 2 || tri_count > n) return -3;  // pair blocks
+    s->tris.resize(tri_count);
     if (s->levels > kStackSize) return -4;
     s->nodes.resize(node_count);
     return (int)node_count;
 }
 
 int emu_levels(emu_scene* s) { return s->levels; }
+uint32_t emu_n_pairs(emu_scene* s) { return (uint32_t)s->tris.size(); }
 void emu_force_lbvh(emu_scene* s, int on) { s->force_lbvh = on; }
 void emu_set_nee(emu_scene* s, int on) { s->nee = on; }
 uint64_t emu_shadow_rays(emu_scene* s) { return s->shadow_rays; }
@@ -279,13 +281,13 @@ void emu_walk_counters(emu_scene* s, uint64_t* out) {
 }
 uint32_t emu_export(emu_scene* s, void* nodes, void* tris) {
     if (nodes) memcpy(nodes, s->nodes.data(), sizeof(Node8) * s->nodes.size());
-    if (tris) memcpy(tris, s->tris.data(), sizeof(Tri48) * s->tris.size());
+    if (tris) memcpy(tris, s->tris.data(), sizeof(TriPair) * s->tris.size());
     return (uint32_t)s->nodes.size();
 }
 // walk a tree handed in from outside (e.g. exported from the GPU) instead of the emulated build
 void emu_import(emu_scene* s, const void* nodes, uint32_t n_nodes, const void* tris, uint32_t n_tris) {
     s->nodes.assign((const Node8*)nodes, (const Node8*)nodes + n_nodes);
-    s->tris.assign((const Tri48*)tris, (const Tri48*)tris + n_tris);
+    s->tris.assign((const TriPair*)tris, (const TriPair*)tris + n_tris);
 }
 
 void emu_trace(emu_scene* s, const float* o, const float* d, int n, float tmin, float tmax, emu_hit* out,

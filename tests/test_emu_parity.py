@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 import owl_path_tracer_b200 as pt
-from checkers import REPO, Emu, Oracle
+from checkers import REPO, Emu, Oracle, unpack_pairs
 
 G = REPO / "tests" / "golden"
 SCENES = {
@@ -107,9 +107,8 @@ def test_triangle_soups_and_edge_counts(n, degenerate):
         c.add_mesh(verts, normals, idx, 0)
         c.set_materials(mats)
         c.build()
-    nodes, tris = np.zeros((e.n_nodes, 80), np.uint8), np.zeros((n, 12), np.float32)
-    e.L.emu_export(e.h, nodes.ctypes.data, tris.ctypes.data)
-    ids = np.sort(tris[:, 3].view(np.uint32))
+    nodes, tris = e.export()
+    ids = np.sort(unpack_pairs(tris)[0])
     assert (ids == np.arange(n)).all()
     org, d = random_rays(800, n, [0, 0, 0], 1.5)
     assert same_hits(o.trace(org, d, brute=True), e.trace(org, d)).all()
@@ -199,11 +198,10 @@ def test_tree_invariants():
     child's node origin box; inner children are numbered by slot order; each triangle once."""
     sc = pt.Scene(scene="cornell-box", width=8, height=8, spp=1, depth=1)
     e = Emu().load_scene(sc)
-    nodes, tris = np.zeros((e.n_nodes, 80), np.uint8), np.zeros((sc.n_triangles, 12), np.float32)
-    e.L.emu_export(e.h, nodes.ctypes.data, tris.ctypes.data)
-    assert (np.sort(tris[:, 3].view(np.uint32)) == np.arange(sc.n_triangles)).all()
+    nodes, tris = e.export()
+    ids, v0, e1, e2, blk = unpack_pairs(tris)
+    assert (np.sort(ids) == np.arange(sc.n_triangles)).all()
     p, scale, imask, cbase, tbase, meta, lo, hi = decode_nodes(nodes)
-    v0, e1, e2 = tris[:, 0:3], tris[:, 4:7], tris[:, 8:11]
     corners = np.stack([v0, v0 + e1, v0 + e2], 1)
     seen_nodes = np.zeros(e.n_nodes, bool)
     seen_nodes[0] = True
@@ -222,9 +220,11 @@ def test_tree_invariants():
                 # the child's grid origin sits 1/8 step below the child's box (collapse_node)
                 assert (lo[n, :, s] <= p[child] + 0.125 * scale[child] + 1e-6).all()
             else:
-                cnt = {1: 1, 3: 2, 7: 3}[m >> 5]
+                cnt = {1: 1, 3: 2, 7: 3}[m >> 5]                      # pair blocks of the leaf
                 first = int(tbase[n]) + (m & 0x1F)
-                c = corners[first:first + cnt].reshape(-1, 3)
+                sel = (blk >= first) & (blk < first + cnt)
+                assert cnt * 2 - 1 <= sel.sum() <= cnt * 2            # only the last block may be half empty
+                c = corners[sel].reshape(-1, 3)
                 assert (c >= lo[n, :, s] - 1e-7).all() and (c <= hi[n, :, s] + 1e-7).all()
         assert rank == bin(int(imask[n])).count("1")
     assert seen_nodes.all()
