@@ -33,7 +33,7 @@ struct b200pt_ctx {
     LaneArrays part[kMaxParts];
     int n_parts = 0;              // parts the lane arrays are currently laid out for
     int lanes_width = 0;          // frame width they were sized for
-    uint32_t* h_counts = nullptr; // pinned: kMaxParts x (kBatch + 1 queue lengths, kBatch shadow counts)
+    uint32_t* h_counts = nullptr; // pinned: kMaxParts x (kBatch + 1 queue lengths, kBatch shadow counts, kBatch parked counts)
     uint32_t* d_cursor = nullptr;  // ray-fetch cursor of the parity-hook kernels
     // host staging of the flattened scene (kept: parity hooks map triangle ids back)
     std::vector<f4> h_pos, h_nrm;
@@ -82,6 +82,8 @@ struct b200pt_ctx {
     std::vector<cudaEvent_t> ev_pool;
 };
 
+constexpr int kCountsStride = 3 * kBatch + 1;  // per part in h_counts
+
 static void free_lanes(b200pt_ctx* c) {
     for (int p = 0; p < kMaxParts; ++p) {
         LaneArrays& L = c->part[p];
@@ -91,10 +93,10 @@ static void free_lanes(b200pt_ctx* c) {
         cudaFree(L.hit);
         cudaFree(L.sh_o); cudaFree(L.sh_d); cudaFree(L.sh_c); cudaFree(L.sh_f);
         cudaFree(L.sh_counts); cudaFree(L.sh_cursor);
-        cudaFree(L.counts); cudaFree(L.cursor);
+        cudaFree(L.counts); cudaFree(L.cursor); cudaFree(L.pending);
         L = LaneArrays{};  // sum, rad, walk_counters are aliases of c->la's
     }
-    cudaFree(c->la.sum); cudaFree(c->la.rad); cudaFree(c->la.walk_counters);
+    cudaFree(c->la.sum); cudaFree(c->la.rad); cudaFree(c->la.walk_counters); cudaFree(c->la.susp);
     cudaFree(c->d_frame); cudaFree(c->d_rgba); cudaFree(c->d_mean);
     if (c->h_rgba) cudaFreeHost(c->h_rgba);
     if (c->h_mean) cudaFreeHost(c->h_mean);
@@ -193,7 +195,7 @@ extern "C" int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     c->part_stream[0] = c->stream;
     for (int p = 1; p < kMaxParts; ++p) CU(cudaStreamCreateWithFlags(&c->part_stream[p], cudaStreamNonBlocking));
     for (int p = 0; p < kMaxParts; ++p) CU(cudaEventCreateWithFlags(&c->part_done[p], cudaEventDisableTiming));
-    CU(cudaMallocHost(&c->h_counts, sizeof(uint32_t) * kMaxParts * (2 * kBatch + 1)));
+    CU(cudaMallocHost(&c->h_counts, sizeof(uint32_t) * kMaxParts * kCountsStride));
     set_persistent_blocks(prop.multiProcessorCount);
     *out = c;
     return B200PT_OK;
@@ -468,6 +470,7 @@ static int ensure_lanes(b200pt_ctx* c, const SceneView& sv, int parts) {
         CU(cudaMalloc(&c->la.sum, sizeof(f4) * need));
         if (nee) CU(cudaMalloc(&c->la.rad, sizeof(f4) * need));
         CU(cudaMalloc(&c->la.walk_counters, sizeof(unsigned long long) * 2));
+        CU(cudaMalloc(&c->la.susp, sizeof(u4) * kSuspWords * (size_t)need));  // touched by parked walks only
         for (int p = 0; p < parts; ++p) {
             LaneArrays& L = c->part[p];
             // + 256: k_shade loads entry i before it knows the queue length
@@ -490,6 +493,8 @@ static int ensure_lanes(b200pt_ctx* c, const SceneView& sv, int parts) {
             }
             CU(cudaMalloc(&L.counts, sizeof(uint32_t) * (kBatch + 1)));
             CU(cudaMalloc(&L.cursor, sizeof(uint32_t) * kBatch));
+            CU(cudaMalloc(&L.pending, sizeof(uint32_t) * kBatch));
+            L.susp = c->la.susp;
             L.sum = c->la.sum;
             L.rad = c->la.rad;
             L.walk_counters = c->la.walk_counters;
@@ -545,6 +550,7 @@ static int render_local(b200pt_ctx* c) {
         cudaStream_t ps = c->part_stream[p];
         CU(cudaMemsetAsync(L.counts, 0, sizeof(uint32_t) * (kBatch + 1), ps));
         CU(cudaMemsetAsync(L.cursor, 0, sizeof(uint32_t) * kBatch, ps));
+        CU(cudaMemsetAsync(L.pending, 0, sizeof(uint32_t) * kBatch, ps));
         if (nee) {
             CU(cudaMemsetAsync(L.sh_counts, 0, sizeof(uint32_t) * kBatch, ps));
             CU(cudaMemsetAsync(L.sh_cursor, 0, sizeof(uint32_t) * kBatch, ps));
@@ -554,8 +560,8 @@ static int render_local(b200pt_ctx* c) {
             launch_init_lanes(sv, L, p, parts, n_part, ps);
             S.kernel_launches++;
             active[p] = n_part;
-            c->h_counts[p * (2 * kBatch + 1)] = n_part;  // pinned: stays valid until the copy ran
-            CU(cudaMemcpyAsync(L.counts, &c->h_counts[p * (2 * kBatch + 1)], sizeof(uint32_t), cudaMemcpyHostToDevice, ps));
+            c->h_counts[p * kCountsStride] = n_part;  // pinned: stays valid until the copy ran
+            CU(cudaMemcpyAsync(L.counts, &c->h_counts[p * kCountsStride], sizeof(uint32_t), cudaMemcpyHostToDevice, ps));
         }
     }
     if (timing) {
@@ -565,6 +571,9 @@ static int render_local(b200pt_ctx* c) {
             c->ev_pool.push_back(e);
         }
     }
+    FILE* iter_log = nullptr;
+    if (timing)
+        if (const char* e = getenv("B200PT_ITER_LOG")) iter_log = fopen(e, "w");
     auto any_active = [&] {
         for (int p = 0; p < parts; ++p)
             if (active[p]) return true;
@@ -595,8 +604,10 @@ static int render_local(b200pt_ctx* c) {
             if (!active[p]) continue;
             const LaneArrays& L = c->part[p];
             cudaStream_t ps = c->part_stream[p];
-            uint32_t* hc = c->h_counts + p * (2 * kBatch + 1);
+            uint32_t* hc = c->h_counts + p * kCountsStride;
             CU(cudaMemcpyAsync(hc, L.counts, sizeof(uint32_t) * (kBatch + 1), cudaMemcpyDeviceToHost, ps));
+            CU(cudaMemcpyAsync(hc + 2 * kBatch + 1, L.pending, sizeof(uint32_t) * kBatch, cudaMemcpyDeviceToHost, ps));
+            CU(cudaMemsetAsync(L.pending, 0, sizeof(uint32_t) * kBatch, ps));
             // next batch starts from the last queue length; the other slots go back to zero
             CU(cudaMemcpyAsync(L.counts, L.counts + kBatch, sizeof(uint32_t), cudaMemcpyDeviceToDevice, ps));
             CU(cudaMemsetAsync(L.counts + 1, 0, sizeof(uint32_t) * kBatch, ps));
@@ -610,9 +621,10 @@ static int render_local(b200pt_ctx* c) {
         for (int p = 0; p < parts; ++p) {
             if (!active[p]) continue;
             CU(cudaStreamSynchronize(c->part_stream[p]));
-            const uint32_t* hc = c->h_counts + p * (2 * kBatch + 1);
+            const uint32_t* hc = c->h_counts + p * kCountsStride;
             for (int k = 0; k < kBatch; ++k) {
-                S.rays += hc[k];
+                // a lane whose walk was parked in iteration k sits in queue k+1 with the same ray: count it once
+                S.rays += hc[k] - hc[2 * kBatch + 1 + k];
                 if (nee) S.shadow_rays += hc[kBatch + 1 + k];
                 if (p == 0 && hc[k]) S.iterations++;
             }
@@ -627,9 +639,12 @@ static int render_local(b200pt_ctx* c) {
                 S.extend_ms += a;
                 S.shade_ms += b;
                 S.shadow_ms += s;
+                if (iter_log && c->h_counts[k])  // development: queue length, parked lanes, kernel times per iteration
+                    fprintf(iter_log, "%u %u %.4f %.4f\n", c->h_counts[k], c->h_counts[2 * kBatch + 1 + k], a, b);
             }
         }
     }
+    if (iter_log) fclose(iter_log);
     for (int p = 1; p < parts; ++p) {  // the frame is complete on `stream` once every part is
         CU(cudaEventRecord(c->part_done[p], c->part_stream[p]));
         CU(cudaStreamWaitEvent(st, c->part_done[p], 0));

@@ -27,6 +27,12 @@ namespace pt {
 #ifndef PT_TRI_LOOP
 #define PT_TRI_LOOP 1        // stay in the triangle phase while the vote still holds (skips the loop head per triangle)
 #endif
+#ifndef PT_SUSPEND_LANES
+#define PT_SUSPEND_LANES 3   // SUSPEND walks: once the queue is drained, a warp left with <= this many rays parks them
+#endif
+#ifndef PT_SUSPEND_MIN
+#define PT_SUSPEND_MIN 100000 // ... only in launches of at least this many rays (smaller ones run every ray to its end)
+#endif
 #ifndef PT_PREFETCH_TRI
 #define PT_PREFETCH_TRI 0    // prefetch.global.L1 of the first leaf triangle at the end of a node step
 #endif
@@ -49,15 +55,26 @@ __device__ __forceinline__ f4 ldg4f(const f4* p) {
 //        it sits in a register and the byte-permute selector of plane_q is the immediate.
 // ANY:  shadow rays — the first accepted triangle ends the ray (any hit in (tmin, tmax)); the hit record then
 //       only says whether something was hit.
-// Src:  bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax)   (i < n)
+// SUSPEND: bounded tails.  A launch ends with every warp waiting for the longest of its ~32 resident rays while
+//       its other lanes idle (traversal lengths are heavy-tailed: the last ray of a warp typically takes 5-10x
+//       the mean).  With SUSPEND, a warp that is out of new rays and down to PT_SUSPEND_LANES rays parks them:
+//       traversal state (closest hit so far, pending groups, stack) goes to a per-lane save area, the hit
+//       record says kPending, and the ray continues in the NEXT launch of this walker, refilled into a full
+//       warp like any other ray (k_shade passes a pending lane through untouched).  The result of a walk
+//       does not depend on where it was interrupted.
+// Src:  bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax)   (i < n); true = entry i continues a parked walk
+//       void restore(i, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack)        (SUSPEND only)
 // Sink: void store(uint32_t i, const Hit& h)
-template <bool COUNT, bool ANY, class Src, class Sink>
+//       void suspend(i, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack)        (SUSPEND only)
+constexpr uint32_t kPending = 0xFFFFFFFEu;  // hit.tri of a parked ray
+template <bool COUNT, bool ANY, bool SUSPEND, class Src, class Sink>
 __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const TriPair* __restrict__ tris, uint32_t n,
                                           uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic) {
     const unsigned FULL = 0xffffffffu;
     const int lid = threadIdx.x & 31;
 
     bool has_ray = false, exhausted = false;
+    const int park = (SUSPEND && n >= (uint32_t)PT_SUSPEND_MIN) ? PT_SUSPEND_LANES : 0;  // 0: only an empty warp leaves
     uint32_t ray_index = 0;
     f3 o{0, 0, 0}, d{0, 0, 1};
     float tmin = 0, tmax = 0;
@@ -105,7 +122,15 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         }
         unsigned act = __ballot_sync(FULL, has_ray);
         // ---- refill idle lanes (also the ones that retired just above)
-        if (!exhausted && __popc(~act) >= kRefill) {
+        if (exhausted) {
+            // out of new rays: run what is left; a SUSPEND walk parks the last few rays of the warp instead
+            if constexpr (SUSPEND) {
+                if (__popc(act) <= park) {
+                    if (has_ray) sink.suspend(ray_index, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack);
+                    break;
+                }
+            }
+        } else if (__popc(~act) >= kRefill) {
             const unsigned idle = ~act;
             const int cnt = __popc(idle);
             uint32_t base = 0;
@@ -114,7 +139,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
             if (!has_ray) {
                 const uint32_t i = base + (uint32_t)__popc(idle & ((1u << lid) - 1u));
                 if (i < n) {
-                    src.load(i, o, d, tmin, tmax);
+                    const bool resumed = src.load(i, o, d, tmin, tmax);
                     ray_index = i;
                     has_ray = true;
                     idx = safe_rcp_dir(d.x);
@@ -126,6 +151,9 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
                     ng_mask = 0x80000000u;
                     tg_mask = 0;
                     sp = 0;
+                    if constexpr (SUSPEND) {
+                        if (__builtin_expect(resumed, 0)) src.restore(i, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack);
+                    }
                 }
             }
             if (base + (uint32_t)cnt >= n) exhausted = true;

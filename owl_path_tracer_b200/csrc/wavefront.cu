@@ -26,6 +26,11 @@ namespace pt {
 #define PT_SHADE_MIN_BLOCKS 4   // register cap of k_shade: 65536 / (128 * blocks)
 #endif
 constexpr int kBlock = 128;
+#ifndef PT_WALK_BLOCK
+#define PT_WALK_BLOCK 128       // threads per block of the persistent walker kernels
+#endif
+constexpr int kWalkBlock = PT_WALK_BLOCK;
+constexpr int kWalkMinBlocks = PT_EXTEND_MIN_BLOCKS * 128 / kWalkBlock;   // same warps per SM whatever the block size
 
 __device__ __forceinline__ f4 ld4(const f4* p) {
     const float4 v = *reinterpret_cast<const float4*>(p);
@@ -58,29 +63,66 @@ __global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays 
 struct LaneRaySource {   // entry i of the current state set
     const f4* ray_o;
     const f4* ray_d;
-    __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
+    const uint32_t* queue;   // lane id of entry i: addresses the save area of parked walks
+    const u4* susp;
+    __device__ __forceinline__ bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
         const f4 a = ld4(ray_o + i), b = ld4(ray_d + i);
         o = f3{a.x, a.y, a.z};
         d = f3{b.x, b.y, b.z};
         tmin = kTMin;
         tmax = kTMax;
+        return (f2u(b.w) >> 31) != 0;   // k_shade sets bit 31 of the control word of a lane whose walk is parked
+    }
+    __device__ __forceinline__ void restore(uint32_t i, Hit& hit, uint32_t& ng_base, uint32_t& ng_mask, uint32_t& tg_base,
+                                            uint32_t& tg_mask, int& sp, uint32_t& top_b, uint32_t& top_m, uint2* stack) const {
+        const u4* p = susp + (size_t)queue[i] * kSuspWords;
+        const u4 h = p[0], g = p[1], t = p[2];
+        hit = Hit{u2f(h.x), u2f(h.y), u2f(h.z), h.w};
+        ng_base = g.x;
+        ng_mask = g.y;
+        tg_base = g.z;
+        tg_mask = g.w;
+        sp = (int)t.x;
+        top_b = t.y;
+        top_m = t.z;
+        for (int e = 0; e + 1 < sp; e += 2) {
+            const u4 w = p[3 + (e >> 1)];
+            stack[e] = make_uint2(w.x, w.y);
+            if (e + 2 < sp) stack[e + 1] = make_uint2(w.z, w.w);
+        }
     }
 };
 struct LaneHitSink {
     f4* hit;
+    const uint32_t* queue;
+    u4* susp;
     __device__ __forceinline__ void store(uint32_t i, const Hit& h) const { st4(hit + i, f4{h.t, h.u, h.v, u2f(h.tri)}); }
+    __device__ __forceinline__ void suspend(uint32_t i, const Hit& h, uint32_t ng_base, uint32_t ng_mask, uint32_t tg_base,
+                                            uint32_t tg_mask, int sp, uint32_t top_b, uint32_t top_m, const uint2* stack) const {
+        u4* p = susp + (size_t)queue[i] * kSuspWords;
+        p[0] = u4{f2u(h.t), f2u(h.u), f2u(h.v), h.tri};
+        p[1] = u4{ng_base, ng_mask, tg_base, tg_mask};
+        p[2] = u4{(uint32_t)sp, top_b, top_m, 0u};
+        for (int e = 0; e + 1 < sp; e += 2) {   // entries 0 .. sp-2 live in local memory, the top in registers
+            const uint2 a = stack[e];
+            const uint2 b = (e + 2 < sp) ? stack[e + 1] : make_uint2(0u, 0u);
+            p[3 + (e >> 1)] = u4{a.x, a.y, b.x, b.y};
+        }
+        st4(hit + i, f4{0.0f, 0.0f, 0.0f, u2f(kPending)});
+    }
 };
 
 // persistent warps: every warp pulls rays of queue k until the queue is drained
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_extend(SceneView sv, LaneArrays la, int k) {
+__global__ void __launch_bounds__(kWalkBlock, kWalkMinBlocks) k_extend(SceneView sv, LaneArrays la, int k) {
     const uint32_t n = la.counts[k];
     WalkCounters wc{0, 0};
     if (n) {
         // (k & 1) selects the state set; written out so that the parameter struct is never indexed dynamically
-        warp_walk<COUNT, false>(sv.nodes, sv.tris, n, la.cursor + k,
-                         LaneRaySource{(k & 1) ? la.ray_o[1] : la.ray_o[0], (k & 1) ? la.ray_d[1] : la.ray_d[0]},
-                         LaneHitSink{la.hit}, wc, sv.plane_magic);
+        const uint32_t* q = (k & 1) ? la.queue[1] : la.queue[0];
+        warp_walk<COUNT, false, true>(sv.nodes, sv.tris, n, la.cursor + k,
+                         LaneRaySource{(k & 1) ? la.ray_o[1] : la.ray_o[0], (k & 1) ? la.ray_d[1] : la.ray_d[0], q, la.susp},
+                         LaneHitSink{la.hit, q, la.susp}, wc, sv.plane_magic);
     }
     if (COUNT) {
         unsigned long long a = wc.nodes, b = wc.tris;
@@ -112,8 +154,29 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
     bool keep = false, shadow = false;
     LaneState L;
     f3 last_term = mk3(0.0f);
-    uint32_t shadow_flags = 0;
-    if (i < n) {
+    uint32_t shadow_flags = 0, resume_bit = 0;
+    const bool parked = i < n && f2u(hv.w) == kPending;
+    if (parked) {
+        // the walk of this ray was interrupted (pt_walk_warp.cuh SUSPEND): nothing to shade yet, the lane moves
+        // to the next queue unchanged and the next k_extend picks the walk up where it stopped
+        const f4 o = ld4(in_o + i);
+        L.o = f3{o.x, o.y, o.z};
+        L.prev_pdf = o.w;
+        L.d = f3{d.x, d.y, d.z};
+        L.thr = f3{t.x, t.y, t.z};
+        L.rng = f2u(t.w);
+        const uint32_t ctl = f2u(d.w);
+        L.sample = ctl_sample(ctl);
+        L.depth = ctl_depth(ctl);
+        L.lobe = ctl_lobe(ctl);
+        resume_bit = 0x80000000u;
+        keep = true;
+    }
+    {
+        const unsigned mp = __ballot_sync(0xffffffffu, parked);
+        if (mp && (threadIdx.x & 31) == __ffs(mp) - 1) atomicAdd(la.pending + k, (uint32_t)__popc(mp));
+    }
+    if (i < n && !parked) {
         f4 s = ld4(la.sum + lane);
         if (NEE) L.prev_pdf = in_o[i].w;  // density of the current ray under BSDF sampling (ray_o.w)
         L.o = mk3(0.0f);  // only written: the old origin is never needed again
@@ -164,7 +227,7 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
         if (keep) {
             const uint32_t pos = base + __popc(m & ((1u << lid) - 1u));
             st4(out_o + pos, f4{L.o.x, L.o.y, L.o.z, NEE ? L.prev_pdf : 0.0f});
-            st4(out_d + pos, f4{L.d.x, L.d.y, L.d.z, u2f(pack_ctl(L.sample, L.depth, L.lobe))});
+            st4(out_d + pos, f4{L.d.x, L.d.y, L.d.z, u2f(pack_ctl(L.sample, L.depth, L.lobe) | resume_bit)});
             st4(out_t + pos, f4{L.thr.x, L.thr.y, L.thr.z, u2f(L.rng)});
             out_q[pos] = lane;
         }
@@ -194,12 +257,13 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
 struct ShadowRaySource {
     const f4* sh_o;
     const f4* sh_d;
-    __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
+    __device__ __forceinline__ bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
         const f4 a = ld4(sh_o + i), b = ld4(sh_d + i);
         o = f3{a.x, a.y, a.z};
         d = f3{b.x, b.y, b.z};
         tmin = kTMin;
         tmax = a.w;
+        return false;
     }
 };
 struct ShadowSink {
@@ -230,11 +294,11 @@ struct ShadowSink {
     }
 };
 
-__global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_shadow(SceneView sv, LaneArrays la, int k) {
+__global__ void __launch_bounds__(kWalkBlock, kWalkMinBlocks) k_shadow(SceneView sv, LaneArrays la, int k) {
     const uint32_t n = la.sh_counts[k];
     WalkCounters wc{0, 0};
     if (n)
-        warp_walk<false, true>(sv.nodes, sv.tris, n, la.sh_cursor + k, ShadowRaySource{la.sh_o, la.sh_d},
+        warp_walk<false, true, false>(sv.nodes, sv.tris, n, la.sh_cursor + k, ShadowRaySource{la.sh_o, la.sh_d},
                                ShadowSink{la.sh_d, la.sh_c, la.sh_f, la.rad, la.sum}, wc, sv.plane_magic);
 }
 
@@ -263,22 +327,24 @@ __global__ void __launch_bounds__(256) k_scatter_rows(SceneView sv, const f4* __
 
 struct CameraRaySource {
     SceneView sv;
-    __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
+    __device__ __forceinline__ bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
         const int px = (int)(i % (uint32_t)sv.width), py = (int)(i / (uint32_t)sv.width);
         uint32_t rng = rng_seed((uint32_t)px, (uint32_t)py);
         camera_ray(sv, px, py, rng, o, d);
         tmin = kTMin;
         tmax = kTMax;
+        return false;
     }
 };
 struct ArrayRaySource {
     const float *o, *d;
     float tmin, tmax;
-    __device__ __forceinline__ void load(uint32_t i, f3& oo, f3& dd, float& t0, float& t1) const {
+    __device__ __forceinline__ bool load(uint32_t i, f3& oo, f3& dd, float& t0, float& t1) const {
         oo = f3{o[3 * i], o[3 * i + 1], o[3 * i + 2]};
         dd = f3{d[3 * i], d[3 * i + 1], d[3 * i + 2]};
         t0 = tmin;
         t1 = tmax;
+        return false;
     }
 };
 struct ArrayHitSink {
@@ -286,16 +352,16 @@ struct ArrayHitSink {
     __device__ __forceinline__ void store(uint32_t i, const Hit& h) const { st4(hits + i, f4{h.t, h.u, h.v, u2f(h.tri)}); }
 };
 
-__global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_primary(SceneView sv, f4* hits, uint32_t* cursor) {
+__global__ void __launch_bounds__(kWalkBlock, kWalkMinBlocks) k_primary(SceneView sv, f4* hits, uint32_t* cursor) {
     WalkCounters wc{0, 0};
-    warp_walk<false, false>(sv.nodes, sv.tris, (uint32_t)(sv.width * sv.height), cursor, CameraRaySource{sv}, ArrayHitSink{hits}, wc,
+    warp_walk<false, false, false>(sv.nodes, sv.tris, (uint32_t)(sv.width * sv.height), cursor, CameraRaySource{sv}, ArrayHitSink{hits}, wc,
                      sv.plane_magic);
 }
 
-__global__ void __launch_bounds__(kBlock, PT_EXTEND_MIN_BLOCKS) k_trace(SceneView sv, const float* __restrict__ o, const float* __restrict__ d,
+__global__ void __launch_bounds__(kWalkBlock, kWalkMinBlocks) k_trace(SceneView sv, const float* __restrict__ o, const float* __restrict__ d,
                                                   int n, float tmin, float tmax, f4* hits, uint32_t* cursor) {
     WalkCounters wc{0, 0};
-    warp_walk<false, false>(sv.nodes, sv.tris, (uint32_t)n, cursor, ArrayRaySource{o, d, tmin, tmax}, ArrayHitSink{hits}, wc,
+    warp_walk<false, false, false>(sv.nodes, sv.tris, (uint32_t)n, cursor, ArrayRaySource{o, d, tmin, tmax}, ArrayHitSink{hits}, wc,
                      sv.plane_magic);
 }
 
@@ -324,18 +390,18 @@ __global__ void k_sample_disney(const Material* __restrict__ mats, int n, const 
 }
 
 static inline unsigned blocks(uint32_t n, int b) { return n ? (n + b - 1) / b : 1; }
-static int g_persistent_blocks = 148 * PT_BLOCKS_PER_SM;
-void set_persistent_blocks(int sm_count) { g_persistent_blocks = sm_count * PT_BLOCKS_PER_SM; }
-static inline unsigned pblocks(uint32_t n) { return std::min<unsigned>(blocks(n, kBlock), (unsigned)g_persistent_blocks); }
+static int g_persistent_blocks = 148 * PT_BLOCKS_PER_SM * 128 / kWalkBlock;
+void set_persistent_blocks(int sm_count) { g_persistent_blocks = sm_count * PT_BLOCKS_PER_SM * 128 / kWalkBlock; }
+static inline unsigned pblocks(uint32_t n) { return std::min<unsigned>(blocks(n, kWalkBlock), (unsigned)g_persistent_blocks); }
 
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, int part, int parts, uint32_t n_part, cudaStream_t st) {
     k_init_lanes<<<blocks(n_part, kBlock), kBlock, 0, st>>>(sv, la, part, parts, n_part);
 }
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st) {
     if (count)
-        k_extend<true><<<pblocks(max_count), kBlock, 0, st>>>(sv, la, k);
+        k_extend<true><<<pblocks(max_count), kWalkBlock, 0, st>>>(sv, la, k);
     else
-        k_extend<false><<<pblocks(max_count), kBlock, 0, st>>>(sv, la, k);
+        k_extend<false><<<pblocks(max_count), kWalkBlock, 0, st>>>(sv, la, k);
 }
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st) {
     if (sv.nee)
@@ -344,7 +410,7 @@ void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max
         k_shade<false><<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
 }
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st) {
-    k_shadow<<<pblocks(max_count), kBlock, 0, st>>>(sv, la, k);
+    k_shadow<<<pblocks(max_count), kWalkBlock, 0, st>>>(sv, la, k);
 }
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st) {
     k_resolve<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, inv_spp, rgba, mean);
@@ -353,11 +419,11 @@ void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStre
     k_scatter_rows<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, frame);
 }
 void launch_primary(const SceneView& sv, f4* hits, uint32_t* cursor, cudaStream_t st) {
-    k_primary<<<pblocks(sv.width * sv.height), kBlock, 0, st>>>(sv, hits, cursor);
+    k_primary<<<pblocks(sv.width * sv.height), kWalkBlock, 0, st>>>(sv, hits, cursor);
 }
 void launch_trace(const SceneView& sv, const float* o, const float* d, int n, float tmin, float tmax, f4* hits,
                   uint32_t* cursor, cudaStream_t st) {
-    k_trace<<<pblocks(n), kBlock, 0, st>>>(sv, o, d, n, tmin, tmax, hits, cursor);
+    k_trace<<<pblocks(n), kWalkBlock, 0, st>>>(sv, o, d, n, tmin, tmax, hits, cursor);
 }
 void launch_sample_disney(const Material* mats, int n, const int32_t* material, const float* wo, const int32_t* lobe_in,
                           const uint32_t* rng_in, float* f, float* wi, float* pdf, int32_t* lobe_out, uint32_t* rng_out,

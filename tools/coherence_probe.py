@@ -67,6 +67,15 @@ def main():
     px = np.nonzero(hit)[0]; x, y = px % W, px // W
     run("tiles_8x4", np.lexsort((x % 8, y % 4, x // 8, y // 4)))
     run("tiles_8x4_by_octant", np.lexsort((octant, x // 8, y // 4)))
+    # throughput against launch size: random subsets of the same ray population
+    for frac in (1.0, 0.5, 0.25, 0.125, 0.0625, 0.03125):
+        k = int(n * frac)
+        sub = rs.permutation(n)[:k]
+        o, d = np.ascontiguousarray(O1[sub]), np.ascontiguousarray(D1[sub])
+        ctx.trace(o, d); ctx.trace(o, d)
+        ms = ctx.stats()["render_ms"]
+        out[f"subset_{k}"] = dict(ms=ms, mrays=k / ms * 1e-3)
+        print("subset", k, out[f"subset_{k}"], flush=True)
     print(json.dumps(out))
     (R / "gpurun_out").mkdir(exist_ok=True)
     (R / "gpurun_out" / f"coherence_{scene}.json").write_text(json.dumps(out, indent=1))
