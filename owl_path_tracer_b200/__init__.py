@@ -35,7 +35,7 @@ class B200ptError(RuntimeError):
 
 class Config(C.Structure):
     _fields_ = [("device_ordinal", C.c_int32), ("rank", C.c_int32), ("world_size", C.c_int32),
-                ("shard_mode", C.c_int32), ("flags", C.c_int32)]
+                ("shard_mode", C.c_int32), ("flags", C.c_int32), ("streams_per_pixel", C.c_int32)]
 
 
 MATERIAL_FIELDS = ["base_color_r", "base_color_g", "base_color_b", "subsurface", "metallic", "specular",

@@ -9,9 +9,10 @@ from . import B200ptError, Config, HIT_DTYPE, MATERIAL_DTYPE, Stats, _ptr, _view
 
 
 class Context:
-    def __init__(self, device=0, rank=0, world_size=1, shard_mode=0, flags=0):
+    def __init__(self, device=0, rank=0, world_size=1, shard_mode=0, flags=0, streams=1):
+        """streams: RNG streams per pixel on this GPU (b200pt_config.streams_per_pixel); 1 = the reference's order."""
         self._L = lib()
-        cfg = Config(device, rank, world_size, shard_mode, flags)
+        cfg = Config(device, rank, world_size, shard_mode, flags, streams)
         self._h = C.c_void_p()
         self.rank, self.world_size = rank, world_size
         self._ck(self._L.b200pt_create(C.byref(cfg), C.byref(self._h)), "create")

@@ -71,7 +71,8 @@ struct b200pt_ctx {
     int width = 0, height = 0, max_samples = 0, max_depth = 0;
     // lanes + outputs
     LaneArrays la;
-    f4* d_frame = nullptr;      // full-frame sum buffer when lanes != pixels (ROWS sharding)
+    f4* d_frame = nullptr;      // full-frame sum buffer when lanes != pixels (ROWS sharding, several streams per pixel)
+    bool use_frame = false;     // the last render left its sums in d_frame
     uint32_t* d_rgba = nullptr;
     f4* d_mean = nullptr;
     uint32_t* h_rgba = nullptr;  // pinned
@@ -113,10 +114,14 @@ static void free_scene(b200pt_ctx* c) {
     c->built = false;
 }
 
-// samples per pixel this rank renders, and the lane -> pixel mapping
-static int rank_samples(const b200pt_ctx* c) {
-    if (c->cfg.world_size <= 1 || c->cfg.shard_mode == B200PT_SHARD_ROWS) return c->max_samples;
-    return c->max_samples / c->cfg.world_size + (c->cfg.rank < c->max_samples % c->cfg.world_size ? 1 : 0);
+// streams per pixel on this rank (b200pt_config.streams_per_pixel): SPP sharding only, and never more streams
+// in the whole job than samples
+static int rank_streams(const b200pt_ctx* c) {
+    int v = c->cfg.streams_per_pixel;
+    if (v <= 1 || (c->cfg.world_size > 1 && c->cfg.shard_mode == B200PT_SHARD_ROWS)) return 1;
+    const int world = std::max(c->cfg.world_size, 1);
+    while (v > 1 && (long long)v * world > (long long)c->max_samples) --v;
+    return v;
 }
 static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     SceneView sv{};
@@ -150,7 +155,7 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     memcpy(sv.cam_vertical, c->cam + 9, 12);
     sv.width = c->width;
     sv.height = c->height;
-    sv.max_samples = full_frame ? c->max_samples : rank_samples(c);
+    sv.max_samples = c->max_samples;
     sv.max_depth = c->max_depth;
     sv.n_materials = c->n_mats;
     sv.row_first = 0;
@@ -164,8 +169,18 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
             sv.row_step = c->cfg.world_size;
             const int rows = c->height > c->cfg.rank ? (c->height - c->cfg.rank + c->cfg.world_size - 1) / c->cfg.world_size : 0;
             sv.n_lanes = c->width * rows;
-        } else {
-            sv.seed_row_offset = c->cfg.rank * c->height;
+        }
+    }
+    if (!full_frame && !(c->cfg.world_size > 1 && c->cfg.shard_mode == B200PT_SHARD_ROWS)) {
+        // SPP sharding: the job's samples are split over world_size * V streams, this rank owns V
+        const int V = rank_streams(c), world = std::max(c->cfg.world_size, 1), G = world * V, g0 = c->cfg.rank * V;
+        const int rem = c->max_samples % G;
+        sv.max_samples = c->max_samples / G;
+        sv.stream_extra = std::max(0, std::min(V, rem - g0));
+        sv.seed_row_offset = g0 * c->height;
+        if (V > 1) {
+            sv.n_pix_lanes = sv.n_lanes;
+            sv.n_lanes *= V;
         }
     }
     return sv;
@@ -463,7 +478,8 @@ static uint32_t part_lanes(const SceneView& sv, int p, int parts) {
 static int ensure_lanes(b200pt_ctx* c, const SceneView& sv, int parts) {
     const size_t px = (size_t)c->width * c->height;
     const uint32_t need = (uint32_t)std::max(sv.n_lanes, 1);
-    if (c->la.capacity < need || c->fb_pixels != px || c->n_parts != parts || c->lanes_width != c->width) {
+    const bool need_frame = sv.n_pix_lanes > 0 || (c->cfg.world_size > 1 && c->cfg.shard_mode == B200PT_SHARD_ROWS);
+    if (c->la.capacity < need || c->fb_pixels != px || c->n_parts != parts || c->lanes_width != c->width || (need_frame && !c->d_frame)) {
         CU(cudaDeviceSynchronize());
         free_lanes(c);
         const bool nee = (c->cfg.flags & B200PT_FLAG_NEE) != 0;
@@ -503,7 +519,7 @@ static int ensure_lanes(b200pt_ctx* c, const SceneView& sv, int parts) {
         c->la.capacity = need;
         c->n_parts = parts;
         c->lanes_width = c->width;
-        if (c->cfg.world_size > 1 && c->cfg.shard_mode == B200PT_SHARD_ROWS) CU(cudaMalloc(&c->d_frame, sizeof(f4) * px));
+        if (need_frame) CU(cudaMalloc(&c->d_frame, sizeof(f4) * px));
         CU(cudaMalloc(&c->d_rgba, sizeof(uint32_t) * px));
         CU(cudaMalloc(&c->d_mean, sizeof(f4) * px));
         CU(cudaMallocHost(&c->h_rgba, sizeof(uint32_t) * px));
@@ -542,7 +558,7 @@ static int render_local(b200pt_ctx* c) {
     CU(cudaMemsetAsync(c->la.walk_counters, 0, sizeof(unsigned long long) * 2, st));
     CU(cudaEventRecord(c->ev0, st));  // the other parts' streams start behind this point
     uint32_t active[kMaxParts] = {};
-    const bool any_work = sv.n_lanes > 0 && sv.max_samples > 0 && sv.max_depth > 0;
+    const bool any_work = sv.n_lanes > 0 && sv.max_samples + sv.stream_extra > 0 && sv.max_depth > 0;
     if (!any_work) CU(cudaMemsetAsync(c->la.sum, 0, sizeof(f4) * c->la.capacity, st));
     for (int p = 1; p < parts; ++p) CU(cudaStreamWaitEvent(c->part_stream[p], c->ev0, 0));
     for (int p = 0; p < parts; ++p) {
@@ -649,10 +665,16 @@ static int render_local(b200pt_ctx* c) {
         CU(cudaEventRecord(c->part_done[p], c->part_stream[p]));
         CU(cudaStreamWaitEvent(st, c->part_done[p], 0));
     }
-    if (c->d_frame) {  // ROWS sharding: lane sums -> full frame, zeros elsewhere
+    c->use_frame = false;
+    if (sv.n_pix_lanes > 0) {  // several streams per pixel: add the streams' sums in stream order
+        launch_fold_streams(c->la.sum, c->d_frame, (uint32_t)sv.n_pix_lanes, sv.n_lanes / sv.n_pix_lanes, st);
+        S.kernel_launches++;
+        c->use_frame = true;
+    } else if (c->cfg.world_size > 1 && c->cfg.shard_mode == B200PT_SHARD_ROWS) {  // lane sums -> full frame, zeros elsewhere
         CU(cudaMemsetAsync(c->d_frame, 0, sizeof(f4) * c->fb_pixels, st));
         if (sv.n_lanes > 0) launch_scatter_rows(sv, c->la.sum, c->d_frame, st);
         S.kernel_launches++;
+        c->use_frame = true;
     }
     CU(cudaEventRecord(c->ev1, st));
     CU(cudaStreamSynchronize(st));
@@ -661,7 +683,11 @@ static int render_local(b200pt_ctx* c) {
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     S.render_ms = ms;
     S.other_ms = timing ? ms - S.extend_ms - S.shade_ms - S.shadow_ms : 0;
-    S.paths = (uint64_t)std::max(sv.n_lanes, 0) * (uint64_t)sv.max_samples;
+    {
+        const uint64_t pix = (uint64_t)std::max(sv.n_pix_lanes > 0 ? sv.n_pix_lanes : sv.n_lanes, 0);
+        const uint64_t V = sv.n_pix_lanes > 0 ? (uint64_t)(sv.n_lanes / sv.n_pix_lanes) : 1u;
+        S.paths = pix * (V * (uint64_t)sv.max_samples + (uint64_t)sv.stream_extra);
+    }
     if (count) {
         unsigned long long wc[2];
         CU(cudaMemcpy(wc, c->la.walk_counters, sizeof wc, cudaMemcpyDeviceToHost));
@@ -678,7 +704,7 @@ extern "C" int b200pt_resolve(b200pt_ctx* c) {
     if (!c->rendered) return fail(B200PT_ERR_INVALID, "resolve: nothing rendered");
     CU(cudaSetDevice(c->cfg.device_ordinal));
     const SceneView full = make_view(c, true);
-    const f4* src = c->d_frame ? c->d_frame : c->la.sum;
+    const f4* src = c->use_frame ? c->d_frame : c->la.sum;
     const float inv = 1.0f / static_cast<float>(c->max_samples);  // device.cu:247
     launch_resolve(full, src, inv, c->d_rgba, c->d_mean, c->stream);
     c->stats.kernel_launches++;
@@ -700,7 +726,7 @@ extern "C" int b200pt_render(b200pt_ctx* c) {
 extern "C" int b200pt_accum_buffer(b200pt_ctx* c, void** device_ptr, size_t* n_floats) {
     if (!c || !device_ptr || !n_floats) return fail(B200PT_ERR_INVALID, "accum_buffer: null");
     if (!c->rendered) return fail(B200PT_ERR_INVALID, "accum_buffer: nothing rendered");
-    *device_ptr = c->d_frame ? (void*)c->d_frame : (void*)c->la.sum;
+    *device_ptr = c->use_frame ? (void*)c->d_frame : (void*)c->la.sum;
     *n_floats = 4 * c->fb_pixels;
     return B200PT_OK;
 }

@@ -62,6 +62,7 @@ void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st);
 void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStream_t st);
+void launch_fold_streams(const f4* sum, f4* out, uint32_t n_pix, int streams, cudaStream_t st);
 void launch_primary(const SceneView& sv, f4* hits, uint32_t* cursor, cudaStream_t st);
 void launch_trace(const SceneView& sv, const float* o, const float* d, int n, float tmin, float tmax, f4* hits,
                   uint32_t* cursor, cudaStream_t st);

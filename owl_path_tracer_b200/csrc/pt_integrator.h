@@ -69,13 +69,18 @@ struct SceneView {
     float env_intensity;
     float cam_origin[3], cam_llc[3], cam_horizontal[3], cam_vertical[3];
     int32_t width, height;     // full frame
-    int32_t max_samples;       // samples this rank renders per pixel
+    int32_t max_samples;       // samples a stream of this rank renders per pixel (streams < stream_extra: one more)
     int32_t max_depth;
     int32_t n_materials;
     // lane -> pixel:  x = lane % width, y = row_first + row_step * (lane / width)
     int32_t row_first, row_step;
-    int32_t seed_row_offset;   // added to y when seeding (per-rank streams: rank * height)
+    int32_t seed_row_offset;   // added to y when seeding (per-rank streams: first stream of the rank * height)
     int32_t n_lanes;
+    // Several RNG streams per pixel on one GPU (b200pt_config.streams_per_pixel = V > 1, SPP sharding): the rank's
+    // lanes are V copies of its pixels, lane = v * n_pix_lanes + pixel lane; copy v is stream g = rank * V + v of
+    // the world_size * V streams the samples are split over — the very streams an (world_size * V)-GPU job uses.
+    int32_t n_pix_lanes;       // pixel lanes of the rank; 0: one stream (lane = pixel lane)
+    int32_t stream_extra;      // the first stream_extra streams of the rank render max_samples + 1 samples
     // next-event estimation (B200PT_FLAG_NEE); n_lights == 0 or nee == 0: the reference's estimator verbatim
     const LightTri* lights;
     const float* light_cdf;    // n_lights ascending values, last = 1
@@ -97,7 +102,14 @@ PT_HD uint32_t ctl_sample(uint32_t c) { return c & 0xFFFFFu; }
 PT_HD uint32_t ctl_depth(uint32_t c) { return (c >> 20) & 0xFFu; }
 PT_HD int ctl_lobe(uint32_t c) { return (int)((c >> 28) & 7u) - 1; }
 
+PT_HD uint32_t lane_stream(const SceneView& sv, uint32_t lane) {
+    return sv.n_pix_lanes > 0 ? lane / (uint32_t)sv.n_pix_lanes : 0u;
+}
+PT_HD uint32_t lane_samples(const SceneView& sv, uint32_t lane) {
+    return (uint32_t)sv.max_samples + (lane_stream(sv, lane) < (uint32_t)sv.stream_extra ? 1u : 0u);
+}
 PT_HD void lane_pixel(const SceneView& sv, uint32_t lane, int& x, int& y) {
+    if (sv.n_pix_lanes > 0) lane %= (uint32_t)sv.n_pix_lanes;
     x = (int)(lane % (uint32_t)sv.width);
     y = sv.row_first + sv.row_step * (int)(lane / (uint32_t)sv.width);
 }
@@ -180,6 +192,7 @@ struct LaneState {
     bool sample_ended;
     uint32_t rng;
     uint32_t sample;  // index of the sample in flight
+    uint32_t max_samples;  // samples this lane renders (lane_samples)
     uint32_t depth;   // loop counter of trace_path
     int lobe;         // sampled_lobe, persists across bounces (device.cu:127)
     // next-event estimation mode only
@@ -201,7 +214,7 @@ PT_HD ShadeResult end_sample(const SceneView& sv, LaneState& L, int px, int py, 
     L.contrib = contrib;  // caller does color += trace_path(...), device.cu:243
     L.sample_ended = true;
     L.sample += 1;
-    if (L.sample >= (uint32_t)sv.max_samples) return LANE_DONE;
+    if (L.sample >= L.max_samples) return LANE_DONE;
     camera_ray(sv, px, py, L.rng, L.o, L.d);
     L.thr = mk3(1.0f);
     L.depth = 0;

@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays 
     const uint32_t lane = ((i / w) * (uint32_t)parts + (uint32_t)part) * w + i % w;
     int px, py;
     lane_pixel(sv, lane, px, py);
-    uint32_t rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset));  // device.cu:226
+    uint32_t rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset + (int)lane_stream(sv, lane) * sv.height));  // device.cu:226
     f3 o, d;
     camera_ray(sv, px, py, rng, o, d);
     st4(la.ray_o[0] + i, f4{o.x, o.y, o.z, -1.0f});  // .w: prev_pdf of the NEE mode (camera ray: count emitters fully)
@@ -187,6 +187,7 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
         L.sample = ctl_sample(ctl);
         L.depth = ctl_depth(ctl);
         L.lobe = ctl_lobe(ctl);
+        L.max_samples = lane_samples(sv, lane);
         Hit h{hv.x, hv.y, hv.z, f2u(hv.w)};
         int px, py;
         lane_pixel(sv, lane, px, py);
@@ -316,6 +317,21 @@ __global__ void __launch_bounds__(256) k_resolve(SceneView sv, const f4* __restr
     st4(mean + ofs, f4{c.x, c.y, c.z, 1.0f});
 }
 
+// several streams per pixel: per-pixel sum of the streams' sums, added in stream order (the order in which the
+// oracle adds the partial frames of the corresponding ranks)
+__global__ void __launch_bounds__(256) k_fold_streams(const f4* __restrict__ sum, f4* __restrict__ out, uint32_t n_pix, int streams) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pix) return;
+    f4 a = ld4(sum + i);
+    for (int v = 1; v < streams; ++v) {
+        const f4 b = ld4(sum + (size_t)v * n_pix + i);
+        a.x += b.x;
+        a.y += b.y;
+        a.z += b.z;
+    }
+    st4(out + i, a);
+}
+
 // ROWS sharding: lane-indexed sums -> full-frame buffer (x + W*y), zero elsewhere
 __global__ void __launch_bounds__(256) k_scatter_rows(SceneView sv, const f4* __restrict__ sum, f4* __restrict__ frame) {
     const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
@@ -414,6 +430,9 @@ void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t ma
 }
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st) {
     k_resolve<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, inv_spp, rgba, mean);
+}
+void launch_fold_streams(const f4* sum, f4* out, uint32_t n_pix, int streams, cudaStream_t st) {
+    k_fold_streams<<<blocks(n_pix, 256), 256, 0, st>>>(sum, out, n_pix, streams);
 }
 void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStream_t st) {
     k_scatter_rows<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, frame);

@@ -360,6 +360,7 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
             int px, py;
             lane_pixel(sv, lane, px, py);
             LaneState L{};
+            L.max_samples = (uint32_t)sv.max_samples;
             L.rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset));
             camera_ray(sv, px, py, L.rng, L.o, L.d);
             L.thr = mk3(1.0f);

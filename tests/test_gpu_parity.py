@@ -231,6 +231,34 @@ def test_sharded_ranks_on_one_gpu(mode):
         assert (bits(ref) == bits(o.render()["sum"])).all()
 
 
+def test_streams_per_pixel_are_the_streams_of_a_larger_job():
+    """V streams per pixel on one GPU = the streams g = rank*V + v of a (world*V)-rank SPP-sharded job: every
+    rank's buffer equals the oracle's partial frames of its streams added in stream order, bit for bit."""
+    from owl_path_tracer_b200.distributed import accum_tensor
+    sc = pt.Scene(scene="cornell-box", width=64, height=48, spp=10, depth=6, env="color", env_intensity=0.0)
+    o = Oracle(det=True).load_scene(sc)
+    for world, V in ((1, 4), (2, 2), (1, 3)):
+        G = world * V
+        rays = 0
+        for r in range(world):
+            ctx = gpu_for(sc, rank=r, world_size=world, shard_mode=pt.SHARD_SPP, streams=V)
+            ctx.render()
+            got = accum_tensor(ctx).cpu().numpy().reshape(48, 64, 4)
+            ref = None
+            for v in range(V):
+                part = o.render(rank=r * V + v, world=G, shard_mode=pt.SHARD_SPP)
+                ref = part["sum"].copy() if ref is None else ref + part["sum"]
+                rays += part["rays"]
+            assert (bits(got[..., :3]) == bits(ref[..., :3])).all()
+            rays -= ctx.stats()["rays"]
+            if world == 1:   # resolved frame = folded sum / total spp (the frame is stored top row first)
+                f = ctx.framebuffer_f32()[..., :3]
+                want = ref[..., :3] * np.float32(1.0) / np.float32(10)
+                assert np.allclose(np.sort(f.ravel()), np.sort(want.ravel()), rtol=1e-6, atol=0)
+            ctx.close()
+        assert rays == 0
+
+
 def test_full_size_properties_dragon_1080p():
     """BASELINE's headline size (dragon 1920x1080, depth 8) at low spp: size-independent
     properties — run-to-run determinism, ROWS-sharded tiles reproduce the frame bit for bit,

@@ -34,7 +34,7 @@ def test_c_abi_exports_every_declared_symbol():
 
 def test_struct_layouts_match_header():
     assert pt.MATERIAL_DTYPE.itemsize == 68 and pt.HIT_DTYPE.itemsize == 20
-    assert C.sizeof(pt.Config) == 20
+    assert C.sizeof(pt.Config) == 24          # b200pt_config: six int32
 
 
 def test_no_cpu_fallback():

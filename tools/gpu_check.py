@@ -57,6 +57,17 @@ if __name__ == "__main__":
                 ctx.close()
         os.environ.pop("B200PT_PARTS", None)
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "streams":
+        # several RNG streams per pixel: frame time at equal total work
+        for scene, spp in (("dragon", 128), ("car", 128)):
+            for V in (1, 2, 4, 8, 16):
+                sc = pt.Scene(scene=scene, width=1920, height=1080, spp=spp, depth=8, env="color", env_intensity=0.0)
+                ctx = pt.Context(flags=0, streams=V); ctx.bind(sc); ctx.render(); ctx.render()
+                st = ctx.stats()
+                print(json.dumps(dict(scene=scene, spp=spp, streams=V, render_ms=st['render_ms'], mrays=st['rays'] / st['render_ms'] * 1e-3,
+                                      rays=st['rays'], paths=st['paths'], launches=st['kernel_launches'])), flush=True)
+                ctx.close()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "nee":
         # NEE mode: throughput with the shadow kernel, and error at equal spp / equal time against a long render
         for scene, w, h, spp, env in (("cornell-box", 512, 512, 64, "color"), ("sphere", 1024, 1024, 32, "map"), ("car", 1920, 1080, 32, "color"), ("dragon", 1920, 1080, 32, "color")):
