@@ -113,6 +113,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--streams-mode", type=int, default=8, help="also time the frame with this many RNG streams per pixel (0: skip)")
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (a smaller workload is NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -202,6 +203,24 @@ def main():
         step_e2e()
     e2e = timed(step_e2e, args.steps)
 
+    # Throughput mode (reported beside the headline, never as `value`): 8 RNG streams per pixel on each GPU
+    # (b200pt_config.streams_per_pixel) — the streams an 8x larger SPP-sharded job uses, same total samples.
+    tm = None
+    if args.streams_mode > 1:
+        c8 = pt.Context(device=local, rank=rank, world_size=world, shard_mode=pt.SHARD_SPP, flags=0, streams=args.streams_mode)
+        c8.bind(sc)
+        main_ctx, ctx = ctx, c8
+        for _ in range(min(args.warmup, 2)):
+            step_resident()
+        r8 = timed(step_resident, args.steps)
+        ctx = main_ctx
+        c8.close()
+        tm = dict(streams_per_pixel=args.streams_mode, value=r8["rays_all"] / (r8["wall_ms"] * 1e-3) * 1e-6, unit="Mrays/s",
+                  ms_per_step=r8["wall_ms"] / args.steps,
+                  note="same frame, same total spp; every pixel rendered by %d concurrent RNG streams (the streams of a %d-rank "
+                       "SPP-sharded job, bit-equal to the oracle with that keying: tests/test_gpu_parity.py); not the reference's "
+                       "single-stream order, hence not the headline" % (args.streams_mode, world * args.streams_mode))
+
     # Per-kernel times: the timed region above renders two interleaved sub-frames on two streams without
     # per-kernel events (the events cost ~3 % and overlapped kernels cannot be timed one by one), so the
     # launch durations of the roofline come from one more frame of the same workload (this rank's share),
@@ -279,7 +298,7 @@ def main():
                      ms_per_step=e2e["wall_ms"] / args.steps),
             gpu_launches=res["launches_all"],
             kernel_ms_per_step=dict(extend=kt["extend_ms"], shade=kt["shade_ms"], frame_serial=kt["render_ms"]) if kt else None,
-            clocks=clocks, roofline=roof, cpu_baseline=cpu,
+            clocks=clocks, roofline=roof, cpu_baseline=cpu, throughput_mode=tm,
             parity="tests/test_gpu_parity.py: bit-exact vs oracle (hits, float frame); relMSE <= 1e-3 vs glibc oracle",
             notes=sc.notes)
         print(json.dumps(line), flush=True)
