@@ -42,7 +42,7 @@ struct LaneArrays {
     uint32_t* sh_counts = nullptr;  // kBatch request counts
     uint32_t* sh_cursor = nullptr;  // kBatch fetch cursors of k_shadow
     // parked walks (pt_walk_warp.cuh SUSPEND): per lane kSuspWords 16-byte words — hit so far | node group,
-    // triangle group | sp, stack top | stack entries below the top, two per word
+    // triangle group | sp, stack top | the (at most kSuspStack) stack entries below the top, two per word
     u4* susp = nullptr;
     uint32_t* pending = nullptr;  // kBatch counts of the lanes k_shade passed through because their walk is parked
     uint32_t* counts = nullptr;   // kBatch + 1 queue lengths
@@ -51,7 +51,7 @@ struct LaneArrays {
     uint32_t capacity = 0;
 };
 
-constexpr int kSuspWords = 3 + kStackSize;  // 2 * kStackSize stack entries of 8 bytes (pt_walk_warp.cuh kWalkStack)
+constexpr int kSuspWords = 3 + kSuspStack / 2;  // 176 bytes per lane: hit, groups, top + kSuspStack stack entries of 8 bytes
 constexpr int kMaxParts = 4;  // interleaved sub-frames walked on separate streams (api.cu: render_local)
 constexpr int kBatch = 32;  // wavefront iterations between host checks (even: the state sets alternate with k)
 

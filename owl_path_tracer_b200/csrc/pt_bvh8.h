@@ -88,6 +88,8 @@ struct Hit {
     uint32_t tri;  // global triangle id, 0xFFFFFFFF = miss
 };
 constexpr uint32_t kNoHit = 0xFFFFFFFFu;
+constexpr uint32_t kPending = 0xFFFFFFFEu;  // hit.tri of a parked walk (pt_walk_warp.cuh SUSPEND)
+constexpr int kSuspStack = 16;               // a walk is parked only while at most this many entries sit below its stack top
 constexpr int kStackSize = 32;  // node groups; the builder refuses deeper trees
 
 // Moller-Trumbore with edges e1 = v1 - v0, e2 = v2 - v0.  Expression order is part of

@@ -66,7 +66,6 @@ __device__ __forceinline__ f4 ldg4f(const f4* p) {
 //       void restore(i, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack)        (SUSPEND only)
 // Sink: void store(uint32_t i, const Hit& h)
 //       void suspend(i, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack)        (SUSPEND only)
-constexpr uint32_t kPending = 0xFFFFFFFEu;  // hit.tri of a parked ray
 template <bool COUNT, bool ANY, bool SUSPEND, class Src, class Sink>
 __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const TriPair* __restrict__ tris, uint32_t n,
                                           uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic) {
@@ -125,7 +124,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         if (exhausted) {
             // out of new rays: run what is left; a SUSPEND walk parks the last few rays of the warp instead
             if constexpr (SUSPEND) {
-                if (__popc(act) <= park) {
+                if (__popc(act) <= park && __all_sync(FULL, !has_ray || sp <= kSuspStack + 1)) {
                     if (has_ray) sink.suspend(ray_index, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack);
                     break;
                 }
