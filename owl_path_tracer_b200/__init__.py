@@ -152,6 +152,7 @@ def host_lib() -> C.CDLL:
     H.b200pt_scene_bind.argtypes = [P, P]
     H.b200pt_scene_test_loop.argtypes = [P, P, C.c_char_p]
     H.b200pt_write_png.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
+    H.b200pt_write_pfm.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
     H.b200pt_write_obj.argtypes = [P, C.c_char_p]
     H._typed = True
     return H

@@ -184,7 +184,13 @@ void render_frame(b200pt_ctx* ctx, const program_data& pdata, const test_data& t
     result.width = pdata.buffer_size[0];
     result.height = pdata.buffer_size[1];
     result.pixels.assign(fb, fb + (size_t)result.width * result.height);
-    write_image(result, pdata.scene + "_" + tdata.name + "_" + tdata.attribute_name + "(" + values + ").png", out_dir);
+    const std::string stem = pdata.scene + "_" + tdata.name + "_" + tdata.attribute_name + "(" + values + ")";
+    write_image(result, stem + ".png", out_dir);
+    if (pdata.write_pfm) {  // float output next to the PNG (the reference only has the 8-bit image)
+        const float* mean = nullptr;
+        check(b200pt_framebuffer_f32(ctx, &mean), "framebuffer_f32");
+        write_pfm(out_dir + "/" + stem + ".pfm", result.width, result.height, mean);
+    }
 }
 
 // test_loop, application.hpp:89-108

@@ -145,6 +145,9 @@ int b200pt_scene_test_loop(b200pt_scene* s, b200pt_ctx* ctx, const char* out_dir
 int b200pt_write_png(const char* path, int32_t w, int32_t h, const uint32_t* rgba) {
     return guard([&] { host::write_png(path, w, h, rgba); });
 }
+int b200pt_write_pfm(const char* path, int32_t w, int32_t h, const float* rgba_top_first) {
+    return guard([&] { host::write_pfm(path, w, h, rgba_top_first); });
+}
 int b200pt_write_obj(const b200pt_scene* s, const char* path) {
     return guard([&] {
         FILE* f = fopen(path, "w");

@@ -333,6 +333,23 @@ std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::s
 // ------------------------------------------------------------------ PNG
 static uint32_t be32(const unsigned char* p) { return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]; }
 
+void write_pfm(const std::string& file_path, int w, int h, const float* rgba_top_first) {
+    FILE* f = fopen(file_path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + file_path);
+    fprintf(f, "PF\n%d %d\n-1.0\n", w, h);  // negative scale: little endian
+    std::vector<float> row((size_t)w * 3);
+    for (int y = h - 1; y >= 0; --y) {  // PFM stores the bottom row first
+        const float* src = rgba_top_first + (size_t)y * (size_t)w * 4;
+        for (int x = 0; x < w; ++x) {
+            row[3 * (size_t)x + 0] = src[4 * (size_t)x + 0];
+            row[3 * (size_t)x + 1] = src[4 * (size_t)x + 1];
+            row[3 * (size_t)x + 2] = src[4 * (size_t)x + 2];
+        }
+        fwrite(row.data(), sizeof(float), row.size(), f);
+    }
+    fclose(f);
+}
+
 void write_png(const std::string& file_path, int w, int h, const uint32_t* rgba) {
     std::vector<unsigned char> raw((size_t)h * (1 + (size_t)w * 4));
     for (int y = 0; y < h; ++y) {

@@ -15,6 +15,8 @@ std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::s
 image_buffer load_image(const std::string& name, const std::string& path);     // image_buffer.cpp:36-59 (v-flipped)
 void write_image(const image_buffer& i, const std::string& name, const std::string& path);  // image_buffer.cpp:25-34
 void write_png(const std::string& file_path, int w, int h, const uint32_t* rgba);
+// Portable Float Map ("PF", little endian, rows bottom to top) of a top-row-first float RGBA frame
+void write_pfm(const std::string& file_path, int w, int h, const float* rgba_top_first);
 image_buffer ldr_from_rgbe(int w, int h, const unsigned char* rgbe);          // stb hdr -> 8 bit route
 void rgbe_from_float(const float* rgb, unsigned char* rgbe);
 void flip_rows(image_buffer& img);                                             // image_buffer.cpp:50-55

@@ -6,6 +6,7 @@
 // directory.  Optional flags (all default to the reference behaviour):
 //   --assets DIR  --scene NAME  --size W H  --spp N  --depth N  --env color|auto|map
 //   --env-intensity F  --detail N  --device K  --out DIR  --stats
+//   --nee (light sampling + MIS mode)  --streams V (RNG streams per pixel)  --pfm (float frame next to the PNG)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -18,8 +19,8 @@ int main(int argc, char** argv) {
     std::string assets_path = std::filesystem::current_path().string() + "/assets";
     std::string out_dir = std::filesystem::current_path().string();
     host::load_options opt;
-    int device = 0;
-    bool stats = false;
+    int device = 0, flags = 0, streams = 1;
+    bool stats = false, pfm = false;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto need = [&](int n) {
@@ -43,6 +44,15 @@ int main(int argc, char** argv) {
         else if (a == "--device") { need(1); device = atoi(argv[++i]); }
         else if (a == "--out") { need(1); out_dir = argv[++i]; }
         else if (a == "--stats") stats = true;
+        else if (a == "--nee") flags |= B200PT_FLAG_NEE;
+        else if (a == "--streams") { need(1); streams = atoi(argv[++i]); }
+        else if (a == "--pfm") pfm = true;
+        else if (a == "--help" || a == "-h") {
+            printf("path_tracer [--assets DIR] [--scene NAME] [--size W H] [--spp N] [--depth N] [--env color|auto|map]\n"
+                   "            [--env-intensity F] [--detail N] [--device K] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"
+                   "without arguments: ./assets/settings.json and its scene, as the reference's executable\n");
+            return 0;
+        }
         else {
             fprintf(stderr, "unknown argument %s\n", a.c_str());
             return 2;
@@ -58,6 +68,9 @@ int main(int argc, char** argv) {
         cfg.device_ordinal = device;
         cfg.rank = 0;
         cfg.world_size = 1;
+        cfg.flags = flags;
+        cfg.streams_per_pixel = streams;
+        pdata.write_pfm = pfm;
         b200pt_ctx* ctx = nullptr;
         if (b200pt_create(&cfg, &ctx) != B200PT_OK) {
             fprintf(stderr, "b200pt_create failed: %s\n", b200pt_last_error());

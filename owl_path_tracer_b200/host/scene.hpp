@@ -85,6 +85,7 @@ struct program_data {
     std::vector<std::pair<std::string, std::shared_ptr<mesh>>> meshes;
     std::vector<entity> entities;
     std::vector<std::string> notes;  // which inputs were procedural stand-ins
+    bool write_pfm = false;          // also write the float frame (mean radiance before quantisation) as .pfm
 };
 
 }  // namespace host

@@ -96,6 +96,13 @@ def test_converged_image_vs_independent_oracle():
     assert rel_mse(pool(g), pool(o)) <= 1e-3
     assert abs(g.mean() - o.mean()) <= 0.005 * o.mean()
     ctx.close()
+    # the same gate for the throughput mode: 8 RNG streams per pixel against the single-stream oracle
+    ctx = gpu_for(sc, streams=8)
+    ctx.render()
+    g8 = ctx.framebuffer_f32()[..., :3]
+    assert rel_mse(pool(g8), pool(o)) <= 1e-3
+    assert abs(g8.mean() - o.mean()) <= 0.005 * o.mean()
+    ctx.close()
 
 
 def test_material_sweep_frames():

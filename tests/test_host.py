@@ -120,6 +120,20 @@ def png_pixels(path):
     return np.ascontiguousarray(raw[:, 1:]).view(np.uint32).reshape(h, w)
 
 
+def test_pfm_writer(tmp_path):
+    """Float frame next to the PNG (path_tracer --pfm): RGB, little endian, bottom row first."""
+    H = pt.host_lib()
+    rs = np.random.RandomState(1)
+    img = rs.rand(5, 7, 4).astype(np.float32) * 30.0
+    p = tmp_path / "x.pfm"
+    assert H.b200pt_write_pfm(str(p).encode(), 7, 5, img.ctypes.data) == 0
+    raw = p.read_bytes()
+    head, w_h, scale, body = raw.split(b"\n", 3)
+    assert head == b"PF" and w_h == b"7 5" and float(scale) < 0
+    back = np.frombuffer(body, "<f4").reshape(5, 7, 3)[::-1]
+    assert np.array_equal(back, img[..., :3])
+
+
 def test_png_writer_and_texture_reader_round_trip(tmp_path):
     H = pt.host_lib()
     rs = np.random.RandomState(0)
