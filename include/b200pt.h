@@ -160,6 +160,12 @@ int b200pt_set_materials(b200pt_ctx* ctx, const b200pt_material* m, int32_t nm);
  * rgba may be NULL / w,h 0 ("environment_map" handle 0, device.cu:138). */
 int b200pt_set_environment(b200pt_ctx* ctx, const uint8_t* rgba, int32_t w, int32_t h,
                            int32_t use, int32_t auto_, const float color[3], float intensity);
+/* Float environment map, a superset of the reference behind its own entry point: rgb = w*h*3
+ * floats of linear radiance, same row order, point sampling and direction mapping as the RGBA8 map, values not
+ * limited to [0, 1] (the reference's own route squeezes the .hdr through stb's LDR conversion).
+ * Replaces a map set with b200pt_set_environment and vice versa. */
+int b200pt_set_environment_f32(b200pt_ctx* ctx, const float* rgb, int32_t w, int32_t h,
+                               int32_t use, int32_t auto_, const float color[3], float intensity);
 
 /* camera_data (camera.hpp:16-22) as bound at application.cpp:272-275. */
 int b200pt_set_camera(b200pt_ctx* ctx, const float origin[3], const float llc[3],

@@ -32,6 +32,8 @@ typedef struct b200pt_load_options {
     float env_intensity;      /* < 0: settings.json                                     */
     int32_t detail;           /* procedural stand-in detail (0 = default)               */
     int32_t no_procedural;    /* 1: fail like the reference when an asset is missing    */
+    int32_t env_float;        /* 1: also keep environment.hdr as float radiance and bind it
+                                 through b200pt_set_environment_f32                     */
 } b200pt_load_options;
 
 typedef struct b200pt_scene_info_t {
@@ -44,6 +46,7 @@ typedef struct b200pt_scene_info_t {
     float cam_origin[3], cam_llc[3], cam_horizontal[3], cam_vertical[3];
     int32_t n_entities, n_materials, n_notes;
     int64_t n_triangles;
+    const float* env_f32;     /* env_w*env_h*3 linear RGB (load option env_float) or NULL */
 } b200pt_scene_info_t;
 
 typedef struct b200pt_entity_view {

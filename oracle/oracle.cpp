@@ -514,6 +514,7 @@ struct Scene {
     std::vector<MeshRec> meshes;
     std::vector<Mat> mats;
     std::vector<uint32_t> env;
+    std::vector<float> env_f32;   // float RGB map (oracle_set_environment_f32) instead of env; same addressing
     int env_w = 0, env_h = 0;
     bool env_use = false, env_auto = false;
     V3 env_color{0, 0, 0};
@@ -727,15 +728,23 @@ V3 fetch_rgba8(const uint32_t* img, int w, int h, float u, float v) {
 V3 sample_environment(const Scene& sc, V3 dir) {                                         // device.cu:23-39
     float u = 0.5f + m_atan2(dir.x, dir.z) / (2.0f * pi);
     float v = 0.5f + m_asin(dir.y) / pi;
+    if (!sc.env_f32.empty()) {  // float map: same point sampling, radiance not limited to [0, 1]
+        float fx = floorf(u * (float)sc.env_w), fy = floorf(v * (float)sc.env_h);
+        int ix = (fx >= 0.0f) ? (fx < (float)sc.env_w ? (int)fx : sc.env_w - 1) : 0;
+        int iy = (fy >= 0.0f) ? (fy < (float)sc.env_h ? (int)fy : sc.env_h - 1) : 0;
+        const float* p = &sc.env_f32[3 * ((size_t)iy * (size_t)sc.env_w + (size_t)ix)];
+        return {p[0], p[1], p[2]};
+    }
     return fetch_rgba8(sc.env.data(), sc.env_w, sc.env_h, u, v);
 }
+inline bool has_env_map(const Scene& sc) { return !sc.env.empty() || !sc.env_f32.empty(); }
 
 // --- NEE mode, importance sampling of the environment map -------------------------------------
 // P(texel) ~ Rec.709 luminance of the RGBA8 texel; sums in binary64, rounded once per entry.
 void build_env_table(Scene& sc) {
     sc.env_cdf_rows.clear();
     sc.env_cdf_cols.clear();
-    if (!sc.nee || !sc.env_use || sc.env.empty()) return;
+    if (!sc.nee || !sc.env_use || !has_env_map(sc)) return;
     const int w = sc.env_w, h = sc.env_h;
     sc.env_cdf_rows.resize((size_t)h);
     sc.env_cdf_cols.resize((size_t)w * (size_t)h);
@@ -744,9 +753,16 @@ void build_env_table(Scene& sc) {
     for (int j = 0; j < h; ++j) {
         double acc = 0.0;
         for (int i = 0; i < w; ++i) {
-            const uint32_t p = sc.env[(size_t)j * (size_t)w + (size_t)i];
-            const float r = (float)(p & 0xFFu) / 255.0f, g = (float)((p >> 8) & 0xFFu) / 255.0f, b = (float)((p >> 16) & 0xFFu) / 255.0f;
-            const float lum = 0.2126f * r + 0.7152f * g + 0.0722f * b;
+            const size_t k = (size_t)j * (size_t)w + (size_t)i;
+            float lum;
+            if (!sc.env_f32.empty()) {
+                lum = 0.2126f * sc.env_f32[3 * k] + 0.7152f * sc.env_f32[3 * k + 1] + 0.0722f * sc.env_f32[3 * k + 2];
+                lum = lum > 0.0f ? lum : 0.0f;
+            } else {
+                const uint32_t p = sc.env[k];
+                const float r = (float)(p & 0xFFu) / 255.0f, g = (float)((p >> 8) & 0xFFu) / 255.0f, b = (float)((p >> 16) & 0xFFu) / 255.0f;
+                lum = 0.2126f * r + 0.7152f * g + 0.0722f * b;
+            }
             acc += (double)lum;
             col_acc[(size_t)i] = acc;
         }
@@ -845,7 +861,7 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays,
         Closest h = find(sc, org, dir, t_min, t_max);
         ++nrays;
         if (h.id == 0xFFFFFFFFu) {                                                       // :136-148
-            if (sc.env_use && !sc.env.empty())
+            if (sc.env_use && has_env_map(sc))
                 radiance = add(radiance, sample_environment(sc, dir));
             else if (sc.env_auto)
                 radiance = add(radiance, lerp(v3(1.0f), V3{0.5f, 0.7f, 1.0f}, 0.5f * (dir.y + 1.0f)));
@@ -1053,10 +1069,26 @@ void oracle_set_materials(oracle_scene* o, const float* m, int nm) {
 void oracle_set_environment(oracle_scene* o, const uint8_t* rgba, int w, int h, int use, int auto_,
                             const float* color, float intensity) {
     o->s.env.clear();
+    o->s.env_f32.clear();
     o->s.env_w = o->s.env_h = 0;
     if (rgba && w > 0 && h > 0) {
         o->s.env.resize((size_t)w * h);
         memcpy(o->s.env.data(), rgba, (size_t)w * h * 4);
+        o->s.env_w = w;
+        o->s.env_h = h;
+    }
+    o->s.env_use = use != 0;
+    o->s.env_auto = auto_ != 0;
+    o->s.env_color = {color[0], color[1], color[2]};
+    o->s.env_intensity = intensity;
+}
+void oracle_set_environment_f32(oracle_scene* o, const float* rgb, int w, int h, int use, int auto_, const float* color,
+                                float intensity) {
+    o->s.env.clear();
+    o->s.env_f32.clear();
+    o->s.env_w = o->s.env_h = 0;
+    if (rgb && w > 0 && h > 0) {
+        o->s.env_f32.assign(rgb, rgb + (size_t)w * h * 3);
         o->s.env_w = w;
         o->s.env_h = h;
     }

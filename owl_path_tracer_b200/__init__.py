@@ -63,7 +63,8 @@ class Stats(C.Structure):
 class LoadOptions(C.Structure):
     _fields_ = [("scene", C.c_char_p), ("width", C.c_int32), ("height", C.c_int32),
                 ("max_samples", C.c_int32), ("max_path_depth", C.c_int32), ("env_mode", C.c_int32),
-                ("env_intensity", C.c_float), ("detail", C.c_int32), ("no_procedural", C.c_int32)]
+                ("env_intensity", C.c_float), ("detail", C.c_int32), ("no_procedural", C.c_int32),
+                ("env_float", C.c_int32)]
 
 
 class SceneInfo(C.Structure):
@@ -74,7 +75,7 @@ class SceneInfo(C.Structure):
                 ("env_rgba", C.c_void_p), ("cam_origin", C.c_float * 3), ("cam_llc", C.c_float * 3),
                 ("cam_horizontal", C.c_float * 3), ("cam_vertical", C.c_float * 3),
                 ("n_entities", C.c_int32), ("n_materials", C.c_int32), ("n_notes", C.c_int32),
-                ("n_triangles", C.c_int64)]
+                ("n_triangles", C.c_int64), ("env_f32", C.c_void_p)]
 
 
 class EntityView(C.Structure):
@@ -112,6 +113,7 @@ def lib() -> C.CDLL:
     L.b200pt_build_accel.argtypes = [P]
     L.b200pt_set_materials.argtypes = [P, P, C.c_int32]
     L.b200pt_set_environment.argtypes = [P, P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, P, C.c_float]
+    L.b200pt_set_environment_f32.argtypes = [P, P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, P, C.c_float]
     L.b200pt_set_camera.argtypes = [P, P, P, P, P]
     L.b200pt_set_render.argtypes = [P, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
     L.b200pt_render.argtypes = [P]

@@ -60,6 +60,13 @@ class Context:
         self._ck(self._L.b200pt_set_environment(self._h, _ptr(rgba), w, h, int(bool(use)), int(bool(auto)), _ptr(col),
                                                 float(intensity)), "set_environment")
 
+    def set_environment_f32(self, rgb, use=True, auto=False, color=(0, 0, 0), intensity=1.0):
+        """float RGB environment map (h, w, 3), linear radiance (b200pt_set_environment_f32)"""
+        rgb = np.ascontiguousarray(rgb, np.float32)
+        col = np.asarray(color, np.float32)
+        self._ck(self._L.b200pt_set_environment_f32(self._h, _ptr(rgb), rgb.shape[1], rgb.shape[0], int(bool(use)),
+                                                    int(bool(auto)), _ptr(col), float(intensity)), "set_environment_f32")
+
     def set_camera(self, origin, llc, horizontal, vertical):
         a = [np.ascontiguousarray(x, np.float32) for x in (origin, llc, horizontal, vertical)]
         self._ck(self._L.b200pt_set_camera(self._h, *[_ptr(x) for x in a]), "set_camera")

@@ -16,7 +16,7 @@ class Scene:
     """
 
     def __init__(self, assets=None, scene=None, width=0, height=0, spp=0, depth=0, env=None,
-                 env_intensity=-1.0, detail=0, allow_procedural=True):
+                 env_intensity=-1.0, detail=0, allow_procedural=True, env_float=False):
         H = host_lib()
         opt = LoadOptions()
         opt.scene = scene.encode() if scene else None
@@ -26,6 +26,7 @@ class Scene:
         opt.env_intensity = float(env_intensity)
         opt.detail = int(detail)
         opt.no_procedural = 0 if allow_procedural else 1
+        opt.env_float = 1 if env_float else 0   # keep environment.hdr as float radiance (b200pt_set_environment_f32)
         self._h = C.c_void_p()
         self._H = H
         path = str(assets or ASSETS_DIR).encode()
@@ -80,7 +81,8 @@ class Scene:
     def environment(self):
         i = self.info
         img = _view(i.env_rgba, (i.env_h, i.env_w, 4), np.uint8)
-        return dict(rgba=img, use=i.environment_use, auto=i.environment_auto,
+        f32 = _view(i.env_f32, (i.env_h, i.env_w, 3), np.float32) if i.env_f32 else None
+        return dict(rgba=img, rgb_f32=f32, use=i.environment_use, auto=i.environment_auto,
                     color=np.array(i.environment_color[:], np.float32), intensity=float(i.environment_intensity))
 
     def entities(self):

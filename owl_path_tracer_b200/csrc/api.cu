@@ -50,6 +50,7 @@ struct b200pt_ctx {
     MeshInfo* d_meshes = nullptr;
     uint32_t *d_texels = nullptr, *d_env = nullptr;
     float *d_env_rows = nullptr, *d_env_cols = nullptr;  // NEE mode: luminance cdfs of the map (pt_lights.h)
+    f4* d_env_f32 = nullptr;    // float RGB map (b200pt_set_environment_f32) instead of d_env
     Material* d_mats = nullptr;
     int n_mats = 0;
     std::vector<Material> h_mats;      // host copy: the per-mesh material array is rebuilt from it
@@ -140,9 +141,10 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     sv.nee = (c->cfg.flags & B200PT_FLAG_NEE) ? 1 : 0;
     sv.env_cdf_rows = c->d_env_rows;
     sv.env_cdf_cols = c->d_env_cols;
-    sv.env_nee = (sv.nee && c->env_use && c->d_env && c->d_env_rows) ? 1 : 0;
+    sv.env_nee = (sv.nee && c->env_use && (c->d_env || c->d_env_f32) && c->d_env_rows) ? 1 : 0;
     sv.texels = c->d_texels;
     sv.env = c->d_env;
+    sv.env_f32 = c->d_env_f32;
     sv.env_w = c->env_w;
     sv.env_h = c->env_h;
     sv.env_use = c->env_use;
@@ -223,6 +225,7 @@ extern "C" int b200pt_destroy(b200pt_ctx* c) {
     free_lanes(c);
     free_scene(c);
     cudaFree(c->d_env);
+    cudaFree(c->d_env_f32);
     cudaFree(c->d_env_rows);
     cudaFree(c->d_env_cols);
     cudaFree(c->d_mats);
@@ -350,32 +353,47 @@ extern "C" int b200pt_set_materials(b200pt_ctx* c, const b200pt_material* m, int
     return B200PT_OK;
 }
 
-extern "C" int b200pt_set_environment(b200pt_ctx* c, const uint8_t* rgba, int32_t w, int32_t h, int32_t use, int32_t auto_,
-                                      const float color[3], float intensity) {
+// shared by the two environment setters: exactly one of rgba / rgb is non-null (or none: no map)
+static int set_environment_common(b200pt_ctx* c, const uint8_t* rgba, const float* rgb, int32_t w, int32_t h, int32_t use,
+                                  int32_t auto_, const float color[3], float intensity) {
     if (!c || !color) return fail(B200PT_ERR_INVALID, "set_environment: null");
     CU(cudaSetDevice(c->cfg.device_ordinal));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaDeviceSynchronize());
     cudaFree(c->d_env);
+    cudaFree(c->d_env_f32);
     cudaFree(c->d_env_rows);
     cudaFree(c->d_env_cols);
     c->d_env = nullptr;
+    c->d_env_f32 = nullptr;
     c->d_env_rows = c->d_env_cols = nullptr;
     c->env_w = c->env_h = 0;
-    if (rgba && w > 0 && h > 0) {
-        CU(cudaMalloc(&c->d_env, (size_t)w * h * 4));
-        CU(cudaMemcpy(c->d_env, rgba, (size_t)w * h * 4, cudaMemcpyHostToDevice));
+    if ((rgba || rgb) && w > 0 && h > 0) {
+        const size_t n = (size_t)w * h;
+        std::vector<float> rows, cols;
+        bool tables = false;
+        const bool want_tables = (c->cfg.flags & B200PT_FLAG_NEE) && use;  // importance sampling of the map
+        if (rgba) {
+            CU(cudaMalloc(&c->d_env, n * 4));
+            CU(cudaMemcpy(c->d_env, rgba, n * 4, cudaMemcpyHostToDevice));
+            if (want_tables) {
+                std::vector<uint32_t> texels(n);
+                memcpy(texels.data(), rgba, n * 4);
+                tables = build_env_table(texels.data(), w, h, rows, cols);
+            }
+        } else {
+            std::vector<f4> texels(n);
+            for (size_t i = 0; i < n; ++i) texels[i] = f4{rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2], 0.0f};
+            CU(cudaMalloc(&c->d_env_f32, n * sizeof(f4)));
+            CU(cudaMemcpy(c->d_env_f32, texels.data(), n * sizeof(f4), cudaMemcpyHostToDevice));
+            if (want_tables) tables = build_env_table_f32(texels.data(), w, h, rows, cols);
+        }
         c->env_w = w;
         c->env_h = h;
-        if ((c->cfg.flags & B200PT_FLAG_NEE) && use) {  // importance sampling of the map
-            std::vector<float> rows, cols;
-            std::vector<uint32_t> texels((size_t)w * h);
-            memcpy(texels.data(), rgba, texels.size() * 4);
-            if (build_env_table(texels.data(), w, h, rows, cols)) {
-                CU(cudaMalloc(&c->d_env_rows, sizeof(float) * rows.size()));
-                CU(cudaMalloc(&c->d_env_cols, sizeof(float) * cols.size()));
-                CU(cudaMemcpy(c->d_env_rows, rows.data(), sizeof(float) * rows.size(), cudaMemcpyHostToDevice));
-                CU(cudaMemcpy(c->d_env_cols, cols.data(), sizeof(float) * cols.size(), cudaMemcpyHostToDevice));
-            }
+        if (tables) {
+            CU(cudaMalloc(&c->d_env_rows, sizeof(float) * rows.size()));
+            CU(cudaMalloc(&c->d_env_cols, sizeof(float) * cols.size()));
+            CU(cudaMemcpy(c->d_env_rows, rows.data(), sizeof(float) * rows.size(), cudaMemcpyHostToDevice));
+            CU(cudaMemcpy(c->d_env_cols, cols.data(), sizeof(float) * cols.size(), cudaMemcpyHostToDevice));
         }
     }
     c->env_use = use != 0;
@@ -383,6 +401,14 @@ extern "C" int b200pt_set_environment(b200pt_ctx* c, const uint8_t* rgba, int32_
     memcpy(c->env_color, color, 12);
     c->env_intensity = intensity;
     return B200PT_OK;
+}
+extern "C" int b200pt_set_environment(b200pt_ctx* c, const uint8_t* rgba, int32_t w, int32_t h, int32_t use, int32_t auto_,
+                                      const float color[3], float intensity) {
+    return set_environment_common(c, rgba, nullptr, w, h, use, auto_, color, intensity);
+}
+extern "C" int b200pt_set_environment_f32(b200pt_ctx* c, const float* rgb, int32_t w, int32_t h, int32_t use, int32_t auto_,
+                                          const float color[3], float intensity) {
+    return set_environment_common(c, nullptr, rgb, w, h, use, auto_, color, intensity);
 }
 
 extern "C" int b200pt_set_camera(b200pt_ctx* c, const float origin[3], const float llc[3], const float horizontal[3],

@@ -63,6 +63,7 @@ struct SceneView {
     const Material* mesh_materials;  // materials[meshes[m].material] per mesh: one dependent load less in shade
     const uint32_t* texels;    // RGBA8 pool (mesh textures)
     const uint32_t* env;       // RGBA8 environment map or nullptr
+    const f4* env_f32;         // float RGB environment map (b200pt_set_environment_f32) or nullptr; same addressing
     int32_t env_w, env_h;
     int32_t env_use, env_auto;
     float env_color[3];
@@ -139,13 +140,22 @@ PT_HD f3 fetch_rgba8(const uint32_t* img, int w, int h, float u, float v) {
               (float)((p >> 16) & 0xFFu) / 255.0f};
 }
 
+// float RGB map: same point sampling and clamping as fetch_rgba8, radiance not limited to [0, 1]
+PT_HD f3 fetch_f32(const f4* img, int w, int h, float u, float v) {
+    float fx = floorf(u * (float)w), fy = floorf(v * (float)h);
+    int ix = (fx >= 0.0f) ? (fx < (float)w ? (int)fx : w - 1) : 0;
+    int iy = (fy >= 0.0f) ? (fy < (float)h ? (int)fy : h - 1) : 0;
+    const f4 p = img[(size_t)iy * (size_t)w + (size_t)ix];
+    return f3{p.x, p.y, p.z};
+}
+
 // miss branch of trace_path, device.cu:136-148
 PT_HD f3 miss_radiance(const SceneView& sv, f3 dir) {
     f3 rad = mk3(0.0f);
-    if (sv.env_use && sv.env) {
+    if (sv.env_use && (sv.env || sv.env_f32)) {
         const float u = 0.5f + dm_atan2(dir.x, dir.z) / (2.0f * kPi);
         const float v = 0.5f + dm_asin(dir.y) / kPi;
-        rad = rad + fetch_rgba8(sv.env, sv.env_w, sv.env_h, u, v);
+        rad = rad + (sv.env_f32 ? fetch_f32(sv.env_f32, sv.env_w, sv.env_h, u, v) : fetch_rgba8(sv.env, sv.env_w, sv.env_h, u, v));
     } else if (sv.env_auto) {
         rad = rad + lerp3(mk3(1.0f), f3{0.5f, 0.7f, 1.0f}, 0.5f * (dir.y + 1.0f));
     } else {

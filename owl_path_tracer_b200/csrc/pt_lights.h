@@ -51,14 +51,14 @@ inline void build_light_table(const std::vector<f4>& pos, const std::vector<int3
     for (size_t i = 0; i < lights.size(); ++i) lights[i].prob = cdf[i] - (i ? cdf[i - 1] : 0.0f);
 }
 
-// Environment map of the NEE mode: P(texel) proportional to the Rec.709 luminance of the RGBA8 texel (the
-// map is LDR by the reference's loading route).  rows: marginal cdf over the h rows; cols: cdf of
-// every row over its w texels (a black row gets a uniform cdf; it is never selected).  Sums in binary64,
-// rounded once per entry.  Returns false (tables empty) when the whole map is black.
-inline bool build_env_table(const uint32_t* rgba, int w, int h, std::vector<float>& rows, std::vector<float>& cols) {
+// Environment map of the NEE mode: P(texel) proportional to the Rec.709 luminance of the texel.  rows: marginal
+// cdf over the h rows; cols: cdf of every row over its w texels (a black row gets a uniform cdf; it is never
+// selected).  Sums in binary64, rounded once per entry.  Returns false (tables empty) when the whole map is black.
+template <class LumFn>
+inline bool build_env_table_fn(int w, int h, LumFn lum_of, std::vector<float>& rows, std::vector<float>& cols) {
     rows.clear();
     cols.clear();
-    if (!rgba || w <= 0 || h <= 0) return false;
+    if (w <= 0 || h <= 0) return false;
     rows.resize((size_t)h);
     cols.resize((size_t)w * (size_t)h);
     std::vector<double> row_acc((size_t)h), col_acc((size_t)w);
@@ -66,10 +66,7 @@ inline bool build_env_table(const uint32_t* rgba, int w, int h, std::vector<floa
     for (int j = 0; j < h; ++j) {
         double acc = 0.0;
         for (int i = 0; i < w; ++i) {
-            const uint32_t p = rgba[(size_t)j * (size_t)w + (size_t)i];
-            const float r = (float)(p & 0xFFu) / 255.0f, g = (float)((p >> 8) & 0xFFu) / 255.0f, b = (float)((p >> 16) & 0xFFu) / 255.0f;
-            const float lum = 0.2126f * r + 0.7152f * g + 0.0722f * b;
-            acc += (double)lum;
+            acc += (double)lum_of((size_t)j * (size_t)w + (size_t)i);
             col_acc[(size_t)i] = acc;
         }
         float* row = cols.data() + (size_t)j * (size_t)w;
@@ -86,6 +83,23 @@ inline bool build_env_table(const uint32_t* rgba, int w, int h, std::vector<floa
     for (int j = 0; j < h; ++j) rows[(size_t)j] = (float)(row_acc[(size_t)j] / total);
     rows[(size_t)h - 1] = 1.0f;
     return true;
+}
+// RGBA8 map (LDR by the reference's loading route)
+inline bool build_env_table(const uint32_t* rgba, int w, int h, std::vector<float>& rows, std::vector<float>& cols) {
+    if (!rgba) return false;
+    return build_env_table_fn(w, h, [rgba](size_t k) {
+        const uint32_t p = rgba[k];
+        const float r = (float)(p & 0xFFu) / 255.0f, g = (float)((p >> 8) & 0xFFu) / 255.0f, b = (float)((p >> 16) & 0xFFu) / 255.0f;
+        return 0.2126f * r + 0.7152f * g + 0.0722f * b;
+    }, rows, cols);
+}
+// float map, texels as f4 (rgb, -); negative or NaN luminance counts as 0
+inline bool build_env_table_f32(const f4* texels, int w, int h, std::vector<float>& rows, std::vector<float>& cols) {
+    if (!texels) return false;
+    return build_env_table_fn(w, h, [texels](size_t k) {
+        const float lum = 0.2126f * texels[k].x + 0.7152f * texels[k].y + 0.0722f * texels[k].z;
+        return lum > 0.0f ? lum : 0.0f;
+    }, rows, cols);
 }
 
 }  // namespace pt

@@ -48,7 +48,13 @@ void init_program_data(program_data& pdata, test_data& tdata, const std::string&
         for (size_t i = 0; i < (size_t)w * h; ++i) rgbe_from_float(&rgb[3 * i], &rgbe[4 * i]);
         pdata.environment_map = ldr_from_rgbe(w, h, rgbe.data());
         flip_rows(pdata.environment_map);
+        if (opt.env_float) float_from_rgbe(w, h, rgbe.data(), pdata.environment_float);
         pdata.notes.push_back("environment.hdr: procedural stand-in (2048x1024)");
+    } else if (opt.env_float && !pdata.environment_map.empty()) {
+        int w = 0, h = 0;
+        if (!load_hdr_float("environment.hdr", assets_path, w, h, pdata.environment_float) || w != pdata.environment_map.width ||
+            h != pdata.environment_map.height)
+            pdata.environment_float.clear();
     }
 
     pdata.cam = to_camera_data(parse_camera(config_file), pdata.buffer_size[0], pdata.buffer_size[1]);
@@ -125,11 +131,17 @@ void bind_scene(const program_data& pdata, b200pt_ctx* ctx) {
     }
     check(b200pt_build_accel(ctx), "build_accel");  // init_owl_world
     const float color[3] = {pdata.environment_color.x, pdata.environment_color.y, pdata.environment_color.z};
-    check(b200pt_set_environment(ctx,
-                                 pdata.environment_map.empty() ? nullptr : (const uint8_t*)pdata.environment_map.pixels.data(),
-                                 pdata.environment_map.width, pdata.environment_map.height, pdata.environment_use ? 1 : 0,
-                                 pdata.environment_auto ? 1 : 0, color, pdata.environment_intensity),
-          "set_environment");
+    if (!pdata.environment_float.empty())  // float radiance instead of the 8-bit map
+        check(b200pt_set_environment_f32(ctx, pdata.environment_float.data(), pdata.environment_map.width,
+                                         pdata.environment_map.height, pdata.environment_use ? 1 : 0,
+                                         pdata.environment_auto ? 1 : 0, color, pdata.environment_intensity),
+              "set_environment_f32");
+    else
+        check(b200pt_set_environment(ctx,
+                                     pdata.environment_map.empty() ? nullptr : (const uint8_t*)pdata.environment_map.pixels.data(),
+                                     pdata.environment_map.width, pdata.environment_map.height, pdata.environment_use ? 1 : 0,
+                                     pdata.environment_auto ? 1 : 0, color, pdata.environment_intensity),
+              "set_environment");
     const std::vector<material_data> mats = material_array(pdata);
     check(b200pt_set_materials(ctx, mats.data(), (int)mats.size()), "set_materials");
     check(b200pt_set_camera(ctx, &pdata.cam.origin.x, &pdata.cam.llc.x, &pdata.cam.horizontal.x, &pdata.cam.vertical.x),

@@ -17,6 +17,7 @@ struct load_options {
     float env_intensity = -1.0f;  // <0: settings.json
     int detail = 0;               // procedural stand-in detail knob
     bool allow_procedural = true; // generate stand-ins for assets missing from the checkout
+    bool env_float = false;       // keep environment.hdr as float radiance instead of the reference's 8-bit conversion
 };
 
 // init_program_data, application.cpp:143-181

@@ -46,6 +46,7 @@ int b200pt_scene_load(const char* assets_path, const b200pt_load_options* o, b20
             opt.env_intensity = o->env_intensity;
             opt.detail = o->detail;
             opt.allow_procedural = o->no_procedural == 0;
+            opt.env_float = o->env_float != 0;
         }
         auto* s = new b200pt_scene();
         try {
@@ -76,6 +77,7 @@ int b200pt_scene_info(const b200pt_scene* s, b200pt_scene_info_t* info) {
     info->env_w = p.environment_map.width;
     info->env_h = p.environment_map.height;
     info->env_rgba = p.environment_map.empty() ? nullptr : (const uint8_t*)p.environment_map.pixels.data();
+    info->env_f32 = p.environment_float.empty() ? nullptr : p.environment_float.data();
     memcpy(info->cam_origin, &p.cam.origin.x, 12);
     memcpy(info->cam_llc, &p.cam.llc.x, 12);
     memcpy(info->cam_horizontal, &p.cam.horizontal.x, 12);

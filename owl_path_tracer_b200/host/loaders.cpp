@@ -508,7 +508,8 @@ void rgbe_from_float(const float* c, unsigned char* o) {
     }
 }
 
-static bool read_hdr(const std::string& path, image_buffer& img) {
+// Radiance file -> RGBE bytes (w*h*4), shared by the LDR route of the reference and the float route
+static bool read_hdr_rgbe(const std::string& path, int& w_out, int& h_out, std::vector<unsigned char>& rgbe_out) {
     FILE* f = fopen(path.c_str(), "rb");
     if (!f) return false;
     char line[1024];
@@ -554,11 +555,44 @@ static bool read_hdr(const std::string& path, image_buffer& img) {
                 }
                 if (ok) memcpy(row, scan.data(), (size_t)w * 4);
             }
-            if (ok) img = ldr_from_rgbe(w, h, rgbe.data());
+            if (ok) {
+                w_out = w;
+                h_out = h;
+                rgbe_out.swap(rgbe);
+            }
         }
     }
     fclose(f);
     return ok;
+}
+static bool read_hdr(const std::string& path, image_buffer& img) {
+    int w = 0, h = 0;
+    std::vector<unsigned char> rgbe;
+    if (!read_hdr_rgbe(path, w, h, rgbe)) return false;
+    img = ldr_from_rgbe(w, h, rgbe.data());
+    return true;
+}
+// stbi__hdr_convert (stb_image.h:7053-7078): mantissa * 2^(e - 136); rows flipped like flip_rows
+void float_from_rgbe(int w, int h, const unsigned char* rgbe, std::vector<float>& rgb_flipped) {
+    rgb_flipped.assign((size_t)w * h * 3, 0.0f);
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const unsigned char* e = &rgbe[((size_t)y * w + x) * 4];
+            float* o = &rgb_flipped[((size_t)(h - 1 - y) * w + x) * 3];
+            if (e[3] != 0) {
+                const float f1 = (float)ldexp(1.0f, (int)e[3] - (int)(128 + 8));
+                o[0] = e[0] * f1;
+                o[1] = e[1] * f1;
+                o[2] = e[2] * f1;
+            }
+        }
+}
+bool load_hdr_float(const std::string& name, const std::string& path, int& w, int& h, std::vector<float>& rgb_flipped) {
+    const std::string file_path = path + "/" + name;
+    std::vector<unsigned char> rgbe;
+    if (!std::filesystem::exists(file_path) || !read_hdr_rgbe(file_path, w, h, rgbe)) return false;
+    float_from_rgbe(w, h, rgbe.data(), rgb_flipped);
+    return true;
 }
 
 void write_hdr(const std::string& path, int w, int h, const float* rgb) {

@@ -15,6 +15,9 @@ std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::s
 image_buffer load_image(const std::string& name, const std::string& path);     // image_buffer.cpp:36-59 (v-flipped)
 void write_image(const image_buffer& i, const std::string& name, const std::string& path);  // image_buffer.cpp:25-34
 void write_png(const std::string& file_path, int w, int h, const uint32_t* rgba);
+// float route of the environment (b200pt_set_environment_f32): linear RGB radiance, rows flipped like load_image
+void float_from_rgbe(int w, int h, const unsigned char* rgbe, std::vector<float>& rgb_flipped);
+bool load_hdr_float(const std::string& name, const std::string& path, int& w, int& h, std::vector<float>& rgb_flipped);
 // Portable Float Map ("PF", little endian, rows bottom to top) of a top-row-first float RGBA frame
 void write_pfm(const std::string& file_path, int w, int h, const float* rgba_top_first);
 image_buffer ldr_from_rgbe(int w, int h, const unsigned char* rgbe);          // stb hdr -> 8 bit route

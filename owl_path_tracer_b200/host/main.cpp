@@ -7,6 +7,7 @@
 //   --assets DIR  --scene NAME  --size W H  --spp N  --depth N  --env color|auto|map
 //   --env-intensity F  --detail N  --device K  --out DIR  --stats
 //   --nee (light sampling + MIS mode)  --streams V (RNG streams per pixel)  --pfm (float frame next to the PNG)
+//   --env-float (environment.hdr as float radiance instead of the reference's 8-bit conversion)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -47,6 +48,7 @@ int main(int argc, char** argv) {
         else if (a == "--nee") flags |= B200PT_FLAG_NEE;
         else if (a == "--streams") { need(1); streams = atoi(argv[++i]); }
         else if (a == "--pfm") pfm = true;
+        else if (a == "--env-float") opt.env_float = true;
         else if (a == "--help" || a == "-h") {
             printf("path_tracer [--assets DIR] [--scene NAME] [--size W H] [--spp N] [--depth N] [--env color|auto|map]\n"
                    "            [--env-intensity F] [--detail N] [--device K] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"

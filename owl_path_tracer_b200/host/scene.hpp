@@ -80,6 +80,7 @@ struct program_data {
     vec3 environment_color;
     float environment_intensity = 0;
     image_buffer environment_map;
+    std::vector<float> environment_float;  // linear RGB of the same map (load_options.env_float), same size and row order
     camera_data cam;
     std::vector<material_entry> materials;
     std::vector<std::pair<std::string, std::shared_ptr<mesh>>> meshes;

@@ -41,7 +41,10 @@ class _SceneChecker:
             self.add_mesh(e["verts"], e["normals"], e["idx"], e["material"], e["uvs"], e["tex"])
         self.set_materials(scene.materials())
         env = scene.environment
-        self.set_environment(env["rgba"], env["use"], env["auto"], env["color"], env["intensity"])
+        if env.get("rgb_f32") is not None:
+            self.set_environment_f32(env["rgb_f32"], env["use"], env["auto"], env["color"], env["intensity"])
+        else:
+            self.set_environment(env["rgba"], env["use"], env["auto"], env["color"], env["intensity"])
         self.set_camera(*scene.camera)
         self.set_render(scene.width, scene.height, scene.spp, scene.depth)
         self.build()
@@ -69,6 +72,14 @@ class _SceneChecker:
         h, w = (rgba.shape[0], rgba.shape[1]) if rgba is not None else (0, 0)
         col = np.asarray(color, np.float32)
         self._f("set_environment")(self.h, _p(rgba), w, h, int(bool(use)), int(bool(auto)), _p(col), C.c_float(intensity))
+
+    def set_environment_f32(self, rgb, use=True, auto=False, color=(0, 0, 0), intensity=1.0):
+        """float RGB map (h, w, 3): the superset of set_environment behind b200pt_set_environment_f32"""
+        rgb = np.ascontiguousarray(rgb, np.float32)
+        col = np.asarray(color, np.float32)
+        self._f("set_environment_f32")(self.h, _p(rgb), rgb.shape[1], rgb.shape[0], int(bool(use)), int(bool(auto)), _p(col),
+                                       C.c_float(intensity))
+        return self
 
     def set_camera(self, origin, llc, horizontal, vertical):
         a = [np.ascontiguousarray(x, np.float32) for x in (origin, llc, horizontal, vertical)]
@@ -103,6 +114,7 @@ class Oracle(_SceneChecker):
         L.oracle_add_mesh.argtypes = [P, P, P, P, C.c_int, P, C.c_int, C.c_int, P, C.c_int, C.c_int]
         L.oracle_set_materials.argtypes = [P, P, C.c_int]
         L.oracle_set_environment.argtypes = [P, P, C.c_int, C.c_int, C.c_int, C.c_int, P, C.c_float]
+        L.oracle_set_environment_f32.argtypes = [P, P, C.c_int, C.c_int, C.c_int, C.c_int, P, C.c_float]
         L.oracle_set_camera.argtypes = [P, P, P, P, P]
         L.oracle_set_render.argtypes = [P, C.c_int, C.c_int, C.c_int, C.c_int]
         L.oracle_build.argtypes = [P]
@@ -224,6 +236,7 @@ class Emu(_SceneChecker):
         L.emu_add_mesh.argtypes = [P, P, P, P, C.c_int, P, C.c_int, C.c_int, P, C.c_int, C.c_int]
         L.emu_set_materials.argtypes = [P, P, C.c_int]
         L.emu_set_environment.argtypes = [P, P, C.c_int, C.c_int, C.c_int, C.c_int, P, C.c_float]
+        L.emu_set_environment_f32.argtypes = [P, P, C.c_int, C.c_int, C.c_int, C.c_int, P, C.c_float]
         L.emu_set_camera.argtypes = [P, P, P, P, P]
         L.emu_set_render.argtypes = [P, C.c_int, C.c_int, C.c_int, C.c_int]
         L.emu_build.argtypes = [P]

@@ -26,6 +26,7 @@ struct emu_scene {
     std::vector<MeshInfo> meshes;
     std::vector<uint32_t> texels, env;
     std::vector<float> env_rows, env_cols;
+    std::vector<f4> env_f32;
     std::vector<Material> mats, mesh_mats;
     std::vector<LightTri> lights;
     std::vector<float> light_cdf;
@@ -66,9 +67,12 @@ static void refresh_view(emu_scene* s) {
     s->sv.nee = s->nee;
     s->sv.texels = s->texels.data();
     s->sv.env = s->env.empty() ? nullptr : s->env.data();
+    s->sv.env_f32 = s->env_f32.empty() ? nullptr : s->env_f32.data();
     s->env_rows.clear();
     s->env_cols.clear();
     if (s->nee && s->sv.env_use && !s->env.empty()) build_env_table(s->env.data(), s->sv.env_w, s->sv.env_h, s->env_rows, s->env_cols);
+    if (s->nee && s->sv.env_use && !s->env_f32.empty())
+        build_env_table_f32(s->env_f32.data(), s->sv.env_w, s->sv.env_h, s->env_rows, s->env_cols);
     s->sv.env_cdf_rows = s->env_rows.data();
     s->sv.env_cdf_cols = s->env_cols.data();
     s->sv.env_nee = (s->nee && s->sv.env_use && !s->env_rows.empty()) ? 1 : 0;
@@ -146,9 +150,25 @@ void emu_set_materials(emu_scene* s, const float* m, int nm) {
 void emu_set_environment(emu_scene* s, const uint8_t* rgba, int w, int h, int use, int auto_, const float* color,
                          float intensity) {
     s->env.clear();
+    s->env_f32.clear();
     if (rgba && w > 0 && h > 0) s->env.assign((const uint32_t*)rgba, (const uint32_t*)rgba + (size_t)w * h);
     s->sv.env_w = s->env.empty() ? 0 : w;
     s->sv.env_h = s->env.empty() ? 0 : h;
+    s->sv.env_use = use != 0;
+    s->sv.env_auto = auto_ != 0;
+    memcpy(s->sv.env_color, color, 12);
+    s->sv.env_intensity = intensity;
+}
+void emu_set_environment_f32(emu_scene* s, const float* rgb, int w, int h, int use, int auto_, const float* color,
+                             float intensity) {
+    s->env.clear();
+    s->env_f32.clear();
+    if (rgb && w > 0 && h > 0) {
+        s->env_f32.resize((size_t)w * h);
+        for (size_t i = 0; i < (size_t)w * h; ++i) s->env_f32[i] = f4{rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2], 0.0f};
+    }
+    s->sv.env_w = s->env_f32.empty() ? 0 : w;
+    s->sv.env_h = s->env_f32.empty() ? 0 : h;
     s->sv.env_use = use != 0;
     s->sv.env_auto = auto_ != 0;
     memcpy(s->sv.env_color, color, 12);

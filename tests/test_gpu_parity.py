@@ -96,12 +96,15 @@ def test_converged_image_vs_independent_oracle():
     assert rel_mse(pool(g), pool(o)) <= 1e-3
     assert abs(g.mean() - o.mean()) <= 0.005 * o.mean()
     ctx.close()
-    # the same gate for the throughput mode: 8 RNG streams per pixel against the single-stream oracle
+    # Throughput mode, 8 RNG streams per pixel: an INDEPENDENT estimate of the same image (the gate above is
+    # met because product and oracle walk the same streams and differ only where a last-ulp difference flips a
+    # decision).  Bit parity of this mode is against the oracle with the same keying
+    # (test_streams_per_pixel_are_the_streams_of_a_larger_job); here: same expectation, Monte-Carlo-level distance.
     ctx = gpu_for(sc, streams=8)
     ctx.render()
     g8 = ctx.framebuffer_f32()[..., :3]
-    assert rel_mse(pool(g8), pool(o)) <= 1e-3
     assert abs(g8.mean() - o.mean()) <= 0.005 * o.mean()
+    assert rel_mse(pool(g8), pool(o)) <= 0.05
     ctx.close()
 
 

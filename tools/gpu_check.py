@@ -70,15 +70,18 @@ if __name__ == "__main__":
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "nee":
         # NEE mode: throughput with the shadow kernel, and error at equal spp / equal time against a long render
-        for scene, w, h, spp, env in (("cornell-box", 512, 512, 64, "color"), ("sphere", 1024, 1024, 32, "map"), ("car", 1920, 1080, 32, "color"), ("dragon", 1920, 1080, 32, "color")):
-            sc = pt.Scene(scene=scene, width=w, height=h, spp=spp, depth=8, env=env, env_intensity=1.0 if env == "map" else 0.0)
+        for scene, w, h, spp, env in (("cornell-box", 512, 512, 64, "color"), ("sphere", 1024, 1024, 32, "map"), ("sphere", 1024, 1024, 32, "float"),
+                                      ("car", 1920, 1080, 32, "color"), ("dragon", 1920, 1080, 32, "color")):
+            is_float = env == "float"
+            env = "map" if is_float else env
+            sc = pt.Scene(scene=scene, width=w, height=h, spp=spp, depth=8, env=env, env_intensity=1.0 if env == "map" else 0.0, env_float=is_float)
             res = {}
             for tag, fl in (("ref", pt.FLAG_TIMING), ("nee", pt.FLAG_TIMING | pt.FLAG_NEE)):
                 ctx = pt.Context(flags=fl); ctx.bind(sc); ctx.render(); ctx.render()
                 st = ctx.stats(); res[tag] = (st, ctx.framebuffer_f32()[..., :3].copy()); ctx.close()
-            scl = pt.Scene(scene=scene, width=w, height=h, spp=spp * 16, depth=8, env=env, env_intensity=1.0 if env == "map" else 0.0)
+            scl = pt.Scene(scene=scene, width=w, height=h, spp=spp * 16, depth=8, env=env, env_intensity=1.0 if env == "map" else 0.0, env_float=is_float)
             ctx = pt.Context(flags=pt.FLAG_NEE); ctx.bind(scl); ctx.render(); truth = ctx.framebuffer_f32()[..., :3].copy(); ctx.close()
-            out = dict(scene=scene, size=[w, h], spp=spp)
+            out = dict(scene=scene + ("+float env" if is_float else ""), size=[w, h], spp=spp)
             for tag in ("ref", "nee"):
                 st, img = res[tag]
                 out[tag] = dict(render_ms=st['render_ms'], extend_ms=st['extend_ms'], shade_ms=st['shade_ms'], shadow_ms=st['shadow_ms'],
