@@ -185,6 +185,47 @@ int b200pt_render(b200pt_ctx* ctx);
 int b200pt_accum_buffer(b200pt_ctx* ctx, void** device_ptr, size_t* n_floats);
 int b200pt_resolve(b200pt_ctx* ctx);
 
+/* ---- Progressive surface (the reference renders a frame in one blocking launch and has none of
+ * this — opt-in, the entry points above are unchanged) -------------------------------------------------
+ *
+ * b200pt_render_pass renders the NEXT n_samples samples of every pixel (clamped to what is left of
+ * max_samples), continuing each pixel's RNG stream where its last sample left it, and resolves the frame as the
+ * mean over the samples rendered so far.  Because the reference draws all samples of a pixel from one stream in
+ * order (device.cu:226-243), the frame after k samples IS the reference's frame at max_samples = k, bit for
+ * bit, and after the last pass it is the frame b200pt_render produces (tests/test_progressive.py).  The frame
+ * in progress is dropped by b200pt_render_restart and by any call that changes the scene, camera, environment,
+ * materials, size or depth; b200pt_set_render with only a new max_samples extends or shortens it.
+ * world_size 1 and one stream per pixel only. */
+typedef struct b200pt_pass_info {
+    int32_t samples_done;     /* samples per pixel in the frame now                                       */
+    int32_t samples_in_pass;  /* samples this pass added                                                  */
+    int32_t complete;         /* 1: samples_done == max_samples                                           */
+    int32_t stopped_early;    /* b200pt_render_progressive: 1 when the target was met before max_samples  */
+    double rel_variance;      /* mean over pixels of  Var[pixel mean] / (mean^2 + 1e-2)  in Rec.709 luminance, from the
+                                 per-pixel first and second moments of the sample values: an estimate of the
+                                 relMSE (same epsilon) of the frame against its own limit; 0 while
+                                 samples_done < 2                                                         */
+    double render_ms;         /* device time of this pass                                                 */
+    uint64_t rays;            /* radiance segments traced by this pass                                    */
+} b200pt_pass_info;
+int b200pt_render_pass(b200pt_ctx* ctx, int32_t n_samples, b200pt_pass_info* info /* may be NULL */);
+int b200pt_render_restart(b200pt_ctx* ctx);
+
+/* Called after every pass with the resolved frame (RGBA8 top row first, float RGBA mean; both borrowed until the
+ * next pass).  Return non-zero to stop. */
+typedef int (*b200pt_pass_fn)(void* user, const b200pt_pass_info* info, const uint32_t* rgba, const float* mean);
+/* Passes of pass_samples until max_samples, until rel_variance <= target_rel_variance (0: no early stop), or until
+ * the callback (may be NULL) asks to stop.  Starts a new frame. */
+int b200pt_render_progressive(b200pt_ctx* ctx, int32_t pass_samples, double target_rel_variance,
+                              b200pt_pass_fn on_pass, void* user, b200pt_pass_info* last /* may be NULL */);
+
+/* Output transfer applied by the resolve step to the RGBA8 frame (the float frame stays linear).
+ * LINEAR is the reference as shipped; GAMMA22 is the line it carries commented out (device.cu:248):
+ * color = saturate(pow(color, 1 / 2.2)). */
+#define B200PT_TRANSFER_LINEAR  0
+#define B200PT_TRANSFER_GAMMA22 1
+int b200pt_set_output(b200pt_ctx* ctx, int32_t transfer);
+
 /* Same frame, but the caller's HOST settings are re-uploaded and the RGBA8 frame is
  * copied back into host memory inside the call (the "e2e" path of bench.py:
  * materials H2D + render + D2H framebuffer, what test_loop does per frame). */

@@ -528,6 +528,7 @@ struct Scene {
     std::vector<int32_t> tri_mesh;  // global id -> mesh
     // next-event estimation mode (oracle_set_nee): emissive triangles, chosen by area * emission
     bool nee = false;
+    int transfer = 0;      // output transfer of the RGBA8 frame (oracle_set_output)
     struct Light {
         int mesh, prim;
         float area, prob, emission;
@@ -1001,18 +1002,26 @@ uint32_t quantise8(float f) {  // owl_device.h:79-82; NaN -> 0 as on the device
 }
 
 // device.cu:220-254 for one pixel; returns the SUM over samples (caller scales)
-V3 render_pixel(Scene& sc, int x, int y, int seed_row_offset, int nsamples, Finder find, uint64_t& nrays, uint64_t& nshadow) {
+// lum2 (not in the reference): sum over the samples of the squared Rec.709 luminance of the sample value, the second
+// moment behind the progressive mode's variance estimate (b200pt_pass_info::rel_variance)
+V3 render_pixel(Scene& sc, int x, int y, int seed_row_offset, int nsamples, Finder find, uint64_t& nrays, uint64_t& nshadow,
+                float* lum2 = nullptr) {
     Rng rng;
     rng.seed((uint32_t)x, (uint32_t)(y + seed_row_offset));
     V3 color = v3(0.0f);
+    float second = 0.0f;
     for (int s = 0; s < nsamples; ++s) {
         float rx = rng.next();
         float ry = rng.next();
         float su = ((float)x + rx) / (float)sc.width;
         float sv = ((float)y + ry) / (float)sc.height;
         V3 dir = normalize(sub(add(add(sc.cam_llc, scale(su, sc.cam_h)), scale(sv, sc.cam_v)), sc.cam_origin));
-        color = add(color, trace_path(sc, sc.cam_origin, dir, rng, find, nrays, nshadow));
+        const V3 value = trace_path(sc, sc.cam_origin, dir, rng, find, nrays, nshadow);
+        color = add(color, value);
+        const float l = luminance(value);
+        second += l * l;
     }
+    if (lum2) *lum2 = second;
     return color;
 }
 
@@ -1112,6 +1121,8 @@ void oracle_set_render(oracle_scene* o, int w, int h, int spp, int depth) {
 void oracle_build(oracle_scene* o) { build_bvh(o->s); }
 // next-event estimation mode on/off (see trace_path); shadow rays of the last render
 void oracle_set_nee(oracle_scene* o, int on) { o->s.nee = on != 0; }
+// 0: linear (the reference as shipped); 1: color = saturate(pow(color, 1/2.2)), device.cu:248 (commented out there)
+void oracle_set_output(oracle_scene* o, int transfer) { o->s.transfer = transfer; }
 uint64_t oracle_shadow_rays(oracle_scene* o) { return o->s.shadow_rays.load(); }
 
 // camera.cpp:3-22.  out: origin, llc, horizontal, vertical (12 floats)
@@ -1167,12 +1178,13 @@ uint64_t oracle_render(oracle_scene* o, int rank, int world, int shard_mode, int
             if (y >= y1) break;
             if (y < row_first || (y - row_first) % row_step != 0) continue;
             for (int x = x0; x < x1; ++x) {
-                V3 c = render_pixel(sc, x, y, seed_off, nsamples, find, nr, ns);
+                float second = 0.0f;
+                V3 c = render_pixel(sc, x, y, seed_off, nsamples, find, nr, ns, &second);
                 float* d = sum_out + 4 * ((size_t)x + (size_t)W * y);
                 d[0] = c.x;
                 d[1] = c.y;
                 d[2] = c.z;
-                d[3] = 0.0f;
+                d[3] = second;
             }
         }
         total += nr;
@@ -1195,8 +1207,14 @@ uint64_t oracle_render(oracle_scene* o, int rank, int world, int shard_mode, int
                     mean_out[4 * ofs + 2] = c.z;
                     mean_out[4 * ofs + 3] = 1.0f;
                 }
-                if (rgba_out)
+                if (rgba_out) {
+                    if (sc.transfer == 1) {  // the reference's commented-out line, device.cu:248
+                        const float g = 1.0f / 2.2f;
+                        c = {fminf(fmaxf(m_pow(c.x, g), 0.0f), 1.0f), fminf(fmaxf(m_pow(c.y, g), 0.0f), 1.0f),
+                             fminf(fmaxf(m_pow(c.z, g), 0.0f), 1.0f)};
+                    }
                     rgba_out[ofs] = (quantise8(c.x) << 0) + (quantise8(c.y) << 8) + (quantise8(c.z) << 16) + (0xffU << 24);
+                }
             }
     }
     return total.load();

@@ -60,6 +60,20 @@ class Stats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class PassInfo(C.Structure):
+    """b200pt_pass_info (progressive passes)."""
+    _fields_ = [("samples_done", C.c_int32), ("samples_in_pass", C.c_int32), ("complete", C.c_int32),
+                ("stopped_early", C.c_int32), ("rel_variance", C.c_double), ("render_ms", C.c_double),
+                ("rays", C.c_uint64)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+PASS_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(PassInfo), C.c_void_p, C.c_void_p)
+TRANSFER_LINEAR, TRANSFER_GAMMA22 = 0, 1
+
+
 class LoadOptions(C.Structure):
     _fields_ = [("scene", C.c_char_p), ("width", C.c_int32), ("height", C.c_int32),
                 ("max_samples", C.c_int32), ("max_path_depth", C.c_int32), ("env_mode", C.c_int32),
@@ -117,6 +131,10 @@ def lib() -> C.CDLL:
     L.b200pt_set_camera.argtypes = [P, P, P, P, P]
     L.b200pt_set_render.argtypes = [P, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
     L.b200pt_render.argtypes = [P]
+    L.b200pt_render_pass.argtypes = [P, C.c_int32, C.POINTER(PassInfo)]
+    L.b200pt_render_restart.argtypes = [P]
+    L.b200pt_render_progressive.argtypes = [P, C.c_int32, C.c_double, PASS_FN, C.c_void_p, C.POINTER(PassInfo)]
+    L.b200pt_set_output.argtypes = [P, C.c_int32]
     L.b200pt_accum_buffer.argtypes = [P, C.POINTER(P), C.POINTER(C.c_size_t)]
     L.b200pt_resolve.argtypes = [P]
     L.b200pt_render_to_host.argtypes = [P, P, C.c_int32, P]

@@ -5,7 +5,7 @@ import ctypes as C
 
 import numpy as np
 
-from . import B200ptError, Config, HIT_DTYPE, MATERIAL_DTYPE, Stats, _ptr, _view, host_lib, lib
+from . import B200ptError, Config, HIT_DTYPE, MATERIAL_DTYPE, PASS_FN, PassInfo, Stats, _ptr, _view, host_lib, lib
 
 
 class Context:
@@ -85,6 +85,36 @@ class Context:
     # ---- frames
     def render(self):
         self._ck(self._L.b200pt_render(self._h), "render")
+
+    # ---- progressive surface (b200pt_render_pass / b200pt_render_progressive / b200pt_set_output)
+    def render_pass(self, n_samples):
+        """Next n_samples samples of every pixel; the frame is the mean over the samples so far.  Returns the pass info."""
+        info = PassInfo()
+        self._ck(self._L.b200pt_render_pass(self._h, int(n_samples), C.byref(info)), "render_pass")
+        return info.as_dict()
+
+    def render_restart(self):
+        self._ck(self._L.b200pt_render_restart(self._h), "render_restart")
+
+    def render_progressive(self, pass_samples, target_rel_variance=0.0, on_pass=None):
+        """Passes until max_samples, until rel_variance <= target, or until on_pass(info, rgba, mean) returns True.
+        rgba / mean are views that stay valid during the callback only."""
+        last = PassInfo()
+        H, W = self.height, self.width
+
+        def tramp(_user, info, rgba, mean):
+            if on_pass is None:
+                return 0
+            stop = on_pass(info.contents.as_dict(), _view(rgba, (H, W), np.uint32), _view(mean, (H, W, 4), np.float32))
+            return 1 if stop else 0
+
+        cb = PASS_FN(tramp)
+        self._ck(self._L.b200pt_render_progressive(self._h, int(pass_samples), float(target_rel_variance), cb, None,
+                                                   C.byref(last)), "render_progressive")
+        return last.as_dict()
+
+    def set_output(self, transfer):
+        self._ck(self._L.b200pt_set_output(self._h, int(transfer)), "set_output")
 
     def resolve(self):
         self._ck(self._L.b200pt_resolve(self._h), "resolve")

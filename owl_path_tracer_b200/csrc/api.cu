@@ -80,6 +80,12 @@ struct b200pt_ctx {
     float* h_mean = nullptr;     // pinned
     size_t fb_pixels = 0;
     bool rendered = false, resolved = false;
+    // progressive passes (b200pt_render_pass): samples of every pixel already in `sum`; 0 = no frame in progress
+    int pass_done = 0;
+    int resolve_samples = 0;    // divisor of the next resolve (max_samples for a complete frame)
+    int transfer = 0;           // b200pt_set_output
+    double* d_pass_partial = nullptr;
+    std::vector<double> h_pass_partial;
     b200pt_stats stats{};
     std::vector<cudaEvent_t> ev_pool;
 };
@@ -98,8 +104,10 @@ static void free_lanes(b200pt_ctx* c) {
         cudaFree(L.counts); cudaFree(L.cursor); cudaFree(L.pending);
         L = LaneArrays{};  // sum, rad, walk_counters are aliases of c->la's
     }
-    cudaFree(c->la.sum); cudaFree(c->la.rad); cudaFree(c->la.walk_counters); cudaFree(c->la.susp);
-    cudaFree(c->d_frame); cudaFree(c->d_rgba); cudaFree(c->d_mean);
+    cudaFree(c->la.sum); cudaFree(c->la.rad); cudaFree(c->la.walk_counters); cudaFree(c->la.susp); cudaFree(c->la.rng_save);
+    cudaFree(c->d_frame); cudaFree(c->d_rgba); cudaFree(c->d_mean); cudaFree(c->d_pass_partial);
+    c->d_pass_partial = nullptr;
+    c->pass_done = 0;
     if (c->h_rgba) cudaFreeHost(c->h_rgba);
     if (c->h_mean) cudaFreeHost(c->h_mean);
     c->la = LaneArrays{};
@@ -297,6 +305,7 @@ extern "C" int b200pt_build_accel(b200pt_ctx* c) {
     if (!c) return fail(B200PT_ERR_INVALID, "build_accel: null context");
     if (c->h_meshes.empty()) return fail(B200PT_ERR_EMPTY, "no geometries");
     CU(cudaSetDevice(c->cfg.device_ordinal));
+    c->pass_done = 0;
     free_scene(c);
     const size_t nv = c->h_pos.size(), nt = c->h_idx4.size() / 4;
     CU(cudaMalloc(&c->d_pos, sizeof(f4) * nv));
@@ -332,6 +341,7 @@ extern "C" int b200pt_build_accel(b200pt_ctx* c) {
 extern "C" int b200pt_set_materials(b200pt_ctx* c, const b200pt_material* m, int32_t nm) {
     if (!c || !m || nm <= 0) return fail(B200PT_ERR_INVALID, "set_materials: null/empty");
     CU(cudaSetDevice(c->cfg.device_ordinal));
+    c->pass_done = 0;
     for (const MeshInfo& mi : c->h_meshes)
         if (mi.material >= nm) return fail(B200PT_ERR_BOUNDS, "set_materials: a mesh refers to material " + std::to_string(mi.material));
     std::vector<Material> tmp((size_t)nm);
@@ -356,6 +366,7 @@ extern "C" int b200pt_set_materials(b200pt_ctx* c, const b200pt_material* m, int
 // shared by the two environment setters: exactly one of rgba / rgb is non-null (or none: no map)
 static int set_environment_common(b200pt_ctx* c, const uint8_t* rgba, const float* rgb, int32_t w, int32_t h, int32_t use,
                                   int32_t auto_, const float color[3], float intensity) {
+    if (c) c->pass_done = 0;
     if (!c || !color) return fail(B200PT_ERR_INVALID, "set_environment: null");
     CU(cudaSetDevice(c->cfg.device_ordinal));
     CU(cudaDeviceSynchronize());
@@ -414,6 +425,7 @@ extern "C" int b200pt_set_environment_f32(b200pt_ctx* c, const float* rgb, int32
 extern "C" int b200pt_set_camera(b200pt_ctx* c, const float origin[3], const float llc[3], const float horizontal[3],
                                  const float vertical[3]) {
     if (!c || !origin || !llc || !horizontal || !vertical) return fail(B200PT_ERR_INVALID, "set_camera: null");
+    c->pass_done = 0;
     memcpy(c->cam, origin, 12);
     memcpy(c->cam + 3, llc, 12);
     memcpy(c->cam + 6, horizontal, 12);
@@ -427,6 +439,8 @@ extern "C" int b200pt_set_render(b200pt_ctx* c, int32_t width, int32_t height, i
     if (max_samples >= (1 << 20) || max_path_depth > 255)
         return fail(B200PT_ERR_INVALID, "set_render: max_samples < 2^20 and max_path_depth <= 255 supported");
     if ((int64_t)width * height > (int64_t)1 << 30) return fail(B200PT_ERR_INVALID, "set_render: frame too large");
+    // a frame in progress (b200pt_render_pass) survives a change of the sample budget only
+    if (width != c->width || height != c->height || max_path_depth != c->max_depth) c->pass_done = 0;
     c->width = width;
     c->height = height;
     c->max_samples = max_samples;
@@ -510,6 +524,8 @@ static int ensure_lanes(b200pt_ctx* c, const SceneView& sv, int parts) {
         free_lanes(c);
         const bool nee = (c->cfg.flags & B200PT_FLAG_NEE) != 0;
         CU(cudaMalloc(&c->la.sum, sizeof(f4) * need));
+        CU(cudaMalloc(&c->la.rng_save, sizeof(uint32_t) * need));
+        CU(cudaMalloc(&c->d_pass_partial, sizeof(double) * pass_stats_blocks(need)));
         if (nee) CU(cudaMalloc(&c->la.rad, sizeof(f4) * need));
         CU(cudaMalloc(&c->la.walk_counters, sizeof(unsigned long long) * 2));
         CU(cudaMalloc(&c->la.susp, sizeof(u4) * kSuspWords * (size_t)need));  // touched by parked walks only
@@ -538,6 +554,7 @@ static int ensure_lanes(b200pt_ctx* c, const SceneView& sv, int parts) {
             CU(cudaMalloc(&L.pending, sizeof(uint32_t) * kBatch));
             L.susp = c->la.susp;
             L.sum = c->la.sum;
+            L.rng_save = c->la.rng_save;
             L.rad = c->la.rad;
             L.walk_counters = c->la.walk_counters;
             L.capacity = (uint32_t)padded;
@@ -564,10 +581,16 @@ static int check_ready(b200pt_ctx* c, const char* who) {
     return B200PT_OK;
 }
 
-static int render_local(b200pt_ctx* c) {
+// Renders samples first_sample .. first_sample + n_pass - 1 of every pixel of this rank (n_pass == 0: the whole
+// frame, the reference's launch).  first_sample > 0 continues the streams and sums the previous pass left.
+static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
     CU(cudaSetDevice(c->cfg.device_ordinal));
     if (int r = sync_mesh_materials(c)) return r;
-    const SceneView sv = make_view(c, false);
+    SceneView sv = make_view(c, false);
+    if (n_pass > 0) {
+        sv.first_sample = first_sample;
+        sv.max_samples = first_sample + n_pass;
+    }
     const int parts = choose_parts(c, sv);
     if (int r = ensure_lanes(c, sv, parts)) return r;
     const bool count = (c->cfg.flags & B200PT_FLAG_COUNTERS) != 0;
@@ -584,8 +607,8 @@ static int render_local(b200pt_ctx* c) {
     CU(cudaMemsetAsync(c->la.walk_counters, 0, sizeof(unsigned long long) * 2, st));
     CU(cudaEventRecord(c->ev0, st));  // the other parts' streams start behind this point
     uint32_t active[kMaxParts] = {};
-    const bool any_work = sv.n_lanes > 0 && sv.max_samples + sv.stream_extra > 0 && sv.max_depth > 0;
-    if (!any_work) CU(cudaMemsetAsync(c->la.sum, 0, sizeof(f4) * c->la.capacity, st));
+    const bool any_work = sv.n_lanes > 0 && sv.max_samples + sv.stream_extra > sv.first_sample && sv.max_depth > 0;
+    if (!any_work && sv.first_sample == 0) CU(cudaMemsetAsync(c->la.sum, 0, sizeof(f4) * c->la.capacity, st));
     for (int p = 1; p < parts; ++p) CU(cudaStreamWaitEvent(c->part_stream[p], c->ev0, 0));
     for (int p = 0; p < parts; ++p) {
         const LaneArrays& L = c->part[p];
@@ -712,7 +735,7 @@ static int render_local(b200pt_ctx* c) {
     {
         const uint64_t pix = (uint64_t)std::max(sv.n_pix_lanes > 0 ? sv.n_pix_lanes : sv.n_lanes, 0);
         const uint64_t V = sv.n_pix_lanes > 0 ? (uint64_t)(sv.n_lanes / sv.n_pix_lanes) : 1u;
-        S.paths = pix * (V * (uint64_t)sv.max_samples + (uint64_t)sv.stream_extra);
+        S.paths = pix * (V * (uint64_t)(sv.max_samples - sv.first_sample) + (uint64_t)sv.stream_extra);
     }
     if (count) {
         unsigned long long wc[2];
@@ -722,6 +745,8 @@ static int render_local(b200pt_ctx* c) {
     }
     c->rendered = true;
     c->resolved = false;
+    c->resolve_samples = n_pass > 0 ? first_sample + n_pass : c->max_samples;
+    c->pass_done = n_pass > 0 ? first_sample + n_pass : 0;
     return B200PT_OK;
 }
 
@@ -731,8 +756,8 @@ extern "C" int b200pt_resolve(b200pt_ctx* c) {
     CU(cudaSetDevice(c->cfg.device_ordinal));
     const SceneView full = make_view(c, true);
     const f4* src = c->use_frame ? c->d_frame : c->la.sum;
-    const float inv = 1.0f / static_cast<float>(c->max_samples);  // device.cu:247
-    launch_resolve(full, src, inv, c->d_rgba, c->d_mean, c->stream);
+    const float inv = 1.0f / static_cast<float>(c->resolve_samples);  // device.cu:247 (max_samples for a complete frame)
+    launch_resolve(full, src, inv, c->transfer, c->d_rgba, c->d_mean, c->stream);
     c->stats.kernel_launches++;
     CU(cudaMemcpyAsync(c->h_rgba, c->d_rgba, sizeof(uint32_t) * c->fb_pixels, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(c->h_mean, c->d_mean, sizeof(f4) * c->fb_pixels, cudaMemcpyDeviceToHost, c->stream));
@@ -746,6 +771,74 @@ extern "C" int b200pt_render(b200pt_ctx* c) {
     if (int r = check_ready(c, "render")) return r;
     if (int r = render_local(c)) return r;
     if (c->cfg.world_size == 1) return b200pt_resolve(c);
+    return B200PT_OK;
+}
+
+// ---- progressive surface ----------------------------------------------------------------
+extern "C" int b200pt_set_output(b200pt_ctx* c, int32_t transfer) {
+    if (!c) return fail(B200PT_ERR_INVALID, "set_output: null context");
+    if (transfer != B200PT_TRANSFER_LINEAR && transfer != B200PT_TRANSFER_GAMMA22) return fail(B200PT_ERR_INVALID, "set_output: unknown transfer");
+    c->transfer = transfer;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_render_restart(b200pt_ctx* c) {
+    if (!c) return fail(B200PT_ERR_INVALID, "render_restart: null context");
+    c->pass_done = 0;
+    return B200PT_OK;
+}
+
+static int pass_statistics(b200pt_ctx* c, int n_samples, double* rel_variance) {
+    const uint32_t n = (uint32_t)(c->width * c->height);
+    const unsigned nb = pass_stats_blocks(n);
+    launch_pass_stats(c->la.sum, n, n_samples, c->d_pass_partial, c->stream);
+    c->stats.kernel_launches++;
+    c->h_pass_partial.resize(nb);
+    CU(cudaMemcpyAsync(c->h_pass_partial.data(), c->d_pass_partial, sizeof(double) * nb, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    double t = 0.0;
+    for (unsigned b = 0; b < nb; ++b) t += c->h_pass_partial[b];   // fixed order: the figure is reproducible
+    *rel_variance = n ? t / (double)n : 0.0;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_render_pass(b200pt_ctx* c, int32_t n_samples, b200pt_pass_info* info) {
+    if (int r = check_ready(c, "render_pass")) return r;
+    if (c->cfg.world_size != 1 || c->cfg.streams_per_pixel > 1)
+        return fail(B200PT_ERR_INVALID, "render_pass: progressive passes need world_size 1 and one stream per pixel");
+    if (n_samples <= 0) return fail(B200PT_ERR_INVALID, "render_pass: n_samples must be positive");
+    if (c->pass_done >= c->max_samples)
+        return fail(B200PT_ERR_INVALID, "render_pass: all max_samples samples are rendered (b200pt_render_restart starts over)");
+    const int n = std::min(n_samples, c->max_samples - c->pass_done);
+    if (int r = render_local(c, c->pass_done, n)) return r;
+    if (int r = b200pt_resolve(c)) return r;
+    if (info) {
+        memset(info, 0, sizeof *info);
+        info->samples_done = c->pass_done;
+        info->samples_in_pass = n;
+        info->complete = c->pass_done >= c->max_samples ? 1 : 0;
+        info->render_ms = c->stats.render_ms;
+        info->rays = c->stats.rays;
+        if (int r = pass_statistics(c, c->pass_done, &info->rel_variance)) return r;
+    }
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_render_progressive(b200pt_ctx* c, int32_t pass_samples, double target_rel_variance, b200pt_pass_fn on_pass,
+                                         void* user, b200pt_pass_info* last) {
+    if (int r = check_ready(c, "render_progressive")) return r;
+    if (pass_samples <= 0) return fail(B200PT_ERR_INVALID, "render_progressive: pass_samples must be positive");
+    if (int r = b200pt_render_restart(c)) return r;
+    b200pt_pass_info info{};
+    for (;;) {
+        if (int r = b200pt_render_pass(c, pass_samples, &info)) return r;
+        const bool converged = target_rel_variance > 0.0 && info.samples_done > 1 && info.rel_variance <= target_rel_variance;
+        if (converged) info.stopped_early = info.complete ? 0 : 1;
+        int stop = 0;
+        if (on_pass) stop = on_pass(user, &info, c->h_rgba, c->h_mean);
+        if (info.complete || converged || stop) break;
+    }
+    if (last) *last = info;
     return B200PT_OK;
 }
 

@@ -32,7 +32,8 @@ struct LaneArrays {
     f4* thr[2] = {nullptr, nullptr};     // throughput.xyz, RNG state
     f4* hit = nullptr;                   // t, u, v, triangle id   (written by k_extend, same index)
     uint32_t* queue[2] = {nullptr, nullptr};  // lane (pixel) id of entry i
-    f4* sum = nullptr;     // per lane: sum of finished samples .xyz, -   (this is the accumulation buffer)
+    f4* sum = nullptr;     // per lane: sum of finished samples .xyz, sum of their squared luminances (this is the accumulation buffer)
+    uint32_t* rng_save = nullptr;  // per lane: RNG state after the pixel's last sample of a pass (progressive passes resume from it)
     // next-event estimation mode (B200PT_FLAG_NEE) only
     f4* rad = nullptr;     // per lane: light-sampled radiance of the sample in flight .xyz
     f4* sh_o = nullptr;    // shadow requests of the current iteration: origin.xyz, tmax
@@ -60,7 +61,9 @@ void launch_init_lanes(const SceneView& sv, const LaneArrays& la, int part, int 
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st);
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
-void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st);
+void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, int transfer, uint32_t* rgba, f4* mean, cudaStream_t st);
+unsigned pass_stats_blocks(uint32_t n_lanes);
+void launch_pass_stats(const f4* sum, uint32_t n_lanes, int n_samples, double* partial, cudaStream_t st);
 void launch_scatter_rows(const SceneView& sv, const f4* sum, f4* frame, cudaStream_t st);
 void launch_fold_streams(const f4* sum, f4* out, uint32_t n_pix, int streams, cudaStream_t st);
 void launch_primary(const SceneView& sv, f4* hits, uint32_t* cursor, cudaStream_t st);

@@ -82,6 +82,9 @@ struct SceneView {
     // the world_size * V streams the samples are split over — the very streams an (world_size * V)-GPU job uses.
     int32_t n_pix_lanes;       // pixel lanes of the rank; 0: one stream (lane = pixel lane)
     int32_t stream_extra;      // the first stream_extra streams of the rank render max_samples + 1 samples
+    // progressive passes (b200pt_render_pass): this launch renders samples first_sample .. max_samples-1
+    // of every pixel; first_sample > 0 continues the pixel's RNG stream (LaneArrays::rng_save) and its sum
+    int32_t first_sample;
     // next-event estimation (B200PT_FLAG_NEE); n_lights == 0 or nee == 0: the reference's estimator verbatim
     const LightTri* lights;
     const float* light_cdf;    // n_lights ascending values, last = 1
@@ -217,6 +220,13 @@ enum ShadeResult { LANE_CONTINUE = 0, LANE_DONE = 1 };
 
 PT_HD bool bad3(f3 v) {
     return isinf(v.x) || isinf(v.y) || isinf(v.z) || isnan(v.x) || isnan(v.y) || isnan(v.z);
+}
+
+// Second moment of the sample values, kept in sum.w: square of the Rec.709 luminance of a finished sample.  The
+// per-pixel variance estimate of the progressive mode (b200pt_pass_info::rel_variance) is built from it.
+PT_HD float sample_lum2(f3 value) {
+    const float l = lum709(value);
+    return l * l;
 }
 
 // finish the sample in flight with `contrib`, then start the next one or retire the lane
@@ -407,6 +417,16 @@ PT_HD uint32_t to_8bit(float f) {
     if (s >= 255.0f) return 255u;
     if (s <= 0.0f) return 0u;
     return (uint32_t)(int)s;
+}
+// Output transfer of the resolve step.  0: the reference as shipped (linear values straight into make_rgba).
+// 1: the line the reference carries commented out, device.cu:248: color = saturate(pow(color, 1 / 2.2)).
+PT_HD f3 output_transfer(f3 c, int transfer) {
+    if (transfer == 1) {
+        const float g = 1.0f / 2.2f;
+        c = f3{fminf(fmaxf(dm_pow(c.x, g), 0.0f), 1.0f), fminf(fmaxf(dm_pow(c.y, g), 0.0f), 1.0f),
+               fminf(fmaxf(dm_pow(c.z, g), 0.0f), 1.0f)};
+    }
+    return c;
 }
 PT_HD uint32_t to_rgba(f3 c) {
     return (to_8bit(c.x) << 0) + (to_8bit(c.y) << 8) + (to_8bit(c.z) << 16) + (0xffU << 24);

@@ -33,6 +33,9 @@ namespace pt {
 #ifndef PT_SUSPEND_MIN
 #define PT_SUSPEND_MIN 100000 // ... only in launches of at least this many rays (smaller ones run every ray to its end)
 #endif
+#ifndef PT_SUSPEND_STEPS
+#define PT_SUSPEND_STEPS 0   // ... and (if > 0) any warp parks whatever it still holds this many loop steps after the queue drained
+#endif
 #ifndef PT_PREFETCH_TRI
 #define PT_PREFETCH_TRI 0    // prefetch.global.L1 of the first leaf triangle at the end of a node step
 #endif
@@ -74,6 +77,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
 
     bool has_ray = false, exhausted = false;
     const int park = (SUSPEND && n >= (uint32_t)PT_SUSPEND_MIN) ? PT_SUSPEND_LANES : 0;  // 0: only an empty warp leaves
+    int slice = PT_SUSPEND_STEPS;  // time slice left once the queue is drained (warp-uniform)
     uint32_t ray_index = 0;
     f3 o{0, 0, 0}, d{0, 0, 1};
     float tmin = 0, tmax = 0;
@@ -124,7 +128,9 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         if (exhausted) {
             // out of new rays: run what is left; a SUSPEND walk parks the last few rays of the warp instead
             if constexpr (SUSPEND) {
-                if (__popc(act) <= park && __all_sync(FULL, !has_ray || sp <= kSuspStack + 1)) {
+                bool leave = __popc(act) <= park;
+                if (PT_SUSPEND_STEPS > 0 && park > 0 && --slice < 0) leave = true;
+                if (leave && __all_sync(FULL, !has_ray || sp <= kSuspStack + 1)) {
                     if (has_ray) sink.suspend(ray_index, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack);
                     break;
                 }

@@ -49,14 +49,18 @@ __global__ void __launch_bounds__(kBlock) k_init_lanes(SceneView sv, LaneArrays 
     const uint32_t lane = ((i / w) * (uint32_t)parts + (uint32_t)part) * w + i % w;
     int px, py;
     lane_pixel(sv, lane, px, py);
-    uint32_t rng = rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset + (int)lane_stream(sv, lane) * sv.height));  // device.cu:226
+    // first pass of a frame: seed the pixel's stream (device.cu:226) and clear its sum; a later progressive pass
+    // continues the stream where the pixel's last sample left it
+    const bool first = sv.first_sample == 0;
+    uint32_t rng = first ? rng_seed((uint32_t)px, (uint32_t)(py + sv.seed_row_offset + (int)lane_stream(sv, lane) * sv.height))
+                         : la.rng_save[lane];
     f3 o, d;
     camera_ray(sv, px, py, rng, o, d);
     st4(la.ray_o[0] + i, f4{o.x, o.y, o.z, -1.0f});  // .w: prev_pdf of the NEE mode (camera ray: count emitters fully)
     if (la.rad) st4(la.rad + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
-    st4(la.ray_d[0] + i, f4{d.x, d.y, d.z, u2f(pack_ctl(0, 0, LOBE_NONE))});
+    st4(la.ray_d[0] + i, f4{d.x, d.y, d.z, u2f(pack_ctl((uint32_t)sv.first_sample, 0, LOBE_NONE))});
     st4(la.thr[0] + i, f4{1.0f, 1.0f, 1.0f, u2f(rng)});
-    st4(la.sum + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
+    if (first) st4(la.sum + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
     la.queue[0][i] = lane;
 }
 
@@ -202,9 +206,11 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
                     last_term = L.contrib;
                 } else {
                     const f4 g = ld4(la.rad + lane);
-                    s.x += g.x + L.contrib.x;
-                    s.y += g.y + L.contrib.y;
-                    s.z += g.z + L.contrib.z;
+                    const f3 value{g.x + L.contrib.x, g.y + L.contrib.y, g.z + L.contrib.z};
+                    s.x += value.x;
+                    s.y += value.y;
+                    s.z += value.z;
+                    s.w += sample_lum2(value);
                     st4(la.sum + lane, s);
                     st4(la.rad + lane, f4{0.0f, 0.0f, 0.0f, 0.0f});
                 }
@@ -213,9 +219,11 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
             s.x += L.contrib.x;
             s.y += L.contrib.y;
             s.z += L.contrib.z;
+            s.w += sample_lum2(L.contrib);
             st4(la.sum + lane, s);
         }
         keep = r == LANE_CONTINUE;
+        if (!keep) la.rng_save[lane] = L.rng;  // the pixel's stream after its last sample of this pass
     }
     // warp-aggregated append of the survivors to the other state set
     const unsigned m = __ballot_sync(0xffffffffu, keep);
@@ -285,9 +293,11 @@ struct ShadowSink {
         if (f2u(c.w) & 1u) {
             const f4 f = ld4(sh_f + i);
             f4 s = ld4(sum + lane);
-            s.x += g.x + f.x;
-            s.y += g.y + f.y;
-            s.z += g.z + f.z;
+            const f3 value{g.x + f.x, g.y + f.y, g.z + f.z};
+            s.x += value.x;
+            s.y += value.y;
+            s.z += value.z;
+            s.w += sample_lum2(value);
             st4(sum + lane, s);
             g = f4{0.0f, 0.0f, 0.0f, 0.0f};
         }
@@ -304,7 +314,7 @@ __global__ void __launch_bounds__(kWalkBlock, kWalkMinBlocks) k_shadow(SceneView
 }
 
 // device.cu:246-253.  sum is indexed by lane; the frame is written row-flipped.
-__global__ void __launch_bounds__(256) k_resolve(SceneView sv, const f4* __restrict__ sum, float inv_spp,
+__global__ void __launch_bounds__(256) k_resolve(SceneView sv, const f4* __restrict__ sum, float inv_spp, int transfer,
                                                  uint32_t* __restrict__ rgba, f4* __restrict__ mean) {
     const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
     if (lane >= (uint32_t)sv.n_lanes) return;
@@ -313,8 +323,34 @@ __global__ void __launch_bounds__(256) k_resolve(SceneView sv, const f4* __restr
     const f4 s = ld4(sum + lane);
     const f3 c = f3{s.x, s.y, s.z} * inv_spp;
     const size_t ofs = (size_t)px + (size_t)sv.width * (size_t)(sv.height - 1 - py);
-    rgba[ofs] = to_rgba(c);
+    rgba[ofs] = to_rgba(output_transfer(c, transfer));   // the float frame stays linear
     st4(mean + ofs, f4{c.x, c.y, c.z, 1.0f});
+}
+
+// Progressive mode: how converged is the frame after `n` samples per pixel?  Per pixel, from sum.xyz (sum of the
+// sample values) and sum.w (sum of their squared luminances): m = lum(sum)/n, unbiased sample variance
+// s2 = max(0, w/n - m^2) n/(n-1), variance of the mean s2/n, relative to m^2 + 1e-2 (the epsilon of the relMSE
+// gate).  The mean of that over the pixels estimates the relMSE of the frame against its own limit.
+// binary64 throughout; one partial per block added in a fixed tree so that the result does not depend on timing.
+__global__ void __launch_bounds__(256) k_pass_stats(const f4* __restrict__ sum, uint32_t n_lanes, int n, double* __restrict__ partial) {
+    __shared__ double sh[256];
+    const uint32_t lane = blockIdx.x * blockDim.x + threadIdx.x;
+    double rel = 0.0;
+    if (lane < n_lanes && n > 1) {
+        const f4 s = ld4(sum + lane);
+        const double dn = (double)n;
+        const double m = (0.2126 * (double)s.x + 0.7152 * (double)s.y + 0.0722 * (double)s.z) / dn;
+        const double s2 = fmax(0.0, (double)s.w / dn - m * m) * (dn / (dn - 1.0));
+        rel = (s2 / dn) / (m * m + 1e-2);
+        if (!(rel == rel)) rel = 0.0;   // NaN sums (a NaN sample value) do not poison the frame's figure
+    }
+    sh[threadIdx.x] = rel;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if ((int)threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
 }
 
 // several streams per pixel: per-pixel sum of the streams' sums, added in stream order (the order in which the
@@ -428,8 +464,12 @@ void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st) {
     k_shadow<<<pblocks(max_count), kWalkBlock, 0, st>>>(sv, la, k);
 }
-void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, uint32_t* rgba, f4* mean, cudaStream_t st) {
-    k_resolve<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, inv_spp, rgba, mean);
+void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, int transfer, uint32_t* rgba, f4* mean, cudaStream_t st) {
+    k_resolve<<<blocks(sv.n_lanes, 256), 256, 0, st>>>(sv, sum, inv_spp, transfer, rgba, mean);
+}
+unsigned pass_stats_blocks(uint32_t n_lanes) { return blocks(n_lanes, 256); }
+void launch_pass_stats(const f4* sum, uint32_t n_lanes, int n_samples, double* partial, cudaStream_t st) {
+    k_pass_stats<<<blocks(n_lanes, 256), 256, 0, st>>>(sum, n_lanes, n_samples, partial);
 }
 void launch_fold_streams(const f4* sum, f4* out, uint32_t n_pix, int streams, cudaStream_t st) {
     k_fold_streams<<<blocks(n_pix, 256), 256, 0, st>>>(sum, out, n_pix, streams);

@@ -119,6 +119,7 @@ class Oracle(_SceneChecker):
         L.oracle_set_render.argtypes = [P, C.c_int, C.c_int, C.c_int, C.c_int]
         L.oracle_build.argtypes = [P]
         L.oracle_set_nee.argtypes = [P, C.c_int]
+        L.oracle_set_output.argtypes = [P, C.c_int]
         L.oracle_shadow_rays.argtypes = [P]
         L.oracle_shadow_rays.restype = C.c_uint64
         L.oracle_camera.argtypes = [P, P, P, C.c_float, C.c_int, C.c_int, P]
@@ -153,6 +154,11 @@ class Oracle(_SceneChecker):
     def set_nee(self, on=True):
         """Next-event estimation mode (light sampling + MIS); off = the reference's estimator."""
         self.L.oracle_set_nee(self.h, int(on))
+        return self
+
+    def set_output(self, transfer):
+        """0: linear RGBA8 (reference as shipped); 1: saturate(pow(c, 1/2.2)), device.cu:248."""
+        self.L.oracle_set_output(self.h, int(transfer))
         return self
 
     def primary_hits(self, brute=False, threads=NCPU):
@@ -323,3 +329,17 @@ def rel_mse(img, ref, eps=1e-2):
     a = np.asarray(img, np.float64)[..., :3]
     b = np.asarray(ref, np.float64)[..., :3]
     return float(np.mean(np.sum((a - b) ** 2, -1) / (np.sum(b * b, -1) + eps)))
+
+
+def rel_variance(sum4, n):
+    """b200pt_pass_info::rel_variance restated in numpy (binary64): mean over pixels of the variance of the pixel
+    mean relative to mean^2 + 1e-2, in Rec.709 luminance, from sum.xyz (sample sum) and sum.w (sum of squared
+    sample luminances) after n samples."""
+    s = np.asarray(sum4, np.float64).reshape(-1, 4)
+    if n < 2:
+        return 0.0
+    m = (0.2126 * s[:, 0] + 0.7152 * s[:, 1] + 0.0722 * s[:, 2]) / n
+    s2 = np.maximum(0.0, s[:, 3] / n - m * m) * (n / (n - 1.0))
+    rel = (s2 / n) / (m * m + 1e-2)
+    rel = np.where(np.isnan(rel), 0.0, rel)
+    return float(rel.sum() / rel.size)

@@ -388,6 +388,7 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
             L.depth = 0;
             L.lobe = LOBE_NONE;
             f3 sum = mk3(0.0f), gathered = mk3(0.0f);
+            float second = 0.0f;  // sum.w of the kernels: sum of squared sample luminances
             L.prev_pdf = -1.0f;
             if (sv.max_samples > 0 && sv.max_depth > 0) {
                 for (;;) {
@@ -416,10 +417,12 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
                         }
                         if (L.sample_ended) {
                             sum = sum + (gathered + L.contrib);
+                            second += sample_lum2(gathered + L.contrib);
                             gathered = mk3(0.0f);
                         }
                     } else if (L.sample_ended) {
                         sum = sum + L.contrib;
+                        second += sample_lum2(L.contrib);
                     }
                     if (r == LANE_DONE) break;
                 }
@@ -428,6 +431,7 @@ uint64_t emu_render(emu_scene* s, int rank, int world, int shard_mode, int nthre
             o[0] = sum.x;
             o[1] = sum.y;
             o[2] = sum.z;
+            o[3] = second;
         }
         rays += nr;
         cnt_shadow += nsh;

@@ -44,6 +44,12 @@ if __name__ == "__main__":
         timing("dragon", 1920, 1080, 32, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
         timing("car", 1920, 1080, 32, 8, flags=pt.FLAG_TIMING, env="color", env_intensity=0.0)
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "ab2":
+        # product configuration (two concurrent sub-frames, no per-kernel events), parity at a size where walks get parked
+        check("dragon", 640, 360, 4, 8, env="color", env_intensity=0.0)
+        timing("dragon", 1920, 1080, 128, 8, env="color", env_intensity=0.0)
+        timing("car", 1920, 1080, 128, 8, env="color", env_intensity=0.0)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "parts":
         # concurrent sub-frames: frame time without per-kernel events, for B200PT_PARTS = 1..4
         for scene, spp in (("dragon", 32), ("car", 32), ("dragon", 128)):
