@@ -126,6 +126,7 @@ typedef struct b200pt_stats {
     double shadow_ms;         /* share spent in the shadow kernel (FLAG_TIMING)    */
     uint32_t n_lights;        /* emissive triangles in the light table (FLAG_NEE)  */
     uint32_t reserved;
+    double refit_ms;          /* last b200pt_refit_accel                           */
 } b200pt_stats;
 
 typedef struct b200pt_ctx b200pt_ctx;
@@ -151,6 +152,18 @@ int b200pt_add_mesh(b200pt_ctx* ctx, const float* verts, const float* normals, c
  * structure, built on the GPU (LBVH -> 8-wide compressed).  B200PT_ERR_EMPTY when
  * no mesh was added. */
 int b200pt_build_accel(b200pt_ctx* ctx);
+
+/* Moving geometry (the reference rebuilds everything when anything moves — it has no such call).
+ * b200pt_update_mesh replaces the positions (and, when normals != NULL, the normals) of mesh `mesh_index`; nv
+ * must be the mesh's vertex count, indices and uvs stay.  b200pt_refit_accel then recomputes triangle blocks,
+ * child boxes and quantisation grids of the existing tree bottom-up on the GPU (one launch per level) without
+ * touching its topology: 0.1-0.2 ms where a build takes milliseconds.  The closest hit is defined
+ * independently of the tree (smallest t, ties to the smaller triangle id), so a refitted tree returns exactly
+ * the hits of a freshly built one (tests/test_refit.py); only the traversal cost degrades when the motion is
+ * large — rebuild with b200pt_build_accel then.  Rendering between update and refit / build is an error. */
+int b200pt_update_mesh(b200pt_ctx* ctx, int32_t mesh_index, const float* verts, const float* normals /* may be NULL */,
+                       int32_t nv);
+int b200pt_refit_accel(b200pt_ctx* ctx);
 
 /* material buffer upload (application.cpp:257-259) and its per-frame re-upload
  * reset_field (application.cpp:297-304).  Cheap; never rebuilds the BVH. */

@@ -54,7 +54,8 @@ class Stats(C.Structure):
                 ("paths", C.c_uint64), ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("iterations", C.c_uint64), ("bvh_nodes", C.c_uint32),
                 ("bvh_tris", C.c_uint32), ("bvh_bytes", C.c_uint64), ("shadow_rays", C.c_uint64),
-                ("shadow_ms", C.c_double), ("n_lights", C.c_uint32), ("reserved", C.c_uint32)]
+                ("shadow_ms", C.c_double), ("n_lights", C.c_uint32), ("reserved", C.c_uint32),
+                ("refit_ms", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -131,6 +132,8 @@ def lib() -> C.CDLL:
     L.b200pt_set_camera.argtypes = [P, P, P, P, P]
     L.b200pt_set_render.argtypes = [P, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
     L.b200pt_render.argtypes = [P]
+    L.b200pt_update_mesh.argtypes = [P, C.c_int32, P, P, C.c_int32]
+    L.b200pt_refit_accel.argtypes = [P]
     L.b200pt_render_pass.argtypes = [P, C.c_int32, C.POINTER(PassInfo)]
     L.b200pt_render_restart.argtypes = [P]
     L.b200pt_render_progressive.argtypes = [P, C.c_int32, C.c_double, PASS_FN, C.c_void_p, C.POINTER(PassInfo)]

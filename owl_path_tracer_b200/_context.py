@@ -49,6 +49,15 @@ class Context:
     def build_accel(self):
         self._ck(self._L.b200pt_build_accel(self._h), "build_accel")
 
+    def update_mesh(self, mesh_index, verts, normals=None):
+        """New vertex positions (and normals) of a mesh; follow with refit_accel() or build_accel()."""
+        verts = np.ascontiguousarray(verts, np.float32)
+        normals = None if normals is None else np.ascontiguousarray(normals, np.float32)
+        self._ck(self._L.b200pt_update_mesh(self._h, int(mesh_index), _ptr(verts), _ptr(normals), verts.shape[0]), "update_mesh")
+
+    def refit_accel(self):
+        self._ck(self._L.b200pt_refit_accel(self._h), "refit_accel")
+
     def set_materials(self, mats):
         mats = np.ascontiguousarray(mats, MATERIAL_DTYPE)
         self._ck(self._L.b200pt_set_materials(self._h, _ptr(mats), mats.shape[0]), "set_materials")

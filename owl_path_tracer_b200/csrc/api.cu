@@ -65,6 +65,10 @@ struct b200pt_ctx {
     size_t lights_capacity = 0;
     DeviceBVH bvh;
     bool built = false;
+    // b200pt_update_mesh / b200pt_refit_accel
+    std::vector<int32_t> h_mesh_vbase, h_mesh_nv;  // vertex range of every mesh in the flattened arrays
+    bool geometry_moved = false;                   // vertices changed since the tree was built / refitted
+    float* d_node_box = nullptr;                   // refit scratch, 6 floats per wide node
     // settings
     int env_w = 0, env_h = 0, env_use = 0, env_auto = 0;
     float env_color[3] = {0, 0, 0}, env_intensity = 0;
@@ -117,7 +121,8 @@ static void free_lanes(b200pt_ctx* c) {
 }
 static void free_scene(b200pt_ctx* c) {
     cudaFree(c->d_pos); cudaFree(c->d_nrm); cudaFree(c->d_uv); cudaFree(c->d_idx4); cudaFree(c->d_meshes);
-    cudaFree(c->d_texels); cudaFree(c->bvh.nodes); cudaFree(c->bvh.tris);
+    cudaFree(c->d_texels); cudaFree(c->bvh.nodes); cudaFree(c->bvh.tris); cudaFree(c->d_node_box);
+    c->d_node_box = nullptr;
     c->d_pos = c->d_nrm = nullptr; c->d_uv = nullptr; c->d_idx4 = nullptr; c->d_meshes = nullptr; c->d_texels = nullptr;
     c->bvh = DeviceBVH{};
     c->built = false;
@@ -295,6 +300,8 @@ extern "C" int b200pt_add_mesh(b200pt_ctx* c, const float* verts, const float* n
         c->h_texels.insert(c->h_texels.end(), px, px + (size_t)tex_w * tex_h);
     }
     c->h_meshes.push_back(mi);
+    c->h_mesh_vbase.push_back(vbase);
+    c->h_mesh_nv.push_back(nv);
     c->built = false;
     c->mesh_mats_dirty = true;
     if (mesh_index) *mesh_index = mesh;
@@ -335,6 +342,69 @@ extern "C" int b200pt_build_accel(b200pt_ctx* c) {
     c->stats.bvh_tris = (uint32_t)nt;
     c->stats.bvh_bytes = (uint64_t)c->bvh.n_nodes * sizeof(Node8) + (uint64_t)c->bvh.n_tris * sizeof(TriPair);
     c->built = true;
+    c->geometry_moved = false;
+    return B200PT_OK;
+}
+
+// ---- moving geometry: new vertex positions / normals for a mesh, then a refit of the tree
+static void scene_bounds(b200pt_ctx* c) {
+    for (int a = 0; a < 3; ++a) {
+        c->lo[a] = 3e38f;
+        c->hi[a] = -3e38f;
+    }
+    c->max_abs = 0;
+    for (const f4& p : c->h_pos) {
+        const float v[3] = {p.x, p.y, p.z};
+        for (int a = 0; a < 3; ++a) {
+            c->lo[a] = fminf(c->lo[a], v[a]);
+            c->hi[a] = fmaxf(c->hi[a], v[a]);
+            c->max_abs = fmaxf(c->max_abs, fabsf(v[a]));
+        }
+    }
+}
+
+extern "C" int b200pt_update_mesh(b200pt_ctx* c, int32_t mesh_index, const float* verts, const float* normals, int32_t nv) {
+    if (!c || !verts) return fail(B200PT_ERR_INVALID, "update_mesh: null argument");
+    if (mesh_index < 0 || mesh_index >= (int32_t)c->h_meshes.size()) return fail(B200PT_ERR_BOUNDS, "update_mesh: no such mesh");
+    const int32_t vbase = c->h_mesh_vbase[(size_t)mesh_index];
+    if (nv != c->h_mesh_nv[(size_t)mesh_index])
+        return fail(B200PT_ERR_INVALID, "update_mesh: the mesh has " + std::to_string(c->h_mesh_nv[(size_t)mesh_index]) +
+                                            " vertices (topology is fixed; rebuild the scene to change it)");
+    for (int i = 0; i < nv; ++i) {
+        c->h_pos[(size_t)vbase + i] = f4{verts[3 * i], verts[3 * i + 1], verts[3 * i + 2], 0.0f};
+        if (normals) c->h_nrm[(size_t)vbase + i] = f4{normals[3 * i], normals[3 * i + 1], normals[3 * i + 2], 0.0f};
+    }
+    scene_bounds(c);
+    c->pass_done = 0;
+    c->mesh_mats_dirty = true;  // NEE mode: the light table holds positions and areas
+    if (c->built) {             // before the first build the staging arrays are all there is
+        CU(cudaSetDevice(c->cfg.device_ordinal));
+        CU(cudaMemcpyAsync(c->d_pos + vbase, c->h_pos.data() + vbase, sizeof(f4) * (size_t)nv, cudaMemcpyHostToDevice, c->stream));
+        if (normals)
+            CU(cudaMemcpyAsync(c->d_nrm + vbase, c->h_nrm.data() + vbase, sizeof(f4) * (size_t)nv, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        c->geometry_moved = true;
+    }
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_refit_accel(b200pt_ctx* c) {
+    if (!c) return fail(B200PT_ERR_INVALID, "refit_accel: null context");
+    if (!c->built) return fail(B200PT_ERR_INVALID, "refit_accel: call b200pt_build_accel first");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    if (!c->d_node_box) CU(cudaMalloc(&c->d_node_box, sizeof(float) * 6 * (size_t)c->bvh.n_nodes));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    std::string err;
+    if (!refit_bvh_device(c->d_pos, c->d_idx4, c->max_abs, &c->bvh, c->d_node_box, c->stream, err))
+        return fail(B200PT_ERR_CUDA, "bvh refit: " + err);
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->stats.refit_ms = ms;
+    c->geometry_moved = false;
+    c->pass_done = 0;
     return B200PT_OK;
 }
 
@@ -578,6 +648,8 @@ static int check_ready(b200pt_ctx* c, const char* who) {
     if (!c->built) return fail(B200PT_ERR_INVALID, std::string(who) + ": call b200pt_build_accel first");
     if (!c->d_mats) return fail(B200PT_ERR_INVALID, std::string(who) + ": call b200pt_set_materials first");
     if (c->width <= 0) return fail(B200PT_ERR_INVALID, std::string(who) + ": call b200pt_set_render first");
+    if (c->geometry_moved)
+        return fail(B200PT_ERR_INVALID, std::string(who) + ": vertices moved (b200pt_update_mesh): call b200pt_refit_accel or b200pt_build_accel first");
     return B200PT_OK;
 }
 

@@ -240,6 +240,7 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
         }
         levels = 0;
         n_items = 1;
+        out->level_end.assign(1, 1u);  // level 0: the root
         while (n_items > 0) {
             ++levels;
             k_collapse<<<(n_items + 63) / 64, 64, 0, st>>>(qa, n_items, bin, vals2, tri_lo, tri_hi, d_pos, d_idx4, nodes,
@@ -248,6 +249,7 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
             CK(cudaMemcpyAsync(h_counters, counters, sizeof h_counters, cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
             n_items = h_counters[2];
+            if (n_items) out->level_end.push_back(h_counters[0]);  // the children this level allocated form the next one
             CK(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), st));
             std::swap(qa, qb);
             if (levels > 4 * kStackSize) {
@@ -280,6 +282,32 @@ fail:
     cudaFree(arena);
     cudaFree(tris);
     return false;
+}
+
+__global__ void k_refit_wide(uint32_t first, uint32_t count, Node8* nodes, TriPair* tris, const f4* __restrict__ pos,
+                             const int32_t* __restrict__ idx4, float pad, float* node_box) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) refit_wide_node(first + i, nodes, tris, pos, idx4, pad, node_box);
+}
+
+bool refit_bvh_device(const f4* d_pos, const int32_t* d_idx4, float max_abs, DeviceBVH* bvh, float* d_node_box, cudaStream_t st,
+                      std::string& err) {
+    if (!bvh->nodes || bvh->level_end.empty() || bvh->level_end.back() != bvh->n_nodes) {
+        err = "no tree to refit";
+        return false;
+    }
+    const float pad = max_abs * 3.8146973e-6f /* 2^-18 */ + 1e-30f;  // build_bvh_device's margin
+    for (int l = (int)bvh->level_end.size() - 1; l >= 0; --l) {
+        const uint32_t first = l ? bvh->level_end[(size_t)l - 1] : 0u, count = bvh->level_end[(size_t)l] - first;
+        if (!count) continue;
+        k_refit_wide<<<(count + 63) / 64, 64, 0, st>>>(first, count, bvh->nodes, bvh->tris, d_pos, d_idx4, pad, d_node_box);
+        const cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            err = std::string("k_refit_wide: ") + cudaGetErrorString(e);
+            return false;
+        }
+    }
+    return true;
 }
 
 }  // namespace pt

@@ -16,10 +16,16 @@ struct DeviceBVH {
     TriPair* tris = nullptr;
     uint32_t n_nodes = 0, n_tris = 0;
     int levels = 0;
+    std::vector<uint32_t> level_end;  // nodes of level l are [level_end[l-1], level_end[l]) (level 0 = the root): refit order
 };
 
 bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const float scene_lo[3],
                       const float scene_hi[3], float max_abs, DeviceBVH* out, cudaStream_t st, std::string& err);
+
+// Vertices moved, topology kept: triangle blocks, child boxes and quantisation grids of the wide tree are
+// recomputed bottom-up, one launch per level (pt_build.h refit_wide_node).  node_box: scratch, 6 floats per node.
+bool refit_bvh_device(const f4* d_pos, const int32_t* d_idx4, float max_abs, DeviceBVH* bvh, float* d_node_box, cudaStream_t st,
+                      std::string& err);
 
 // Path state, structure of arrays with 16-byte elements (one LDG.128 / STG.128 each).
 // The state of the paths in flight is kept COMPACT: entry i of set (k & 1) belongs to the i-th

@@ -625,4 +625,106 @@ PT_HD void collapse_node(CollapseItem item, const BinNode* bin, const uint32_t* 
     (void)n_tris;
 }
 
+// ---- refit of the finished wide tree (b200pt_refit_accel): vertices moved, topology kept.
+// Wide node `ni`: its leaf slots get their triangle blocks rewritten from the current vertex positions and their
+// boxes from the triangles' padded boxes (tri_box, the builder's own), its inner slots take the box the child
+// wrote into node_box one level below; the node then gets a new quantisation grid and child planes by the very
+// rules of collapse_node (1.01 x extent, origin 1/8 step below, 1/64 step outward slack).  w1 (child base,
+// triangle base, meta bytes) and the slot assignment are untouched.  node_box: 6 floats per node (lo, hi).
+// Callers run the levels of the tree bottom-up (node indices of a level are contiguous: DeviceBVH::level_end).
+PT_HD void refit_wide_node(uint32_t ni, Node8* nodes, TriPair* tris, const f4* pos, const int32_t* idx4, float pad,
+                           float* node_box) {
+    Node8 n = nodes[ni];
+    const uint32_t imask = n.w[0].w >> 24;
+    const uint32_t child_base = n.w[1].x, tri_base = n.w[1].y;
+    float clo[8][3], chi[8][3];
+    bool present[8];
+    float nlo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, nhi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    for (int s = 0; s < 8; ++s) {
+        const uint32_t meta = ((s < 4 ? n.w[1].z : n.w[1].w) >> (8 * (s & 3))) & 0xFFu;
+        present[s] = meta != 0;
+        if (!present[s]) continue;
+        for (int a = 0; a < 3; ++a) {
+            clo[s][a] = 3.0e38f;
+            chi[s][a] = -3.0e38f;
+        }
+        if ((meta & 0x18u) == 0x18u) {  // inner child: (1 << 5) | (24 + s)
+            const uint32_t child = child_base + (uint32_t)popc32(imask & ((1u << s) - 1u));
+            for (int a = 0; a < 3; ++a) {
+                clo[s][a] = node_box[6 * (size_t)child + a];
+                chi[s][a] = node_box[6 * (size_t)child + 3 + a];
+            }
+        } else {
+            const int nb = popc32(meta >> 5);
+            const uint32_t first = tri_base + (meta & 0x1Fu);
+            for (int blk = 0; blk < nb; ++blk) {
+                TriPair o = tris[first + (uint32_t)blk];
+                const uint32_t id[2] = {f2u(o.w[4].z), f2u(o.w[4].w)};
+                float v[2][9];
+                for (int half = 0; half < 2; ++half) {
+                    if (id[half] != 0xFFFFFFFFu) {
+                        const uint32_t t = id[half];
+                        const f4 a = pos[idx4[4 * (size_t)t + 0]], b = pos[idx4[4 * (size_t)t + 1]],
+                                 c = pos[idx4[4 * (size_t)t + 2]];
+                        v[half][0] = a.x; v[half][1] = a.y; v[half][2] = a.z;
+                        v[half][3] = b.x - a.x; v[half][4] = b.y - a.y; v[half][5] = b.z - a.z;
+                        v[half][6] = c.x - a.x; v[half][7] = c.y - a.y; v[half][8] = c.z - a.z;
+                        float lo[3], hi[3];
+                        tri_box(pos, idx4, t, pad, lo, hi);
+                        for (int k = 0; k < 3; ++k) {
+                            clo[s][k] = fminf(clo[s][k], lo[k]);
+                            chi[s][k] = fmaxf(chi[s][k], hi[k]);
+                        }
+                    } else {
+                        for (int q2 = 0; q2 < 9; ++q2) v[half][q2] = 0.0f;
+                    }
+                }
+                o.w[0] = f4{v[0][0], v[1][0], v[0][1], v[1][1]};
+                o.w[1] = f4{v[0][2], v[1][2], v[0][3], v[1][3]};
+                o.w[2] = f4{v[0][4], v[1][4], v[0][5], v[1][5]};
+                o.w[3] = f4{v[0][6], v[1][6], v[0][7], v[1][7]};
+                o.w[4] = f4{v[0][8], v[1][8], u2f(id[0]), u2f(id[1])};
+                tris[first + (uint32_t)blk] = o;
+            }
+        }
+        for (int a = 0; a < 3; ++a) {
+            nlo[a] = fminf(nlo[a], clo[s][a]);
+            nhi[a] = fmaxf(nhi[a], chi[s][a]);
+        }
+    }
+    for (int a = 0; a < 3; ++a) {
+        node_box[6 * (size_t)ni + a] = nlo[a];
+        node_box[6 * (size_t)ni + 3 + a] = nhi[a];
+    }
+    // same grid and outward quantisation as collapse_node
+    const uint32_t ex = quant_exponent((nhi[0] - nlo[0]) * 1.01f), ey = quant_exponent((nhi[1] - nlo[1]) * 1.01f),
+                   ez = quant_exponent((nhi[2] - nlo[2]) * 1.01f);
+    const float inv[3] = {u2f((254u - ex) << 23), u2f((254u - ey) << 23), u2f((254u - ez) << 23)};
+    nlo[0] = nlo[0] - 0.125f * u2f(ex << 23);
+    nlo[1] = nlo[1] - 0.125f * u2f(ey << 23);
+    nlo[2] = nlo[2] - 0.125f * u2f(ez << 23);
+    uint8_t q[6][8];
+    for (int a = 0; a < 6; ++a)
+        for (int s = 0; s < 8; ++s) q[a][s] = 0;
+    for (int s = 0; s < 8; ++s) {
+        if (!present[s]) continue;
+        for (int a = 0; a < 3; ++a) {
+            float ql = floorf((clo[s][a] - nlo[a]) * inv[a] - 0.015625f);
+            float qh = ceilf((chi[s][a] - nlo[a]) * inv[a] + 0.015625f);
+            ql = fminf(fmaxf(ql, 0.0f), 255.0f);
+            qh = fminf(fmaxf(qh, 0.0f), 255.0f);
+            q[a][s] = (uint8_t)ql;
+            q[3 + a][s] = (uint8_t)qh;
+        }
+    }
+    auto pack4 = [](const uint8_t* p) {
+        return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+    };
+    n.w[0] = u4{f2u(nlo[0]), f2u(nlo[1]), f2u(nlo[2]), ex | (ey << 8) | (ez << 16) | (imask << 24)};
+    n.w[2] = u4{pack4(q[0]), pack4(q[0] + 4), pack4(q[1]), pack4(q[1] + 4)};
+    n.w[3] = u4{pack4(q[2]), pack4(q[2] + 4), pack4(q[3]), pack4(q[3] + 4)};
+    n.w[4] = u4{pack4(q[4]), pack4(q[4] + 4), pack4(q[5]), pack4(q[5] + 4)};
+    nodes[ni] = n;
+}
+
 }  // namespace pt

@@ -189,14 +189,42 @@ bool modify_material(program_data& pdata, const test_data& test, float value) { 
 void render_frame(b200pt_ctx* ctx, const program_data& pdata, const test_data& tdata, const std::string& values,
                   const std::string& out_dir) {
     host::say("TRACING\n");
-    check(b200pt_render(ctx), "render");
+    const std::string stem = pdata.scene + "_" + tdata.name + "_" + tdata.attribute_name + "(" + values + ")";
+    if (pdata.progressive_pass > 0) {
+        // the same frame in passes: every pass continues the pixels' RNG streams, so the last pass leaves the
+        // image of the blocking launch (or, with a target, the reference's image at the sample count reached)
+        struct pass_ctx {
+            const program_data* pdata;
+            const std::string* stem;
+            const std::string* out_dir;
+        } pc{&pdata, &stem, &out_dir};
+        auto on_pass = [](void* user, const b200pt_pass_info* info, const uint32_t* rgba, const float*) -> int {
+            const pass_ctx* pc = static_cast<const pass_ctx*>(user);
+            char line[160];
+            snprintf(line, sizeof line, "pass: %d spp, rel. variance %.3e, %.1f ms, %.0f Mrays/s\n", info->samples_done,
+                     info->rel_variance, info->render_ms, info->render_ms > 0 ? info->rays / info->render_ms * 1e-3 : 0.0);
+            host::say("%s", line);
+            if (pc->pdata->save_passes) {
+                image_buffer img;
+                img.width = pc->pdata->buffer_size[0];
+                img.height = pc->pdata->buffer_size[1];
+                img.pixels.assign(rgba, rgba + (size_t)img.width * img.height);
+                write_image(img, *pc->stem + "_pass" + std::to_string(info->samples_done) + ".png", *pc->out_dir);
+            }
+            return 0;
+        };
+        b200pt_pass_info last{};
+        check(b200pt_render_progressive(ctx, pdata.progressive_pass, pdata.target_error, on_pass, &pc, &last), "render_progressive");
+        if (last.stopped_early) host::say("target reached after %d samples per pixel\n", last.samples_done);
+    } else {
+        check(b200pt_render(ctx), "render");
+    }
     const uint32_t* fb = nullptr;
     check(b200pt_framebuffer_rgba8(ctx, &fb), "framebuffer");
     image_buffer result;
     result.width = pdata.buffer_size[0];
     result.height = pdata.buffer_size[1];
     result.pixels.assign(fb, fb + (size_t)result.width * result.height);
-    const std::string stem = pdata.scene + "_" + tdata.name + "_" + tdata.attribute_name + "(" + values + ")";
     write_image(result, stem + ".png", out_dir);
     if (pdata.write_pfm) {  // float output next to the PNG (the reference only has the 8-bit image)
         const float* mean = nullptr;

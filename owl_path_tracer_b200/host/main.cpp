@@ -8,6 +8,8 @@
 //   --env-intensity F  --detail N  --device K  --out DIR  --stats
 //   --nee (light sampling + MIS mode)  --streams V (RNG streams per pixel)  --pfm (float frame next to the PNG)
 //   --env-float (environment.hdr as float radiance instead of the reference's 8-bit conversion)
+//   --progressive N (frame in passes of N samples)  --target-error E (stop once the relative-variance figure <= E)
+//   --save-passes (PNG after every pass)  --gamma (RGBA8 through saturate(pow(c, 1/2.2)), the reference's device.cu:248)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -21,7 +23,9 @@ int main(int argc, char** argv) {
     std::string out_dir = std::filesystem::current_path().string();
     host::load_options opt;
     int device = 0, flags = 0, streams = 1;
-    bool stats = false, pfm = false;
+    bool stats = false, pfm = false, gamma = false, save_passes = false;
+    int progressive = 0;
+    double target_error = 0.0;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         auto need = [&](int n) {
@@ -49,9 +53,14 @@ int main(int argc, char** argv) {
         else if (a == "--streams") { need(1); streams = atoi(argv[++i]); }
         else if (a == "--pfm") pfm = true;
         else if (a == "--env-float") opt.env_float = true;
+        else if (a == "--progressive") { need(1); progressive = atoi(argv[++i]); }
+        else if (a == "--target-error") { need(1); target_error = atof(argv[++i]); }
+        else if (a == "--save-passes") save_passes = true;
+        else if (a == "--gamma") gamma = true;
         else if (a == "--help" || a == "-h") {
             printf("path_tracer [--assets DIR] [--scene NAME] [--size W H] [--spp N] [--depth N] [--env color|auto|map]\n"
                    "            [--env-intensity F] [--detail N] [--device K] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"
+                   "            [--env-float] [--progressive N] [--target-error E] [--save-passes] [--gamma]\n"
                    "without arguments: ./assets/settings.json and its scene, as the reference's executable\n");
             return 0;
         }
@@ -73,12 +82,20 @@ int main(int argc, char** argv) {
         cfg.flags = flags;
         cfg.streams_per_pixel = streams;
         pdata.write_pfm = pfm;
+        pdata.progressive_pass = progressive;
+        pdata.target_error = target_error;
+        pdata.save_passes = save_passes;
+        if (target_error > 0.0 && progressive <= 0) pdata.progressive_pass = 16;
         b200pt_ctx* ctx = nullptr;
         if (b200pt_create(&cfg, &ctx) != B200PT_OK) {
             fprintf(stderr, "b200pt_create failed: %s\n", b200pt_last_error());
             return 1;
         }
         host::bind_scene(pdata, ctx);
+        if (gamma && b200pt_set_output(ctx, B200PT_TRANSFER_GAMMA22) != B200PT_OK) {
+            fprintf(stderr, "b200pt_set_output failed: %s\n", b200pt_last_error());
+            return 1;
+        }
         host::test_loop(ctx, pdata, tdata, out_dir);
         if (stats) {
             b200pt_stats st{};

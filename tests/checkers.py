@@ -247,6 +247,8 @@ class Emu(_SceneChecker):
         L.emu_set_render.argtypes = [P, C.c_int, C.c_int, C.c_int, C.c_int]
         L.emu_build.argtypes = [P]
         L.emu_levels.argtypes = [P]
+        L.emu_update_mesh.argtypes = [P, C.c_int, P, P, C.c_int]
+        L.emu_refit.argtypes = [P]
         L.emu_walk_counters.argtypes = [P, P]
         L.emu_force_lbvh.argtypes = [P, C.c_int]
         L.emu_set_nee.argtypes = [P, C.c_int]
@@ -271,6 +273,14 @@ class Emu(_SceneChecker):
         assert r > 0, f"emu_build failed: {r}"
         self.n_nodes = r
         return r
+
+    def update_mesh(self, mesh, verts, normals=None):
+        verts = np.ascontiguousarray(verts, np.float32)
+        normals = None if normals is None else np.ascontiguousarray(normals, np.float32)
+        assert self.L.emu_update_mesh(self.h, int(mesh), _p(verts), None if normals is None else _p(normals), verts.shape[0]) == 0
+
+    def refit(self):
+        assert self.L.emu_refit(self.h) == 0
 
     @property
     def levels(self):

@@ -36,6 +36,8 @@ struct emu_scene {
     std::vector<TriPair> tris;
     float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}, max_abs = 0;
     int levels = 0;
+    std::vector<uint32_t> level_end;          // DeviceBVH::level_end of the emulated build
+    std::vector<int32_t> mesh_vbase, mesh_nv;  // vertex range of every mesh (emu_update_mesh)
     int ploc_rounds = 0;
     int debug_px = -1, debug_py = -1;  // print every ray of this pixel (debugging aid)
     int force_lbvh = 0;  // tools/bvh_quality.py: build the fallback tree on purpose
@@ -140,6 +142,8 @@ int emu_add_mesh(emu_scene* s, const float* verts, const float* normals, const f
         s->texels.insert(s->texels.end(), px, px + (size_t)tw * th);
     }
     s->meshes.push_back(mi);
+    s->mesh_vbase.push_back(vbase);
+    s->mesh_nv.push_back(nv);
     return mesh;
 }
 
@@ -267,6 +271,7 @@ int emu_build(emu_scene* s) {
     tri_count = 0;
     qa[0] = CollapseItem{root, 0u};
     s->levels = 0;
+    s->level_end.assign(1, 1u);
     while (n_items) {
         ++s->levels;
         uint32_t next_count = 0;
@@ -274,6 +279,7 @@ int emu_build(emu_scene* s) {
             collapse_node(qa[i], bin.data(), order.data(), tri_lo.data(), tri_hi.data(), s->pos.data(), s->idx4.data(),
                           s->nodes.data(), &node_count, s->tris.data(), &tri_count, qb.data(), &next_count, (int)n, plans.data());
         n_items = next_count;
+        if (n_items) s->level_end.push_back(node_count);
         std::swap(qa, qb);
         if (s->levels > 4 * kStackSize) return -2;
     }
@@ -287,6 +293,42 @@ int emu_build(emu_scene* s) {
 }
 
 int emu_levels(emu_scene* s) { return s->levels; }
+
+// b200pt_update_mesh + b200pt_refit_accel: same per-node function as k_refit_wide, levels bottom-up
+int emu_update_mesh(emu_scene* s, int mesh, const float* verts, const float* normals, int nv) {
+    if (mesh < 0 || mesh >= (int)s->meshes.size() || nv != s->mesh_nv[mesh]) return -1;
+    const int32_t vb = s->mesh_vbase[mesh];
+    for (int i = 0; i < nv; ++i) {
+        s->pos[vb + i] = f4{verts[3 * i], verts[3 * i + 1], verts[3 * i + 2], 0};
+        if (normals) s->nrm[vb + i] = f4{normals[3 * i], normals[3 * i + 1], normals[3 * i + 2], 0};
+    }
+    s->max_abs = 0;
+    for (int a = 0; a < 3; ++a) {
+        s->lo[a] = 3e38f;
+        s->hi[a] = -3e38f;
+    }
+    for (const f4& p : s->pos) {
+        const float v[3] = {p.x, p.y, p.z};
+        for (int a = 0; a < 3; ++a) {
+            s->lo[a] = fminf(s->lo[a], v[a]);
+            s->hi[a] = fmaxf(s->hi[a], v[a]);
+            s->max_abs = fmaxf(s->max_abs, fabsf(v[a]));
+        }
+    }
+    return 0;
+}
+int emu_refit(emu_scene* s) {
+    if (s->level_end.empty() || s->level_end.back() != s->nodes.size()) return -1;
+    const float pad = s->max_abs * 3.8146973e-6f + 1e-30f;
+    std::vector<float> node_box(6 * s->nodes.size());
+    for (int l = (int)s->level_end.size() - 1; l >= 0; --l) {
+        const uint32_t first = l ? s->level_end[l - 1] : 0u;
+        for (uint32_t i = first; i < s->level_end[l]; ++i)
+            refit_wide_node(i, s->nodes.data(), s->tris.data(), s->pos.data(), s->idx4.data(), pad, node_box.data());
+    }
+    refresh_view(s);
+    return 0;
+}
 uint32_t emu_n_pairs(emu_scene* s) { return (uint32_t)s->tris.size(); }
 void emu_force_lbvh(emu_scene* s, int on) { s->force_lbvh = on; }
 void emu_set_nee(emu_scene* s, int on) { s->nee = on; }

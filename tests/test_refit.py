@@ -1,0 +1,148 @@
+"""Moving geometry: b200pt_update_mesh + b200pt_refit_accel.
+
+The closest hit is defined independently of the tree (smallest Moller-Trumbore t, ties to the smaller triangle
+id), so a tree whose boxes were refitted to moved vertices must return exactly the hits — and therefore exactly
+the frame — of the oracle that was handed the moved geometry from the start.  The CPU test runs the refit
+function itself (pt_build.h refit_wide_node, compiled for the host by tests/emu); the GPU tests run k_refit_wide
+through the C ABI."""
+import numpy as np
+import pytest
+
+import owl_path_tracer_b200 as pt
+from checkers import Emu, Oracle
+
+CORNELL = dict(scene="cornell-box", depth=8, env="color", env_intensity=0.0)
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def same_hits(a, b):
+    return ((a["mesh"] == b["mesh"]) & (a["prim"] == b["prim"]) & (bits(a["t"]) == bits(b["t"])) &
+            (bits(a["u"]) == bits(b["u"])) & (bits(a["v"]) == bits(b["v"])))
+
+
+def moved(entities, which, scale, shift, wobble):
+    """entity `which` scaled about its centroid, shifted, and displaced along a sine field (normals kept)."""
+    out = []
+    for i, e in enumerate(entities):
+        v = np.array(e["verts"], np.float32)
+        if i == which:
+            c = v.mean(axis=0, dtype=np.float64).astype(np.float32)
+            v = (v - c) * np.float32(scale) + c + np.asarray(shift, np.float32)
+            v = v + np.float32(wobble) * np.sin(v[:, [1, 2, 0]] * np.float32(7.0)).astype(np.float32)
+            v = np.ascontiguousarray(v, np.float32)
+        out.append(dict(e, verts=v))
+    return out
+
+
+def checker_with(cls, sc, entities, **kw):
+    o = cls(**kw)
+    for e in entities:
+        o.add_mesh(e["verts"], e["normals"], e["idx"], e["material"], e["uvs"], e["tex"])
+    o.set_materials(sc.materials())
+    env = sc.environment
+    o.set_environment(env["rgba"], env["use"], env["auto"], env["color"], env["intensity"])
+    o.set_camera(*sc.camera)
+    o.set_render(sc.width, sc.height, sc.spp, sc.depth)
+    o.build()
+    return o
+
+
+def stress_rays(entities, which, n, seed):
+    """rays from random points towards points on the moved mesh's triangles (grazing and direct)"""
+    rng = np.random.default_rng(seed)
+    e = entities[which]
+    tri = e["idx"][rng.integers(0, len(e["idx"]), n)]
+    w = rng.dirichlet((1, 1, 1), n).astype(np.float32)
+    target = (e["verts"][tri] * w[:, :, None]).sum(axis=1)
+    allv = np.concatenate([x["verts"] for x in entities])
+    lo, hi = allv.min(axis=0), allv.max(axis=0)
+    org = (lo + (hi - lo) * rng.random((n, 3))).astype(np.float32)
+    d = target - org
+    d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-20)
+    return np.ascontiguousarray(org, np.float32), np.ascontiguousarray(d, np.float32)
+
+
+MOTIONS = [dict(scale=1.0, shift=(0.0, 0.0, 0.0), wobble=0.0),          # nothing moved: refit must be harmless
+           dict(scale=1.0, shift=(0.05, 0.02, -0.03), wobble=0.01),     # a small step of an animation
+           dict(scale=1.6, shift=(-0.4, 0.3, 0.2), wobble=0.05)]        # large: boxes grow a lot, hits must still be exact
+
+
+def test_refitted_tree_on_the_host_emulation_equals_the_oracle_on_the_moved_scene():
+    sc = pt.Scene(width=48, height=48, spp=2, **CORNELL)
+    ents = sc.entities()
+    which = max(range(len(ents)), key=lambda i: len(ents[i]["idx"]))     # the sphere (most triangles)
+    e = Emu().load_scene(sc)
+    for m in MOTIONS:
+        new = moved(ents, which, **m)
+        e.update_mesh(which, new[which]["verts"])
+        e.refit()
+        o = checker_with(Oracle, sc, new, det=True)
+        assert same_hits(e.primary_hits(), o.primary_hits()).all(), m
+        org, d = stress_rays(new, which, 4000, 7)
+        assert same_hits(e.trace(org, d), o.trace(org, d)).all(), m
+        re, ro = e.render(), o.render()
+        assert (bits(re["sum"]) == bits(ro["sum"])).all() and re["rays"] == ro["rays"], m
+
+
+@pytest.mark.gpu
+def test_refit_on_the_gpu_equals_the_oracle_and_a_fresh_build():
+    sc = pt.Scene(width=96, height=96, spp=4, **CORNELL)
+    ents = sc.entities()
+    which = max(range(len(ents)), key=lambda i: len(ents[i]["idx"]))
+    ctx = pt.Context()
+    ctx.bind(sc)
+    ctx.render()
+    for m in MOTIONS:
+        new = moved(ents, which, **m)
+        ctx.update_mesh(which, new[which]["verts"])
+        with pytest.raises(pt.B200ptError, match="refit_accel"):
+            ctx.render()                                     # stale tree: refuse, do not render garbage
+        ctx.refit_accel()
+        o = checker_with(Oracle, sc, new, det=True)
+        assert same_hits(ctx.primary_hits(), o.primary_hits()).all(), m
+        org, d = stress_rays(new, which, 20000, 11)
+        assert same_hits(ctx.trace(org, d), o.trace(org, d)).all(), m
+        ctx.render()
+        ro = o.render()
+        assert ctx.stats()["rays"] == ro["rays"]
+        assert (bits(ctx.framebuffer_f32()[..., :3]) == bits(ro["mean"][..., :3])).all(), m
+        assert (ctx.framebuffer_rgba8() == ro["rgba"]).all()
+    refit_frame = ctx.framebuffer_f32().copy()
+    ctx.build_accel()                                        # fresh topology for the moved scene: same frame
+    ctx.render()
+    assert (bits(ctx.framebuffer_f32()) == bits(refit_frame)).all()
+    with pytest.raises(pt.B200ptError, match="vertices"):
+        ctx.update_mesh(which, new[which]["verts"][:-1])
+    with pytest.raises(pt.B200ptError, match="no such mesh"):
+        ctx.update_mesh(99, new[which]["verts"])
+    ctx.close()
+
+
+@pytest.mark.gpu
+def test_refit_of_the_dragon_is_cheaper_than_a_build_and_keeps_hits_exact():
+    sc = pt.Scene(scene="dragon", width=320, height=180, spp=1, depth=8, env="color", env_intensity=0.0)
+    ents = sc.entities()
+    which = max(range(len(ents)), key=lambda i: len(ents[i]["idx"]))
+    ctx = pt.Context(flags=pt.FLAG_COUNTERS)
+    ctx.bind(sc)
+    build_ms = ctx.stats()["build_ms"]
+    new = moved(ents, which, scale=1.02, shift=(0.01, 0.03, 0.0), wobble=0.002)
+    ctx.update_mesh(which, new[which]["verts"])
+    ctx.refit_accel()
+    refit_ms = ctx.stats()["refit_ms"]
+    assert 0.0 < refit_ms < build_ms
+    fresh = pt.Context()
+    for e in new:
+        fresh.add_mesh(e["verts"], e["normals"], e["idx"], e["material"], e["uvs"], e["tex"])
+    fresh.build_accel()
+    fresh.set_materials(sc.materials())
+    fresh.set_camera(*sc.camera)
+    fresh.set_render(sc.width, sc.height, sc.spp, sc.depth)
+    org, d = stress_rays(new, which, 200000, 3)
+    a, b = ctx.trace(org, d), fresh.trace(org, d)
+    assert same_hits(a, b).all() and (a["mesh"] >= 0).mean() > 0.5
+    ctx.close()
+    fresh.close()
