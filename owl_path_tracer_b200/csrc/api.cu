@@ -23,6 +23,13 @@ static int fail(int code, const std::string& msg) {
         if (e_ != cudaSuccess) return fail(B200PT_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+#ifndef PT_FUSE_MIN
+#define PT_FUSE_MIN 0
+#endif
+#ifndef PT_FUSE_SEGS
+#define PT_FUSE_SEGS 8
+#endif
+
 struct b200pt_ctx {
     b200pt_config cfg{};
     cudaStream_t stream = nullptr;
@@ -95,6 +102,8 @@ struct b200pt_ctx {
 };
 
 constexpr int kCountsStride = 3 * kBatch + 1;  // per part in h_counts
+constexpr int kFuseMinDefault = PT_FUSE_MIN;   // queue length below which the fused tail kernel takes over (0: never)
+constexpr int kFuseSegsDefault = PT_FUSE_SEGS; // segments per lane and launch of the fused tail kernel
 
 static void free_lanes(b200pt_ctx* c) {
     for (int p = 0; p < kMaxParts; ++p) {
@@ -711,6 +720,14 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
     FILE* iter_log = nullptr;
     if (timing)
         if (const char* e = getenv("B200PT_ITER_LOG")) iter_log = fopen(e, "w");
+    // Tail of the frame (wavefront.cu k_fused): once a part's queue is shorter than fuse_min its lanes run whole
+    // segments, `fuse_segs` per launch, in one kernel.  The first iteration after the switch is a normal one that
+    // resumes the parked walks and parks none.  Off with counters (the fused walk does not count) and in NEE mode.
+    int fuse_min = kFuseMinDefault, fuse_segs = kFuseSegsDefault;
+    if (const char* e = getenv("B200PT_FUSE_MIN")) fuse_min = atoi(e);
+    if (const char* e = getenv("B200PT_FUSE_SEGS")) fuse_segs = std::max(1, atoi(e));
+    if (nee || count) fuse_min = 0;
+    bool fused[kMaxParts] = {};
     auto any_active = [&] {
         for (int p = 0; p < parts; ++p)
             if (active[p]) return true;
@@ -724,7 +741,20 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
                 const LaneArrays& L = c->part[p];
                 cudaStream_t ps = c->part_stream[p];
                 if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k], ps));
-                launch_extend(sv, L, k, active[p], count, ps);
+                if (fused[p]) {  // extend + shade of up to fuse_segs segments per lane; its time is booked as extend time
+                    launch_fused(sv, L, k, active[p], fuse_segs, ps);
+                    if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 1], ps));
+                    S.kernel_launches += 1;
+                    continue;
+                }
+                if (k == 0 && active[p] < (uint32_t)fuse_min) {
+                    LaneArrays T = L;
+                    T.no_park = 1;
+                    launch_extend(sv, T, k, active[p], count, ps);
+                    fused[p] = true;
+                } else {
+                    launch_extend(sv, L, k, active[p], count, ps);
+                }
                 if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 1], ps));
                 launch_shade(sv, L, k, active[p], ps);
                 if (nee) {

@@ -56,6 +56,7 @@ struct LaneArrays {
     uint32_t* cursor = nullptr;   // kBatch ray-fetch cursors of the persistent extend kernel
     unsigned long long* walk_counters = nullptr;  // nodes, tris (FLAG_COUNTERS)
     uint32_t capacity = 0;
+    uint32_t no_park = 0;         // 1: k_extend resumes parked walks but parks none (last wavefront iteration before k_fused)
 };
 
 constexpr int kSuspWords = 3 + kSuspStack / 2;  // 176 bytes per lane: hit, groups, top + kSuspStack stack entries of 8 bytes
@@ -66,6 +67,7 @@ constexpr int kBatch = 32;  // wavefront iterations between host checks (even: t
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, int part, int parts, uint32_t n_part, cudaStream_t st);
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st);
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
+void launch_fused(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, int segments, cudaStream_t st);
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, int transfer, uint32_t* rgba, f4* mean, cudaStream_t st);
 unsigned pass_stats_blocks(uint32_t n_lanes);

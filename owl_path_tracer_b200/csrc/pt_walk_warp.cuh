@@ -71,12 +71,15 @@ __device__ __forceinline__ f4 ldg4f(const f4* p) {
 //       void suspend(i, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack)        (SUSPEND only)
 template <bool COUNT, bool ANY, bool SUSPEND, class Src, class Sink>
 __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const TriPair* __restrict__ tris, uint32_t n,
-                                          uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic) {
+                                          uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic,
+                                          const bool allow_park = true) {
     const unsigned FULL = 0xffffffffu;
     const int lid = threadIdx.x & 31;
 
     bool has_ray = false, exhausted = false;
-    const int park = (SUSPEND && n >= (uint32_t)PT_SUSPEND_MIN) ? PT_SUSPEND_LANES : 0;  // 0: only an empty warp leaves
+    // 0: only an empty warp leaves.  allow_park = false: this launch resumes parked walks but parks none (the
+    // iteration before the fused tail kernel takes over, wavefront.cu k_fused)
+    const int park = (SUSPEND && allow_park && n >= (uint32_t)PT_SUSPEND_MIN) ? PT_SUSPEND_LANES : 0;
     int slice = PT_SUSPEND_STEPS;  // time slice left once the queue is drained (warp-uniform)
     uint32_t ray_index = 0;
     f3 o{0, 0, 0}, d{0, 0, 1};
