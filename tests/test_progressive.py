@@ -100,15 +100,25 @@ def test_progressive_loop_early_stop_callback_and_restart():
     full = ctx.framebuffer_f32().copy()
     ctx.render()
     assert (bits(full) == bits(ctx.framebuffer_f32())).all()
-    # the estimate falls as 1/n; a target between two passes stops the loop early
+    # In the cornell box (tiny emitter, no light sampling) the figure RISES over the first passes: most pixels have
+    # not seen the light yet and report no variance at all; it stays near the measured relMSE of such frames (0.7 at
+    # 64 spp).  A well-lit scene shows the 1/n law; a target stops the loop at the first pass at or below it.
     v = []
     ctx.render_progressive(8, 0.0, lambda info, *_: v.append(info["rel_variance"]) and False)
-    assert all(b < a for a, b in zip(v, v[1:])) and v[0] / v[-1] > 4.0
+    assert len(v) == 8 and all(x > 0 for x in v)
+    cube = pt.Scene(scene="cube", width=64, height=64, spp=64, depth=8, env="auto", env_intensity=1.0)
+    cc = pt.Context()
+    cc.bind(cube)
+    v = []
+    cc.render_progressive(8, 0.0, lambda info, *_: v.append(info["rel_variance"]) and False)
+    assert all(b < a for a, b in zip(v, v[1:])) and 6.0 < v[0] / v[-1] < 10.0       # 8 -> 64 samples: ~ 1/8
     target = 0.5 * (v[1] + v[2])
-    early = ctx.render_progressive(8, target)
-    assert early["stopped_early"] == 1 and early["samples_done"] == 24 and early["rel_variance"] <= target
-    o = Oracle(det=True).load_scene(pt.Scene(width=64, height=64, spp=24, **CORNELL))
-    assert (bits(ctx.framebuffer_f32()[..., :3]) == bits(o.render()["mean"][..., :3])).all()
+    early = cc.render_progressive(8, target)
+    assert early["samples_done"] == 24 and early["rel_variance"] == v[2]
+    assert early["stopped_early"] == 1 and early["complete"] == 0
+    o = Oracle(det=True).load_scene(pt.Scene(scene="cube", width=64, height=64, spp=24, depth=8, env="auto", env_intensity=1.0))
+    assert (bits(cc.framebuffer_f32()[..., :3]) == bits(o.render()["mean"][..., :3])).all()
+    cc.close()
     # callback stop
     n = []
     stopped = ctx.render_progressive(8, 0.0, lambda info, *_: n.append(1) or len(n) == 2)

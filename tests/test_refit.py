@@ -65,6 +65,20 @@ def stress_rays(entities, which, n, seed):
     return np.ascontiguousarray(org, np.float32), np.ascontiguousarray(d, np.float32)
 
 
+def accepted_outside_its_triangle(hit, org, d, entities):
+    """float32 Moller-Trumbore accepts, very rarely, a 'hit' whose point lies far outside the triangle: the ray is
+    nearly parallel to the triangle's plane, det ~ 0, and u, v, t are cancellation noise that happens to fall in
+    range.  Such a point is not inside the triangle's bounding box, so whether a walk ever tests that triangle
+    depends on the order in which boxes are visited — the one case where two valid trees may disagree."""
+    if hit["mesh"] < 0:
+        return False
+    e = entities[int(hit["mesh"])]
+    tri = e["verts"][e["idx"][int(hit["prim"])]].astype(np.float64)
+    p = org.astype(np.float64) + float(hit["t"]) * d.astype(np.float64)
+    tol = 1e-4 * max(1.0, float(np.abs(p).max()))
+    return bool((p < tri.min(axis=0) - tol).any() or (p > tri.max(axis=0) + tol).any())
+
+
 MOTIONS = [dict(scale=1.0, shift=(0.0, 0.0, 0.0), wobble=0.0),          # nothing moved: refit must be harmless
            dict(scale=1.0, shift=(0.05, 0.02, -0.03), wobble=0.01),     # a small step of an animation
            dict(scale=1.6, shift=(-0.4, 0.3, 0.2), wobble=0.05)]        # large: boxes grow a lot, hits must still be exact
@@ -143,6 +157,9 @@ def test_refit_of_the_dragon_is_cheaper_than_a_build_and_keeps_hits_exact():
     fresh.set_render(sc.width, sc.height, sc.spp, sc.depth)
     org, d = stress_rays(new, which, 200000, 3)
     a, b = ctx.trace(org, d), fresh.trace(org, d)
-    assert same_hits(a, b).all() and (a["mesh"] >= 0).mean() > 0.5
+    differ = np.nonzero(~same_hits(a, b))[0]
+    assert (a["mesh"] >= 0).mean() > 0.5 and len(differ) <= 20           # 200,000 rays aimed at the surface
+    for i in differ:   # two valid trees may only disagree about a numerically bogus acceptance (see the helper)
+        assert accepted_outside_its_triangle(a[i], org[i], d[i], new) or accepted_outside_its_triangle(b[i], org[i], d[i], new), i
     ctx.close()
     fresh.close()
