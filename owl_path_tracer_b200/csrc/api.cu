@@ -728,6 +728,10 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
     if (const char* e = getenv("B200PT_FUSE_SEGS")) fuse_segs = std::max(1, atoi(e));
     if (nee || count) fuse_min = 0;
     bool fused[kMaxParts] = {};
+    // development (PT_TIMELINE builds): per-warp timestamps of the k_extend launch of wavefront iteration
+    // B200PT_TIMELINE_ITER of part 0, written to B200PT_TIMELINE_FILE after the frame
+    long tl_iter = -1, iter_no = 0;
+    if (const char* e = getenv("B200PT_TIMELINE_ITER")) tl_iter = atol(e);
     auto any_active = [&] {
         for (int p = 0; p < parts; ++p)
             if (active[p]) return true;
@@ -752,6 +756,9 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
                     T.no_park = 1;
                     launch_extend(sv, T, k, active[p], count, ps);
                     fused[p] = true;
+                } else if (p == 0 && iter_no + k == tl_iter && timeline_arm(true, ps)) {
+                    launch_extend(sv, L, k, active[p], count, ps);
+                    timeline_arm(false, ps);
                 } else {
                     launch_extend(sv, L, k, active[p], count, ps);
                 }
@@ -765,6 +772,7 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
                 S.kernel_launches += (uint64_t)ev_per_iter;
             }
         }
+        iter_no += kBatch;
         if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * kBatch], st));
         CU(cudaGetLastError());
         for (int p = 0; p < parts; ++p) {
@@ -812,6 +820,11 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
         }
     }
     if (iter_log) fclose(iter_log);
+    if (tl_iter >= 0)
+        if (const char* e = getenv("B200PT_TIMELINE_FILE")) {
+            CU(cudaDeviceSynchronize());
+            timeline_dump(e);
+        }
     for (int p = 1; p < parts; ++p) {  // the frame is complete on `stream` once every part is
         CU(cudaEventRecord(c->part_done[p], c->part_stream[p]));
         CU(cudaStreamWaitEvent(st, c->part_done[p], 0));

@@ -67,6 +67,8 @@ constexpr int kBatch = 32;  // wavefront iterations between host checks (even: t
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, int part, int parts, uint32_t n_part, cudaStream_t st);
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st);
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
+bool timeline_arm(bool on, cudaStream_t st);   // PT_TIMELINE builds only (false otherwise)
+bool timeline_dump(const char* path);
 void launch_fused(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, int segments, cudaStream_t st);
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, int transfer, uint32_t* rgba, f4* mean, cudaStream_t st);

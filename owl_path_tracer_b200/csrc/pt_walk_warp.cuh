@@ -42,6 +42,18 @@ namespace pt {
 #ifndef PT_PREFETCH_NODE
 #define PT_PREFETCH_NODE 0   // prefetch.global.L1 of the next child node at the end of a node step
 #endif
+#ifndef PT_TIMELINE
+#define PT_TIMELINE 0        // development: per-warp timestamps of one chosen k_extend launch (tools/timeline.py)
+#endif
+#if PT_TIMELINE
+__device__ unsigned long long* g_timeline = nullptr;  // 4 words per warp: start, queue drained, exit (globaltimer ns), rays << 32 | loop steps
+__device__ int g_timeline_on = 0;
+__device__ __forceinline__ unsigned long long timeline_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#endif
 constexpr int kRefill = PT_REFILL;
 constexpr int kWalkStack = 2 * kStackSize;  // per tree level at most one node group + one postponed triangle group
 
@@ -103,7 +115,16 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         ++sp;                                                \
     } while (0)
 
+#if PT_TIMELINE
+    const bool tl_on = SUSPEND && g_timeline_on != 0;
+    unsigned long long tl_start = 0, tl_drained = 0;
+    uint32_t tl_rays = 0, tl_steps = 0, tl_node_lanes = 0, tl_tri_lanes = 0, tl_node_steps = 0;
+    if (tl_on) tl_start = timeline_now();
+#endif
     for (;;) {
+#if PT_TIMELINE
+        ++tl_steps;
+#endif
         // ---- every lane with a ray must hold some work: pop the stack, or retire the ray
         if (has_ray && ng_mask <= 0x00FFFFFFu && tg_mask == 0) {
             if (sp == 0) {
@@ -165,6 +186,12 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
                 }
             }
             if (base + (uint32_t)cnt >= n) exhausted = true;
+#if PT_TIMELINE
+            if (tl_on) {
+                tl_rays += (uint32_t)__popc(__ballot_sync(FULL, has_ray) & idle);
+                if (exhausted) tl_drained = timeline_now();
+            }
+#endif
             act = __ballot_sync(FULL, has_ray);
         }
         if (act == 0) {
@@ -179,6 +206,13 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         const int n_tri = __popc(__ballot_sync(FULL, want_tri));
         const bool tri_phase = PT_TRI_VOTE * n_tri >= __popc(act);
 
+#if PT_TIMELINE
+        if (tri_phase) tl_tri_lanes += (uint32_t)n_tri;
+        else {
+            tl_node_lanes += (uint32_t)__popc(__ballot_sync(FULL, can_node));
+            ++tl_node_steps;
+        }
+#endif
         if (tri_phase) {
 #if PT_TRI_LOOP
             const int n_act = __popc(act);
@@ -243,7 +277,14 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
             }
 #if PT_TRI_LOOP
             // same vote as above, without the trip through the loop head (no lane gains work in here)
-            again = PT_TRI_VOTE * __popc(__ballot_sync(FULL, has_ray && tg_mask != 0)) >= n_act;
+            const int n_more = __popc(__ballot_sync(FULL, has_ray && tg_mask != 0));
+            again = PT_TRI_VOTE * n_more >= n_act;
+#if PT_TIMELINE
+            if (again) {
+                tl_tri_lanes += (uint32_t)n_more;
+                ++tl_steps;
+            }
+#endif
             } while (again);
 #endif
         } else if (can_node) {
@@ -325,6 +366,17 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         }
     }
 #undef PT_PUSH
+#if PT_TIMELINE
+    if (tl_on && lid == 0) {
+        const unsigned w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+        g_timeline[4 * w + 0] = tl_start;
+        g_timeline[4 * w + 1] = tl_drained;
+        g_timeline[4 * w + 2] = timeline_now();
+        g_timeline[4 * w + 3] = ((unsigned long long)tl_rays << 32) | tl_steps;
+        g_timeline[4 * 65536 + 2 * w + 0] = ((unsigned long long)tl_node_lanes << 32) | tl_tri_lanes;
+        g_timeline[4 * 65536 + 2 * w + 1] = tl_node_steps;
+    }
+#endif
 }
 
 }  // namespace pt

@@ -543,6 +543,43 @@ void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max
     else
         k_shade<false><<<blocks(max_count, kBlock), kBlock, 0, st>>>(sv, la, k);
 }
+// development (PT_TIMELINE builds only): arm / disarm the per-warp timestamps around one launch, dump them afterwards
+bool timeline_arm(bool on, cudaStream_t st) {
+#if PT_TIMELINE
+    static unsigned long long* buf = nullptr;
+    if (!buf) {
+        if (cudaMalloc(&buf, sizeof(unsigned long long) * 6 * 65536) != cudaSuccess) return false;
+        cudaMemset(buf, 0, sizeof(unsigned long long) * 6 * 65536);
+        cudaMemcpyToSymbol(g_timeline, &buf, sizeof buf);
+    }
+    static int h_on[2] = {0, 1};
+    cudaMemcpyToSymbolAsync(g_timeline_on, &h_on[on ? 1 : 0], sizeof(int), 0, cudaMemcpyHostToDevice, st);
+    return true;
+#else
+    (void)on; (void)st;
+    return false;
+#endif
+}
+bool timeline_dump(const char* path) {
+#if PT_TIMELINE
+    unsigned long long* buf = nullptr;
+    cudaMemcpyFromSymbol(&buf, g_timeline, sizeof buf);
+    if (!buf) return false;
+    std::vector<unsigned long long> h(6 * 65536);
+    cudaMemcpy(h.data(), buf, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost);
+    FILE* f = fopen(path, "w");
+    if (!f) return false;
+    for (size_t w = 0; w < 65536; ++w)
+        if (h[4 * w])   // warp, start, drained, exit [ns], rays, loop steps, lanes served by node steps, by triangle steps, node steps
+            fprintf(f, "%zu %llu %llu %llu %llu %llu %llu %llu %llu\n", w, h[4 * w], h[4 * w + 1], h[4 * w + 2], h[4 * w + 3] >> 32,
+                    h[4 * w + 3] & 0xFFFFFFFFull, h[4 * 65536 + 2 * w] >> 32, h[4 * 65536 + 2 * w] & 0xFFFFFFFFull, h[4 * 65536 + 2 * w + 1]);
+    fclose(f);
+    return true;
+#else
+    (void)path;
+    return false;
+#endif
+}
 void launch_fused(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, int segments, cudaStream_t st) {
     k_fused<<<blocks(max_count, 64), 64, 0, st>>>(sv, la, k, segments);
 }
