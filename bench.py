@@ -105,7 +105,17 @@ def run_reference(args):
                 e2e=dict(value=rate, unit="Mrays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 note="reference's own OWL/OptiX build is unavailable on this box (no OptiX SDK, no RT cores); this is the "
                      "scalar CPU restatement of its integrator (oracle/oracle.cpp)")
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+# stdout carries exactly ONE line, the JSON: everything native libraries print there (NCCL's version banner on
+# some boxes) is sent to stderr by pointing fd 1 at fd 2 for the whole run; emit() writes to the saved fd.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
 
 
 def main():
@@ -301,7 +311,7 @@ def main():
             clocks=clocks, roofline=roof, cpu_baseline=cpu, throughput_mode=tm,
             parity="tests/test_gpu_parity.py: bit-exact vs oracle (hits, float frame); relMSE <= 1e-3 vs glibc oracle",
             notes=sc.notes)
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
