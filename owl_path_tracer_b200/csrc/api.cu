@@ -92,6 +92,7 @@ struct b200pt_ctx {
     size_t fb_pixels = 0;
     bool rendered = false, resolved = false;
     // progressive passes (b200pt_render_pass): samples of every pixel already in `sum`; 0 = no frame in progress
+    int l2_persist_mode = 0;    // B200PT_L2_PERSIST experiment (render_local)
     int pass_done = 0;
     int resolve_samples = 0;    // divisor of the next resolve (max_samples for a complete frame)
     int transfer = 0;           // b200pt_set_output
@@ -674,6 +675,33 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
     }
     const int parts = choose_parts(c, sv);
     if (int r = ensure_lanes(c, sv, parts)) return r;
+    {
+        // Experiment (B200PT_L2_PERSIST = 1 tris | 2 nodes | 0 off): keep the triangle blocks (or the nodes) in the
+        // persisting part of L2 so that the lane state streaming through L2 every iteration cannot evict them.
+        const char* e = getenv("B200PT_L2_PERSIST");
+        const int mode = e ? atoi(e) : 0;
+        if (mode != c->l2_persist_mode) {
+            cudaDeviceProp prop;
+            CU(cudaGetDeviceProperties(&prop, c->cfg.device_ordinal));
+            cudaStreamAttrValue attr{};
+            if (mode > 0) {
+                const void* base = mode == 2 ? (const void*)c->bvh.nodes : (const void*)c->bvh.tris;
+                size_t bytes = mode == 2 ? sizeof(Node8) * (size_t)c->bvh.n_nodes : sizeof(TriPair) * (size_t)c->bvh.n_tris;
+                bytes = std::min(bytes, (size_t)prop.accessPolicyMaxWindowSize);
+                CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min(bytes, (size_t)prop.persistingL2CacheMaxSize)));
+                attr.accessPolicyWindow.base_ptr = const_cast<void*>(base);
+                attr.accessPolicyWindow.num_bytes = bytes;
+                attr.accessPolicyWindow.hitRatio = 1.0f;
+                attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            } else {
+                attr.accessPolicyWindow.num_bytes = 0;
+                CU(cudaCtxResetPersistingL2Cache());
+            }
+            for (int p = 0; p < kMaxParts; ++p) CU(cudaStreamSetAttribute(c->part_stream[p], cudaStreamAttributeAccessPolicyWindow, &attr));
+            c->l2_persist_mode = mode;
+        }
+    }
     const bool count = (c->cfg.flags & B200PT_FLAG_COUNTERS) != 0;
     const bool timing = (c->cfg.flags & B200PT_FLAG_TIMING) != 0 && parts == 1;
     const bool nee = sv.nee != 0;

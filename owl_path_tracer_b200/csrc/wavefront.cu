@@ -36,6 +36,20 @@ __device__ __forceinline__ f4 ld4(const f4* p) {
     const float4 v = *reinterpret_cast<const float4*>(p);
     return f4{v.x, v.y, v.z, v.w};
 }
+// last read of a state entry (k_shade consumes set k, nobody reads it again): PT_STATE_CS >= 1 loads it with the
+// streaming hint (ld.global.cs, evict-first) so the dead lines leave L2 before the BVH does; PT_STATE_CS == 2 also
+// writes the hit records with st.global.cs
+#ifndef PT_STATE_CS
+#define PT_STATE_CS 0
+#endif
+__device__ __forceinline__ f4 ld4_last(const f4* p) {
+#if PT_STATE_CS
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(p));
+#else
+    const float4 v = *reinterpret_cast<const float4*>(p);
+#endif
+    return f4{v.x, v.y, v.z, v.w};
+}
 __device__ __forceinline__ void st4(f4* p, f4 v) { *reinterpret_cast<float4*>(p) = make_float4(v.x, v.y, v.z, v.w); }
 
 // Part `part` of `parts` owns the rows r = part (mod parts) of the rank's lanes; its state arrays are indexed
@@ -154,7 +168,7 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
     // follows the lane id
     const uint32_t n = la.counts[k];
     const uint32_t lane = in_q[i];
-    const f4 d = ld4(in_d + i), t = ld4(in_t + i), hv = ld4(la.hit + i);
+    const f4 d = ld4_last(in_d + i), t = ld4_last(in_t + i), hv = ld4_last(la.hit + i);
     bool keep = false, shadow = false;
     LaneState L;
     f3 last_term = mk3(0.0f);
@@ -163,7 +177,7 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
     if (parked) {
         // the walk of this ray was interrupted (pt_walk_warp.cuh SUSPEND): nothing to shade yet, the lane moves
         // to the next queue unchanged and the next k_extend picks the walk up where it stopped
-        const f4 o = ld4(in_o + i);
+        const f4 o = ld4_last(in_o + i);
         L.o = f3{o.x, o.y, o.z};
         L.prev_pdf = o.w;
         L.d = f3{d.x, d.y, d.z};
