@@ -12,6 +12,13 @@
 
 #include "device_ctx.h"
 #include "pt_walk_warp.cuh"
+#ifndef PT_BATCH_TRI
+#define PT_BATCH_TRI 0         // 1: the walker kernels use warp_walk_batch (deferred, batched triangle tests)
+#endif
+#if PT_BATCH_TRI
+#include "pt_walk_batch.cuh"
+#define warp_walk warp_walk_batch
+#endif
 
 namespace pt {
 
