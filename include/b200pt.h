@@ -208,7 +208,7 @@ int b200pt_resolve(b200pt_ctx* ctx);
  * bit, and after the last pass it is the frame b200pt_render produces (tests/test_progressive.py).  The frame
  * in progress is dropped by b200pt_render_restart and by any call that changes the scene, camera, environment,
  * materials, size or depth; b200pt_set_render with only a new max_samples extends or shortens it.
- * world_size 1 and one stream per pixel only. */
+ * One stream per pixel only; several ranks: see b200pt_pass_stats below. */
 typedef struct b200pt_pass_info {
     int32_t samples_done;     /* samples per pixel in the frame now                                       */
     int32_t samples_in_pass;  /* samples this pass added                                                  */
@@ -223,6 +223,12 @@ typedef struct b200pt_pass_info {
 } b200pt_pass_info;
 int b200pt_render_pass(b200pt_ctx* ctx, int32_t n_samples, b200pt_pass_info* info /* may be NULL */);
 int b200pt_render_restart(b200pt_ctx* ctx);
+/* Several ranks (SPP sharding, max_samples a multiple of world_size): n_samples counts samples of THIS rank's stream,
+ * the pass adds n_samples * world_size samples to the frame.  b200pt_render_pass then leaves a COPY of the rank's
+ * sums behind b200pt_accum_buffer (the rank's own sums must survive the in-place reduce); the caller reduces the
+ * copies into rank 0's, calls b200pt_resolve there, and b200pt_pass_stats for the figure of the combined frame
+ * (owl_path_tracer_b200/distributed.py render_pass).  info->rel_variance of b200pt_render_pass itself is 0 then. */
+int b200pt_pass_stats(b200pt_ctx* ctx, b200pt_pass_info* info);
 
 /* Called after every pass with the resolved frame (RGBA8 top row first, float RGBA mean; both borrowed until the
  * next pass).  Return non-zero to stop. */

@@ -136,6 +136,7 @@ def lib() -> C.CDLL:
     L.b200pt_refit_accel.argtypes = [P]
     L.b200pt_render_pass.argtypes = [P, C.c_int32, C.POINTER(PassInfo)]
     L.b200pt_render_restart.argtypes = [P]
+    L.b200pt_pass_stats.argtypes = [P, C.POINTER(PassInfo)]
     L.b200pt_render_progressive.argtypes = [P, C.c_int32, C.c_double, PASS_FN, C.c_void_p, C.POINTER(PassInfo)]
     L.b200pt_set_output.argtypes = [P, C.c_int32]
     L.b200pt_accum_buffer.argtypes = [P, C.POINTER(P), C.POINTER(C.c_size_t)]

@@ -102,6 +102,12 @@ class Context:
         self._ck(self._L.b200pt_render_pass(self._h, int(n_samples), C.byref(info)), "render_pass")
         return info.as_dict()
 
+    def pass_stats(self):
+        """Figure of the frame behind accum_buffer (after the reduce on rank 0 of a multi-rank pass)."""
+        info = PassInfo()
+        self._ck(self._L.b200pt_pass_stats(self._h, C.byref(info)), "pass_stats")
+        return info.as_dict()
+
     def render_restart(self):
         self._ck(self._L.b200pt_render_restart(self._h), "render_restart")
 

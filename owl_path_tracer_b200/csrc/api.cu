@@ -934,7 +934,7 @@ extern "C" int b200pt_render_restart(b200pt_ctx* c) {
 static int pass_statistics(b200pt_ctx* c, int n_samples, double* rel_variance) {
     const uint32_t n = (uint32_t)(c->width * c->height);
     const unsigned nb = pass_stats_blocks(n);
-    launch_pass_stats(c->la.sum, n, n_samples, c->d_pass_partial, c->stream);
+    launch_pass_stats(c->use_frame ? c->d_frame : c->la.sum, n, n_samples, c->d_pass_partial, c->stream);
     c->stats.kernel_launches++;
     c->h_pass_partial.resize(nb);
     CU(cudaMemcpyAsync(c->h_pass_partial.data(), c->d_pass_partial, sizeof(double) * nb, cudaMemcpyDeviceToHost, c->stream));
@@ -947,30 +947,55 @@ static int pass_statistics(b200pt_ctx* c, int n_samples, double* rel_variance) {
 
 extern "C" int b200pt_render_pass(b200pt_ctx* c, int32_t n_samples, b200pt_pass_info* info) {
     if (int r = check_ready(c, "render_pass")) return r;
-    if (c->cfg.world_size != 1 || c->cfg.streams_per_pixel > 1)
-        return fail(B200PT_ERR_INVALID, "render_pass: progressive passes need world_size 1 and one stream per pixel");
+    const int world = std::max(c->cfg.world_size, 1);
+    if (c->cfg.streams_per_pixel > 1 || (world > 1 && c->cfg.shard_mode != B200PT_SHARD_SPP))
+        return fail(B200PT_ERR_INVALID, "render_pass: progressive passes need one stream per pixel and, on several ranks, SPP sharding");
+    if (world > 1 && c->max_samples % world != 0)
+        return fail(B200PT_ERR_INVALID, "render_pass: max_samples must be a multiple of world_size");
     if (n_samples <= 0) return fail(B200PT_ERR_INVALID, "render_pass: n_samples must be positive");
-    if (c->pass_done >= c->max_samples)
+    const int budget = c->max_samples / world;   // samples of this rank's stream
+    if (c->pass_done >= budget)
         return fail(B200PT_ERR_INVALID, "render_pass: all max_samples samples are rendered (b200pt_render_restart starts over)");
-    const int n = std::min(n_samples, c->max_samples - c->pass_done);
+    const int n = std::min(n_samples, budget - c->pass_done);
     if (int r = render_local(c, c->pass_done, n)) return r;
-    if (int r = b200pt_resolve(c)) return r;
+    if (world > 1) {
+        // the rank's sums must survive the in-place reduce: the collective runs on a copy
+        if (!c->d_frame) CU(cudaMalloc(&c->d_frame, sizeof(f4) * c->fb_pixels));
+        CU(cudaMemcpyAsync(c->d_frame, c->la.sum, sizeof(f4) * c->fb_pixels, cudaMemcpyDeviceToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        c->use_frame = true;
+        c->resolve_samples = c->pass_done * world;
+    } else if (int r = b200pt_resolve(c)) {
+        return r;
+    }
     if (info) {
         memset(info, 0, sizeof *info);
-        info->samples_done = c->pass_done;
-        info->samples_in_pass = n;
-        info->complete = c->pass_done >= c->max_samples ? 1 : 0;
+        info->samples_done = c->pass_done * world;
+        info->samples_in_pass = n * world;
+        info->complete = c->pass_done >= budget ? 1 : 0;
         info->render_ms = c->stats.render_ms;
         info->rays = c->stats.rays;
-        if (int r = pass_statistics(c, c->pass_done, &info->rel_variance)) return r;
+        if (world == 1)
+            if (int r = pass_statistics(c, c->pass_done, &info->rel_variance)) return r;
     }
     return B200PT_OK;
+}
+
+extern "C" int b200pt_pass_stats(b200pt_ctx* c, b200pt_pass_info* info) {
+    if (int r = check_ready(c, "pass_stats")) return r;
+    if (!info || !c->rendered) return fail(B200PT_ERR_INVALID, "pass_stats: nothing rendered / null output");
+    memset(info, 0, sizeof *info);
+    info->samples_done = c->resolve_samples;
+    info->complete = c->resolve_samples >= c->max_samples ? 1 : 0;
+    return pass_statistics(c, c->resolve_samples, &info->rel_variance);
 }
 
 extern "C" int b200pt_render_progressive(b200pt_ctx* c, int32_t pass_samples, double target_rel_variance, b200pt_pass_fn on_pass,
                                          void* user, b200pt_pass_info* last) {
     if (int r = check_ready(c, "render_progressive")) return r;
     if (pass_samples <= 0) return fail(B200PT_ERR_INVALID, "render_progressive: pass_samples must be positive");
+    if (c->cfg.world_size > 1)
+        return fail(B200PT_ERR_INVALID, "render_progressive: one rank only (several ranks: b200pt_render_pass + reduce + b200pt_pass_stats per pass)");
     if (int r = b200pt_render_restart(c)) return r;
     b200pt_pass_info info{};
     for (;;) {

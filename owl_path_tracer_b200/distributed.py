@@ -42,6 +42,22 @@ def render_frame(ctx, group=None):
             ctx.resolve()
 
 
+def render_pass(ctx, n_samples, group=None):
+    """One progressive pass on every rank (n_samples of each rank's stream) -> reduce of the copies -> rank 0 resolves
+    the frame over all samples so far and returns the pass info with the combined frame's variance figure."""
+    info = ctx.render_pass(n_samples)
+    if ctx.world_size > 1:
+        import torch
+        t = accum_tensor(ctx)
+        torch.cuda.current_stream().synchronize()
+        reduce_sum_to_rank0(t, group)
+        torch.cuda.current_stream().synchronize()
+        if ctx.rank == 0:
+            ctx.resolve()
+            info["rel_variance"] = ctx.pass_stats()["rel_variance"]
+    return info
+
+
 def shard_samples(total_spp: int, rank: int, world: int) -> int:
     """Samples per pixel rank `rank` renders in SPP mode (same rule as api.cu rank_samples)."""
     return total_spp // world + (1 if rank < total_spp % world else 0)

@@ -152,8 +152,47 @@ def test_gamma_output_and_errors():
     with pytest.raises(pt.B200ptError, match="positive"):
         ctx.render_pass(0)
     ctx.close()
-    two = pt.Context(rank=0, world_size=2)
+    two = pt.Context(rank=0, world_size=2, shard_mode=pt.SHARD_ROWS)
     two.bind(sc)
-    with pytest.raises(pt.B200ptError, match="world_size 1"):
+    with pytest.raises(pt.B200ptError, match="SPP sharding"):
         two.render_pass(1)
+    with pytest.raises(pt.B200ptError, match="one rank only"):
+        two.render_progressive(1)
     two.close()
+    odd = pt.Context(rank=0, world_size=3)
+    odd.bind(sc)
+    with pytest.raises(pt.B200ptError, match="multiple of world_size"):
+        odd.render_pass(1)
+    odd.close()
+
+
+@pytest.mark.gpu
+def test_passes_on_two_ranks_sum_to_the_oracles_frame():
+    """Ranks emulated one after the other on the test GPU: after every pass the reduce of the ranks' copies (here: a
+    torch add into rank 0's) resolved on rank 0 is the oracle's 2-rank SPP frame at that sample count, bit for bit."""
+    from owl_path_tracer_b200.distributed import accum_tensor
+    W, H, world = 64, 48, 2
+    sc = pt.Scene(width=W, height=H, spp=8, **CORNELL)
+    ranks = []
+    for r in range(world):
+        c = pt.Context(rank=r, world_size=world, shard_mode=pt.SHARD_SPP)
+        c.bind(sc)
+        ranks.append(c)
+    done = 0
+    for n in (1, 3):
+        infos = [c.render_pass(n) for c in ranks]
+        done += n
+        assert all(i["samples_done"] == done * world for i in infos)
+        t0 = accum_tensor(ranks[0])
+        t0 += accum_tensor(ranks[1])            # what dist.reduce(dst=0) leaves on rank 0
+        ranks[0].resolve()
+        o = Oracle(det=True).load_scene(pt.Scene(width=W, height=H, spp=done * world, **CORNELL))
+        total = o.render(rank=0, world=world, shard_mode=pt.SHARD_SPP)["sum"] + o.render(rank=1, world=world, shard_mode=pt.SHARD_SPP)["sum"]
+        want = (total[..., :3] * (np.float32(1.0) / np.float32(done * world)))[::-1]     # the frame is stored top row first
+        assert (bits(ranks[0].framebuffer_f32()[..., :3]) == bits(np.ascontiguousarray(want))).all(), f"after {done} samples per rank"
+        st = ranks[0].pass_stats()
+        assert st["samples_done"] == done * world
+        assert st["rel_variance"] == pytest.approx(rel_variance(total, done * world), rel=1e-9)
+    assert infos[0]["complete"] == 1
+    for c in ranks:
+        c.close()
