@@ -76,6 +76,7 @@ struct b200pt_ctx {
     std::vector<int32_t> h_mesh_vbase, h_mesh_nv;  // vertex range of every mesh in the flattened arrays
     bool geometry_moved = false;                   // vertices changed since the tree was built / refitted
     float* d_node_box = nullptr;                   // refit scratch, 6 floats per wide node
+    TriShade* d_tri_rec = nullptr;                 // per-triangle shading records (SceneView::tri_rec)
     // settings
     int env_w = 0, env_h = 0, env_use = 0, env_auto = 0;
     float env_color[3] = {0, 0, 0}, env_intensity = 0;
@@ -131,8 +132,9 @@ static void free_lanes(b200pt_ctx* c) {
 }
 static void free_scene(b200pt_ctx* c) {
     cudaFree(c->d_pos); cudaFree(c->d_nrm); cudaFree(c->d_uv); cudaFree(c->d_idx4); cudaFree(c->d_meshes);
-    cudaFree(c->d_texels); cudaFree(c->bvh.nodes); cudaFree(c->bvh.tris); cudaFree(c->d_node_box);
+    cudaFree(c->d_texels); cudaFree(c->bvh.nodes); cudaFree(c->bvh.tris); cudaFree(c->d_node_box); cudaFree(c->d_tri_rec);
     c->d_node_box = nullptr;
+    c->d_tri_rec = nullptr;
     c->d_pos = c->d_nrm = nullptr; c->d_uv = nullptr; c->d_idx4 = nullptr; c->d_meshes = nullptr; c->d_texels = nullptr;
     c->bvh = DeviceBVH{};
     c->built = false;
@@ -155,6 +157,7 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     sv.vpos = c->d_pos;
     sv.vnrm = c->d_nrm;
     sv.vuv = c->d_uv;
+    sv.tri_rec = getenv("B200PT_NO_TRIREC") ? nullptr : c->d_tri_rec;   // (the env switch is the A/B of tools/trirec_ab.py)
     sv.meshes = c->d_meshes;
     sv.materials = c->d_mats;
     sv.mesh_materials = c->d_mesh_mats;
@@ -339,6 +342,8 @@ extern "C" int b200pt_build_accel(b200pt_ctx* c) {
         CU(cudaMalloc(&c->d_texels, sizeof(uint32_t) * c->h_texels.size()));
         CU(cudaMemcpyAsync(c->d_texels, c->h_texels.data(), sizeof(uint32_t) * c->h_texels.size(), cudaMemcpyHostToDevice, c->stream));
     }
+    CU(cudaMalloc(&c->d_tri_rec, sizeof(TriShade) * nt));
+    launch_tri_records(c->d_pos, c->d_nrm, c->d_idx4, (uint32_t)nt, c->d_tri_rec, c->stream);
     CU(cudaEventRecord(c->ev0, c->stream));
     std::string err;
     if (!build_bvh_device(c->d_pos, c->d_idx4, (uint32_t)nt, c->lo, c->hi, c->max_abs, &c->bvh, c->stream, err))
@@ -392,6 +397,7 @@ extern "C" int b200pt_update_mesh(b200pt_ctx* c, int32_t mesh_index, const float
         CU(cudaMemcpyAsync(c->d_pos + vbase, c->h_pos.data() + vbase, sizeof(f4) * (size_t)nv, cudaMemcpyHostToDevice, c->stream));
         if (normals)
             CU(cudaMemcpyAsync(c->d_nrm + vbase, c->h_nrm.data() + vbase, sizeof(f4) * (size_t)nv, cudaMemcpyHostToDevice, c->stream));
+        launch_tri_records(c->d_pos, c->d_nrm, c->d_idx4, (uint32_t)(c->h_idx4.size() / 4), c->d_tri_rec, c->stream);
         CU(cudaStreamSynchronize(c->stream));
         c->geometry_moved = true;
     }

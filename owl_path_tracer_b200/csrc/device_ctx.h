@@ -69,6 +69,7 @@ void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t ma
 void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 bool timeline_arm(bool on, cudaStream_t st);   // PT_TIMELINE builds only (false otherwise)
 bool timeline_dump(const char* path);
+void launch_tri_records(const f4* pos, const f4* nrm, const int32_t* idx4, uint32_t n, TriShade* out, cudaStream_t st);
 void launch_fused(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, int segments, cudaStream_t st);
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, int transfer, uint32_t* rgba, f4* mean, cudaStream_t st);

@@ -58,6 +58,10 @@ struct SceneView {
     const f4* vpos;            // per global vertex
     const f4* vnrm;
     const f2* vuv;
+    // Per-triangle shading records (device only; nullptr: fetch through idx4 as the host emulation does): the three
+    // positions and normals of a triangle side by side, 96 bytes, p0.w = mesh index.  One gather instead of two
+    // dependent ones (idx4, then six scattered vertices) in the shade step; same values, same arithmetic.
+    const struct TriShade* tri_rec;
     const MeshInfo* meshes;
     const Material* materials;
     const Material* mesh_materials;  // materials[meshes[m].material] per mesh: one dependent load less in shade
@@ -97,6 +101,11 @@ struct SceneView {
     int32_t env_nee;            // 1: NEE mode, map in use, tables present
     uint32_t plane_magic;      // 0x3F800000, see plane_q (pt_bvh8.h): a runtime value on purpose
 };
+
+struct TriShade {
+    f4 p0, p1, p2, n0, n1, n2;   // p0.w: mesh index (bits)
+};
+static_assert(sizeof(TriShade) == 96, "TriShade is 96 bytes");
 
 // packed per-lane control word: sample index (20 bits) | depth (8 bits) | lobe+1 (3 bits)
 PT_HD uint32_t pack_ctl(uint32_t sample, uint32_t depth, int lobe) {
@@ -267,15 +276,23 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
             rad = rad * power_heuristic(L.prev_pdf, p_sel * env_pdf(sv, L.d));
         return end_sample(sv, L, px, py, rad * L.thr);
     }
-    const TriIdx ix = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + hit.tri);
-    const int i0 = ix.i0, i1 = ix.i1, i2 = ix.i2, mesh = ix.mesh;
-    // everything below depends on idx4 only: mesh record, its material and the six vertex
-    // attributes are fetched side by side (entity_data + material_buffer[material_index],
-    // device.cu:150-154)
+    int i0 = 0, i1 = 0, i2 = 0, mesh;
+    f4 p0, p1, p2, n0, n1, n2;
+    if (sv.tri_rec) {
+        const TriShade r = load_ro(sv.tri_rec + hit.tri);
+        p0 = r.p0; p1 = r.p1; p2 = r.p2;
+        n0 = r.n0; n1 = r.n1; n2 = r.n2;
+        mesh = (int)f2u(r.p0.w);
+    } else {
+        const TriIdx ix = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + hit.tri);
+        i0 = ix.i0; i1 = ix.i1; i2 = ix.i2;
+        mesh = ix.mesh;
+        p0 = load_ro(sv.vpos + i0); p1 = load_ro(sv.vpos + i1); p2 = load_ro(sv.vpos + i2);
+        n0 = load_ro(sv.vnrm + i0); n1 = load_ro(sv.vnrm + i1); n2 = load_ro(sv.vnrm + i2);
+    }
+    // mesh record and its material (entity_data + material_buffer[material_index], device.cu:150-154)
     const MeshInfo mi = load_ro(sv.meshes + mesh);
     Material m = load_ro(sv.mesh_materials + mesh);
-    const f4 p0 = load_ro(sv.vpos + i0), p1 = load_ro(sv.vpos + i1), p2 = load_ro(sv.vpos + i2);
-    const f4 n0 = load_ro(sv.vnrm + i0), n1 = load_ro(sv.vnrm + i1), n2 = load_ro(sv.vnrm + i2);
 
     if (m.emission > 0.0f) {  // device.cu:157-161: radiance = emission (overwrites)
         if (tri_l && L.prev_pdf > 0.0f && mi.light_first >= 0) {
@@ -296,6 +313,10 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
     const f3 vp = bw * f3{p0.x, p0.y, p0.z} + bu * f3{p1.x, p1.y, p1.z} + bv * f3{p2.x, p2.y, p2.z};
     const f3 vn = normalize(bw * f3{n0.x, n0.y, n0.z} + bu * f3{n1.x, n1.y, n1.z} + bv * f3{n2.x, n2.y, n2.z});
     if (mi.tex_offset >= 0) {  // device.cu:75-94
+        if (sv.tri_rec) {  // the records carry no uv indices: textured meshes take the idx4 route for them
+            const TriIdx ix = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + hit.tri);
+            i0 = ix.i0; i1 = ix.i1; i2 = ix.i2;
+        }
         const f2 t0 = sv.vuv[i0], t1 = sv.vuv[i1], t2 = sv.vuv[i2];
         const float tu = bw * t0.x + bu * t1.x + bv * t2.x;
         const float tv = bw * t0.y + bu * t1.y + bv * t2.y;

@@ -601,6 +601,25 @@ bool timeline_dump(const char* path) {
     return false;
 #endif
 }
+// per-triangle shading records (SceneView::tri_rec): gathered once per build / vertex update
+__global__ void __launch_bounds__(256) k_tri_records(const f4* __restrict__ pos, const f4* __restrict__ nrm, const int32_t* __restrict__ idx4,
+                                                     uint32_t n, TriShade* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int i0 = idx4[4 * (size_t)i + 0], i1 = idx4[4 * (size_t)i + 1], i2 = idx4[4 * (size_t)i + 2], mesh = idx4[4 * (size_t)i + 3];
+    TriShade r;
+    r.p0 = pos[i0];
+    r.p0.w = u2f((uint32_t)mesh);
+    r.p1 = pos[i1];
+    r.p2 = pos[i2];
+    r.n0 = nrm[i0];
+    r.n1 = nrm[i1];
+    r.n2 = nrm[i2];
+    out[i] = r;
+}
+void launch_tri_records(const f4* pos, const f4* nrm, const int32_t* idx4, uint32_t n, TriShade* out, cudaStream_t st) {
+    k_tri_records<<<blocks(n, 256), 256, 0, st>>>(pos, nrm, idx4, n, out);
+}
 void launch_fused(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, int segments, cudaStream_t st) {
     k_fused<<<blocks(max_count, 64), 64, 0, st>>>(sv, la, k, segments);
 }
