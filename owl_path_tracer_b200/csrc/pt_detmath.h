@@ -5,8 +5,10 @@
 // disney_helper.cuh:6, sample_methods.hpp:38-41).  CUDA's libm and glibc do not
 // agree bit for bit, so paths would diverge after the first bounce and the GPU could
 // only be checked statistically.  These versions evaluate in binary64 with nothing
-// but +,-,*,/,sqrt,floor,frexp,ldexp (all exactly specified by IEEE-754 / exact by
-// construction) and round ONCE to binary32.  The same source therefore returns the
+// but +,-,*,/,fma,sqrt,floor,frexp,ldexp (all exactly specified by IEEE-754 / exact by
+// construction; the Horner steps of the polynomials are explicit fma() calls — one correctly rounded
+// operation on both sides, half the binary64 instructions of a separate multiply and add, which matter on
+// the GPU: they were a quarter of k_shade's instruction stream) and round ONCE to binary32.  The same source therefore returns the
 // same bits from nvcc (-fmad=false) and from g++ (-ffp-contract=off), and the result
 // is within 1 ulp of the true value (the binary64 intermediate is good to ~1e-14
 // relative for the argument ranges the integrator produces: |x| < 1e4 for the
@@ -31,25 +33,25 @@ constexpr double kInvLn2 = 1.44269504088896338700e+00;
 PT_HD double sin_poly(double r) {  // |r| <= pi/4, odd Taylor series to r^17
     double r2 = r * r;
     double p = 1.0 / 355687428096000.0;
-    p = p * r2 - 1.0 / 1307674368000.0;
-    p = p * r2 + 1.0 / 6227020800.0;
-    p = p * r2 - 1.0 / 39916800.0;
-    p = p * r2 + 1.0 / 362880.0;
-    p = p * r2 - 1.0 / 5040.0;
-    p = p * r2 + 1.0 / 120.0;
-    p = p * r2 - 1.0 / 6.0;
+    p = fma(p, r2, -(1.0 / 1307674368000.0));
+    p = fma(p, r2, 1.0 / 6227020800.0);
+    p = fma(p, r2, -(1.0 / 39916800.0));
+    p = fma(p, r2, 1.0 / 362880.0);
+    p = fma(p, r2, -(1.0 / 5040.0));
+    p = fma(p, r2, 1.0 / 120.0);
+    p = fma(p, r2, -(1.0 / 6.0));
     return r + r * (r2 * p);
 }
 PT_HD double cos_poly(double r) {  // |r| <= pi/4, even Taylor series to r^16
     double r2 = r * r;
     double p = 1.0 / 20922789888000.0;
-    p = p * r2 - 1.0 / 87178291200.0;
-    p = p * r2 + 1.0 / 479001600.0;
-    p = p * r2 - 1.0 / 3628800.0;
-    p = p * r2 + 1.0 / 40320.0;
-    p = p * r2 - 1.0 / 720.0;
-    p = p * r2 + 1.0 / 24.0;
-    p = p * r2 - 0.5;
+    p = fma(p, r2, -(1.0 / 87178291200.0));
+    p = fma(p, r2, 1.0 / 479001600.0);
+    p = fma(p, r2, -(1.0 / 3628800.0));
+    p = fma(p, r2, 1.0 / 40320.0);
+    p = fma(p, r2, -(1.0 / 720.0));
+    p = fma(p, r2, 1.0 / 24.0);
+    p = fma(p, r2, -(0.5));
     return 1.0 + r2 * p;
 }
 // x = k*pi/2 + r.  Returns the quadrant k mod 4.
@@ -76,23 +78,23 @@ PT_HD double atan_core(double a) {  // a >= 0 (may be +inf); result in [0, pi/2]
     double u = shift ? (t - 1.0) / (t + 1.0) : t;
     double u2 = u * u;
     double p = 1.0 / 37.0;
-    p = 1.0 / 35.0 - u2 * p;
-    p = 1.0 / 33.0 - u2 * p;
-    p = 1.0 / 31.0 - u2 * p;
-    p = 1.0 / 29.0 - u2 * p;
-    p = 1.0 / 27.0 - u2 * p;
-    p = 1.0 / 25.0 - u2 * p;
-    p = 1.0 / 23.0 - u2 * p;
-    p = 1.0 / 21.0 - u2 * p;
-    p = 1.0 / 19.0 - u2 * p;
-    p = 1.0 / 17.0 - u2 * p;
-    p = 1.0 / 15.0 - u2 * p;
-    p = 1.0 / 13.0 - u2 * p;
-    p = 1.0 / 11.0 - u2 * p;
-    p = 1.0 / 9.0 - u2 * p;
-    p = 1.0 / 7.0 - u2 * p;
-    p = 1.0 / 5.0 - u2 * p;
-    p = 1.0 / 3.0 - u2 * p;
+    p = fma(-u2, p, 1.0 / 35.0);
+    p = fma(-u2, p, 1.0 / 33.0);
+    p = fma(-u2, p, 1.0 / 31.0);
+    p = fma(-u2, p, 1.0 / 29.0);
+    p = fma(-u2, p, 1.0 / 27.0);
+    p = fma(-u2, p, 1.0 / 25.0);
+    p = fma(-u2, p, 1.0 / 23.0);
+    p = fma(-u2, p, 1.0 / 21.0);
+    p = fma(-u2, p, 1.0 / 19.0);
+    p = fma(-u2, p, 1.0 / 17.0);
+    p = fma(-u2, p, 1.0 / 15.0);
+    p = fma(-u2, p, 1.0 / 13.0);
+    p = fma(-u2, p, 1.0 / 11.0);
+    p = fma(-u2, p, 1.0 / 9.0);
+    p = fma(-u2, p, 1.0 / 7.0);
+    p = fma(-u2, p, 1.0 / 5.0);
+    p = fma(-u2, p, 1.0 / 3.0);
     double r = u - u * (u2 * p);
     if (shift) r = kPio4 + r;
     if (inv) r = (kPio2Hi - r) + kPio2Lo;
@@ -108,16 +110,16 @@ PT_HD double log_core(double x) {  // x > 0, finite, normal
     double s = (m - 1.0) / (m + 1.0);
     double s2 = s * s;
     double p = 1.0 / 23.0;
-    p = p * s2 + 1.0 / 21.0;
-    p = p * s2 + 1.0 / 19.0;
-    p = p * s2 + 1.0 / 17.0;
-    p = p * s2 + 1.0 / 15.0;
-    p = p * s2 + 1.0 / 13.0;
-    p = p * s2 + 1.0 / 11.0;
-    p = p * s2 + 1.0 / 9.0;
-    p = p * s2 + 1.0 / 7.0;
-    p = p * s2 + 1.0 / 5.0;
-    p = p * s2 + 1.0 / 3.0;
+    p = fma(p, s2, 1.0 / 21.0);
+    p = fma(p, s2, 1.0 / 19.0);
+    p = fma(p, s2, 1.0 / 17.0);
+    p = fma(p, s2, 1.0 / 15.0);
+    p = fma(p, s2, 1.0 / 13.0);
+    p = fma(p, s2, 1.0 / 11.0);
+    p = fma(p, s2, 1.0 / 9.0);
+    p = fma(p, s2, 1.0 / 7.0);
+    p = fma(p, s2, 1.0 / 5.0);
+    p = fma(p, s2, 1.0 / 3.0);
     double lm = 2.0 * (s + s * (s2 * p));
     double ed = (double)e;
     return ed * kLn2Hi + (ed * kLn2Lo + lm);
@@ -128,19 +130,19 @@ PT_HD double exp_core(double z) {
     double k = floor(z * kInvLn2 + 0.5);
     double r = (z - k * kLn2Hi) - k * kLn2Lo;
     double p = 1.0 / 6227020800.0;
-    p = p * r + 1.0 / 479001600.0;
-    p = p * r + 1.0 / 39916800.0;
-    p = p * r + 1.0 / 3628800.0;
-    p = p * r + 1.0 / 362880.0;
-    p = p * r + 1.0 / 40320.0;
-    p = p * r + 1.0 / 5040.0;
-    p = p * r + 1.0 / 720.0;
-    p = p * r + 1.0 / 120.0;
-    p = p * r + 1.0 / 24.0;
-    p = p * r + 1.0 / 6.0;
-    p = p * r + 0.5;
-    p = p * r + 1.0;
-    p = p * r + 1.0;
+    p = fma(p, r, 1.0 / 479001600.0);
+    p = fma(p, r, 1.0 / 39916800.0);
+    p = fma(p, r, 1.0 / 3628800.0);
+    p = fma(p, r, 1.0 / 362880.0);
+    p = fma(p, r, 1.0 / 40320.0);
+    p = fma(p, r, 1.0 / 5040.0);
+    p = fma(p, r, 1.0 / 720.0);
+    p = fma(p, r, 1.0 / 120.0);
+    p = fma(p, r, 1.0 / 24.0);
+    p = fma(p, r, 1.0 / 6.0);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
     return ldexp(p, (int)k);
 }
 PT_HD bool is_nan(double v) { return v != v; }
