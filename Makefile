@@ -13,7 +13,7 @@ BIN = $(PKG)/bin
 
 NVFLAGS = -std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false \
           -Xcompiler -fPIC -Xcompiler -ffp-contract=off --expt-relaxed-constexpr -cudart static
-CXXFLAGS = -std=c++17 -O2 -fPIC -Wall -Wno-unused-function
+CXXFLAGS = -std=c++17 -O2 -fPIC -Wall -Wno-unused-function -pthread
 
 CUHDR = $(wildcard $(CSRC)/*.h) $(wildcard $(CSRC)/*.cuh) include/b200pt.h
 HOSTHDR = $(wildcard $(HOST)/*.hpp) include/b200pt.h include/b200pt_host.h

@@ -12,7 +12,11 @@
 #include <cstring>
 #include <filesystem>
 #include <fstream>
+#include <algorithm>
+#include <atomic>
 #include <map>
+#include <mutex>
+#include <thread>
 #include <sstream>
 #include <stdexcept>
 
@@ -183,6 +187,108 @@ inline int fix_index(int idx, int n) {
     return n + idx;
 }
 
+// The file is cut into chunks at line ends and the chunks are parsed by concurrent threads (the
+// reference parses serially through tinyobjloader).  A chunk cannot resolve its own indices — a negative index
+// counts back from the attributes seen so far in the WHOLE file — so it keeps the raw integers together with its
+// local attribute counts at each face; a serial merge adds the chunk bases, fixes the indices and cuts the shapes.
+// One chunk is the serial parser: both paths are the same code, tests/test_host.py compares their output.
+struct obj_chunk {
+    struct raw_index {
+        int v = 0, vt = 0, vn = 0;
+        bool has_vt = false, has_vn = false;
+    };
+    struct shape_break {
+        size_t face;       // the o/g line stands before this face of the chunk
+        std::string name;
+    };
+    std::vector<float> vertices, normals, texcoords;
+    std::vector<raw_index> indices;
+    std::vector<int> face_sizes;
+    std::vector<int> face_counts;   // per face: vertices, normals, texcoords of the chunk seen before it
+    std::vector<shape_break> breaks;
+};
+
+void parse_obj_chunk(const char* p, const char* end, obj_chunk& c) {
+    auto is_sp = [](char ch) { return ch == ' ' || ch == '\t'; };
+    while (p < end) {
+        const char* eol = (const char*)memchr(p, '\n', (size_t)(end - p));
+        if (!eol) eol = end;
+        const char* q = p;
+        while (q < eol && is_sp(*q)) ++q;
+        if (q + 1 < eol && q[0] == 'v' && is_sp(q[1])) {
+            char* e;
+            q += 2;
+            for (int k = 0; k < 3; ++k) {
+                c.vertices.push_back((float)strtod(q, &e));
+                q = e;
+            }
+        } else if (q + 2 < eol && q[0] == 'v' && q[1] == 'n' && is_sp(q[2])) {
+            char* e;
+            q += 3;
+            for (int k = 0; k < 3; ++k) {
+                c.normals.push_back((float)strtod(q, &e));
+                q = e;
+            }
+        } else if (q + 2 < eol && q[0] == 'v' && q[1] == 't' && is_sp(q[2])) {
+            char* e;
+            q += 3;
+            for (int k = 0; k < 2; ++k) {
+                c.texcoords.push_back((float)strtod(q, &e));
+                q = e;
+            }
+        } else if (q + 1 < eol && q[0] == 'f' && is_sp(q[1])) {
+            q += 2;
+            int n = 0;
+            c.face_counts.push_back((int)c.vertices.size() / 3);
+            c.face_counts.push_back((int)c.normals.size() / 3);
+            c.face_counts.push_back((int)c.texcoords.size() / 2);
+            while (q < eol) {
+                while (q < eol && (is_sp(*q) || *q == '\r')) ++q;
+                if (q >= eol) break;
+                obj_chunk::raw_index ix;
+                char* e;
+                ix.v = (int)strtol(q, &e, 10);
+                q = e;
+                if (q < eol && *q == '/') {
+                    ++q;
+                    if (q < eol && *q == '/') {
+                        ++q;
+                        ix.vn = (int)strtol(q, &e, 10);
+                        ix.has_vn = true;
+                        q = e;
+                    } else {
+                        ix.vt = (int)strtol(q, &e, 10);
+                        ix.has_vt = true;
+                        q = e;
+                        if (q < eol && *q == '/') {
+                            ++q;
+                            ix.vn = (int)strtol(q, &e, 10);
+                            ix.has_vn = true;
+                            q = e;
+                        }
+                    }
+                }
+                c.indices.push_back(ix);
+                ++n;
+            }
+            c.face_sizes.push_back(n);
+        } else if (q + 1 < eol && (q[0] == 'o' || q[0] == 'g') && is_sp(q[1])) {
+            q += 2;
+            while (q < eol && is_sp(*q)) ++q;
+            const char* e = eol;
+            while (e > q && (e[-1] == '\r' || is_sp(e[-1]))) --e;
+            c.breaks.push_back({c.face_sizes.size(), std::string(q, e)});
+        }
+        p = eol + 1;
+    }
+}
+
+int obj_threads(size_t bytes) {
+    if (const char* e = getenv("B200PT_OBJ_THREADS")) return std::max(1, atoi(e));
+    const size_t by_size = bytes / (256u << 10);   // a chunk below 256 KB is not worth a thread
+    return (int)std::max<size_t>(1, std::min<size_t>({by_size, (size_t)std::thread::hardware_concurrency(), (size_t)16}));
+}
+
 bool parse_obj(const std::string& path, obj_attrib& at, std::vector<obj_shape>& shapes, std::string& err) {
     FILE* f = fopen(path.c_str(), "rb");
     if (!f) {
@@ -202,82 +308,65 @@ bool parse_obj(const std::string& path, obj_attrib& at, std::vector<obj_shape>& 
         }
         fclose(f);
     }
+    // chunks: cut at the first line end at or after i * size / T
+    const int T = obj_threads(data.size());
+    const char* base = data.c_str();
+    const char* end = base + data.size();
+    std::vector<const char*> cut((size_t)T + 1, end);
+    cut[0] = base;
+    for (int i = 1; i < T; ++i) {
+        const char* p = base + data.size() * (size_t)i / (size_t)T;
+        if (p < cut[(size_t)i - 1]) p = cut[(size_t)i - 1];
+        const char* nl = (const char*)memchr(p, '\n', (size_t)(end - p));
+        cut[(size_t)i] = nl ? nl + 1 : end;
+    }
+    std::vector<obj_chunk> chunks((size_t)T);
+    {
+        std::vector<std::thread> th;
+        for (int i = 1; i < T; ++i) th.emplace_back(parse_obj_chunk, cut[(size_t)i], cut[(size_t)i + 1], std::ref(chunks[(size_t)i]));
+        parse_obj_chunk(cut[0], cut[1], chunks[0]);
+        for (auto& t : th) t.join();
+    }
+    // merge in file order
+    size_t tv = 0, tn = 0, tt = 0;
+    for (const obj_chunk& c : chunks) {
+        tv += c.vertices.size();
+        tn += c.normals.size();
+        tt += c.texcoords.size();
+    }
+    at.vertices.reserve(tv);
+    at.normals.reserve(tn);
+    at.texcoords.reserve(tt);
     obj_shape cur;
     auto flush = [&]() {
         if (!cur.face_sizes.empty()) shapes.push_back(cur);
         cur.indices.clear();
         cur.face_sizes.clear();
     };
-    const char* p = data.c_str();
-    const char* end = p + data.size();
-    while (p < end) {
-        const char* eol = (const char*)memchr(p, '\n', (size_t)(end - p));
-        if (!eol) eol = end;
-        const char* q = p;
-        while (q < eol && (*q == ' ' || *q == '\t')) ++q;
-        auto is_sp = [](char c) { return c == ' ' || c == '\t'; };
-        if (q + 1 < eol && q[0] == 'v' && is_sp(q[1])) {
-            char* e;
-            q += 2;
-            for (int k = 0; k < 3; ++k) {
-                at.vertices.push_back((float)strtod(q, &e));
-                q = e;
+    for (const obj_chunk& c : chunks) {
+        const int bv = (int)at.vertices.size() / 3, bn = (int)at.normals.size() / 3, bt = (int)at.texcoords.size() / 2;
+        size_t next_break = 0, corner = 0;
+        for (size_t face = 0; face <= c.face_sizes.size(); ++face) {
+            while (next_break < c.breaks.size() && c.breaks[next_break].face == face) {
+                flush();
+                cur.name = c.breaks[next_break].name;
+                ++next_break;
             }
-        } else if (q + 2 < eol && q[0] == 'v' && q[1] == 'n' && is_sp(q[2])) {
-            char* e;
-            q += 3;
-            for (int k = 0; k < 3; ++k) {
-                at.normals.push_back((float)strtod(q, &e));
-                q = e;
-            }
-        } else if (q + 2 < eol && q[0] == 'v' && q[1] == 't' && is_sp(q[2])) {
-            char* e;
-            q += 3;
-            for (int k = 0; k < 2; ++k) {
-                at.texcoords.push_back((float)strtod(q, &e));
-                q = e;
-            }
-        } else if (q + 1 < eol && q[0] == 'f' && is_sp(q[1])) {
-            q += 2;
-            int n = 0;
-            const int nv = (int)at.vertices.size() / 3, nn = (int)at.normals.size() / 3,
-                      nt = (int)at.texcoords.size() / 2;
-            while (q < eol) {
-                while (q < eol && (is_sp(*q) || *q == '\r')) ++q;
-                if (q >= eol) break;
+            if (face == c.face_sizes.size()) break;
+            const int nv = bv + c.face_counts[3 * face], nn = bn + c.face_counts[3 * face + 1], nt = bt + c.face_counts[3 * face + 2];
+            for (int k = 0; k < c.face_sizes[face]; ++k) {
+                const obj_chunk::raw_index& r = c.indices[corner++];
                 obj_index ix;
-                char* e;
-                ix.v = fix_index((int)strtol(q, &e, 10), nv);
-                q = e;
-                if (q < eol && *q == '/') {
-                    ++q;
-                    if (q < eol && *q == '/') {
-                        ++q;
-                        ix.vn = fix_index((int)strtol(q, &e, 10), nn);
-                        q = e;
-                    } else {
-                        ix.vt = fix_index((int)strtol(q, &e, 10), nt);
-                        q = e;
-                        if (q < eol && *q == '/') {
-                            ++q;
-                            ix.vn = fix_index((int)strtol(q, &e, 10), nn);
-                            q = e;
-                        }
-                    }
-                }
+                ix.v = fix_index(r.v, nv);
+                if (r.has_vt) ix.vt = fix_index(r.vt, nt);
+                if (r.has_vn) ix.vn = fix_index(r.vn, nn);
                 cur.indices.push_back(ix);
-                ++n;
             }
-            cur.face_sizes.push_back(n);
-        } else if (q + 1 < eol && (q[0] == 'o' || q[0] == 'g') && is_sp(q[1])) {
-            flush();
-            q += 2;
-            while (q < eol && is_sp(*q)) ++q;
-            const char* e = eol;
-            while (e > q && (e[-1] == '\r' || is_sp(e[-1]))) --e;
-            cur.name.assign(q, e);
+            cur.face_sizes.push_back(c.face_sizes[face]);
         }
-        p = eol + 1;
+        at.vertices.insert(at.vertices.end(), c.vertices.begin(), c.vertices.end());
+        at.normals.insert(at.normals.end(), c.normals.begin(), c.normals.end());
+        at.texcoords.insert(at.texcoords.end(), c.texcoords.begin(), c.texcoords.end());
     }
     flush();
     return true;
@@ -289,12 +378,20 @@ bool parse_obj(const std::string& path, obj_attrib& at, std::vector<obj_shape>& 
 // (the reference assumes triangles and would mis-index them).
 std::shared_ptr<mesh> create_mesh(const obj_shape& shape, const obj_attrib& at) {
     auto m = std::make_shared<mesh>();
-    std::map<int32_t, int32_t> vertex_mapping;
+    // position index -> local vertex id.  The reference keeps a std::map (mesh_loader.cpp:12); a flat table over the
+    // index range the shape uses gives the same mapping without the tree (0.4 s of a 1 M-triangle load)
+    int32_t lo = INT32_MAX, hi = -1;
+    for (const obj_index& ix : shape.indices) {
+        if (ix.v < 0) continue;
+        lo = std::min(lo, (int32_t)ix.v);
+        hi = std::max(hi, (int32_t)ix.v);
+    }
+    std::vector<int32_t> vertex_mapping(hi >= lo ? (size_t)(hi - lo) + 1 : 0, -1);
     size_t offset = 0;
     auto corner = [&](const obj_index& ix) -> int32_t {
-        auto it = vertex_mapping.find(ix.v);
-        if (it == vertex_mapping.end()) {
-            it = vertex_mapping.insert({ix.v, (int32_t)(m->vertices.size() / 3)}).first;
+        int32_t* it = &vertex_mapping[(size_t)(ix.v - lo)];
+        if (*it < 0) {
+            *it = (int32_t)(m->vertices.size() / 3);
             for (int k = 0; k < 3; ++k) m->vertices.push_back(at.vertices[3 * (size_t)ix.v + k]);
         }
         if (ix.vn >= 0)
@@ -303,7 +400,7 @@ std::shared_ptr<mesh> create_mesh(const obj_shape& shape, const obj_attrib& at) 
         if (ix.vt >= 0)
             while (m->texcoords.size() / 2 < m->vertices.size() / 3)
                 for (int k = 0; k < 2; ++k) m->texcoords.push_back(at.texcoords[2 * (size_t)ix.vt + k]);
-        return it->second;
+        return *it;
     };
     for (int fs : shape.face_sizes) {
         for (int t = 1; t + 1 < fs; ++t) {
@@ -325,8 +422,31 @@ std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::s
     std::vector<obj_shape> shapes;
     std::string err;
     if (!parse_obj(obj_file, at, shapes, err)) throw std::runtime_error(err);
-    std::vector<std::pair<std::string, std::shared_ptr<mesh>>> out;
-    for (auto& s : shapes) out.emplace_back(s.name, create_mesh(s, at));
+    // the shapes are independent: their vertex maps are built by concurrent threads, results keep the file order
+    std::vector<std::pair<std::string, std::shared_ptr<mesh>>> out(shapes.size());
+    std::atomic<size_t> next{0};
+    std::mutex mu;
+    std::string first_error;
+    auto work = [&]() {
+        for (;;) {
+            const size_t i = next.fetch_add(1);
+            if (i >= shapes.size()) break;
+            try {
+                out[i] = {shapes[i].name, create_mesh(shapes[i], at)};
+            } catch (const std::exception& e) {
+                std::lock_guard<std::mutex> g(mu);
+                if (first_error.empty()) first_error = e.what();
+            }
+        }
+    };
+    size_t bytes = 0;
+    for (const auto& sh : shapes) bytes += sh.indices.size() * sizeof(obj_index);
+    const int T = (int)std::min<size_t>((size_t)obj_threads(bytes * 4), std::max<size_t>(shapes.size(), 1));
+    std::vector<std::thread> th;
+    for (int i = 1; i < T; ++i) th.emplace_back(work);
+    work();
+    for (auto& t : th) t.join();
+    if (!first_error.empty()) throw std::runtime_error(first_error);
     return out;
 }
 

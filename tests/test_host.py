@@ -101,6 +101,72 @@ f 5//3 6//3 7//3
     assert e["uvs"].tolist() == [[0, 0]] * 3 + [[1, 1]]
 
 
+def test_parallel_obj_parse_equals_the_serial_parse(tmp_path, monkeypatch):
+    """the OBJ file is parsed in chunks by concurrent threads and the shapes' vertex maps are built
+    concurrently; one chunk / one thread is the serial parser.  Same entities, bit for bit, whatever the thread count —
+    on the reference's own cornell-box file and on a synthetic file whose negative (relative) indices, groups, quads,
+    CRLF line ends and comments straddle the chunk cuts."""
+    import json
+    def entities(assets, threads):
+        monkeypatch.setenv("B200PT_OBJ_THREADS", str(threads))
+        sc = pt.Scene(assets=assets, width=8, height=8, spp=1, depth=1)
+        return [(e["name"], e["verts"].copy(), e["normals"].copy(), e["idx"].copy(), None if e["uvs"] is None else e["uvs"].copy())
+                for e in sc.entities()]
+    def same(a, b):
+        assert [x[0] for x in a] == [x[0] for x in b] and len(a) > 0
+        for x, y in zip(a, b):
+            for u, v in zip(x[1:], y[1:]):
+                assert (u is None) == (v is None)
+                if u is not None:
+                    assert u.shape == v.shape and (u.view(np.uint32) == v.view(np.uint32)).all()
+    # (a) the reference's cornell box
+    (tmp_path / "a").mkdir()
+    for f in ("cornell-box.json", "cornell-box.obj.scene"):
+        (tmp_path / "a" / f).write_bytes((REPO / "assets" / f).read_bytes())
+    (tmp_path / "a" / "settings.json").write_text((REPO / "assets/settings.json").read_text().replace('"car"', '"cornell-box"'))
+    serial = entities(tmp_path / "a", 1)
+    assert sum(len(e[3]) for e in serial) == 17974
+    for t in (2, 5, 16):
+        same(serial, entities(tmp_path / "a", t))
+    # (b) synthetic: 12 shapes, absolute and relative indices mixed, quads, CRLF, comments
+    rng = np.random.default_rng(5)
+    lines, nv, nn, nt = ["# synthetic"], 0, 0, 0
+    for sidx in range(12):
+        lines.append(("g " if sidx % 3 else "o ") + f"m{sidx}" + ("  " if sidx % 2 else ""))
+        for _ in range(int(rng.integers(40, 400))):
+            k = int(rng.integers(3, 6))
+            for _ in range(k):
+                x, y, z = rng.normal(size=3)
+                lines.append(f"v {x:.6f} {y:.6f} {z:.6f}")
+                lines.append(f"vn {x:.3f} {y:.3f} {z:.3f}")
+                lines.append(f"vt {abs(x) % 1:.4f} {abs(y) % 1:.4f}")
+            nv += k; nn += k; nt += k
+            if rng.random() < 0.2:
+                lines.append("# a comment between attributes and faces")
+            for _ in range(int(rng.integers(1, 4))):
+                corners = []
+                for c in rng.permutation(k)[:int(rng.integers(3, min(k, 4) + 1))]:
+                    if rng.random() < 0.5:   # relative: -1 is the attribute defined last
+                        a = -(k - int(c))
+                        corners.append(f"{a}/{a}/{a}" if rng.random() < 0.7 else f"{a}//{a}")
+                    else:
+                        a = nv - k + int(c) + 1
+                        corners.append(f"{a}/{a}/{a}")
+                lines.append("f " + " ".join(corners))
+    text = "".join(l + ("\r\n" if i % 7 == 0 else "\n") for i, l in enumerate(lines))
+    (tmp_path / "b").mkdir()
+    (tmp_path / "b" / "t.obj.scene").write_text(text)
+    (tmp_path / "b" / "settings.json").write_text((REPO / "assets/settings.json").read_text().replace('"car"', '"t"'))
+    scene = json.loads((REPO / "assets/cube.json").read_text())
+    proto = dict(scene["materials"][0], use_texture=False)
+    scene["materials"] = [dict(proto, name=f"m{i}") for i in range(12)]
+    (tmp_path / "b" / "t.json").write_text(json.dumps(scene))
+    serial = entities(tmp_path / "b", 1)
+    assert len(serial) == 12
+    for t in (2, 3, 7, 16):
+        same(serial, entities(tmp_path / "b", t))
+
+
 def png_pixels(path):
     d = path.read_bytes()
     assert d[:8] == b"\x89PNG\r\n\x1a\n"
