@@ -3,6 +3,8 @@
 #   make product    -> owl_path_tracer_b200/lib/libb200pt.so, libb200pt_host.so, bin/path_tracer
 #   make oracle     -> oracle/liboracle.so, oracle/liboracle_det.so   (test infrastructure)
 #   make emu        -> tests/emu/libemu.so  (host emulation of the kernels' per-lane logic; tests only)
+#   make ref        -> oracle/_ref/libref_device.so, libref_host.so: the REFERENCE'S OWN device.cu / disney/*.cuh /
+#                      loaders compiled for the host from /root/reference (tests only; no-op where it is absent)
 NVCC ?= /usr/local/cuda/bin/nvcc
 CXX ?= g++
 PKG = owl_path_tracer_b200
@@ -18,7 +20,7 @@ CXXFLAGS = -std=c++17 -O2 -fPIC -Wall -Wno-unused-function -pthread
 CUHDR = $(wildcard $(CSRC)/*.h) $(wildcard $(CSRC)/*.cuh) include/b200pt.h
 HOSTHDR = $(wildcard $(HOST)/*.hpp) include/b200pt.h include/b200pt_host.h
 
-all: product oracle emu
+all: product oracle emu ref
 product: $(LIB)/libb200pt.so $(LIB)/libb200pt_host.so $(BIN)/path_tracer
 
 $(LIB)/%.o: $(CSRC)/%.cu $(CUHDR)
@@ -39,6 +41,9 @@ $(BIN)/path_tracer: $(HOST)/main.cpp $(LIB)/libb200pt_host.so
 oracle:
 	$(MAKE) -C oracle
 
+ref:
+	$(MAKE) -C oracle/ref
+
 emu: tests/emu/libemu.so
 tests/emu/libemu.so: tests/emu/emu.cpp $(CUHDR)
 	$(CXX) -std=c++17 -O2 -fPIC -shared -ffp-contract=off -mfma -fno-fast-math -Wall -Wno-unused-function -Wno-unknown-pragmas -pthread -o $@ $<
@@ -46,5 +51,6 @@ tests/emu/libemu.so: tests/emu/emu.cpp $(CUHDR)
 clean:
 	rm -rf $(LIB) $(BIN) tests/emu/libemu.so
 	$(MAKE) -C oracle clean
+	$(MAKE) -C oracle/ref clean
 
-.PHONY: all product oracle emu clean
+.PHONY: all product oracle emu ref clean

@@ -20,10 +20,14 @@
 // over all triangles, and a plain binary BVH (median split) with padded boxes; tests check
 // they agree.
 //
-// PARITY STATUS: unpinned by the reference — it ships no golden vectors, KATs or fixtures
-// for this path (unit_tests/path_tracer_test.cu is a placeholder) and cannot be built here
-// (needs the OptiX SDK and RT cores).  The pins are this file's own frozen outputs under
-// tests/golden/ plus analytic checks (white furnace, pdf normalisation) in tests/.
+// PARITY STATUS: pinned by the reference itself, except at the traversal boundary.  oracle/ref/ compiles the
+// reference's own device.cu (raygen, trace_path, hit / miss programs), device/disney/*.cuh, math.hpp,
+// sample_methods.hpp, random.hpp and camera.cpp for the host (oracle/_ref/libref_device.so; one mechanical edit, see
+// oracle/ref/patch.py) and tests/test_ref_device.py requires the glibc build of this file to equal it BIT FOR BIT:
+// sample_disney on the 960-case grid + 262,144 random cases, RNG, camera, ONB, make_rgba, and whole frames of all six
+// scenes (float mean, RGBA8, ray count).  tests/golden/ref_*.npz are vectors generated from that library
+// (tools/make_golden_ref.py) so the pin also holds where /root/reference is absent.  Unpinned by nature: the closest
+// hit itself (OptiX is closed source and the reference ships no vectors for it) — defined above.
 //
 // Elementary functions: default build uses glibc libm (independent of the product).
 // -DORACLE_DETMATH switches to the product's deterministic functions
@@ -1316,6 +1320,27 @@ void oracle_math(int fn, int n, const float* x, const float* y, float* out) {
         }
     }
 }
+
+// math.hpp:86-107 hook: onb of n, then to_local(w) and to_world(w); out = t b local world per case (12 floats)
+void oracle_onb(const float* n_in, const float* w_in, int n, float* out) {
+    for (int i = 0; i < n; ++i) {
+        V3 nn{n_in[3 * i], n_in[3 * i + 1], n_in[3 * i + 2]}, w{w_in[3 * i], w_in[3 * i + 1], w_in[3 * i + 2]};
+        V3 t{}, b{};
+        onb(nn, t, b);
+        V3 v[4] = {t, b, to_local(t, b, nn, w), to_world(t, b, nn, w)};
+        for (int k = 0; k < 4; ++k) {
+            out[12 * i + 3 * k] = v[k].x;
+            out[12 * i + 3 * k + 1] = v[k].y;
+            out[12 * i + 3 * k + 2] = v[k].z;
+        }
+    }
+}
+
+// lights.hpp:23-28, :56-61 hooks (dead code in the reference; the NEE mode builds on them)
+float oracle_pdf_area_to_solid_angle(float pdf_area, float dist_sqr, float cos_t) {
+    return pdf_area_to_solid_angle(pdf_area, dist_sqr, cos_t);
+}
+float oracle_power_heuristic(float pdf_f, float pdf_g) { return power_heuristic(pdf_f, pdf_g); }
 
 uint32_t oracle_quantise(float r, float g, float b) {
     return (quantise8(r) << 0) + (quantise8(g) << 8) + (quantise8(b) << 16) + (0xffU << 24);

@@ -132,6 +132,11 @@ class Oracle(_SceneChecker):
         L.oracle_math.argtypes = [C.c_int, C.c_int, P, P, P]
         L.oracle_quantise.argtypes = [C.c_float] * 3
         L.oracle_quantise.restype = C.c_uint32
+        L.oracle_onb.argtypes = [P, P, C.c_int, P]
+        L.oracle_pdf_area_to_solid_angle.argtypes = [C.c_float] * 3
+        L.oracle_pdf_area_to_solid_angle.restype = C.c_float
+        L.oracle_power_heuristic.argtypes = [C.c_float] * 2
+        L.oracle_power_heuristic.restype = C.c_float
         self.det = bool(L.oracle_uses_detmath())
         assert self.det == det
         self.h = L.oracle_create()
@@ -184,6 +189,13 @@ class Oracle(_SceneChecker):
 
     def math(self, fn, x, y=None):
         return _math(self.L.oracle_math, fn, x, y)
+
+    def onb(self, n, w):
+        n = np.ascontiguousarray(n, np.float32)
+        w = np.ascontiguousarray(w, np.float32)
+        out = np.empty((n.shape[0], 4, 3), np.float32)
+        self.L.oracle_onb(_p(n), _p(w), n.shape[0], _p(out))
+        return dict(t=out[:, 0], b=out[:, 1], local=out[:, 2], world=out[:, 3])
 
     def camera(self, look_from, look_at, up, vfov, w, h):
         a = [np.asarray(v, np.float32) for v in (look_from, look_at, up)]
@@ -353,3 +365,97 @@ def rel_variance(sum4, n):
     rel = (s2 / n) / (m * m + 1e-2)
     rel = np.where(np.isnan(rel), 0.0, rel)
     return float(rel.sum() / rel.size)
+
+
+# --------------------------------------------------------------------------------------------------
+# The reference itself, compiled for the host (oracle/ref -> oracle/_ref/*.so).  Built here, where
+# /root/reference exists; the .so files travel to the GPU box.  When neither exists the tests that
+# need them are skipped (the committed golden vectors generated FROM them still run).
+REF_DIR = REPO / "oracle" / "_ref"
+
+
+def ref_available():
+    if Path("/root/reference/path_tracer/src/device/device.cu").exists():
+        subprocess.run(["make", "-s", "-C", str(REPO / "oracle" / "ref")], check=True)
+    return (REF_DIR / "libref_device.so").exists() and (REF_DIR / "libref_host.so").exists()
+
+
+class Ref(_SceneChecker):
+    """/root/reference/path_tracer/src/device/device.cu + disney/*.cuh + math/random/sample_methods/camera, run on the CPU.
+    The closest hit (closed-source OptiX in the reference) comes from an Oracle passed to ``render``."""
+    prefix = "ref_"
+
+    def __init__(self):
+        assert ref_available(), "oracle/_ref is not built"
+        self.L = C.CDLL(str(REF_DIR / "libref_device.so"))
+        L = self.L
+        P = C.c_void_p
+        L.ref_create.restype = P
+        L.ref_destroy.argtypes = [P]
+        L.ref_add_mesh.argtypes = [P, P, P, P, C.c_int, P, C.c_int, C.c_int, P, C.c_int, C.c_int]
+        L.ref_set_materials.argtypes = [P, P, C.c_int]
+        L.ref_set_environment.argtypes = [P, P, C.c_int, C.c_int, C.c_int, C.c_int, P, C.c_float]
+        L.ref_set_camera.argtypes = [P, P, P, P, P]
+        L.ref_set_render.argtypes = [P, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.ref_set_tracer.argtypes = [P, P, P]
+        L.ref_render.argtypes = [P] + [C.c_int] * 5 + [P, P]
+        L.ref_render.restype = C.c_uint64
+        L.ref_sample_disney.argtypes = [P, C.c_int] + [P] * 9
+        L.ref_rng.argtypes = [C.c_uint32, C.c_uint32, C.c_int, P, P]
+        L.ref_camera.argtypes = [P, P, P, C.c_float, C.c_int, C.c_int, P]
+        L.ref_onb.argtypes = [P, P, C.c_int, P]
+        L.ref_uv_on_sphere.argtypes = [P, C.c_int, P]
+        L.ref_quantise.argtypes = [C.c_float] * 3
+        L.ref_quantise.restype = C.c_uint32
+        L.ref_triangle_area.argtypes = [P, P, P]
+        L.ref_triangle_area.restype = C.c_float
+        L.ref_pdf_area_to_solid_angle.argtypes = [C.c_float] * 3
+        L.ref_pdf_area_to_solid_angle.restype = C.c_float
+        L.ref_power_heuristic.argtypes = [C.c_float] * 4
+        L.ref_power_heuristic.restype = C.c_float
+        L.ref_uniform_sample_triangle.argtypes = [C.c_float, C.c_float, P]
+        self.h = L.ref_create()
+
+    def build(self):
+        pass   # no acceleration structure of its own: see render(tracer=...)
+
+    def render(self, tracer: "Oracle", window=None, threads=NCPU):
+        """One launch of the reference's __raygen__ray_gen per pixel; closest hits by ``tracer`` (an Oracle holding the
+        same scene).  Returns mean (H, W, 3) float = the argument of make_rgba, rgba (H, W), rays."""
+        W, H = self.width, self.height
+        x0, y0, x1, y1 = window or (0, 0, W, H)
+        self._tracer = tracer   # keep alive
+        fn = C.cast(tracer.L.oracle_trace, C.c_void_p)
+        self.L.ref_set_tracer(self.h, fn, tracer.h)
+        mean = np.zeros((H, W, 3), np.float32)
+        rgba = np.zeros((H, W), np.uint32)
+        rays = self.L.ref_render(self.h, x0, y0, x1, y1, threads, _p(mean), _p(rgba))
+        return dict(mean=mean, rgba=rgba, rays=int(rays))
+
+    def sample_disney(self, mats, material, wo, lobe_in, rng_in):
+        return _sample_disney(self.L.ref_sample_disney, mats, material, wo, lobe_in, rng_in)
+
+    def rng(self, x, y, n):
+        out = np.empty(n, np.float32)
+        st = C.c_uint32()
+        self.L.ref_rng(x, y, n, _p(out), C.byref(st))
+        return out, st.value
+
+    def camera(self, look_from, look_at, up, vfov, w, h):
+        a = [np.asarray(v, np.float32) for v in (look_from, look_at, up)]
+        out = np.empty(12, np.float32)
+        self.L.ref_camera(_p(a[0]), _p(a[1]), _p(a[2]), vfov, w, h, _p(out))
+        return out.reshape(4, 3)
+
+    def onb(self, n, w):
+        n = np.ascontiguousarray(n, np.float32)
+        w = np.ascontiguousarray(w, np.float32)
+        out = np.empty((n.shape[0], 4, 3), np.float32)
+        self.L.ref_onb(_p(n), _p(w), n.shape[0], _p(out))
+        return dict(t=out[:, 0], b=out[:, 1], local=out[:, 2], world=out[:, 3])
+
+    def uv_on_sphere(self, d):
+        d = np.ascontiguousarray(d, np.float32)
+        out = np.empty((d.shape[0], 2), np.float32)
+        self.L.ref_uv_on_sphere(_p(d), d.shape[0], _p(out))
+        return out
