@@ -6,7 +6,9 @@
 #   make ref        -> oracle/_ref/libref_device.so, libref_host.so: the REFERENCE'S OWN device.cu / disney/*.cuh /
 #                      loaders compiled for the host from /root/reference (tests only; no-op where it is absent)
 NVCC ?= /usr/local/cuda/bin/nvcc
-CXX ?= g++
+# the environment may export CXX=/opt/gcc/bin/g++, a wrapper that links libstdc++ statically: several such copies in one
+# Python process (next to torch's dynamic one) break exception handling, so the system compiler is named explicitly
+CXX = /usr/bin/g++
 PKG = owl_path_tracer_b200
 CSRC = $(PKG)/csrc
 HOST = $(PKG)/host

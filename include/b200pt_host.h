@@ -84,6 +84,41 @@ int b200pt_write_png(const char* path, int32_t w, int32_t h, const uint32_t* rgb
 int b200pt_write_pfm(const char* path, int32_t w, int32_t h, const float* rgba_top_first);
 int b200pt_write_obj(const b200pt_scene* s, const char* path);
 
+/* ---- the loaders one stage at a time.  The application above is built from exactly these functions; they are exported
+ * so that tests/test_ref_host.py can hold each of them to the reference's own loader (oracle/_ref/libref_host.so =
+ * utils/mesh_loader.cpp on tinyobjloader, utils/image_buffer.cpp on stb, utils/parser.cpp on nlohmann json). */
+typedef struct b200pt_shapes b200pt_shapes;
+/* load_obj (mesh_loader.cpp:85-121): every shape of the file, before the material match of application.cpp:166-179.
+ * threads: 0 = automatic, n = cut the file into n chunks. */
+int b200pt_obj_load(const char* obj_file, int32_t threads, b200pt_shapes** out);
+int32_t b200pt_obj_count(const b200pt_shapes* s);
+/* material_index = -1, no texture */
+int b200pt_obj_shape(const b200pt_shapes* s, int32_t i, b200pt_entity_view* view);
+void b200pt_obj_free(b200pt_shapes* s);
+/* load_image (image_buffer.cpp:36-59): RGBA8, rows flipped; *.hdr through the 8-bit conversion of stb.  A missing file
+ * gives w = h = 0 and *pixels = NULL with status 0 (the reference continues with an empty image); a file that exists but
+ * cannot be decoded is an error.  Release with b200pt_image_free. */
+int b200pt_image_load(const char* name, const char* path, int32_t* w, int32_t* h, uint32_t** pixels);
+void b200pt_image_free(uint32_t* pixels);
+/* parse_camera (parser.cpp:65-79) + to_camera_data (camera.cpp:3-22): origin, llc, horizontal, vertical */
+int b200pt_parse_camera(const char* config_path, int32_t width, int32_t height, float out12[12]);
+typedef struct b200pt_settings_view {   /* settings_data / test_data of utils/parser.hpp */
+    char scene[256], test_name[256], test_material[256], test_attribute[256];
+    int32_t buffer_size[2], max_samples, max_path_depth, environment_use, environment_auto, test_material_type;
+    float environment_color[3], environment_intensity, test_step_size;
+    int32_t n_vec_values, n_flt_values;
+    float vec_values[64][3], flt_values[64];
+} b200pt_settings_view;
+int b200pt_parse_settings(const char* config_path, b200pt_settings_view* out);
+typedef struct b200pt_materials b200pt_materials;
+/* parse_materials (parser.cpp:19-63): name, 17 floats, "<name>-textures/<filename>" or "" */
+int b200pt_parse_materials(const char* config_path, b200pt_materials** out);
+int32_t b200pt_materials_count(const b200pt_materials* m);
+const char* b200pt_materials_name(const b200pt_materials* m, int32_t i);
+const char* b200pt_materials_file(const b200pt_materials* m, int32_t i);
+const b200pt_material* b200pt_materials_data(const b200pt_materials* m, int32_t i);
+void b200pt_materials_free(b200pt_materials* m);
+
 #ifdef __cplusplus
 }
 #endif

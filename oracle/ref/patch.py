@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """oracle/ref/patch.py — copies the reference sources that make up the render path into a build
-directory (oracle/_ref/build, git-ignored) and applies the ONE mechanical edit g++ needs.
+directory (oracle/_ref/build, git-ignored) and applies the TWO mechanical edits g++ needs.
 
 TEST INFRASTRUCTURE.  No reference text is ever written into the tracked tree.
 
@@ -9,6 +9,11 @@ inside the class body, which MSVC/nvcc accept and g++ rejects (GCC bug 85282).  
 token for token, behind the class as `random::rng<float>` / `random::rng<vec2>`.  Nothing else in any
 file is changed; the name clash of `struct random` with POSIX random(3), the CUDA qualifiers and the
 unqualified ::max are handled from outside by shim/ref_prelude.h.
+
+The second edit (utils/parser.cpp:26,69-70,85,88): `auto config{load_json(...)}` / `auto const cam{config["camera"]}` /
+`auto test{config["test"]}` brace-initialise a nlohmann::json from a json.  MSVC (the reference's compiler) copies; g++
+prefers the initializer_list constructor and builds a one-element ARRAY around the value (a documented nlohmann/GCC
+difference), after which every `config["..."]` throws type_error.305.  The braces become `=`: the MSVC meaning.
 
 Also extracts make_8bit / make_rgba (extern/owl/owl/include/owl/owl_device.h:79-91) into
 gen/owl_make_rgba.inc so the shim's owl_device.h can include the real quantisation.
@@ -56,6 +61,9 @@ def main():
         text = (SRC / f).read_text(encoding="utf-8-sig")
         if f == "random.hpp":
             text = move_specialisations(text)
+        if f == "utils/parser.cpp":
+            text, n = re.subn(r'auto( const)? (\w+)\{(load_json\(config_path\)|config\["\w+"\])\};', r'auto\1 \2 = \3;', text)
+            assert n == 5, f"parser.cpp: expected 5 brace-initialised json copies, found {n}"
         dst.write_text(text)
     gen = OUT / "gen"
     gen.mkdir(parents=True, exist_ok=True)

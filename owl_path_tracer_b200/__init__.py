@@ -178,6 +178,23 @@ def host_lib() -> C.CDLL:
     H.b200pt_write_png.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
     H.b200pt_write_pfm.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
     H.b200pt_write_obj.argtypes = [P, C.c_char_p]
+    H.b200pt_obj_load.argtypes = [C.c_char_p, C.c_int32, C.POINTER(P)]
+    H.b200pt_obj_count.argtypes = [P]
+    H.b200pt_obj_shape.argtypes = [P, C.c_int32, C.POINTER(EntityView)]
+    H.b200pt_obj_free.argtypes = [P]
+    H.b200pt_image_load.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(P)]
+    H.b200pt_image_free.argtypes = [P]
+    H.b200pt_parse_camera.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
+    H.b200pt_parse_settings.argtypes = [C.c_char_p, P]
+    H.b200pt_parse_materials.argtypes = [C.c_char_p, C.POINTER(P)]
+    H.b200pt_materials_count.argtypes = [P]
+    H.b200pt_materials_name.argtypes = [P, C.c_int32]
+    H.b200pt_materials_name.restype = C.c_char_p
+    H.b200pt_materials_file.argtypes = [P, C.c_int32]
+    H.b200pt_materials_file.restype = C.c_char_p
+    H.b200pt_materials_data.argtypes = [P, C.c_int32]
+    H.b200pt_materials_data.restype = P
+    H.b200pt_materials_free.argtypes = [P]
     H._typed = True
     return H
 

@@ -2,7 +2,11 @@
 // Lets a non-C++ caller (the ctypes binding in owl_path_tracer_b200/__init__.py, the
 // parity tests, bench.py) run the same loaders and application stages as the
 // path_tracer executable, and hand the loaded arrays to a checker.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
+#include <memory>
+#include <vector>
 #include <stdexcept>
 #include <string>
 
@@ -170,5 +174,123 @@ int b200pt_write_obj(const b200pt_scene* s, const char* path) {
         fclose(f);
     });
 }
+
+// ---- single stages (differential tests against the reference's own loaders)
+}  // extern "C"
+struct b200pt_shapes {
+    std::vector<std::pair<std::string, std::shared_ptr<host::mesh>>> shapes;
+};
+struct b200pt_materials {
+    std::vector<host::material_entry> entries;
+};
+extern "C" {
+
+int b200pt_obj_load(const char* obj_file, int32_t threads, b200pt_shapes** out) {
+    return guard([&] {
+        auto* s = new b200pt_shapes();
+        try {
+            s->shapes = host::load_obj(obj_file, threads);
+        } catch (...) {
+            delete s;
+            throw;
+        }
+        *out = s;
+    });
+}
+int32_t b200pt_obj_count(const b200pt_shapes* s) { return (int32_t)s->shapes.size(); }
+int b200pt_obj_shape(const b200pt_shapes* s, int32_t i, b200pt_entity_view* v) {
+    return guard([&] {
+        if (i < 0 || (size_t)i >= s->shapes.size()) throw std::out_of_range("shape index");
+        const host::mesh& m = *s->shapes[(size_t)i].second;
+        memset(v, 0, sizeof *v);
+        v->name = s->shapes[(size_t)i].first.c_str();
+        v->verts = m.vertices.data();
+        v->normals = m.normals.empty() ? nullptr : m.normals.data();
+        v->uvs = m.texcoords.empty() ? nullptr : m.texcoords.data();
+        v->nv = (int32_t)(m.vertices.size() / 3);
+        v->idx = m.indices.data();
+        v->nt = (int32_t)(m.indices.size() / 3);
+        v->material_index = -1;
+        // normals / uvs may be shorter than nv (first-occurrence rule, mesh_loader.cpp:52-75): their own counts
+        v->tex_w = (int32_t)(m.normals.size() / 3);
+        v->tex_h = (int32_t)(m.texcoords.size() / 2);
+    });
+}
+void b200pt_obj_free(b200pt_shapes* s) { delete s; }
+
+int b200pt_image_load(const char* name, const char* path, int32_t* w, int32_t* h, uint32_t** pixels) {
+    return guard([&] {
+        host::image_buffer img = host::load_image(name, path);
+        *w = img.width;
+        *h = img.height;
+        *pixels = nullptr;
+        if (!img.pixels.empty()) {
+            *pixels = (uint32_t*)malloc(img.pixels.size() * sizeof(uint32_t));
+            memcpy(*pixels, img.pixels.data(), img.pixels.size() * sizeof(uint32_t));
+        }
+    });
+}
+void b200pt_image_free(uint32_t* pixels) { free(pixels); }
+
+int b200pt_parse_camera(const char* config_path, int32_t width, int32_t height, float out12[12]) {
+    return guard([&] {
+        const host::camera_data d = host::to_camera_data(host::parse_camera(config_path), width, height);
+        const host::vec3* v[4] = {&d.origin, &d.llc, &d.horizontal, &d.vertical};
+        for (int i = 0; i < 4; ++i) {
+            out12[3 * i] = v[i]->x;
+            out12[3 * i + 1] = v[i]->y;
+            out12[3 * i + 2] = v[i]->z;
+        }
+    });
+}
+
+int b200pt_parse_settings(const char* config_path, b200pt_settings_view* o) {
+    return guard([&] {
+        const host::settings_data s = host::parse_settings(config_path);
+        memset(o, 0, sizeof *o);
+        snprintf(o->scene, sizeof o->scene, "%s", s.scene.c_str());
+        snprintf(o->test_name, sizeof o->test_name, "%s", s.test.name.c_str());
+        snprintf(o->test_material, sizeof o->test_material, "%s", s.test.material_name.c_str());
+        snprintf(o->test_attribute, sizeof o->test_attribute, "%s", s.test.attribute_name.c_str());
+        o->buffer_size[0] = s.buffer_size[0];
+        o->buffer_size[1] = s.buffer_size[1];
+        o->max_samples = s.max_samples;
+        o->max_path_depth = s.max_path_depth;
+        o->environment_use = s.environment_use;
+        o->environment_auto = s.environment_auto;
+        o->test_material_type = s.test.material_type;
+        o->environment_color[0] = s.environment_color.x;
+        o->environment_color[1] = s.environment_color.y;
+        o->environment_color[2] = s.environment_color.z;
+        o->environment_intensity = s.environment_intensity;
+        o->test_step_size = s.test.step_size;
+        o->n_vec_values = (int32_t)std::min<size_t>(64, s.test.vec_values.size());
+        o->n_flt_values = (int32_t)std::min<size_t>(64, s.test.flt_values.size());
+        for (int i = 0; i < o->n_vec_values; ++i) {
+            o->vec_values[i][0] = s.test.vec_values[(size_t)i].x;
+            o->vec_values[i][1] = s.test.vec_values[(size_t)i].y;
+            o->vec_values[i][2] = s.test.vec_values[(size_t)i].z;
+        }
+        for (int i = 0; i < o->n_flt_values; ++i) o->flt_values[i] = s.test.flt_values[(size_t)i];
+    });
+}
+
+int b200pt_parse_materials(const char* config_path, b200pt_materials** out) {
+    return guard([&] {
+        auto* m = new b200pt_materials();
+        try {
+            m->entries = host::parse_materials(config_path);
+        } catch (...) {
+            delete m;
+            throw;
+        }
+        *out = m;
+    });
+}
+int32_t b200pt_materials_count(const b200pt_materials* m) { return (int32_t)m->entries.size(); }
+const char* b200pt_materials_name(const b200pt_materials* m, int32_t i) { return m->entries[(size_t)i].name.c_str(); }
+const char* b200pt_materials_file(const b200pt_materials* m, int32_t i) { return m->entries[(size_t)i].texture_file.c_str(); }
+const b200pt_material* b200pt_materials_data(const b200pt_materials* m, int32_t i) { return &m->entries[(size_t)i].data; }
+void b200pt_materials_free(b200pt_materials* m) { delete m; }
 
 }  // extern "C"

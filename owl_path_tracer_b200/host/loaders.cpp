@@ -165,9 +165,18 @@ std::vector<material_entry> parse_materials(const std::string& path) {  // parse
 }
 
 // ------------------------------------------------------------------ OBJ reader
-// The subset of tinyobjloader's ObjReader the reference relies on (triangulate=false):
-// v / vn / vt / f / o / g; 1-based and negative indices; a shape is emitted for every
-// o/g block that has faces.  Everything else (mtllib, usemtl, s, ...) is ignored.
+// The subset of tinyobjloader's LoadObj (extern/tinyobjloader/tiny_obj_loader.h:2432-2994, the version the reference
+// vendors) that mesh_loader.cpp relies on with triangulate=false: v / vn / vt / f / o / g; 1-based and negative indices;
+// everything else (mtllib, usemtl, s, l, p, t, vw, vertex colours) is ignored.  The behaviours below are tinyobj's and
+// are held to it byte for byte by tests/test_ref_host.py (oracle/_ref/libref_host.so = the reference's own loader):
+//   * numbers are read by tinyobj's own decimal routine (tryParseDouble, :866-1010), which is NOT correctly rounded —
+//     digits are accumulated in binary64 (integer part: m = 10 m + d; fraction: m += d * 10^-k; exponent: ldexp(m * 5^e, e))
+//     and the result is cast to float; a token that does not parse yields 0;
+//   * a line ends at "\n", "\r\n" or a lone "\r" (safeGetline);
+//   * `f`: each corner is i, i/j, i//k or i/j/k read with atoi; index 0 or an unparsable corner fails the whole file
+//     ("Failed parse `f' line"); faces with fewer than 3 corners are dropped;
+//   * `o <rest of line>` names the following faces (verbatim, inner and trailing blanks kept); `g a b` joins its words with
+//     one blank; a shape is emitted whenever an o/g line (or the end of file) follows at least one kept face.
 namespace {
 struct obj_index {
     int v = -1, vt = -1, vn = -1;
@@ -181,10 +190,64 @@ struct obj_attrib {
     std::vector<float> vertices, normals, texcoords;
 };
 
-inline int fix_index(int idx, int n) {
-    if (idx > 0) return idx - 1;
-    if (idx == 0) return -1;
-    return n + idx;
+inline int fix_index(int idx, int n) {   // tiny_obj_loader.h:800-822 (0 is rejected by the parser before this point)
+    return idx > 0 ? idx - 1 : n + idx;
+}
+
+// tinyobj's decimal parser restated (tryParseDouble): same operations in the same order, so the same binary64 value.
+bool tinyobj_parse_double(const char* s, const char* s_end, double* result) {
+    if (s >= s_end) return false;
+    static const double neg_pow10[] = {1.0, 0.1, 0.01, 0.001, 0.0001, 0.00001, 0.000001, 0.0000001};
+    auto digit = [](char c) { return (unsigned)(c - '0') < 10u; };
+    double mantissa = 0.0;
+    int exponent = 0;
+    bool negative = false, exp_negative = false, leading_dot = false;
+    const char* c = s;
+    if (*c == '+' || *c == '-') {
+        negative = *c == '-';
+        ++c;
+        if (c != s_end && *c == '.') leading_dot = true;
+    } else if (*c == '.') {
+        leading_dot = true;
+    } else if (!digit(*c)) {
+        return false;
+    }
+    int read = 0;
+    if (!leading_dot) {
+        for (; c != s_end && digit(*c); ++c, ++read) {
+            mantissa *= 10;
+            mantissa += (int)(*c - '0');
+        }
+        if (read == 0) return false;
+    }
+    if (c != s_end) {
+        bool more = true;
+        if (*c == '.') {
+            ++c;
+            for (read = 1; c != s_end && digit(*c); ++c, ++read)
+                mantissa += (int)(*c - '0') * (read < 8 ? neg_pow10[read] : std::pow(10.0, -read));
+        } else if (*c != 'e' && *c != 'E') {
+            more = false;
+        }
+        if (more && c != s_end && (*c == 'e' || *c == 'E')) {
+            ++c;
+            if (c != s_end && (*c == '+' || *c == '-')) {
+                exp_negative = *c == '-';
+                ++c;
+            } else if (c == s_end || !digit(*c)) {
+                return false;
+            }
+            for (read = 0; c != s_end && digit(*c); ++c, ++read) {
+                if (exponent > 2147483647 / 10) return false;
+                exponent *= 10;
+                exponent += (int)(*c - '0');
+            }
+            if (exp_negative) exponent = -exponent;
+            if (read == 0) return false;
+        }
+    }
+    *result = (negative ? -1 : 1) * (exponent ? std::ldexp(mantissa * std::pow(5.0, exponent), exponent) : mantissa);
+    return true;
 }
 
 // The file is cut into chunks at line ends and the chunks are parsed by concurrent threads (the
@@ -206,80 +269,118 @@ struct obj_chunk {
     std::vector<int> face_sizes;
     std::vector<int> face_counts;   // per face: vertices, normals, texcoords of the chunk seen before it
     std::vector<shape_break> breaks;
+    size_t lines = 0;               // line ends seen (for the line number of an error in a later chunk)
+    size_t bad_face_line = 0;       // 1-based line of the chunk whose `f` failed to parse, 0 = none
 };
 
 void parse_obj_chunk(const char* p, const char* end, obj_chunk& c) {
     auto is_sp = [](char ch) { return ch == ' ' || ch == '\t'; };
+    auto is_delim = [](char ch) { return ch == ' ' || ch == '\t' || ch == '\r'; };
+    // next blank-delimited token of the line as a float (parseReal, tiny_obj_loader.h:1012-1020)
+    auto real = [&](const char*& q, const char* eol) {
+        while (q < eol && is_sp(*q)) ++q;
+        const char* e = q;
+        while (e < eol && !is_delim(*e)) ++e;
+        double val = 0.0;
+        tinyobj_parse_double(q, e, &val);
+        q = e;
+        return (float)val;
+    };
+    // atoi on a bounded line: optional blanks, sign, digits; anything else reads as 0
+    auto integer = [&](const char* q, const char* eol) {
+        while (q < eol && (is_sp(*q) || *q == '\r' || *q == '\v' || *q == '\f')) ++q;
+        bool neg = false;
+        if (q < eol && (*q == '+' || *q == '-')) neg = *q++ == '-';
+        long v = 0;
+        for (; q < eol && (unsigned)(*q - '0') < 10u; ++q) v = v * 10 + (*q - '0');
+        return (int)(neg ? -v : v);
+    };
+    auto skip_index = [&](const char*& q, const char* eol) {   // token += strcspn(token, "/ \t\r")
+        while (q < eol && *q != '/' && !is_delim(*q)) ++q;
+    };
     while (p < end) {
-        const char* eol = (const char*)memchr(p, '\n', (size_t)(end - p));
-        if (!eol) eol = end;
+        const char* eol = p;
+        while (eol < end && *eol != '\n' && *eol != '\r') ++eol;
+        const char* next = eol < end ? eol + ((*eol == '\r' && eol + 1 < end && eol[1] == '\n') ? 2 : 1) : end;
+        ++c.lines;
         const char* q = p;
         while (q < eol && is_sp(*q)) ++q;
         if (q + 1 < eol && q[0] == 'v' && is_sp(q[1])) {
-            char* e;
             q += 2;
-            for (int k = 0; k < 3; ++k) {
-                c.vertices.push_back((float)strtod(q, &e));
-                q = e;
-            }
+            for (int k = 0; k < 3; ++k) c.vertices.push_back(real(q, eol));
         } else if (q + 2 < eol && q[0] == 'v' && q[1] == 'n' && is_sp(q[2])) {
-            char* e;
             q += 3;
-            for (int k = 0; k < 3; ++k) {
-                c.normals.push_back((float)strtod(q, &e));
-                q = e;
-            }
+            for (int k = 0; k < 3; ++k) c.normals.push_back(real(q, eol));
         } else if (q + 2 < eol && q[0] == 'v' && q[1] == 't' && is_sp(q[2])) {
-            char* e;
             q += 3;
-            for (int k = 0; k < 2; ++k) {
-                c.texcoords.push_back((float)strtod(q, &e));
-                q = e;
-            }
+            for (int k = 0; k < 2; ++k) c.texcoords.push_back(real(q, eol));
         } else if (q + 1 < eol && q[0] == 'f' && is_sp(q[1])) {
             q += 2;
+            while (q < eol && is_sp(*q)) ++q;
+            const size_t first = c.indices.size();
             int n = 0;
-            c.face_counts.push_back((int)c.vertices.size() / 3);
-            c.face_counts.push_back((int)c.normals.size() / 3);
-            c.face_counts.push_back((int)c.texcoords.size() / 2);
-            while (q < eol) {
-                while (q < eol && (is_sp(*q) || *q == '\r')) ++q;
-                if (q >= eol) break;
+            bool bad = false;
+            while (q < eol) {   // parseTriple, tiny_obj_loader.h:1136-1186
                 obj_chunk::raw_index ix;
-                char* e;
-                ix.v = (int)strtol(q, &e, 10);
-                q = e;
-                if (q < eol && *q == '/') {
+                ix.v = integer(q, eol);
+                bad |= ix.v == 0;
+                skip_index(q, eol);
+                if (!bad && q < eol && *q == '/') {
                     ++q;
                     if (q < eol && *q == '/') {
                         ++q;
-                        ix.vn = (int)strtol(q, &e, 10);
+                        ix.vn = integer(q, eol);
                         ix.has_vn = true;
-                        q = e;
+                        bad |= ix.vn == 0;
+                        skip_index(q, eol);
                     } else {
-                        ix.vt = (int)strtol(q, &e, 10);
+                        ix.vt = integer(q, eol);
                         ix.has_vt = true;
-                        q = e;
-                        if (q < eol && *q == '/') {
+                        bad |= ix.vt == 0;
+                        skip_index(q, eol);
+                        if (!bad && q < eol && *q == '/') {
                             ++q;
-                            ix.vn = (int)strtol(q, &e, 10);
+                            ix.vn = integer(q, eol);
                             ix.has_vn = true;
-                            q = e;
+                            bad |= ix.vn == 0;
+                            skip_index(q, eol);
                         }
                     }
                 }
+                if (bad) break;
                 c.indices.push_back(ix);
                 ++n;
+                while (q < eol && is_delim(*q)) ++q;
             }
-            c.face_sizes.push_back(n);
-        } else if (q + 1 < eol && (q[0] == 'o' || q[0] == 'g') && is_sp(q[1])) {
-            q += 2;
-            while (q < eol && is_sp(*q)) ++q;
-            const char* e = eol;
-            while (e > q && (e[-1] == '\r' || is_sp(e[-1]))) --e;
-            c.breaks.push_back({c.face_sizes.size(), std::string(q, e)});
+            if (bad) {
+                if (!c.bad_face_line) c.bad_face_line = c.lines;
+                c.indices.resize(first);
+            } else if (n >= 3) {   // "Degenerated face found": dropped by exportGroupsToShape (:1416-1424)
+                c.face_counts.push_back((int)c.vertices.size() / 3);
+                c.face_counts.push_back((int)c.normals.size() / 3);
+                c.face_counts.push_back((int)c.texcoords.size() / 2);
+                c.face_sizes.push_back(n);
+            } else {
+                c.indices.resize(first);
+            }
+        } else if (q + 1 < eol && q[0] == 'g' && is_sp(q[1])) {   // :2778-2827: words after the `g`, joined by one blank
+            std::string name;
+            const char* w = q + 1;
+            for (int words = 0;; ++words) {
+                while (w < eol && is_sp(*w)) ++w;
+                if (w >= eol) break;
+                const char* e = w;
+                while (e < eol && !is_delim(*e)) ++e;
+                if (words) name += ' ';
+                name.append(w, e);
+                w = e;
+                while (w < eol && is_delim(*w)) ++w;
+            }
+            c.breaks.push_back({c.face_sizes.size(), name});
+        } else if (q + 1 < eol && q[0] == 'o' && is_sp(q[1])) {   // :2830-2849: the rest of the line, verbatim
+            c.breaks.push_back({c.face_sizes.size(), std::string(q + 2, eol)});
         }
-        p = eol + 1;
+        p = next;
     }
 }
 
@@ -289,7 +390,7 @@ int obj_threads(size_t bytes) {
     return (int)std::max<size_t>(1, std::min<size_t>({by_size, (size_t)std::thread::hardware_concurrency(), (size_t)16}));
 }
 
-bool parse_obj(const std::string& path, obj_attrib& at, std::vector<obj_shape>& shapes, std::string& err) {
+bool parse_obj(const std::string& path, int threads, obj_attrib& at, std::vector<obj_shape>& shapes, std::string& err) {
     FILE* f = fopen(path.c_str(), "rb");
     if (!f) {
         err = "Cannot open file [" + path + "]";
@@ -309,7 +410,7 @@ bool parse_obj(const std::string& path, obj_attrib& at, std::vector<obj_shape>& 
         fclose(f);
     }
     // chunks: cut at the first line end at or after i * size / T
-    const int T = obj_threads(data.size());
+    const int T = threads > 0 ? threads : obj_threads(data.size());
     const char* base = data.c_str();
     const char* end = base + data.size();
     std::vector<const char*> cut((size_t)T + 1, end);
@@ -328,7 +429,14 @@ bool parse_obj(const std::string& path, obj_attrib& at, std::vector<obj_shape>& 
         for (auto& t : th) t.join();
     }
     // merge in file order
-    size_t tv = 0, tn = 0, tt = 0;
+    size_t tv = 0, tn = 0, tt = 0, lines_before = 0;
+    for (const obj_chunk& c : chunks) {
+        if (c.bad_face_line) {   // tiny_obj_loader.h:2664-2671; mesh_loader.cpp:99-101 turns it into a runtime_error
+            err = "Failed parse `f' line(e.g. zero value for face index. line " + std::to_string(lines_before + c.bad_face_line) + ".)\n";
+            return false;
+        }
+        lines_before += c.lines;
+    }
     for (const obj_chunk& c : chunks) {
         tv += c.vertices.size();
         tn += c.normals.size();
@@ -394,12 +502,18 @@ std::shared_ptr<mesh> create_mesh(const obj_shape& shape, const obj_attrib& at) 
             *it = (int32_t)(m->vertices.size() / 3);
             for (int k = 0; k < 3; ++k) m->vertices.push_back(at.vertices[3 * (size_t)ix.v + k]);
         }
-        if (ix.vn >= 0)
+        // tinyobj only warns about attribute indices past the end and the reference then reads out of bounds
+        // (mesh_loader.cpp:56-60, :69-72); here such a file is refused
+        if (ix.vn >= 0) {
+            if (3 * (size_t)ix.vn + 2 >= at.normals.size()) throw std::runtime_error("obj: normal index out of range");
             while (m->normals.size() < m->vertices.size())
                 for (int k = 0; k < 3; ++k) m->normals.push_back(at.normals[3 * (size_t)ix.vn + k]);
-        if (ix.vt >= 0)
+        }
+        if (ix.vt >= 0) {
+            if (2 * (size_t)ix.vt + 1 >= at.texcoords.size()) throw std::runtime_error("obj: texcoord index out of range");
             while (m->texcoords.size() / 2 < m->vertices.size() / 3)
                 for (int k = 0; k < 2; ++k) m->texcoords.push_back(at.texcoords[2 * (size_t)ix.vt + k]);
+        }
         return *it;
     };
     for (int fs : shape.face_sizes) {
@@ -417,11 +531,11 @@ std::shared_ptr<mesh> create_mesh(const obj_shape& shape, const obj_attrib& at) 
 }
 }  // namespace
 
-std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::string& obj_file) {  // mesh_loader.cpp:85-121
+std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::string& obj_file, int threads) {  // mesh_loader.cpp:85-121
     obj_attrib at;
     std::vector<obj_shape> shapes;
     std::string err;
-    if (!parse_obj(obj_file, at, shapes, err)) throw std::runtime_error(err);
+    if (!parse_obj(obj_file, threads, at, shapes, err)) throw std::runtime_error(err);
     // the shapes are independent: their vertex maps are built by concurrent threads, results keep the file order
     std::vector<std::pair<std::string, std::shared_ptr<mesh>>> out(shapes.size());
     std::atomic<size_t> next{0};
@@ -441,7 +555,7 @@ std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::s
     };
     size_t bytes = 0;
     for (const auto& sh : shapes) bytes += sh.indices.size() * sizeof(obj_index);
-    const int T = (int)std::min<size_t>((size_t)obj_threads(bytes * 4), std::max<size_t>(shapes.size(), 1));
+    const int T = (int)std::min<size_t>((size_t)(threads > 0 ? threads : obj_threads(bytes * 4)), std::max<size_t>(shapes.size(), 1));
     std::vector<std::thread> th;
     for (int i = 1; i < T; ++i) th.emplace_back(work);
     work();
@@ -503,51 +617,26 @@ void write_png(const std::string& file_path, int w, int h, const uint32_t* rgba)
     fclose(f);
 }
 
-static bool read_png(const std::string& path, image_buffer& img) {
-    std::ifstream f(path, std::ios::binary);
-    if (!f) return false;
-    std::vector<unsigned char> d((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
-    if (d.size() < 8 || memcmp(d.data(), "\x89PNG\r\n\x1a\n", 8) != 0) return false;
-    size_t p = 8;
-    int w = 0, h = 0, depth = 0, ctype = 0, interlace = 0;
-    std::vector<unsigned char> idat, plte, trns;
-    while (p + 8 <= d.size()) {
-        uint32_t n = be32(&d[p]);
-        std::string type((const char*)&d[p + 4], 4);
-        const unsigned char* body = &d[p + 8];
-        if (p + 12 + n > d.size()) return false;
-        if (type == "IHDR") {
-            w = (int)be32(body);
-            h = (int)be32(body + 4);
-            depth = body[8];
-            ctype = body[9];
-            interlace = body[12];
-        } else if (type == "IDAT")
-            idat.insert(idat.end(), body, body + n);
-        else if (type == "PLTE")
-            plte.assign(body, body + n);
-        else if (type == "tRNS")
-            trns.assign(body, body + n);
-        else if (type == "IEND")
-            break;
-        p += 12 + n;
-    }
-    if (w <= 0 || h <= 0 || interlace != 0 || (depth != 8 && depth != 16)) return false;
-    const int channels = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
-    if (!channels || (ctype == 3 && depth != 8)) return false;
-    const size_t bpp = (size_t)channels * depth / 8, stride = (size_t)w * bpp;
-    std::vector<unsigned char> raw((size_t)h * (stride + 1));
-    uLongf rl = (uLongf)raw.size();
-    if (uncompress(raw.data(), &rl, idat.data(), (uLong)idat.size()) != Z_OK || rl != raw.size()) return false;
-    std::vector<unsigned char> px((size_t)h * stride);
+// PNG decoder with the coverage and the conversions of stb_image (extern/stb/stb_image.h, the decoder behind the
+// reference's load_image): grey / RGB / palette / grey+alpha / RGBA, 1-16 bits, Adam7 interlace, tRNS (palette alpha,
+// colour key for grey and RGB).  Output is RGBA8 the way stbi_load(..., STBI_rgb_alpha) delivers it: grey below 8 bits
+// scaled by 255 / 85 / 17, 16-bit samples reduced to their high byte AFTER the colour key was applied on 16 bits.
+// Held to stb byte for byte by tests/test_ref_host.py.
+static bool png_unfilter(const unsigned char* in, size_t in_size, int w, int h, int channels, int depth,
+                         std::vector<unsigned char>& out, size_t& consumed) {
+    const size_t bits = (size_t)w * channels * depth, stride = (bits + 7) / 8;
+    const size_t bpp = std::max<size_t>(1, (size_t)channels * depth / 8);
+    if (in_size < (stride + 1) * (size_t)h) return false;
+    out.assign(stride * (size_t)h, 0);
     for (int y = 0; y < h; ++y) {
-        const unsigned char* in = &raw[(size_t)y * (stride + 1)];
-        unsigned char* out = &px[(size_t)y * stride];
-        const unsigned char* up = y ? out - stride : nullptr;
-        const int ft = in[0];
+        const unsigned char* src = in + (size_t)y * (stride + 1);
+        unsigned char* row = &out[(size_t)y * stride];
+        const unsigned char* up = y ? row - stride : nullptr;
+        const int ft = src[0];
+        if (ft > 4) return false;
         for (size_t i = 0; i < stride; ++i) {
-            const int a = i >= bpp ? out[i - bpp] : 0, b = up ? up[i] : 0, c = (up && i >= bpp) ? up[i - bpp] : 0;
-            int v = in[1 + i];
+            const int a = i >= bpp ? row[i - bpp] : 0, b = up ? up[i] : 0, c = (up && i >= bpp) ? up[i - bpp] : 0;
+            int v = src[1 + i];
             switch (ft) {
                 case 1: v += a; break;
                 case 2: v += b; break;
@@ -559,26 +648,145 @@ static bool read_png(const std::string& path, image_buffer& img) {
                 }
                 default: break;
             }
-            out[i] = (unsigned char)v;
+            row[i] = (unsigned char)v;
         }
     }
+    consumed = (stride + 1) * (size_t)h;
+    return true;
+}
+
+// sample k of a packed row (depth 1, 2, 4, 8 or 16 bits, big endian)
+static inline unsigned png_sample(const unsigned char* row, size_t k, int depth) {
+    if (depth == 8) return row[k];
+    if (depth == 16) return ((unsigned)row[2 * k] << 8) | row[2 * k + 1];
+    const size_t bit = k * (size_t)depth;
+    return (row[bit >> 3] >> (8 - depth - (int)(bit & 7))) & ((1u << depth) - 1u);
+}
+
+static bool read_png(const std::string& path, image_buffer& img) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) return false;
+    std::vector<unsigned char> d((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    if (d.size() < 8 || memcmp(d.data(), "\x89PNG\r\n\x1a\n", 8) != 0) return false;
+    size_t p = 8;
+    int w = 0, h = 0, depth = 0, ctype = 0, interlace = 0;
+    std::vector<unsigned char> idat, plte, trns;
+    while (p + 8 <= d.size()) {
+        const uint32_t n = be32(&d[p]);
+        const std::string type((const char*)&d[p + 4], 4);
+        if (p + 12 + (size_t)n > d.size()) return false;
+        const unsigned char* body = &d[p + 8];
+        if (type == "IHDR") {
+            if (n != 13) return false;
+            w = (int)be32(body);
+            h = (int)be32(body + 4);
+            depth = body[8];
+            ctype = body[9];
+            interlace = body[12];
+            if (body[10] != 0 || body[11] != 0) return false;
+        } else if (type == "IDAT")
+            idat.insert(idat.end(), body, body + n);
+        else if (type == "PLTE")
+            plte.assign(body, body + n);
+        else if (type == "tRNS")
+            trns.assign(body, body + n);
+        else if (type == "IEND")
+            break;
+        p += 12 + (size_t)n;
+    }
+    if (w <= 0 || h <= 0 || interlace > 1) return false;
+    if (depth != 1 && depth != 2 && depth != 4 && depth != 8 && depth != 16) return false;
+    const int channels = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
+    if (!channels) return false;
+    if (ctype == 3 && (depth == 16 || plte.empty())) return false;
+    if ((ctype == 2 || ctype == 4 || ctype == 6) && depth < 8) return false;
+
+    // inflate: the size is known from the header (per pass when interlaced)
+    static const int px0[7] = {0, 4, 0, 2, 0, 1, 0}, py0[7] = {0, 0, 4, 0, 2, 0, 1};
+    static const int pdx[7] = {8, 8, 4, 4, 2, 2, 1}, pdy[7] = {8, 8, 8, 4, 4, 2, 2};
+    auto row_bytes = [&](int pw) { return ((size_t)pw * channels * depth + 7) / 8 + 1; };
+    size_t raw_size = 0;
+    if (interlace)
+        for (int k = 0; k < 7; ++k) {
+            const int pw = (w - px0[k] + pdx[k] - 1) / pdx[k], ph = (h - py0[k] + pdy[k] - 1) / pdy[k];
+            if (pw > 0 && ph > 0) raw_size += row_bytes(pw) * (size_t)ph;
+        }
+    else
+        raw_size = row_bytes(w) * (size_t)h;
+    std::vector<unsigned char> raw(raw_size);
+    uLongf rl = (uLongf)raw.size();
+    const int zr = uncompress(raw.data(), &rl, idat.data(), (uLong)idat.size());
+    if ((zr != Z_OK && zr != Z_BUF_ERROR) || rl != raw.size()) return false;
+
+    // samples of the whole image, 16 bits each
+    std::vector<uint16_t> smp((size_t)w * h * channels);
+    std::vector<unsigned char> rows;
+    if (!interlace) {
+        size_t used = 0;
+        if (!png_unfilter(raw.data(), raw.size(), w, h, channels, depth, rows, used)) return false;
+        const size_t stride = ((size_t)w * channels * depth + 7) / 8;
+        for (int y = 0; y < h; ++y)
+            for (size_t k = 0; k < (size_t)w * channels; ++k)
+                smp[(size_t)y * w * channels + k] = (uint16_t)png_sample(&rows[(size_t)y * stride], k, depth);
+    } else {
+        size_t off = 0;
+        for (int k = 0; k < 7; ++k) {
+            const int pw = (w - px0[k] + pdx[k] - 1) / pdx[k], ph = (h - py0[k] + pdy[k] - 1) / pdy[k];
+            if (pw <= 0 || ph <= 0) continue;
+            size_t used = 0;
+            if (!png_unfilter(raw.data() + off, raw.size() - off, pw, ph, channels, depth, rows, used)) return false;
+            off += used;
+            const size_t stride = ((size_t)pw * channels * depth + 7) / 8;
+            for (int j = 0; j < ph; ++j)
+                for (int i = 0; i < pw; ++i) {
+                    const size_t dst = ((size_t)(py0[k] + j * pdy[k]) * w + (size_t)(px0[k] + i * pdx[k])) * channels;
+                    for (int c = 0; c < channels; ++c)
+                        smp[dst + c] = (uint16_t)png_sample(&rows[(size_t)j * stride], (size_t)i * channels + c, depth);
+                }
+        }
+    }
+
     img.width = w;
     img.height = h;
     img.pixels.resize((size_t)w * h);
-    const size_t step = depth / 8;
+    // 16 -> 8 bits: high byte; below 8 bits grey is scaled to the full range (palette indices are not)
+    const unsigned scale = depth == 1 ? 255u : depth == 2 ? 85u : depth == 4 ? 17u : 1u;
+    auto to8 = [&](unsigned v) { return depth == 16 ? (v >> 8) & 255u : v; };
+    // colour key (tRNS of grey / RGB): compared on the stored sample width
+    unsigned key[3] = {0, 0, 0};
+    const bool has_key = (ctype == 0 && trns.size() >= 2) || (ctype == 2 && trns.size() >= 6);
+    if (has_key)
+        for (int c = 0; c < channels; ++c) {
+            const unsigned v = ((unsigned)trns[2 * (size_t)c] << 8) | trns[2 * (size_t)c + 1];
+            key[c] = depth == 16 ? v : (v & 255u) * scale;
+        }
     for (size_t i = 0; i < (size_t)w * h; ++i) {
-        const unsigned char* s = &px[i * bpp];
+        const uint16_t* s = &smp[i * channels];
         unsigned r, g, b, a = 255;
-        if (ctype == 0) { r = g = b = s[0]; }
-        else if (ctype == 2) { r = s[0]; g = s[step]; b = s[2 * step]; }
-        else if (ctype == 3) {
-            const unsigned k = s[0];
+        if (ctype == 0) {
+            const unsigned v = depth < 8 ? s[0] * scale : s[0];
+            if (has_key && v == key[0]) a = 0;
+            r = g = b = to8(v);
+        } else if (ctype == 2) {
+            if (has_key && s[0] == key[0] && s[1] == key[1] && s[2] == key[2]) a = 0;
+            r = to8(s[0]);
+            g = to8(s[1]);
+            b = to8(s[2]);
+        } else if (ctype == 3) {
+            const size_t k = s[0];
             r = 3 * k + 2 < plte.size() ? plte[3 * k] : 0;
             g = 3 * k + 2 < plte.size() ? plte[3 * k + 1] : 0;
             b = 3 * k + 2 < plte.size() ? plte[3 * k + 2] : 0;
             a = k < trns.size() ? trns[k] : 255;
-        } else if (ctype == 4) { r = g = b = s[0]; a = s[step]; }
-        else { r = s[0]; g = s[step]; b = s[2 * step]; a = s[3 * step]; }
+        } else if (ctype == 4) {
+            r = g = b = to8(s[0]);
+            a = to8(s[1]);
+        } else {
+            r = to8(s[0]);
+            g = to8(s[1]);
+            b = to8(s[2]);
+            a = to8(s[3]);
+        }
         img.pixels[i] = r | (g << 8) | (b << 16) | (a << 24);
     }
     return true;
@@ -650,10 +858,13 @@ static bool read_hdr_rgbe(const std::string& path, int& w_out, int& h_out, std::
                 if (fread(hd, 1, 4, f) != 4) { ok = false; break; }
                 unsigned char* row = &rgbe[(size_t)y * w * 4];
                 if (w < 8 || w >= 32768 || hd[0] != 2 || hd[1] != 2 || (hd[2] & 0x80)) {
-                    // flat data: this scanline (and, as in stb, the rest of the file) is raw RGBE
-                    memcpy(row, hd, 4);
-                    size_t rest = ((size_t)w * (h - y) - 1) * 4;
-                    if (fread(row + 4, 1, rest, f) != rest) ok = false;
+                    // not run-length encoded: stb (stbi__hdr_load, "yes, this makes no sense") takes these four bytes as
+                    // pixel 0 OF THE IMAGE and reads everything after them as flat RGBE from pixel 1 on, whatever the
+                    // scanline it met them in; bytes past the end of the file read as 0
+                    memcpy(&rgbe[0], hd, 4);
+                    const size_t rest = ((size_t)w * h - 1) * 4;
+                    const size_t got = fread(&rgbe[4], 1, rest, f);
+                    if (got < rest) memset(&rgbe[4 + got], 0, rest - got);
                     break;
                 }
                 if (((hd[2] << 8) | hd[3]) != w) { ok = false; break; }
@@ -759,15 +970,26 @@ image_buffer load_image(const std::string& name, const std::string& path) {  // 
         say("Image file %s does not exist. Continue with empty.\n", file_path.c_str());
         return img;
     }
-    bool ok = false;
-    if (file_path.size() > 4 && file_path.substr(file_path.size() - 4) == ".hdr")
-        ok = read_hdr(file_path, img);
-    else
-        ok = read_png(file_path, img);
-    if (!ok) {
-        say("Image file %s could not be decoded. Continue with empty.\n", file_path.c_str());
-        return image_buffer{};
+    // stbi_load decides by content, not by extension: Radiance files start with "#?RADIANCE" / "#?RGBE", PNG with its
+    // signature.  stb also reads JPEG / BMP / TGA / GIF / PSD / PIC / PNM, which this loader does not: such a file is an
+    // error here, never a silent stand-in.
+    unsigned char magic[10] = {0};
+    {
+        FILE* f = fopen(file_path.c_str(), "rb");
+        if (f) {
+            const size_t got = fread(magic, 1, sizeof magic, f);
+            (void)got;
+            fclose(f);
+        }
     }
+    bool ok = false;
+    if (memcmp(magic, "#?RADIANCE", 10) == 0 || memcmp(magic, "#?RGBE", 6) == 0)
+        ok = read_hdr(file_path, img);
+    else if (memcmp(magic, "\x89PNG\r\n\x1a\n", 8) == 0)
+        ok = read_png(file_path, img);
+    else
+        throw std::runtime_error("unsupported image format (PNG and Radiance .hdr are read): " + file_path);
+    if (!ok) throw std::runtime_error("image file could not be decoded: " + file_path);
     flip_rows(img);
     return img;
 }

@@ -11,7 +11,8 @@ camera_data to_camera_data(const camera& c, int width, int height);            /
 settings_data parse_settings(const std::string& path);                         // parser.cpp:81-117
 camera parse_camera(const std::string& path);                                  // parser.cpp:65-79
 std::vector<material_entry> parse_materials(const std::string& path);          // parser.cpp:19-63
-std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::string& obj_file);  // mesh_loader.cpp:85-121
+// threads: 0 = by file size (B200PT_OBJ_THREADS overrides), n = n chunks
+std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::string& obj_file, int threads = 0);  // mesh_loader.cpp:85-121
 image_buffer load_image(const std::string& name, const std::string& path);     // image_buffer.cpp:36-59 (v-flipped)
 void write_image(const image_buffer& i, const std::string& name, const std::string& path);  // image_buffer.cpp:25-34
 void write_png(const std::string& file_path, int w, int h, const uint32_t* rgba);
