@@ -23,7 +23,7 @@ CUHDR = $(wildcard $(CSRC)/*.h) $(wildcard $(CSRC)/*.cuh) include/b200pt.h
 HOSTHDR = $(wildcard $(HOST)/*.hpp) include/b200pt.h include/b200pt_host.h
 
 all: product oracle emu ref
-product: $(LIB)/libb200pt.so $(LIB)/libb200pt_host.so $(BIN)/path_tracer
+product: $(LIB)/libb200pt.so $(LIB)/libb200pt_scene.so $(LIB)/libb200pt_host.so $(BIN)/path_tracer
 
 $(LIB)/%.o: $(CSRC)/%.cu $(CUHDR)
 	@mkdir -p $(LIB)
@@ -32,13 +32,20 @@ $(LIB)/%.o: $(CSRC)/%.cu $(CUHDR)
 $(LIB)/libb200pt.so: $(LIB)/api.o $(LIB)/wavefront.o $(LIB)/bvh_build.o
 	$(NVCC) -shared -cudart static -gencode arch=compute_100a,code=sm_100a -o $@ $^
 
-HOSTSRC = $(HOST)/loaders.cpp $(HOST)/procedural.cpp $(HOST)/application.cpp $(HOST)/host_api.cpp
-$(LIB)/libb200pt_host.so: $(HOSTSRC) $(HOSTHDR) $(LIB)/libb200pt.so
-	$(CXX) $(CXXFLAGS) -shared -o $@ $(HOSTSRC) -L$(LIB) -lb200pt -lz -Wl,-rpath,'$$ORIGIN'
+# libb200pt_scene.so: loaders + scene stages, NO CUDA dependency (CPU-only processes load scenes through it);
+# libb200pt_host.so: bind / render / test_loop on top of it and of libb200pt.so
+SCENESRC = $(HOST)/loaders.cpp $(HOST)/procedural.cpp $(HOST)/scene_load.cpp $(HOST)/scene_api.cpp
+$(LIB)/libb200pt_scene.so: $(SCENESRC) $(HOSTHDR)
+	@mkdir -p $(LIB)
+	$(CXX) $(CXXFLAGS) -shared -o $@ $(SCENESRC) -lz
+
+HOSTSRC = $(HOST)/application.cpp $(HOST)/host_api.cpp
+$(LIB)/libb200pt_host.so: $(HOSTSRC) $(HOSTHDR) $(LIB)/libb200pt.so $(LIB)/libb200pt_scene.so
+	$(CXX) $(CXXFLAGS) -shared -o $@ $(HOSTSRC) -L$(LIB) -lb200pt_scene -lb200pt -Wl,-rpath,'$$ORIGIN'
 
 $(BIN)/path_tracer: $(HOST)/main.cpp $(LIB)/libb200pt_host.so
 	@mkdir -p $(BIN)
-	$(CXX) $(CXXFLAGS) -fPIE -o $@ $(HOST)/main.cpp -L$(LIB) -lb200pt_host -lb200pt -Wl,-rpath,'$$ORIGIN/../lib'
+	$(CXX) $(CXXFLAGS) -fPIE -o $@ $(HOST)/main.cpp -L$(LIB) -lb200pt_host -lb200pt_scene -lb200pt -Wl,-rpath,'$$ORIGIN/../lib'
 
 oracle:
 	$(MAKE) -C oracle

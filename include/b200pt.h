@@ -198,6 +198,26 @@ int b200pt_render(b200pt_ctx* ctx);
 int b200pt_accum_buffer(b200pt_ctx* ctx, void** device_ptr, size_t* n_floats);
 int b200pt_resolve(b200pt_ctx* ctx);
 
+/* ---- the frame's collective inside the library (NCCL over NVLink / NVSwitch).
+ * Reference: the OWL runtime fans one launch over the devices of a context (extern/owl/owl/RayGen.cpp:140-146; the
+ * reference asks for one device, application.cpp:62).  Here a job is world_size contexts (rank r, one GPU each),
+ * in one process or one per process; samples are sharded over ranks and ONE ncclReduce of the float4 sums per
+ * frame brings them to rank 0.  libnccl.so.2 is opened on first use (the copy a host process already loaded
+ * is reused), so single-GPU users never need it.
+ *   one process per rank:  rank 0 calls b200pt_comm_unique_id, ships the 128 bytes to the others by any means,
+ *                          every rank calls b200pt_comm_init_rank, then b200pt_render_frame per frame.
+ *   one process, n GPUs:   b200pt_comm_init_all(ctxs, n) once, b200pt_render_frame_all(ctxs, n) per frame
+ *                          (one host thread per rank inside the call). */
+#define B200PT_COMM_ID_BYTES 128
+int b200pt_comm_unique_id(void* id_out /* B200PT_COMM_ID_BYTES */);
+int b200pt_comm_init_rank(b200pt_ctx* ctx, const void* id /* B200PT_COMM_ID_BYTES */);
+int b200pt_comm_init_all(b200pt_ctx* const* ctxs, int32_t n);   /* ctxs[r] must be rank r of world_size n */
+/* in-place sum of every rank's b200pt_accum_buffer into rank 0's; blocking on the context's stream */
+int b200pt_reduce(b200pt_ctx* ctx);
+/* render this rank's share + b200pt_reduce + (rank 0) b200pt_resolve.  Collective: every rank calls it. */
+int b200pt_render_frame(b200pt_ctx* ctx);
+int b200pt_render_frame_all(b200pt_ctx* const* ctxs, int32_t n);
+
 /* ---- Progressive surface (the reference renders a frame in one blocking launch and has none of
  * this — opt-in, the entry points above are unchanged) -------------------------------------------------
  *

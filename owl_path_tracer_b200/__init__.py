@@ -3,10 +3,10 @@
 Two shared libraries are bound, both built in-tree by ``make product``:
 
 * ``lib/libb200pt.so``       the CUDA path behind the C ABI of ``include/b200pt.h``
-* ``lib/libb200pt_host.so``  the host application stages (``include/b200pt_host.h``):
-  settings / scene / OBJ / HDR loading, camera, material sweep, PNG output — the same
-  code the ``bin/path_tracer`` executable runs (reference: path_tracer/Main.cpp,
-  path_tracer/src/application.cpp).
+* ``lib/libb200pt_scene.so`` the host stages that never touch the device (``include/b200pt_host.h``): settings /
+  scene / OBJ / HDR loading, camera, material sweep, PNG output (no CUDA dependency)
+* ``lib/libb200pt_host.so``  bind / render / test_loop on top of the two — the same code the ``bin/path_tracer``
+  executable runs (reference: path_tracer/Main.cpp, path_tracer/src/application.cpp).
 
 There is no CPU fallback here: ``Context()`` raises when the CUDA library is missing or no
 sm_100 device is usable.  The scalar oracle lives under ``oracle/`` and is only ever
@@ -100,13 +100,21 @@ class EntityView(C.Structure):
 
 
 _libs = {}
+_overrides = {}
+
+
+def use_library(path, name="libb200pt.so"):
+    """Bind a variant build of a library (tools/ab*.py) instead of lib/<name>.  Must be called before first use."""
+    if name in _libs:
+        raise B200ptError(f"{name} is already loaded")
+    _overrides[name] = Path(path)
 
 
 def _load(name: str) -> C.CDLL:
     if name not in _libs:
         path = LIB_DIR / name
-        if name == "libb200pt.so" and os.environ.get("B200PT_LIB"):   # A/B builds (tools/build_variants.sh)
-            path = Path(os.environ["B200PT_LIB"])
+        if name in _overrides:   # A/B builds: use_library() called explicitly by a tool, never the ambient environment
+            path = _overrides[name]
         if not path.exists():
             raise B200ptError(f"{path} is missing: run `make product` (or __graft_entry__.build()); "
                               "there is no CPU fallback for the render path")
@@ -154,11 +162,33 @@ def lib() -> C.CDLL:
 
 
 def host_lib() -> C.CDLL:
-    """libb200pt_host.so with argument types set (pulls in libb200pt.so)."""
+    """libb200pt_host.so (bind / render / test_loop; pulls in libb200pt.so and libb200pt_scene.so) with argument types
+    set.  Every symbol of include/b200pt_host.h resolves through it."""
     lib()
+    scene_lib()
     H = _load("libb200pt_host.so")
     if getattr(H, "_typed", False):
         return H
+    _type_scene_api(H)
+    P = C.c_void_p
+    H.b200pt_scene_bind.argtypes = [P, P]
+    H.b200pt_scene_test_loop.argtypes = [P, P, C.c_char_p]
+    H._typed = True
+    return H
+
+
+def scene_lib() -> C.CDLL:
+    """libb200pt_scene.so: scene loading, the loaders stage by stage, image / OBJ writers.  Does NOT map the CUDA library,
+    so CPU-only processes (bench.py --impl reference, the oracle tests) stay free of the product's device code."""
+    S = _load("libb200pt_scene.so")
+    if getattr(S, "_typed", False):
+        return S
+    _type_scene_api(S)
+    S._typed = True
+    return S
+
+
+def _type_scene_api(H):
     P = C.c_void_p
     H.b200pt_host_last_error.restype = C.c_char_p
     H.b200pt_scene_load.argtypes = [C.c_char_p, C.POINTER(LoadOptions), C.POINTER(P)]
@@ -173,8 +203,6 @@ def host_lib() -> C.CDLL:
     H.b200pt_scene_note.restype = C.c_char_p
     H.b200pt_scene_set_material_attr.argtypes = [P, C.c_char_p, C.c_char_p, C.c_float]
     H.b200pt_scene_set_material_color.argtypes = [P, C.c_char_p, P]
-    H.b200pt_scene_bind.argtypes = [P, P]
-    H.b200pt_scene_test_loop.argtypes = [P, P, C.c_char_p]
     H.b200pt_write_png.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
     H.b200pt_write_pfm.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
     H.b200pt_write_obj.argtypes = [P, C.c_char_p]
@@ -195,8 +223,6 @@ def host_lib() -> C.CDLL:
     H.b200pt_materials_data.argtypes = [P, C.c_int32]
     H.b200pt_materials_data.restype = P
     H.b200pt_materials_free.argtypes = [P]
-    H._typed = True
-    return H
 
 
 def _ptr(a):
@@ -215,4 +241,4 @@ from ._scene import Scene  # noqa: E402
 from ._context import Context  # noqa: E402
 
 __all__ = ["Scene", "Context", "Config", "Stats", "B200ptError", "MATERIAL_DTYPE", "HIT_DTYPE",
-           "SHARD_SPP", "SHARD_ROWS", "FLAG_COUNTERS", "FLAG_TIMING", "FLAG_NEE", "lib", "host_lib", "ASSETS_DIR"]
+           "SHARD_SPP", "SHARD_ROWS", "FLAG_COUNTERS", "FLAG_TIMING", "FLAG_NEE", "lib", "host_lib", "scene_lib", "use_library", "ASSETS_DIR"]

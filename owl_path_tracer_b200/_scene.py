@@ -5,7 +5,7 @@ import ctypes as C
 
 import numpy as np
 
-from . import (ASSETS_DIR, B200ptError, EntityView, LoadOptions, MATERIAL_DTYPE, SceneInfo, _view, host_lib)
+from . import (ASSETS_DIR, B200ptError, EntityView, LoadOptions, MATERIAL_DTYPE, SceneInfo, _view, scene_lib)
 
 
 class Scene:
@@ -17,7 +17,7 @@ class Scene:
 
     def __init__(self, assets=None, scene=None, width=0, height=0, spp=0, depth=0, env=None,
                  env_intensity=-1.0, detail=0, allow_procedural=True, env_float=False):
-        H = host_lib()
+        H = scene_lib()   # no CUDA library behind this one
         opt = LoadOptions()
         opt.scene = scene.encode() if scene else None
         opt.width, opt.height = int(width), int(height)

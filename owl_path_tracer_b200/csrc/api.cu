@@ -1,8 +1,13 @@
 // api.cu — implementation of the C ABI declared in include/b200pt.h.
 // No CPU fallback: without a usable CUDA device b200pt_create fails.
+#include <dlfcn.h>
+#include <nccl.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
+#include <thread>
 
 #include "device_ctx.h"
 #include "pt_lights.h"
@@ -32,6 +37,7 @@ static int fail(int code, const std::string& msg) {
 
 struct b200pt_ctx {
     b200pt_config cfg{};
+    ncclComm_t comm = nullptr;   // b200pt_comm_init_rank / b200pt_comm_init_all
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // parts of the frame walked concurrently (render_local); part 0 runs on `stream`
@@ -92,6 +98,7 @@ struct b200pt_ctx {
     float* h_mean = nullptr;     // pinned
     size_t fb_pixels = 0;
     bool rendered = false, resolved = false;
+    bool mean_on_host = false;   // h_mean holds the float frame of the last resolve
     // progressive passes (b200pt_render_pass): samples of every pixel already in `sum`; 0 = no frame in progress
     int l2_persist_mode = 0;    // B200PT_L2_PERSIST experiment (render_local)
     int pass_done = 0;
@@ -214,6 +221,8 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     return sv;
 }
 
+static void comm_release(b200pt_ctx* c);
+
 extern "C" int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     if (!cfg || !out) return fail(B200PT_ERR_INVALID, "b200pt_create: null argument");
     if (cfg->world_size < 1 || cfg->rank < 0 || cfg->rank >= cfg->world_size)
@@ -248,6 +257,7 @@ extern "C" int b200pt_destroy(b200pt_ctx* c) {
     if (!c) return B200PT_OK;
     cudaSetDevice(c->cfg.device_ordinal);
     cudaDeviceSynchronize();
+    comm_release(c);
     free_lanes(c);
     free_scene(c);
     cudaFree(c->d_env);
@@ -908,11 +918,22 @@ extern "C" int b200pt_resolve(b200pt_ctx* c) {
     const float inv = 1.0f / static_cast<float>(c->resolve_samples);  // device.cu:247 (max_samples for a complete frame)
     launch_resolve(full, src, inv, c->transfer, c->d_rgba, c->d_mean, c->stream);
     c->stats.kernel_launches++;
+    // the product of a frame is the RGBA8 image (8.3 MB at 1080p); the float frame (33 MB) crosses PCIe only when
+    // somebody asks for it (b200pt_framebuffer_f32, progressive callbacks)
     CU(cudaMemcpyAsync(c->h_rgba, c->d_rgba, sizeof(uint32_t) * c->fb_pixels, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaMemcpyAsync(c->h_mean, c->d_mean, sizeof(f4) * c->fb_pixels, cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
     c->resolved = true;
+    c->mean_on_host = false;
+    return B200PT_OK;
+}
+
+static int fetch_mean(b200pt_ctx* c) {
+    if (c->mean_on_host) return B200PT_OK;
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    CU(cudaMemcpyAsync(c->h_mean, c->d_mean, sizeof(f4) * c->fb_pixels, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->mean_on_host = true;
     return B200PT_OK;
 }
 
@@ -1009,7 +1030,10 @@ extern "C" int b200pt_render_progressive(b200pt_ctx* c, int32_t pass_samples, do
         const bool converged = target_rel_variance > 0.0 && info.samples_done > 1 && info.rel_variance <= target_rel_variance;
         if (converged) info.stopped_early = info.complete ? 0 : 1;
         int stop = 0;
-        if (on_pass) stop = on_pass(user, &info, c->h_rgba, c->h_mean);
+        if (on_pass) {
+            if (int r = fetch_mean(c)) return r;
+            stop = on_pass(user, &info, c->h_rgba, c->h_mean);
+        }
         if (info.complete || converged || stop) break;
     }
     if (last) *last = info;
@@ -1043,6 +1067,7 @@ extern "C" int b200pt_framebuffer_rgba8(b200pt_ctx* c, const uint32_t** out) {
 extern "C" int b200pt_framebuffer_f32(b200pt_ctx* c, const float** out) {
     if (!c || !out) return fail(B200PT_ERR_INVALID, "framebuffer: null");
     if (!c->resolved) return fail(B200PT_ERR_INVALID, "framebuffer: no resolved frame");
+    if (int r = fetch_mean(c)) return r;
     *out = c->h_mean;
     return B200PT_OK;
 }
@@ -1169,5 +1194,139 @@ extern "C" int b200pt_export_bvh(b200pt_ctx* c, void* nodes, uint32_t* n_nodes, 
     if (n_tris) *n_tris = c->bvh.n_tris;
     if (nodes) CU(cudaMemcpy(nodes, c->bvh.nodes, sizeof(Node8) * (size_t)c->bvh.n_nodes, cudaMemcpyDeviceToHost));
     if (tris) CU(cudaMemcpy(tris, c->bvh.tris, sizeof(TriPair) * (size_t)c->bvh.n_tris, cudaMemcpyDeviceToHost));
+    return B200PT_OK;
+}
+
+// ---------------------------------------------------------------------------- the frame's collective (NCCL)
+// libnccl.so.2 is opened on first use: single-GPU users never need it, and inside a process that already carries a
+// copy (torch bundles one) dlopen by soname hands back that copy instead of loading a second one.
+namespace {
+struct NcclApi {
+    void* handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    std::string error;
+};
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        api.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!api.handle) {
+            api.error = std::string("libnccl.so.2 cannot be loaded: ") + dlerror();
+            return;
+        }
+        auto sym = [&](const char* name) {
+            void* p = dlsym(api.handle, name);
+            if (!p && api.error.empty()) api.error = std::string("libnccl.so.2 lacks ") + name;
+            return p;
+        };
+        api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+        api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+        api.CommInitAll = reinterpret_cast<decltype(api.CommInitAll)>(sym("ncclCommInitAll"));
+        api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+        api.Reduce = reinterpret_cast<decltype(api.Reduce)>(sym("ncclReduce"));
+        api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+    });
+    return &api;
+}
+}  // namespace
+#define NC(x)                                                                                                  \
+    do {                                                                                                       \
+        ncclResult_t r_ = (x);                                                                                 \
+        if (r_ != ncclSuccess) return fail(B200PT_ERR_CUDA, std::string(#x) + ": " + nccl_api()->GetErrorString(r_)); \
+    } while (0)
+
+static void comm_release(b200pt_ctx* c) {
+    if (c->comm) {
+        nccl_api()->CommDestroy(c->comm);
+        c->comm = nullptr;
+    }
+}
+
+static int nccl_ready() {
+    NcclApi* a = nccl_api();
+    if (!a->error.empty()) return fail(B200PT_ERR_CUDA, a->error);
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_comm_unique_id(void* id_out) {
+    static_assert(sizeof(ncclUniqueId) == B200PT_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+    if (!id_out) return fail(B200PT_ERR_INVALID, "comm_unique_id: null");
+    if (int r = nccl_ready()) return r;
+    ncclUniqueId id;
+    NC(nccl_api()->GetUniqueId(&id));
+    memcpy(id_out, &id, sizeof id);
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_comm_init_rank(b200pt_ctx* c, const void* id_in) {
+    if (!c || !id_in) return fail(B200PT_ERR_INVALID, "comm_init_rank: null");
+    if (int r = nccl_ready()) return r;
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    comm_release(c);
+    ncclUniqueId id;
+    memcpy(&id, id_in, sizeof id);
+    NC(nccl_api()->CommInitRank(&c->comm, c->cfg.world_size, id, c->cfg.rank));
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_comm_init_all(b200pt_ctx* const* ctxs, int32_t n) {
+    if (!ctxs || n < 1) return fail(B200PT_ERR_INVALID, "comm_init_all: null / empty");
+    if (int r = nccl_ready()) return r;
+    std::vector<int> devs((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        if (!ctxs[i] || ctxs[i]->cfg.rank != i || ctxs[i]->cfg.world_size != n)
+            return fail(B200PT_ERR_INVALID, "comm_init_all: ctxs[r] must be rank r of world_size n");
+        for (int j = 0; j < i; ++j)
+            if (ctxs[j]->cfg.device_ordinal == ctxs[i]->cfg.device_ordinal)
+                return fail(B200PT_ERR_INVALID, "comm_init_all: two ranks on one device");
+        devs[(size_t)i] = ctxs[i]->cfg.device_ordinal;
+        comm_release(ctxs[i]);
+    }
+    std::vector<ncclComm_t> comms((size_t)n);
+    NC(nccl_api()->CommInitAll(comms.data(), n, devs.data()));
+    for (int i = 0; i < n; ++i) ctxs[i]->comm = comms[(size_t)i];
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_reduce(b200pt_ctx* c) {
+    if (!c || !c->rendered) return fail(B200PT_ERR_INVALID, "reduce: nothing rendered");
+    if (c->cfg.world_size == 1) return B200PT_OK;
+    if (!c->comm) return fail(B200PT_ERR_INVALID, "reduce: call b200pt_comm_init_rank / b200pt_comm_init_all first");
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    f4* buf = c->use_frame ? c->d_frame : c->la.sum;
+    NC(nccl_api()->Reduce(buf, buf, 4 * c->fb_pixels, ncclFloat, ncclSum, 0, c->comm, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_render_frame(b200pt_ctx* c) {
+    if (int r = check_ready(c, "render_frame")) return r;
+    if (int r = render_local(c)) return r;
+    if (c->cfg.world_size > 1)
+        if (int r = b200pt_reduce(c)) return r;
+    if (c->cfg.rank == 0) return b200pt_resolve(c);
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_render_frame_all(b200pt_ctx* const* ctxs, int32_t n) {
+    if (!ctxs || n < 1) return fail(B200PT_ERR_INVALID, "render_frame_all: null / empty");
+    if (n == 1) return b200pt_render_frame(ctxs[0]);
+    std::vector<int> status((size_t)n, B200PT_OK);
+    std::vector<std::string> message((size_t)n);
+    std::vector<std::thread> th;
+    for (int i = 0; i < n; ++i)
+        th.emplace_back([&, i] {
+            status[(size_t)i] = b200pt_render_frame(ctxs[i]);
+            if (status[(size_t)i] != B200PT_OK) message[(size_t)i] = g_error;   // g_error is thread-local
+        });
+    for (auto& t : th) t.join();
+    for (int i = 0; i < n; ++i)
+        if (status[(size_t)i] != B200PT_OK) return fail(status[(size_t)i], "rank " + std::to_string(i) + ": " + message[(size_t)i]);
     return B200PT_OK;
 }
