@@ -89,6 +89,31 @@ def cpu_oracle_rate(sample_spp, threads, steps=1, warmup=0):
     return rays / dt * 1e-6, dt / steps, rays // steps
 
 
+def parity_check(frame_f32, sc, world, window=(900, 500, 96, 64)):
+    """The frame that was timed, checked against the oracle (deterministic-math build: bit-comparable): a window of the
+    full frame at the full sample count under the run's (rank, world) keying.  N = 1: bit equality.  N > 1: NCCL's
+    summation order is not the oracle's rank order, so the gate is <= N ulp per channel plus relMSE <= 1e-3."""
+    import numpy as np
+    sys.path.insert(0, str(REPO / "tests"))
+    from checkers import Oracle, rel_mse
+    t0 = time.perf_counter()
+    x0, y0, w, h = window
+    x0, y0 = min(x0, max(0, sc.width - w)), min(y0, max(0, sc.height - h))
+    o = Oracle(det=True).load_scene(sc)
+    total = None
+    for r in range(world):
+        part = o.render(rank=r, world=world, shard_mode=0, window=(x0, y0, x0 + w, y0 + h), threads=host_cores())
+        part = part["sum"][y0:y0 + h, x0:x0 + w, :3]
+        total = part.copy() if total is None else total + part
+    want = total * (np.float32(1.0) / np.float32(sc.spp))
+    got = np.ascontiguousarray(frame_f32[::-1][y0:y0 + h, x0:x0 + w, :3])
+    gb, wb = got.view(np.int32).astype(np.int64), np.ascontiguousarray(want).view(np.int32).astype(np.int64)
+    ulp = int(np.abs(gb - wb).max())
+    return dict(window=[x0, y0, w, h], spp=sc.spp, ranks=world, oracle="oracle/liboracle_det.so (scalar restatement, pinned to "
+                "the reference's own device code by tests/test_ref_device.py)", bit_equal=bool((gb == wb).all()), max_ulp=ulp,
+                rel_mse=rel_mse(got, want), ok=bool(ulp <= (0 if world == 1 else world)), seconds=round(time.perf_counter() - t0, 2))
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -96,7 +121,8 @@ def run_reference(args):
     cores = host_cores()
     spp = 4   # bounded sample: ~4 s per step on 16 cores, so steps+warmup stay within minutes
     rate, sec, rays = cpu_oracle_rate(spp, cores, steps=args.steps, warmup=args.warmup)
-    sample = f"full 1920x1080 dragon frame at {spp} spp per step ({rays} rays), oracle with glibc math, {cores} threads"
+    sample = (f"full 1920x1080 dragon frame at {spp} spp per step ({rays} rays), oracle with glibc math, {cores} threads; "
+              "a scalar port over a median-split binary BVH, NOT a tuned CPU ray tracer")
     line = dict(impl="reference", metric="Mrays/s", value=rate, unit="Mrays/s", n_gpus=args.gpus, steps=args.steps,
                 warmup=args.warmup, ms_per_step=sec * 1e3, higher_is_better=True, scaling="strong", vs_baseline=None,
                 dtype="f32", data="synthetic", config=dict(workload=WORKLOAD_NAME, sample=sample),
@@ -127,6 +153,9 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (a smaller workload is NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity-check", action="store_true")
+    ap.add_argument("--detail", type=int, default=0, help="procedural mesh detail (0 = the 871,406-triangle headline stand-in; "
+                    "larger values are NOT the headline: they exist to push the BVH out of L2)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -135,7 +164,7 @@ def main():
     import torch
     import torch.distributed as dist
     import owl_path_tracer_b200 as pt
-    from owl_path_tracer_b200.distributed import accum_tensor, reduce_sum_to_rank0
+    from owl_path_tracer_b200.distributed import init_comm
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -148,10 +177,13 @@ def main():
     wl = dict(WORKLOAD)
     if args.spp:
         wl["spp"] = args.spp
+    if args.detail:
+        wl["detail"] = args.detail
 
     sc = pt.Scene(**wl)
     ctx = pt.Context(device=local, rank=rank, world_size=world, shard_mode=pt.SHARD_SPP, flags=0)
     ctx.bind(sc)
+    init_comm(ctx)      # the frame's reduce runs inside the library (ncclReduce in b200pt_render_frame)
     mats = sc.materials()
     frame_host = np.empty((sc.height, sc.width), np.uint32)
 
@@ -162,12 +194,7 @@ def main():
         torch.cuda.synchronize()
 
     def step_resident():
-        ctx.render()
-        if world > 1:
-            reduce_sum_to_rank0(accum_tensor(ctx))
-            torch.cuda.synchronize()
-            if rank == 0:
-                ctx.resolve()
+        ctx.render_frame()      # this rank's samples, one ncclReduce of the float4 sums, rank 0 resolves: one C call
 
     def step_e2e():
         if world == 1:
@@ -213,12 +240,20 @@ def main():
         step_e2e()
     e2e = timed(step_e2e, args.steps)
 
+    # what was timed is checked: rank 0 holds the resolved frame of the last step
+    parity = None
+    if not args.no_parity_check:
+        step_resident()
+        if rank == 0:
+            parity = parity_check(ctx.framebuffer_f32(), sc, world)
+
     # Throughput mode (reported beside the headline, never as `value`): 8 RNG streams per pixel on each GPU
     # (b200pt_config.streams_per_pixel) — the streams an 8x larger SPP-sharded job uses, same total samples.
     tm = None
     if args.streams_mode > 1:
         c8 = pt.Context(device=local, rank=rank, world_size=world, shard_mode=pt.SHARD_SPP, flags=0, streams=args.streams_mode)
         c8.bind(sc)
+        init_comm(c8)
         main_ctx, ctx = ctx, c8
         for _ in range(min(args.warmup, 2)):
             step_resident()
@@ -288,7 +323,8 @@ def main():
         cpu_spp = max(2, min(64, int(round(15.0 / max(sec1, 0.05)))))   # then ~15 s of CPU work
         rate, sec, rays = cpu_oracle_rate(cpu_spp, cores)
         cpu = dict(value=rate, unit="Mrays/s", cores=cores, kind="port",
-                   sample=f"full 1920x1080 dragon frame at {cpu_spp} spp ({rays} rays, {sec:.1f} s), oracle/oracle.cpp with glibc math")
+                   sample=f"full 1920x1080 dragon frame at {cpu_spp} spp ({rays} rays, {sec:.1f} s), oracle/oracle.cpp with glibc math; "
+                          "a scalar port over a median-split binary BVH, NOT a tuned CPU ray tracer")
 
     if rank == 0:
         total_spp = wl["spp"]
@@ -297,19 +333,21 @@ def main():
             metric="Mrays/s", value=res["rays_all"] / (res["wall_ms"] * 1e-3) * 1e-6, unit="Mrays/s", n_gpus=world,
             steps=args.steps, warmup=args.warmup, ms_per_step=ms_step, higher_is_better=True, scaling="strong",
             vs_baseline=None, dtype="f32", data="synthetic",
-            config=dict(workload=WORKLOAD_NAME if not args.spp else f"dragon 1920x1080 at {total_spp} spp (reduced, not the headline)",
+            config=dict(workload=WORKLOAD_NAME if not (args.spp or args.detail) else
+                        f"secondary: dragon 1920x1080 at {total_spp} spp, {sc.n_triangles} triangles (not the headline)",
                         parallelism=f"spp-sharded x{world}, scene replicated, one NCCL reduce of the float4 sums per frame",
                         l2="inputs larger than L2: lane state 330 MB + BVH 49 MB per GPU vs 126 MB L2, no flush between steps",
                         rng="one stream per pixel through all its samples (reference order); rank r seeds random(x, y + r*H)"),
             spp_per_s=total_spp / (ms_step * 1e-3),
             device_ms_per_step=res["render_ms"] / args.steps,
             e2e=dict(value=e2e["rays_all"] / (e2e["wall_ms"] * 1e-3) * 1e-6, unit="Mrays/s",
-                     h2d_bytes_per_step=int(mats.nbytes), d2h_bytes_per_step=int(sc.width * sc.height * 20),
+                     h2d_bytes_per_step=int(mats.nbytes), d2h_bytes_per_step=int(sc.width * sc.height * 4),
                      ms_per_step=e2e["wall_ms"] / args.steps),
             gpu_launches=res["launches_all"],
             kernel_ms_per_step=dict(extend=kt["extend_ms"], shade=kt["shade_ms"], frame_serial=kt["render_ms"]) if kt else None,
-            clocks=clocks, roofline=roof, cpu_baseline=cpu, throughput_mode=tm,
-            parity="tests/test_gpu_parity.py: bit-exact vs oracle (hits, float frame); relMSE <= 1e-3 vs glibc oracle",
+            clocks=clocks, roofline=roof, cpu_baseline=cpu, throughput_mode=tm, parity_check=parity,
+            parity="tests/test_gpu_parity.py: bit-exact vs oracle (hits, float frame); relMSE <= 1e-3 vs glibc oracle; "
+                   "oracle == the reference's own device code bit for bit (tests/test_ref_device.py, oracle/_ref)",
             notes=sc.notes)
         emit(line)
     ctx.close()

@@ -149,6 +149,12 @@ def lib() -> C.CDLL:
     L.b200pt_set_output.argtypes = [P, C.c_int32]
     L.b200pt_accum_buffer.argtypes = [P, C.POINTER(P), C.POINTER(C.c_size_t)]
     L.b200pt_resolve.argtypes = [P]
+    L.b200pt_comm_unique_id.argtypes = [P]
+    L.b200pt_comm_init_rank.argtypes = [P, P]
+    L.b200pt_comm_init_all.argtypes = [C.POINTER(P), C.c_int32]
+    L.b200pt_reduce.argtypes = [P]
+    L.b200pt_render_frame.argtypes = [P]
+    L.b200pt_render_frame_all.argtypes = [C.POINTER(P), C.c_int32]
     L.b200pt_render_to_host.argtypes = [P, P, C.c_int32, P]
     L.b200pt_framebuffer_rgba8.argtypes = [P, C.POINTER(P)]
     L.b200pt_framebuffer_f32.argtypes = [P, C.POINTER(P)]

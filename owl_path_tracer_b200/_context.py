@@ -134,6 +134,37 @@ class Context:
     def resolve(self):
         self._ck(self._L.b200pt_resolve(self._h), "resolve")
 
+    # ---- the frame's collective inside the library (NCCL; include/b200pt.h)
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """128 bytes made on rank 0; ship them to the other ranks (any transport) for comm_init_rank."""
+        buf = C.create_string_buffer(128)
+        if lib().b200pt_comm_unique_id(buf) != 0:
+            raise B200ptError("comm_unique_id: " + lib().b200pt_last_error().decode())
+        return buf.raw
+
+    def comm_init_rank(self, unique_id: bytes):
+        self._ck(self._L.b200pt_comm_init_rank(self._h, C.create_string_buffer(unique_id, 128)), "comm_init_rank")
+
+    def reduce(self):
+        self._ck(self._L.b200pt_reduce(self._h), "reduce")
+
+    def render_frame(self):
+        """this rank's share + one ncclReduce of the float4 sums to rank 0 + (rank 0) resolve.  Collective."""
+        self._ck(self._L.b200pt_render_frame(self._h), "render_frame")
+
+    @staticmethod
+    def comm_init_all(ctxs):
+        arr = (C.c_void_p * len(ctxs))(*[c._h for c in ctxs])
+        if lib().b200pt_comm_init_all(arr, len(ctxs)) != 0:
+            raise B200ptError("comm_init_all: " + lib().b200pt_last_error().decode())
+
+    @staticmethod
+    def render_frame_all(ctxs):
+        arr = (C.c_void_p * len(ctxs))(*[c._h for c in ctxs])
+        if lib().b200pt_render_frame_all(arr, len(ctxs)) != 0:
+            raise B200ptError("render_frame_all: " + lib().b200pt_last_error().decode())
+
     def accum_buffer(self):
         """(device pointer, number of floats) of the float4 sum buffer for the NCCL reduce."""
         p, n = C.c_void_p(), C.c_size_t()

@@ -1,6 +1,10 @@
 """Multi-GPU plumbing: one process per GPU, samples (or rows) sharded over ranks, ONE reduce of
-the float4 sum buffer to rank 0 per frame.  torch.distributed is only the carrier:
-NCCL over NVLink on the GPU box, gloo in the CPU tests."""
+the float4 sum buffer to rank 0 per frame.
+
+The collective itself lives in the C ABI (b200pt_comm_init_rank / b200pt_render_frame: ncclReduce inside libb200pt.so,
+the same entry points `path_tracer --gpus N` uses).  torch.distributed only carries the 128-byte NCCL id from rank 0 to
+the other ranks (`init_comm`).  `reduce_sum_to_rank0` on a torch tensor remains for the gloo CPU tests and for callers
+that want the reduce on their own process group."""
 from __future__ import annotations
 
 import numpy as np
@@ -29,8 +33,23 @@ def reduce_sum_to_rank0(tensor, group=None):
     return tensor
 
 
+def init_comm(ctx, group=None):
+    """Create the library's NCCL communicator for this rank: rank 0 makes the id, torch.distributed ships it."""
+    import torch.distributed as dist
+    if ctx.world_size == 1:
+        return
+    box = [ctx.comm_unique_id() if ctx.rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    ctx.comm_init_rank(box[0])
+    ctx._comm_ready = True
+
+
 def render_frame(ctx, group=None):
-    """render this rank's share -> reduce -> rank 0 resolves (scale by 1/total spp, RGBA8 pack)."""
+    """render this rank's share -> reduce -> rank 0 resolves (scale by 1/total spp, RGBA8 pack).  After init_comm the
+    whole sequence is one C call (b200pt_render_frame); otherwise the reduce runs on the torch process group."""
+    if getattr(ctx, "_comm_ready", False) or ctx.world_size == 1:
+        ctx.render_frame()
+        return
     ctx.render()
     if ctx.world_size > 1:
         import torch

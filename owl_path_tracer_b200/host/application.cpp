@@ -83,6 +83,8 @@ void render_frame(b200pt_ctx* ctx, const program_data& pdata, const test_data& t
         b200pt_pass_info last{};
         check(b200pt_render_progressive(ctx, pdata.progressive_pass, pdata.target_error, on_pass, &pc, &last), "render_progressive");
         if (last.stopped_early) host::say("target reached after %d samples per pixel\n", last.samples_done);
+    } else if (pdata.ranks.size() > 1) {
+        check(b200pt_render_frame_all(pdata.ranks.data(), (int32_t)pdata.ranks.size()), "render_frame_all");
     } else {
         check(b200pt_render(ctx), "render");
     }
@@ -123,6 +125,8 @@ void test_loop(b200pt_ctx* ctx, program_data& pdata, const test_data& tdata, con
         }
         const std::vector<material_data> mats = material_array(pdata);  // reset_field, application.cpp:297-304
         check(b200pt_set_materials(ctx, mats.data(), (int)mats.size()), "set_materials");
+        for (size_t r = 1; r < pdata.ranks.size(); ++r)
+            check(b200pt_set_materials(pdata.ranks[r], mats.data(), (int)mats.size()), "set_materials");
         render_frame(ctx, pdata, tdata, buf, out_dir);
     }
 }

@@ -6,6 +6,8 @@
 // directory.  Optional flags (all default to the reference behaviour):
 //   --assets DIR  --scene NAME  --size W H  --spp N  --depth N  --env color|auto|map
 //   --env-intensity F  --detail N  --device K  --out DIR  --stats
+//   --gpus N (devices K .. K+N-1, samples sharded over them, one NCCL reduce per frame; the reference's OWL context can
+//             span devices the same way, extern/owl/owl/RayGen.cpp:140-146, and asks for one, application.cpp:62)
 //   --nee (light sampling + MIS mode)  --streams V (RNG streams per pixel)  --pfm (float frame next to the PNG)
 //   --env-float (environment.hdr as float radiance instead of the reference's 8-bit conversion)
 //   --progressive N (frame in passes of N samples)  --target-error E (stop once the relative-variance figure <= E)
@@ -15,6 +17,7 @@
 #include <cstring>
 #include <filesystem>
 #include <string>
+#include <vector>
 
 #include "application.hpp"
 
@@ -22,7 +25,7 @@ int main(int argc, char** argv) {
     std::string assets_path = std::filesystem::current_path().string() + "/assets";
     std::string out_dir = std::filesystem::current_path().string();
     host::load_options opt;
-    int device = 0, flags = 0, streams = 1;
+    int device = 0, flags = 0, streams = 1, gpus = 1;
     bool stats = false, pfm = false, gamma = false, save_passes = false;
     int progressive = 0;
     double target_error = 0.0;
@@ -47,6 +50,7 @@ int main(int argc, char** argv) {
         else if (a == "--env-intensity") { need(1); opt.env_intensity = (float)atof(argv[++i]); }
         else if (a == "--detail") { need(1); opt.detail = atoi(argv[++i]); }
         else if (a == "--device") { need(1); device = atoi(argv[++i]); }
+        else if (a == "--gpus") { need(1); gpus = atoi(argv[++i]); }
         else if (a == "--out") { need(1); out_dir = argv[++i]; }
         else if (a == "--stats") stats = true;
         else if (a == "--nee") flags |= B200PT_FLAG_NEE;
@@ -59,7 +63,7 @@ int main(int argc, char** argv) {
         else if (a == "--gamma") gamma = true;
         else if (a == "--help" || a == "-h") {
             printf("path_tracer [--assets DIR] [--scene NAME] [--size W H] [--spp N] [--depth N] [--env color|auto|map]\n"
-                   "            [--env-intensity F] [--detail N] [--device K] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"
+                   "            [--env-intensity F] [--detail N] [--device K] [--gpus N] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"
                    "            [--env-float] [--progressive N] [--target-error E] [--save-passes] [--gamma]\n"
                    "without arguments: ./assets/settings.json and its scene, as the reference's executable\n");
             return 0;
@@ -75,26 +79,43 @@ int main(int argc, char** argv) {
         host::init_program_data(pdata, tdata, assets_path, opt);
         for (const std::string& n : pdata.notes) printf("NOTE: %s\n", n.c_str());
 
-        b200pt_config cfg{};
-        cfg.device_ordinal = device;
-        cfg.rank = 0;
-        cfg.world_size = 1;
-        cfg.flags = flags;
-        cfg.streams_per_pixel = streams;
         pdata.write_pfm = pfm;
         pdata.progressive_pass = progressive;
         pdata.target_error = target_error;
         pdata.save_passes = save_passes;
         if (target_error > 0.0 && progressive <= 0) pdata.progressive_pass = 16;
-        b200pt_ctx* ctx = nullptr;
-        if (b200pt_create(&cfg, &ctx) != B200PT_OK) {
-            fprintf(stderr, "b200pt_create failed: %s\n", b200pt_last_error());
-            return 1;
+        if (gpus < 1 || (gpus > 1 && pdata.progressive_pass > 0)) {
+            fprintf(stderr, "--gpus needs N >= 1 and renders whole frames (no --progressive / --target-error)\n");
+            return 2;
         }
-        host::bind_scene(pdata, ctx);
-        if (gamma && b200pt_set_output(ctx, B200PT_TRANSFER_GAMMA22) != B200PT_OK) {
-            fprintf(stderr, "b200pt_set_output failed: %s\n", b200pt_last_error());
-            return 1;
+        std::vector<b200pt_ctx*> ranks;
+        for (int r = 0; r < gpus; ++r) {
+            b200pt_config cfg{};
+            cfg.device_ordinal = device + r;
+            cfg.rank = r;
+            cfg.world_size = gpus;
+            cfg.shard_mode = B200PT_SHARD_SPP;
+            cfg.flags = flags;
+            cfg.streams_per_pixel = streams;
+            b200pt_ctx* c = nullptr;
+            if (b200pt_create(&cfg, &c) != B200PT_OK) {
+                fprintf(stderr, "b200pt_create (rank %d) failed: %s\n", r, b200pt_last_error());
+                return 1;
+            }
+            host::bind_scene(pdata, c);
+            if (gamma && b200pt_set_output(c, B200PT_TRANSFER_GAMMA22) != B200PT_OK) {
+                fprintf(stderr, "b200pt_set_output failed: %s\n", b200pt_last_error());
+                return 1;
+            }
+            ranks.push_back(c);
+        }
+        b200pt_ctx* ctx = ranks[0];
+        if (gpus > 1) {
+            if (b200pt_comm_init_all(ranks.data(), gpus) != B200PT_OK) {
+                fprintf(stderr, "b200pt_comm_init_all failed: %s\n", b200pt_last_error());
+                return 1;
+            }
+            pdata.ranks = ranks;
         }
         host::test_loop(ctx, pdata, tdata, out_dir);
         if (stats) {
@@ -106,7 +127,7 @@ int main(int argc, char** argv) {
                    (unsigned long long)st.paths, st.render_ms > 0 ? st.rays / st.render_ms * 1e-3 : 0.0, st.bvh_nodes,
                    st.bvh_tris);
         }
-        b200pt_destroy(ctx);
+        for (b200pt_ctx* c : ranks) b200pt_destroy(c);
     } catch (const std::exception& e) {
         fprintf(stderr, "error: %s\n", e.what());
         return 1;

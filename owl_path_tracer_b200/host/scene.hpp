@@ -92,6 +92,9 @@ struct program_data {
     int progressive_pass = 0;
     double target_error = 0.0;
     bool save_passes = false;        // write "<stem>_pass<samples>.png" after every pass
+    // several GPUs from one process (path_tracer --gpus N): the contexts of ranks 0 .. N-1, samples sharded over them,
+    // one NCCL reduce per frame inside b200pt_render_frame_all.  Empty: the single context handed to test_loop.
+    std::vector<b200pt_ctx*> ranks;
 };
 
 }  // namespace host
