@@ -285,6 +285,16 @@ int b200pt_primary_hits(b200pt_ctx* ctx, b200pt_hit* out);
 int b200pt_trace(b200pt_ctx* ctx, const float* origins, const float* dirs, int32_t n,
                  float tmin, float tmax, b200pt_hit* out);
 
+/* b200pt_trace without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same results as b200pt_trace (host pointers in and out); the kernel's staging (ray cursor, origins,
+ * directions, raw hits) is a fixed device array inside the library, 2.5 MiB per GPU, held until the process exits.
+ * n > B200PT_TRACE_STATIC_MAX is rejected with B200PT_ERR_BOUNDS.  The call performs no cudaMalloc / cudaFree and
+ * updates no statistics.  All calls on a GPU share the array: calls that overlap on one GPU race (serialise them). */
+#define B200PT_TRACE_STATIC_MAX 65536
+int b200pt_trace_static(b200pt_ctx* ctx, const float* origins, const float* dirs, int32_t n,
+                        float tmin, float tmax, b200pt_hit* out);
+
 int b200pt_get_stats(b200pt_ctx* ctx, b200pt_stats* out);
 
 /* Parity hook for the BSDF (disney/disney.cuh:31-66) evaluated on the device:

@@ -160,6 +160,7 @@ def lib() -> C.CDLL:
     L.b200pt_framebuffer_f32.argtypes = [P, C.POINTER(P)]
     L.b200pt_primary_hits.argtypes = [P, P]
     L.b200pt_trace.argtypes = [P, P, P, C.c_int32, C.c_float, C.c_float, P]
+    L.b200pt_trace_static.argtypes = [P, P, P, C.c_int32, C.c_float, C.c_float, P]
     L.b200pt_get_stats.argtypes = [P, C.POINTER(Stats)]
     L.b200pt_sample_disney.argtypes = [P, C.c_int32] + [P] * 9
     L.b200pt_export_bvh.argtypes = [P, P, C.POINTER(C.c_uint32), P, C.POINTER(C.c_uint32)]

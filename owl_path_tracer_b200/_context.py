@@ -207,6 +207,14 @@ class Context:
         self._ck(self._L.b200pt_trace(self._h, _ptr(o), _ptr(d), o.shape[0], tmin, tmax, _ptr(out)), "trace")
         return out
 
+    def trace_static(self, origins, dirs, tmin=1e-3, tmax=1e10):
+        """b200pt_trace_static: same result as trace(), no device allocation (at most 65536 rays per call)."""
+        o = np.ascontiguousarray(origins, np.float32)
+        d = np.ascontiguousarray(dirs, np.float32)
+        out = np.empty(o.shape[0], HIT_DTYPE)
+        self._ck(self._L.b200pt_trace_static(self._h, _ptr(o), _ptr(d), o.shape[0], tmin, tmax, _ptr(out)), "trace_static")
+        return out
+
     def sample_disney(self, material, wo, lobe_in, rng_in):
         material = np.ascontiguousarray(material, np.int32)
         wo = np.ascontiguousarray(wo, np.float32)

@@ -1330,3 +1330,85 @@ extern "C" int b200pt_render_frame_all(b200pt_ctx* const* ctxs, int32_t n) {
         if (status[(size_t)i] != B200PT_OK) return fail(status[(size_t)i], "rank " + std::to_string(i) + ": " + message[(size_t)i]);
     return B200PT_OK;
 }
+
+// ---------------------------------------------------------------------------- b200pt_trace_static
+// Variant of b200pt_trace that allocates nothing (no cudaMalloc / cudaFree, no allocating library call): the staging
+// the walk kernel needs — ray-fetch cursor, origins, directions, raw hit records — lives in ONE file-scope device array
+// of fixed size.  No counterpart in the reference; added for callers that
+// cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+// Every GPU that loads the library holds the array until the process exits (2.5 MiB).  All calls share it and it keeps
+// the last call's contents: the cursor is cleared on every call, the rest is overwritten before it is read; calls
+// that overlap on one GPU race on it (serialise them).
+namespace {
+constexpr size_t kStaticHeader = 256;   // cursor (4 bytes used), keeps the arrays behind it 256-byte aligned
+constexpr size_t kStaticBytes = kStaticHeader + (size_t)B200PT_TRACE_STATIC_MAX * (12 + 12 + 16);
+static __device__ __align__(256) unsigned char g_trace_scratch[kStaticBytes];
+
+// In host code `g_trace_scratch` is only a stand-in for the symbol, not a device address: the address is asked for once
+// per device, with that device current.
+unsigned char* static_scratch_of(int device, std::string& err) {
+    static std::mutex mu;
+    static unsigned char* table[64] = {};
+    if (device < 0 || device >= 64) {
+        err = "device ordinal out of range";
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> g(mu);
+    if (!table[device]) {
+        cudaError_t e = cudaSetDevice(device);
+        void* p = nullptr;
+        if (e == cudaSuccess) e = cudaGetSymbolAddress(&p, g_trace_scratch);
+        if (e != cudaSuccess || !p) {
+            err = std::string("cudaGetSymbolAddress(g_trace_scratch): ") + cudaGetErrorString(e);
+            return nullptr;
+        }
+        table[device] = static_cast<unsigned char*>(p);
+    }
+    return table[device];
+}
+}  // namespace
+
+extern "C" int b200pt_trace_static(b200pt_ctx* c, const float* origins, const float* dirs, int32_t n, float tmin, float tmax,
+                                   b200pt_hit* out) {
+    if (!c || !c->built) return fail(B200PT_ERR_INVALID, "trace_static: call b200pt_build_accel first");
+    if (!origins || !dirs || !out || n <= 0) return fail(B200PT_ERR_INVALID, "trace_static: null/empty");
+    if (n > B200PT_TRACE_STATIC_MAX)
+        return fail(B200PT_ERR_BOUNDS, "trace_static: " + std::to_string(n) + " rays exceed the fixed scratch of " +
+                                           std::to_string(B200PT_TRACE_STATIC_MAX) + " rays (use b200pt_trace, or split the batch)");
+    std::string err;
+    unsigned char* base = static_scratch_of(c->cfg.device_ordinal, err);
+    if (!base) return fail(B200PT_ERR_CUDA, "trace_static: " + err);
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    uint32_t* d_cursor = reinterpret_cast<uint32_t*>(base);
+    float* d_o = reinterpret_cast<float*>(base + kStaticHeader);
+    float* d_d = reinterpret_cast<float*>(base + kStaticHeader + (size_t)B200PT_TRACE_STATIC_MAX * 12);
+    f4* d_hits = reinterpret_cast<f4*>(base + kStaticHeader + (size_t)B200PT_TRACE_STATIC_MAX * 24);
+    SceneView sv{};
+    sv.nodes = c->bvh.nodes;
+    sv.tris = c->bvh.tris;
+    sv.plane_magic = 0x3F800000u;
+    CU(cudaMemsetAsync(d_cursor, 0, sizeof(uint32_t), c->stream));   // the one thing that must start at zero
+    CU(cudaMemcpyAsync(d_o, origins, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_d, dirs, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    launch_trace(sv, d_o, d_d, n, tmin, tmax, d_hits, d_cursor, c->stream);
+    // raw 16-byte records land at the front of the caller's 20-byte-record buffer and are widened in place, last first
+    // (record i is read from bytes [16 i, 16 i + 16) before bytes [20 i, 20 i + 20) are written): no host staging either
+    CU(cudaMemcpyAsync(out, d_hits, sizeof(f4) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    const unsigned char* raw = reinterpret_cast<const unsigned char*>(out);
+    for (int64_t i = (int64_t)n - 1; i >= 0; --i) {
+        f4 r;
+        memcpy(&r, raw + 16 * (size_t)i, sizeof r);
+        const uint32_t tri = f2u(r.w);
+        b200pt_hit h;
+        if (tri == kNoHit) {
+            h = b200pt_hit{-1, -1, tmax, 0.0f, 0.0f};
+        } else {
+            const int32_t mesh = c->h_idx4[4 * (size_t)tri + 3];
+            h = b200pt_hit{mesh, (int32_t)tri - c->h_meshes[mesh].first_tri, r.x, r.y, r.z};
+        }
+        memcpy(reinterpret_cast<unsigned char*>(out) + sizeof(b200pt_hit) * (size_t)i, &h, sizeof h);
+    }
+    return B200PT_OK;
+}
