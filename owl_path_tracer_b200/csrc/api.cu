@@ -28,11 +28,11 @@ static int fail(int code, const std::string& msg) {
         if (e_ != cudaSuccess) return fail(B200PT_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
-#ifndef PT_FUSE_MIN
-#define PT_FUSE_MIN 0
-#endif
-#ifndef PT_FUSE_SEGS
-#define PT_FUSE_SEGS 8
+// Development knobs (environment variables read inside b200pt_render: parts override, L2 persistence window,
+// per-iteration log, per-warp timeline) exist only in builds made with -DB200PT_DEV=1 (tools/build_variants.sh).
+// The product build reads no environment variable on the render path.
+#ifndef B200PT_DEV
+#define B200PT_DEV 0
 #endif
 
 struct b200pt_ctx {
@@ -111,8 +111,6 @@ struct b200pt_ctx {
 };
 
 constexpr int kCountsStride = 3 * kBatch + 1;  // per part in h_counts
-constexpr int kFuseMinDefault = PT_FUSE_MIN;   // queue length below which the fused tail kernel takes over (0: never)
-constexpr int kFuseSegsDefault = PT_FUSE_SEGS; // segments per lane and launch of the fused tail kernel
 
 static void free_lanes(b200pt_ctx* c) {
     for (int p = 0; p < kMaxParts; ++p) {
@@ -164,7 +162,7 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
     sv.vpos = c->d_pos;
     sv.vnrm = c->d_nrm;
     sv.vuv = c->d_uv;
-    sv.tri_rec = getenv("B200PT_NO_TRIREC") ? nullptr : c->d_tri_rec;   // (the env switch is the A/B of tools/trirec_ab.py)
+    sv.tri_rec = c->d_tri_rec;
     sv.meshes = c->d_meshes;
     sv.materials = c->d_mats;
     sv.mesh_materials = c->d_mesh_mats;
@@ -598,11 +596,12 @@ static int sync_mesh_materials(b200pt_ctx* c) {
 // sub-frames the other part's kernels fill the SMs the tail leaves idle.  B200PT_FLAG_TIMING keeps one part so
 // that the per-kernel event times stay clean; B200PT_PARTS overrides (development).
 static int choose_parts(const b200pt_ctx* c, const SceneView& sv) {
-    int parts = 2;
+    int parts = (c->cfg.flags & B200PT_FLAG_TIMING) ? 1 : 2;
+    if (sv.n_lanes < (1 << 18)) parts = 1;  // small frames: launch-bound already
+#if B200PT_DEV
     if (const char* e = getenv("B200PT_PARTS")) parts = atoi(e);
-    else if (c->cfg.flags & B200PT_FLAG_TIMING) parts = 1;
+#endif
     const int rows = sv.width > 0 ? sv.n_lanes / sv.width : 0;
-    if (sv.n_lanes < (1 << 18)) parts = getenv("B200PT_PARTS") ? parts : 1;  // small frames: launch-bound already
     return std::max(1, std::min({parts, kMaxParts, std::max(rows, 1)}));
 }
 static uint32_t part_lanes(const SceneView& sv, int p, int parts) {
@@ -691,6 +690,7 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
     }
     const int parts = choose_parts(c, sv);
     if (int r = ensure_lanes(c, sv, parts)) return r;
+#if B200PT_DEV
     {
         // Experiment (B200PT_L2_PERSIST = 1 tris | 2 nodes | 0 off): keep the triangle blocks (or the nodes) in the
         // persisting part of L2 so that the lane state streaming through L2 every iteration cannot evict them.
@@ -718,6 +718,7 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
             c->l2_persist_mode = mode;
         }
     }
+#endif
     const bool count = (c->cfg.flags & B200PT_FLAG_COUNTERS) != 0;
     const bool timing = (c->cfg.flags & B200PT_FLAG_TIMING) != 0 && parts == 1;
     const bool nee = sv.nee != 0;
@@ -762,20 +763,14 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
         }
     }
     FILE* iter_log = nullptr;
+    long tl_iter = -1, iter_no = 0;
+#if B200PT_DEV
     if (timing)
         if (const char* e = getenv("B200PT_ITER_LOG")) iter_log = fopen(e, "w");
-    // Tail of the frame (wavefront.cu k_fused): once a part's queue is shorter than fuse_min its lanes run whole
-    // segments, `fuse_segs` per launch, in one kernel.  The first iteration after the switch is a normal one that
-    // resumes the parked walks and parks none.  Off with counters (the fused walk does not count) and in NEE mode.
-    int fuse_min = kFuseMinDefault, fuse_segs = kFuseSegsDefault;
-    if (const char* e = getenv("B200PT_FUSE_MIN")) fuse_min = atoi(e);
-    if (const char* e = getenv("B200PT_FUSE_SEGS")) fuse_segs = std::max(1, atoi(e));
-    if (nee || count) fuse_min = 0;
-    bool fused[kMaxParts] = {};
-    // development (PT_TIMELINE builds): per-warp timestamps of the k_extend launch of wavefront iteration
-    // B200PT_TIMELINE_ITER of part 0, written to B200PT_TIMELINE_FILE after the frame
-    long tl_iter = -1, iter_no = 0;
+    // PT_TIMELINE builds: per-warp timestamps of the k_extend launch of wavefront iteration B200PT_TIMELINE_ITER of
+    // part 0, written to B200PT_TIMELINE_FILE after the frame
     if (const char* e = getenv("B200PT_TIMELINE_ITER")) tl_iter = atol(e);
+#endif
     auto any_active = [&] {
         for (int p = 0; p < parts; ++p)
             if (active[p]) return true;
@@ -789,18 +784,7 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
                 const LaneArrays& L = c->part[p];
                 cudaStream_t ps = c->part_stream[p];
                 if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k], ps));
-                if (fused[p]) {  // extend + shade of up to fuse_segs segments per lane; its time is booked as extend time
-                    launch_fused(sv, L, k, active[p], fuse_segs, ps);
-                    if (timing) CU(cudaEventRecord(c->ev_pool[ev_per_iter * k + 1], ps));
-                    S.kernel_launches += 1;
-                    continue;
-                }
-                if (k == 0 && active[p] < (uint32_t)fuse_min) {
-                    LaneArrays T = L;
-                    T.no_park = 1;
-                    launch_extend(sv, T, k, active[p], count, ps);
-                    fused[p] = true;
-                } else if (p == 0 && iter_no + k == tl_iter && timeline_arm(true, ps)) {
+                if (p == 0 && iter_no + k == tl_iter && timeline_arm(true, ps)) {
                     launch_extend(sv, L, k, active[p], count, ps);
                     timeline_arm(false, ps);
                 } else {
@@ -864,11 +848,13 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
         }
     }
     if (iter_log) fclose(iter_log);
+#if B200PT_DEV
     if (tl_iter >= 0)
         if (const char* e = getenv("B200PT_TIMELINE_FILE")) {
             CU(cudaDeviceSynchronize());
             timeline_dump(e);
         }
+#endif
     for (int p = 1; p < parts; ++p) {  // the frame is complete on `stream` once every part is
         CU(cudaEventRecord(c->part_done[p], c->part_stream[p]));
         CU(cudaStreamWaitEvent(st, c->part_done[p], 0));

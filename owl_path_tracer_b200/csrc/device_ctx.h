@@ -56,7 +56,6 @@ struct LaneArrays {
     uint32_t* cursor = nullptr;   // kBatch ray-fetch cursors of the persistent extend kernel
     unsigned long long* walk_counters = nullptr;  // nodes, tris (FLAG_COUNTERS)
     uint32_t capacity = 0;
-    uint32_t no_park = 0;         // 1: k_extend resumes parked walks but parks none (last wavefront iteration before k_fused)
 };
 
 constexpr int kSuspWords = 3 + kSuspStack / 2;  // 176 bytes per lane: hit, groups, top + kSuspStack stack entries of 8 bytes
@@ -70,7 +69,6 @@ void launch_shade(const SceneView& sv, const LaneArrays& la, int k, uint32_t max
 bool timeline_arm(bool on, cudaStream_t st);   // PT_TIMELINE builds only (false otherwise)
 bool timeline_dump(const char* path);
 void launch_tri_records(const f4* pos, const f4* nrm, const int32_t* idx4, uint32_t n, TriShade* out, cudaStream_t st);
-void launch_fused(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, int segments, cudaStream_t st);
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st);
 void launch_resolve(const SceneView& sv, const f4* sum, float inv_spp, int transfer, uint32_t* rgba, f4* mean, cudaStream_t st);
 unsigned pass_stats_blocks(uint32_t n_lanes);

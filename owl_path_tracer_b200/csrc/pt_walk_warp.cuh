@@ -36,15 +36,6 @@ namespace pt {
 #ifndef PT_SUSPEND_STEPS
 #define PT_SUSPEND_STEPS 0   // ... and (if > 0) any warp parks whatever it still holds this many loop steps after the queue drained
 #endif
-#ifndef PT_PREFETCH_TRI
-#define PT_PREFETCH_TRI 0    // prefetch.global.L1 of the first leaf triangle at the end of a node step
-#endif
-#ifndef PT_PREFETCH_NODE
-#define PT_PREFETCH_NODE 0   // prefetch.global.L1 of the next child node at the end of a node step
-#endif
-#ifndef PT_UNIFIED
-#define PT_UNIFIED 0         // 1: unified step — no phase vote, one shared 80-byte fetch per lane (node or triangle block), see the loop body
-#endif
 #ifndef PT_TIMELINE
 #define PT_TIMELINE 0        // development: per-warp timestamps of one chosen k_extend launch (tools/timeline.py)
 #endif
@@ -86,15 +77,13 @@ __device__ __forceinline__ f4 ldg4f(const f4* p) {
 //       void suspend(i, hit, ng_base, ng_mask, tg_base, tg_mask, sp, top_b, top_m, stack)        (SUSPEND only)
 template <bool COUNT, bool ANY, bool SUSPEND, class Src, class Sink>
 __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const TriPair* __restrict__ tris, uint32_t n,
-                                          uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic,
-                                          const bool allow_park = true) {
+                                          uint32_t* cursor, Src src, Sink sink, WalkCounters& wc, const uint32_t magic) {
     const unsigned FULL = 0xffffffffu;
     const int lid = threadIdx.x & 31;
 
     bool has_ray = false, exhausted = false;
-    // 0: only an empty warp leaves.  allow_park = false: this launch resumes parked walks but parks none (the
-    // iteration before the fused tail kernel takes over, wavefront.cu k_fused)
-    const int park = (SUSPEND && allow_park && n >= (uint32_t)PT_SUSPEND_MIN) ? PT_SUSPEND_LANES : 0;
+    // 0: only an empty warp leaves
+    const int park = (SUSPEND && n >= (uint32_t)PT_SUSPEND_MIN) ? PT_SUSPEND_LANES : 0;
     int slice = PT_SUSPEND_STEPS;  // time slice left once the queue is drained (warp-uniform)
     uint32_t ray_index = 0;
     f3 o{0, 0, 0}, d{0, 0, 1};
@@ -201,127 +190,6 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
             if (exhausted) break;
             continue;
         }
-#if PT_UNIFIED
-        // ---- unified step (PT_UNIFIED): no vote.  Every lane with a ray does the work it holds — the next triangle
-        // block of its leaf group, else the next child node of its node group.  Node8 and TriPair are both five
-        // 16-byte words, so the warp issues ONE sequence of five LDG.128 from a per-lane address and only the
-        // arithmetic diverges: a loop step serves every lane and costs one load latency, where the voted scheme
-        // spends a step per kind (21 of 32 lanes in a node step, 11 of 32 in a triangle step, tools/timeline.py).
-        const bool want_tri = has_ray && tg_mask != 0;
-        const bool can_node = has_ray && !want_tri && ng_mask > 0x00FFFFFFu;
-        const u4* ptr = reinterpret_cast<const u4*>(nodes);
-        if (want_tri) {
-            const int bit = 31 - __clz(tg_mask);
-            tg_mask &= ~(1u << bit);
-            ptr = reinterpret_cast<const u4*>(tris + (tg_base + (uint32_t)bit));
-        } else if (can_node) {
-            const int bit = 31 - __clz(ng_mask);
-            const uint32_t imask = ng_mask & 0xFFu;
-            ng_mask &= ~(1u << bit);
-            if (ng_mask > 0x00FFFFFFu) PT_PUSH(ng_base, ng_mask);
-            const uint32_t slot = (uint32_t)(bit - 24) ^ (octinv4 & 0xFFu);
-            const uint32_t rel = (uint32_t)__popc(imask & ~(0xFFFFFFFFu << slot));
-            ptr = reinterpret_cast<const u4*>(nodes + (ng_base + rel));
-        }
-        u4 w0{0, 0, 0, 0}, w1{0, 0, 0, 0}, w2{0, 0, 0, 0}, w3{0, 0, 0, 0}, w4{0, 0, 0, 0};
-        if (want_tri || can_node) {
-            w0 = ldg4(ptr + 0);
-            w1 = ldg4(ptr + 1);
-            w2 = ldg4(ptr + 2);
-            w3 = ldg4(ptr + 3);
-            w4 = ldg4(ptr + 4);
-        }
-        if (want_tri) {
-            // both triangles of the block at once (see the voted variant below for the layout)
-            const float2 v0x = make_float2(u2f(w0.x), u2f(w0.y)), v0y = make_float2(u2f(w0.z), u2f(w0.w)), v0z = make_float2(u2f(w1.x), u2f(w1.y));
-            const float2 e1x = make_float2(u2f(w1.z), u2f(w1.w)), e1y = make_float2(u2f(w2.x), u2f(w2.y)), e1z = make_float2(u2f(w2.z), u2f(w2.w));
-            const float2 e2x = make_float2(u2f(w3.x), u2f(w3.y)), e2y = make_float2(u2f(w3.z), u2f(w3.w)), e2z = make_float2(u2f(w4.x), u2f(w4.y));
-            const float2 dx = make_float2(d.x, d.x), dy = make_float2(d.y, d.y), dz = make_float2(d.z, d.z);
-            const float2 ndx = make_float2(-d.x, -d.x), ndy = make_float2(-d.y, -d.y), ndz = make_float2(-d.z, -d.z);
-            const float2 px = __ffma2_rn(dy, e2z, __fmul2_rn(ndz, e2y));
-            const float2 py = __ffma2_rn(dz, e2x, __fmul2_rn(ndx, e2z));
-            const float2 pz = __ffma2_rn(dx, e2y, __fmul2_rn(ndy, e2x));
-            const float2 det = __ffma2_rn(e1z, pz, __ffma2_rn(e1y, py, __fmul2_rn(e1x, px)));
-            const float2 inv = make_float2(1.0f / det.x, 1.0f / det.y);
-            const float2 sx = __fadd2_rn(make_float2(o.x, o.x), make_float2(-v0x.x, -v0x.y));
-            const float2 sy = __fadd2_rn(make_float2(o.y, o.y), make_float2(-v0y.x, -v0y.y));
-            const float2 sz = __fadd2_rn(make_float2(o.z, o.z), make_float2(-v0z.x, -v0z.y));
-            const float2 uu = __fmul2_rn(__ffma2_rn(sz, pz, __ffma2_rn(sy, py, __fmul2_rn(sx, px))), inv);
-            const float2 qx = __ffma2_rn(sy, e1z, __fmul2_rn(make_float2(-sz.x, -sz.y), e1y));
-            const float2 qy = __ffma2_rn(sz, e1x, __fmul2_rn(make_float2(-sx.x, -sx.y), e1z));
-            const float2 qz = __ffma2_rn(sx, e1y, __fmul2_rn(make_float2(-sy.x, -sy.y), e1x));
-            const float2 vv = __fmul2_rn(__ffma2_rn(dz, qz, __ffma2_rn(dy, qy, __fmul2_rn(dx, qx))), inv);
-            const float2 tt = __fmul2_rn(__ffma2_rn(e2z, qz, __ffma2_rn(e2y, qy, __fmul2_rn(e2x, qx))), inv);
-            const uint32_t idA = w4.z, idB = w4.w;
-            if (COUNT) wc.tris += 1u + (idB != kNoHit ? 1u : 0u);
-            const bool okA = (det.x != 0.0f) && (uu.x >= 0.0f && uu.x <= 1.0f) && (vv.x >= 0.0f && uu.x + vv.x <= 1.0f) &&
-                             (tt.x > tmin && tt.x < tmax);
-            const bool okB = (det.y != 0.0f) && (uu.y >= 0.0f && uu.y <= 1.0f) && (vv.y >= 0.0f && uu.y + vv.y <= 1.0f) &&
-                             (tt.y > tmin && tt.y < tmax);
-            if (okA && (tt.x < hit.t || (tt.x == hit.t && idA < hit.tri))) {
-                hit.t = tt.x;
-                hit.u = uu.x;
-                hit.v = vv.x;
-                hit.tri = idA;
-            }
-            if (okB && (tt.y < hit.t || (tt.y == hit.t && idB < hit.tri))) {
-                hit.t = tt.y;
-                hit.u = uu.y;
-                hit.v = vv.y;
-                hit.tri = idB;
-            }
-            if (ANY && hit.tri != kNoHit) {  // occluded: drop the rest of the traversal
-                ng_mask = 0;
-                tg_mask = 0;
-                sp = 0;
-            }
-        } else if (can_node) {
-            if (COUNT) wc.nodes++;
-            const uint32_t e = w0.w;
-            float aix, aiy, aiz, aox, aoy, aoz;
-            slab_axis(e & 0xFFu, u2f(w0.x), o.x, idx, aix, aox);
-            slab_axis((e >> 8) & 0xFFu, u2f(w0.y), o.y, idy, aiy, aoy);
-            slab_axis((e >> 16) & 0xFFu, u2f(w0.z), o.z, idz, aiz, aoz);
-            const bool nx = d.x < 0.0f, ny = d.y < 0.0f, nz = d.z < 0.0f;
-            const float2 aix2 = make_float2(aix, aix), aiy2 = make_float2(aiy, aiy), aiz2 = make_float2(aiz, aiz);
-            const float2 aox2 = make_float2(aox, aox), aoy2 = make_float2(aoy, aoy), aoz2 = make_float2(aoz, aoz);
-            uint32_t hitmask = 0;
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                const uint32_t meta4 = half ? w1.w : w1.z;
-                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xFFu;
-                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
-                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlox = half ? w2.y : w2.x, qloy = half ? w2.w : w2.z, qloz = half ? w3.y : w3.x;
-                const uint32_t qhix = half ? w3.w : w3.z, qhiy = half ? w4.y : w4.x, qhiz = half ? w4.w : w4.z;
-                const uint32_t nearx = nx ? qhix : qlox, farx = nx ? qlox : qhix;
-                const uint32_t neary = ny ? qhiy : qloy, fary = ny ? qloy : qhiy;
-                const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
-#pragma unroll
-                for (int j = 0; j < 4; j += 2) {
-                    const float2 tnx = __ffma2_rn(make_float2(plane_q(nearx, j, magic), plane_q(nearx, j + 1, magic)), aix2, aox2);
-                    const float2 tny = __ffma2_rn(make_float2(plane_q(neary, j, magic), plane_q(neary, j + 1, magic)), aiy2, aoy2);
-                    const float2 tnz = __ffma2_rn(make_float2(plane_q(nearz, j, magic), plane_q(nearz, j + 1, magic)), aiz2, aoz2);
-                    const float2 tfx = __ffma2_rn(make_float2(plane_q(farx, j, magic), plane_q(farx, j + 1, magic)), aix2, aox2);
-                    const float2 tfy = __ffma2_rn(make_float2(plane_q(fary, j, magic), plane_q(fary, j + 1, magic)), aiy2, aoy2);
-                    const float2 tfz = __ffma2_rn(make_float2(plane_q(farz, j, magic), plane_q(farz, j + 1, magic)), aiz2, aoz2);
-                    const float tn0 = fmaxf(fmaxf(tnx.x, tny.x), fmaxf(tnz.x, tmin));
-                    const float tf0 = fminf(fminf(tfx.x, tfy.x), fminf(tfz.x, hit.t));
-                    const float tn1 = fmaxf(fmaxf(tnx.y, tny.y), fmaxf(tnz.y, tmin));
-                    const float tf1 = fminf(fminf(tfx.y, tfy.y), fminf(tfz.y, hit.t));
-                    const uint32_t cb0 = (child_bits4 >> (8 * j)) & 0xFFu, bi0 = (bit_index4 >> (8 * j)) & 0xFFu;
-                    const uint32_t cb1 = (child_bits4 >> (8 * j + 8)) & 0xFFu, bi1 = (bit_index4 >> (8 * j + 8)) & 0xFFu;
-                    hitmask |= (tn0 <= tf0) ? (cb0 << bi0) : 0u;
-                    hitmask |= (tn1 <= tf1) ? (cb1 << bi1) : 0u;
-                }
-            }
-            ng_base = w1.x;
-            ng_mask = (hitmask & 0xFF000000u) | (e >> 24);
-            tg_base = w1.y;
-            tg_mask = hitmask & 0x00FFFFFFu;
-        }
-#else
         // ---- vote: triangle phase when at least a third of the working lanes hold triangles.  (A lane
         // with a ray always holds node work or triangles here, so "nobody has node work" already implies
         // that every working lane votes for triangles.)
@@ -471,24 +339,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
             ng_mask = (hitmask & 0xFF000000u) | (e >> 24);
             tg_base = w1.y;
             tg_mask = hitmask & 0x00FFFFFFu;
-#if PT_PREFETCH_TRI
-            if (tg_mask != 0) {
-                const char* tp = reinterpret_cast<const char*>(tris + (tg_base + (uint32_t)(31 - __clz(tg_mask))));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(tp));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 32));
-            }
-#endif
-#if PT_PREFETCH_NODE
-            if (ng_mask > 0x00FFFFFFu) {
-                const uint32_t nslot = (uint32_t)(31 - __clz(ng_mask) - 24) ^ (octinv4 & 0xFFu);
-                const uint32_t nrel = (uint32_t)__popc((ng_mask & 0xFFu) & ~(0xFFFFFFFFu << nslot));
-                const char* np2 = reinterpret_cast<const char*>(nodes + (ng_base + nrel));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(np2));
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(np2 + 64));
-            }
-#endif
         }
-#endif
     }
 #undef PT_PUSH
 #if PT_TIMELINE

@@ -12,13 +12,6 @@
 
 #include "device_ctx.h"
 #include "pt_walk_warp.cuh"
-#ifndef PT_BATCH_TRI
-#define PT_BATCH_TRI 0         // 1: the walker kernels use warp_walk_batch (deferred, batched triangle tests)
-#endif
-#if PT_BATCH_TRI
-#include "pt_walk_batch.cuh"
-#define warp_walk warp_walk_batch
-#endif
 
 namespace pt {
 
@@ -147,7 +140,7 @@ __global__ void __launch_bounds__(kWalkBlock, kWalkMinBlocks) k_extend(SceneView
         const uint32_t* q = (k & 1) ? la.queue[1] : la.queue[0];
         warp_walk<COUNT, false, true>(sv.nodes, sv.tris, n, la.cursor + k,
                          LaneRaySource{(k & 1) ? la.ray_o[1] : la.ray_o[0], (k & 1) ? la.ray_d[1] : la.ray_d[0], q, la.susp},
-                         LaneHitSink{la.hit, q, la.susp}, wc, sv.plane_magic, la.no_park == 0);
+                         LaneHitSink{la.hit, q, la.susp}, wc, sv.plane_magic);
     }
     if (COUNT) {
         unsigned long long a = wc.nodes, b = wc.tris;
@@ -277,88 +270,6 @@ __global__ void __launch_bounds__(kBlock, PT_SHADE_MIN_BLOCKS) k_shade(SceneView
                 st4(la.sh_c + pos, f4{L.sh_c.x, L.sh_c.y, L.sh_c.z, u2f(shadow_flags)});
                 st4(la.sh_f + pos, f4{last_term.x, last_term.y, last_term.z, 0.0f});
             }
-        }
-    }
-}
-
-// ---- k_fused: the tail of a frame.  With one RNG stream per pixel the queue ends in a long tail: a few
-// thousand pixels with long paths still have hundreds of segments to go, and every wavefront iteration then costs
-// the latency of the longest single walk of the launch (~0.1 ms, whatever the queue length) plus two launches,
-// for one segment per pixel.  Below a queue length the host switches to this kernel: one thread per queued lane
-// runs up to `segments` whole segments — scalar walk (walk_closest, the walker the host emulation runs; same
-// hits bit for bit as the warp walker, tests/test_gpu_parity.py) then shade_lane — and writes the survivors to the
-// other state set exactly as k_shade does.  A lane's operations and their order are those of the wavefront, so
-// the frame stays bit-identical; SIMD efficiency is poor, which does not matter while most of the GPU is idle.
-// Input lanes must not be parked (the host runs one wavefront iteration with LaneArrays::no_park first).
-// la.pending[k] is DEcremented by the segments traced beyond the first of each lane, so that the host's
-// rays += queue length - pending stays exact.
-__global__ void __launch_bounds__(64) k_fused(SceneView sv, LaneArrays la, int k, int segments) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool odd = (k & 1) != 0;
-    const f4 *in_o = odd ? la.ray_o[1] : la.ray_o[0], *in_d = odd ? la.ray_d[1] : la.ray_d[0], *in_t = odd ? la.thr[1] : la.thr[0];
-    f4 *out_o = odd ? la.ray_o[0] : la.ray_o[1], *out_d = odd ? la.ray_d[0] : la.ray_d[1], *out_t = odd ? la.thr[0] : la.thr[1];
-    const uint32_t* in_q = odd ? la.queue[1] : la.queue[0];
-    uint32_t* out_q = odd ? la.queue[0] : la.queue[1];
-    const uint32_t n = la.counts[k];
-    bool keep = false;
-    uint32_t extra = 0, lane = 0;
-    LaneState L;
-    if (i < n) {
-        lane = in_q[i];
-        const f4 o = ld4(in_o + i), d = ld4(in_d + i), t = ld4(in_t + i);
-        f4 s = ld4(la.sum + lane);
-        L.o = f3{o.x, o.y, o.z};
-        L.prev_pdf = o.w;
-        L.d = f3{d.x, d.y, d.z};
-        L.thr = f3{t.x, t.y, t.z};
-        L.rng = f2u(t.w);
-        const uint32_t ctl = f2u(d.w);
-        L.sample = ctl_sample(ctl);
-        L.depth = ctl_depth(ctl);
-        L.lobe = ctl_lobe(ctl);
-        L.max_samples = lane_samples(sv, lane);
-        int px, py;
-        lane_pixel(sv, lane, px, py);
-        bool dirty = false;
-        keep = true;
-        for (int seg = 0; seg < segments; ++seg) {
-            Hit h;
-            walk_closest<false>(sv.nodes, sv.tris, L.o, L.d, kTMin, kTMax, h, nullptr);
-            if (seg) ++extra;
-            const ShadeResult r = shade_lane<false>(sv, L, h, px, py);
-            if (L.sample_ended) {  // color += trace_path(...), in sample order
-                s.x += L.contrib.x;
-                s.y += L.contrib.y;
-                s.z += L.contrib.z;
-                s.w += sample_lum2(L.contrib);
-                dirty = true;
-            }
-            if (r != LANE_CONTINUE) {
-                keep = false;
-                break;
-            }
-        }
-        if (dirty) st4(la.sum + lane, s);
-        if (!keep) la.rng_save[lane] = L.rng;
-    }
-    {
-        uint32_t e = extra;
-        for (int sh = 16; sh > 0; sh >>= 1) e += __shfl_down_sync(0xffffffffu, e, sh);
-        if ((threadIdx.x & 31) == 0 && e) atomicSub(la.pending + k, e);
-    }
-    const unsigned m = __ballot_sync(0xffffffffu, keep);
-    if (m) {
-        const int lid = threadIdx.x & 31;
-        const int leader = __ffs(m) - 1;
-        uint32_t base = 0;
-        if (lid == leader) base = atomicAdd(la.counts + k + 1, (uint32_t)__popc(m));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (keep) {
-            const uint32_t pos = base + __popc(m & ((1u << lid) - 1u));
-            st4(out_o + pos, f4{L.o.x, L.o.y, L.o.z, 0.0f});
-            st4(out_d + pos, f4{L.d.x, L.d.y, L.d.z, u2f(pack_ctl(L.sample, L.depth, L.lobe))});
-            st4(out_t + pos, f4{L.thr.x, L.thr.y, L.thr.z, u2f(L.rng)});
-            out_q[pos] = lane;
         }
     }
 }
@@ -619,9 +530,6 @@ __global__ void __launch_bounds__(256) k_tri_records(const f4* __restrict__ pos,
 }
 void launch_tri_records(const f4* pos, const f4* nrm, const int32_t* idx4, uint32_t n, TriShade* out, cudaStream_t st) {
     k_tri_records<<<blocks(n, 256), 256, 0, st>>>(pos, nrm, idx4, n, out);
-}
-void launch_fused(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, int segments, cudaStream_t st) {
-    k_fused<<<blocks(max_count, 64), 64, 0, st>>>(sv, la, k, segments);
 }
 void launch_shadow(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, cudaStream_t st) {
     k_shadow<<<pblocks(max_count), kWalkBlock, 0, st>>>(sv, la, k);

@@ -1,6 +1,6 @@
 #!/bin/bash
 # A/B libraries of the CUDA path: tools/build_variants.sh name "-DPT_X=.. -DPT_Y=.." [name flags]...
-# -> owl_path_tracer_b200/lib/variants/libb200pt_<name>.so   (select with B200PT_LIB=<path>)
+# -> owl_path_tracer_b200/lib/variants/libb200pt_<name>.so   (bound explicitly: tools/ab.py name=<path>, owl_path_tracer_b200.use_library)
 set -e
 cd "$(dirname "$0")/.."
 CSRC=owl_path_tracer_b200/csrc

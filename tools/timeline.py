@@ -1,4 +1,5 @@
-"""Per-warp timeline of single k_extend launches (PT_TIMELINE build, B200PT_LIB=.../libb200pt_timeline.so):
+"""Per-warp timeline of single k_extend launches.  Needs a development build (tools/build_variants.sh timeline
+"-DPT_TIMELINE=1 -DB200PT_DEV=1"), passed as the first argument: python tools/timeline.py <path/to/libb200pt_timeline.so>:
 when does each persistent warp start, see the queue drained, and exit; how many rays and loop steps it ran."""
 import json, os, sys
 from pathlib import Path
@@ -7,6 +8,7 @@ sys.path.insert(0, str(R)); sys.path.insert(0, str(R / "tests"))
 os.environ.setdefault("B200PT_QUIET", "1")
 import numpy as np
 import owl_path_tracer_b200 as pt
+pt.use_library(sys.argv[1])
 out = R / "gpurun_out"; out.mkdir(exist_ok=True)
 sc = pt.Scene(scene="dragon", width=1920, height=1080, spp=32, depth=8, env="color", env_intensity=0.0)
 ctx = pt.Context(flags=pt.FLAG_TIMING); ctx.bind(sc); ctx.render()
