@@ -285,6 +285,30 @@ int b200pt_primary_hits(b200pt_ctx* ctx, b200pt_hit* out);
 int b200pt_trace(b200pt_ctx* ctx, const float* origins, const float* dirs, int32_t n,
                  float tmin, float tmax, b200pt_hit* out);
 
+/* ---- frames back to back (the reference's real workload: test_loop renders 1 + 100/step frames in a row with only the
+ * materials changing, application.hpp:89-108).  With one RNG stream per pixel a frame ends in a long tail — the
+ * average launch carries a third of the lanes — so a PIPELINE of contexts bound to the same scene starts frame k+1
+ * while frame k drains.  Every frame is rendered by exactly the code of b200pt_render_frame on its own context:
+ * frames stay bit-identical to the blocking call.  One host thread per slot lives inside the pipeline object. */
+typedef void (*b200pt_drain_fn)(void* user);
+/* progress notification used by the pipeline (and usable on its own): fn is called once per frame, from inside
+ * b200pt_render / b200pt_render_frame, when the number of pixels still in flight first falls below
+ * fraction * (lanes of the frame); fraction <= 0 or fn == NULL removes it. */
+int b200pt_set_drain_callback(b200pt_ctx* ctx, float fraction, b200pt_drain_fn fn, void* user);
+
+typedef struct b200pt_pipeline b200pt_pipeline;
+/* slots: n_slots >= 1 contexts of the SAME rank with the same scene, camera and frame size bound (the pipeline does not
+ * own them).  start_fraction: frame k+1 starts once frame k has fewer than start_fraction * lanes pixels in flight
+ * (0: default 0.5).  Several ranks: slot j of every rank must share a communicator (b200pt_comm_init_rank on each
+ * slot's context); the frames' reduces are issued in frame order on every rank. */
+int b200pt_pipeline_create(b200pt_ctx* const* slots, int32_t n_slots, float start_fraction, b200pt_pipeline** out);
+/* Queue one frame: materials are copied, rgba_out (W*H uint32, may be NULL; ignored on ranks > 0) is written when the
+ * frame completes.  Blocks only while the slot that takes the frame is still busy with an earlier one. */
+int b200pt_pipeline_submit(b200pt_pipeline* p, const b200pt_material* materials, int32_t count, uint32_t* rgba_out);
+/* Block until every submitted frame is complete; returns the first error any frame met (b200pt_last_error). */
+int b200pt_pipeline_wait(b200pt_pipeline* p);
+int b200pt_pipeline_destroy(b200pt_pipeline* p);   /* waits first */
+
 /* b200pt_trace without any allocation.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
  * Same arguments, same results as b200pt_trace (host pointers in and out); the kernel's staging (ray cursor, origins,

@@ -160,6 +160,11 @@ def lib() -> C.CDLL:
     L.b200pt_framebuffer_f32.argtypes = [P, C.POINTER(P)]
     L.b200pt_primary_hits.argtypes = [P, P]
     L.b200pt_trace.argtypes = [P, P, P, C.c_int32, C.c_float, C.c_float, P]
+    L.b200pt_set_drain_callback.argtypes = [P, C.c_float, P, P]
+    L.b200pt_pipeline_create.argtypes = [C.POINTER(P), C.c_int32, C.c_float, C.POINTER(P)]
+    L.b200pt_pipeline_submit.argtypes = [P, P, C.c_int32, P]
+    L.b200pt_pipeline_wait.argtypes = [P]
+    L.b200pt_pipeline_destroy.argtypes = [P]
     L.b200pt_trace_static.argtypes = [P, P, P, C.c_int32, C.c_float, C.c_float, P]
     L.b200pt_get_stats.argtypes = [P, C.POINTER(Stats)]
     L.b200pt_sample_disney.argtypes = [P, C.c_int32] + [P] * 9
@@ -245,7 +250,7 @@ def _view(addr, shape, dtype):
 
 
 from ._scene import Scene  # noqa: E402
-from ._context import Context  # noqa: E402
+from ._context import Context, Pipeline  # noqa: E402
 
-__all__ = ["Scene", "Context", "Config", "Stats", "B200ptError", "MATERIAL_DTYPE", "HIT_DTYPE",
+__all__ = ["Scene", "Context", "Pipeline", "Config", "Stats", "B200ptError", "MATERIAL_DTYPE", "HIT_DTYPE",
            "SHARD_SPP", "SHARD_ROWS", "FLAG_COUNTERS", "FLAG_TIMING", "FLAG_NEE", "lib", "host_lib", "scene_lib", "use_library", "ASSETS_DIR"]

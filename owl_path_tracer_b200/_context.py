@@ -234,3 +234,41 @@ class Context:
         tris = np.empty((nt.value, 20), np.float32)   # 80-byte blocks of two triangles (pt_bvh8.h TriPair)
         self._ck(self._L.b200pt_export_bvh(self._h, _ptr(nodes), C.byref(nn), _ptr(tris), C.byref(nt)), "export_bvh")
         return nodes, tris
+
+
+class Pipeline:
+    """b200pt_pipeline_*: frames back to back on several contexts bound to the same scene; frame k+1 starts while frame k
+    drains.  Every frame is bit-identical to the blocking render of its materials."""
+
+    def __init__(self, contexts, start_fraction=0.0):
+        self._L = lib()
+        self._ctxs = list(contexts)
+        arr = (C.c_void_p * len(self._ctxs))(*[c._h for c in self._ctxs])
+        self._h = C.c_void_p()
+        if self._L.b200pt_pipeline_create(arr, len(self._ctxs), float(start_fraction), C.byref(self._h)) != 0:
+            raise B200ptError("pipeline_create: " + self._L.b200pt_last_error().decode())
+        self._keep = []
+
+    def submit(self, mats=None, out=None):
+        """Queue one frame; `out` ((H, W) uint32, C-contiguous) is filled when the frame completes (after wait())."""
+        m = None if mats is None else np.ascontiguousarray(mats, MATERIAL_DTYPE)
+        self._keep.append((m, out))
+        if self._L.b200pt_pipeline_submit(self._h, _ptr(m), 0 if m is None else m.shape[0], _ptr(out)) != 0:
+            raise B200ptError("pipeline_submit: " + self._L.b200pt_last_error().decode())
+
+    def wait(self):
+        r = self._L.b200pt_pipeline_wait(self._h)
+        self._keep.clear()
+        if r != 0:
+            raise B200ptError("pipeline: " + self._L.b200pt_last_error().decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.b200pt_pipeline_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -99,6 +99,10 @@ struct b200pt_ctx {
     size_t fb_pixels = 0;
     bool rendered = false, resolved = false;
     bool mean_on_host = false;   // h_mean holds the float frame of the last resolve
+    // b200pt_set_drain_callback
+    float drain_fraction = 0.0f;
+    b200pt_drain_fn drain_fn = nullptr;
+    void* drain_user = nullptr;
     // progressive passes (b200pt_render_pass): samples of every pixel already in `sum`; 0 = no frame in progress
     int l2_persist_mode = 0;    // B200PT_L2_PERSIST experiment (render_local)
     int pass_done = 0;
@@ -776,6 +780,7 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
             if (active[p]) return true;
         return false;
     };
+    bool drain_armed = c->drain_fn != nullptr && c->drain_fraction > 0.0f;
     while (any_active()) {
         // the parts' launches are interleaved so that neither stream runs ahead of the other in the queue
         for (int k = 0; k < kBatch; ++k) {
@@ -833,6 +838,14 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
             }
             active[p] = hc[kBatch];
         }
+        if (drain_armed) {   // b200pt_set_drain_callback: the frame's queue fell below the caller's fraction
+            uint64_t in_flight = 0;
+            for (int p = 0; p < parts; ++p) in_flight += active[p];
+            if ((double)in_flight < (double)c->drain_fraction * (double)sv.n_lanes) {
+                drain_armed = false;
+                c->drain_fn(c->drain_user);
+            }
+        }
         if (timing) {
             for (int k = 0; k < kBatch; ++k) {
                 float a = 0, b = 0, s = 0;
@@ -855,6 +868,7 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
             timeline_dump(e);
         }
 #endif
+    if (drain_armed) c->drain_fn(c->drain_user);   // a frame that never fell below the fraction before it ended
     for (int p = 1; p < parts; ++p) {  // the frame is complete on `stream` once every part is
         CU(cudaEventRecord(c->part_done[p], c->part_stream[p]));
         CU(cudaStreamWaitEvent(st, c->part_done[p], 0));
@@ -892,6 +906,14 @@ static int render_local(b200pt_ctx* c, int first_sample = 0, int n_pass = 0) {
     c->resolved = false;
     c->resolve_samples = n_pass > 0 ? first_sample + n_pass : c->max_samples;
     c->pass_done = n_pass > 0 ? first_sample + n_pass : 0;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_set_drain_callback(b200pt_ctx* c, float fraction, b200pt_drain_fn fn, void* user) {
+    if (!c) return fail(B200PT_ERR_INVALID, "set_drain_callback: null context");
+    c->drain_fraction = (fn && fraction > 0.0f) ? fraction : 0.0f;
+    c->drain_fn = c->drain_fraction > 0.0f ? fn : nullptr;
+    c->drain_user = user;
     return B200PT_OK;
 }
 
@@ -1396,5 +1418,160 @@ extern "C" int b200pt_trace_static(b200pt_ctx* c, const float* origins, const fl
         }
         memcpy(reinterpret_cast<unsigned char*>(out) + sizeof(b200pt_hit) * (size_t)i, &h, sizeof h);
     }
+    return B200PT_OK;
+}
+
+// ---------------------------------------------------------------------------- frame pipeline (b200pt_pipeline_*)
+// One worker thread per slot.  Frame s goes to slot s % n and may start rendering once frame s-1 reported that its queue
+// is draining (b200pt_set_drain_callback) or ended; the frames' reduces (several ranks) run in frame order.
+#include <condition_variable>
+#include <deque>
+
+struct b200pt_pipeline {
+    struct Job {
+        uint64_t seq = 0;
+        std::vector<b200pt_material> mats;
+        uint32_t* rgba_out = nullptr;
+    };
+    struct Slot {
+        b200pt_pipeline* owner = nullptr;
+        b200pt_ctx* ctx = nullptr;
+        std::thread worker;
+        bool has_job = false, busy = false;
+        Job job;
+        uint64_t running_seq = 0;
+    };
+    std::vector<Slot> slots;
+    std::mutex mu;
+    std::condition_variable cv;
+    uint64_t submitted = 0, completed = 0;
+    uint64_t drained_upto = 0;   // frames with seq < drained_upto have drained (or ended)
+    uint64_t reduce_turn = 0;    // seq of the frame whose reduce may run next
+    bool stop = false;
+    int status = B200PT_OK;
+    std::string error;
+
+    void mark_drained(uint64_t seq) {
+        std::lock_guard<std::mutex> g(mu);
+        if (drained_upto < seq + 1) drained_upto = seq + 1;
+        cv.notify_all();
+    }
+    void record_error(int code) {   // g_error of the calling thread holds the message
+        std::lock_guard<std::mutex> g(mu);
+        if (status == B200PT_OK) {
+            status = code;
+            error = g_error;
+        }
+    }
+    static void on_drain(void* user) {
+        Slot* s = static_cast<Slot*>(user);
+        s->owner->mark_drained(s->running_seq);
+    }
+    void run(Slot* s) {
+        for (;;) {
+            Job job;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return stop || (s->has_job && drained_upto >= s->job.seq); });
+                if (stop && !s->has_job) return;
+                job = std::move(s->job);
+                s->has_job = false;
+                s->busy = true;
+                s->running_seq = job.seq;
+            }
+            b200pt_ctx* c = s->ctx;
+            int r = B200PT_OK;
+            if (!job.mats.empty()) r = b200pt_set_materials(c, job.mats.data(), (int32_t)job.mats.size());
+            if (r == B200PT_OK) r = check_ready(c, "pipeline");
+            if (r == B200PT_OK) r = render_local(c);
+            mark_drained(job.seq);   // whatever happened, the next frame must not wait for this one
+            {   // the collective in frame order (every rank issues the same sequence); a failed frame still takes its turn
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return reduce_turn == job.seq; });
+            }
+            if (r == B200PT_OK && c->cfg.world_size > 1) r = b200pt_reduce(c);
+            {
+                std::lock_guard<std::mutex> g(mu);
+                reduce_turn = job.seq + 1;
+                cv.notify_all();
+            }
+            if (r == B200PT_OK && c->cfg.rank == 0) {
+                r = b200pt_resolve(c);
+                if (r == B200PT_OK && job.rgba_out) memcpy(job.rgba_out, c->h_rgba, sizeof(uint32_t) * c->fb_pixels);
+            }
+            if (r != B200PT_OK) record_error(r);
+            {
+                std::lock_guard<std::mutex> g(mu);
+                s->busy = false;
+                ++completed;
+                cv.notify_all();
+            }
+        }
+    }
+};
+
+extern "C" int b200pt_pipeline_create(b200pt_ctx* const* slots, int32_t n, float start_fraction, b200pt_pipeline** out) {
+    if (!slots || n < 1 || !out) return fail(B200PT_ERR_INVALID, "pipeline_create: null / empty");
+    for (int i = 0; i < n; ++i) {
+        if (!slots[i]) return fail(B200PT_ERR_INVALID, "pipeline_create: null slot");
+        if (slots[i]->cfg.rank != slots[0]->cfg.rank || slots[i]->cfg.world_size != slots[0]->cfg.world_size ||
+            slots[i]->width != slots[0]->width || slots[i]->height != slots[0]->height)
+            return fail(B200PT_ERR_INVALID, "pipeline_create: the slots must be contexts of one rank with the same frame size");
+        for (int j = 0; j < i; ++j)
+            if (slots[j] == slots[i]) return fail(B200PT_ERR_INVALID, "pipeline_create: a context can fill one slot only");
+    }
+    auto* p = new b200pt_pipeline();
+    p->slots.resize((size_t)n);
+    const float f = start_fraction > 0.0f ? start_fraction : 0.5f;
+    for (int i = 0; i < n; ++i) {
+        b200pt_pipeline::Slot& s = p->slots[(size_t)i];
+        s.owner = p;
+        s.ctx = slots[i];
+        b200pt_set_drain_callback(s.ctx, f, &b200pt_pipeline::on_drain, &s);
+    }
+    for (auto& s : p->slots) s.worker = std::thread([p, sp = &s] { p->run(sp); });
+    *out = p;
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_pipeline_submit(b200pt_pipeline* p, const b200pt_material* m, int32_t nm, uint32_t* rgba_out) {
+    if (!p) return fail(B200PT_ERR_INVALID, "pipeline_submit: null");
+    std::unique_lock<std::mutex> lk(p->mu);
+    b200pt_pipeline::Slot& s = p->slots[(size_t)(p->submitted % p->slots.size())];
+    p->cv.wait(lk, [&] { return !s.has_job && !s.busy; });
+    s.job.seq = p->submitted++;
+    s.job.mats.assign(m ? m : nullptr, m ? m + nm : nullptr);
+    s.job.rgba_out = rgba_out;
+    s.has_job = true;
+    p->cv.notify_all();
+    return B200PT_OK;
+}
+
+extern "C" int b200pt_pipeline_wait(b200pt_pipeline* p) {
+    if (!p) return fail(B200PT_ERR_INVALID, "pipeline_wait: null");
+    std::unique_lock<std::mutex> lk(p->mu);
+    p->cv.wait(lk, [&] { return p->completed == p->submitted; });
+    const int st = p->status;
+    if (st != B200PT_OK) {
+        g_error = p->error;
+        p->status = B200PT_OK;
+        p->error.clear();
+    }
+    return st;
+}
+
+extern "C" int b200pt_pipeline_destroy(b200pt_pipeline* p) {
+    if (!p) return B200PT_OK;
+    b200pt_pipeline_wait(p);
+    {
+        std::lock_guard<std::mutex> g(p->mu);
+        p->stop = true;
+        p->cv.notify_all();
+    }
+    for (auto& s : p->slots) {
+        s.worker.join();
+        b200pt_set_drain_callback(s.ctx, 0.0f, nullptr, nullptr);
+    }
+    delete p;
     return B200PT_OK;
 }

@@ -157,7 +157,20 @@ PT_HD double copysign_d(double mag, double sgn) {
 
 }  // namespace dmi
 
+// -DPT_LIBM_MATH=1 (measurement builds only, tools/build_variants.sh): the DEVICE code calls CUDA's float functions
+// instead — what the deterministic design costs (frames then differ from the oracle in the last ulp of some draws
+// and are compared by relMSE, not by bits).  The product is built without it.
+#ifndef PT_LIBM_MATH
+#define PT_LIBM_MATH 0
+#endif
+#if PT_LIBM_MATH && defined(__CUDA_ARCH__)
+#define PT_LIBM(expr) return (expr)
+#else
+#define PT_LIBM(expr)
+#endif
+
 PT_HD float dm_sin(float x) {
+    PT_LIBM(sinf(x));
     double xd = x;
     if (dmi::is_nan(xd) || dmi::is_inf(xd)) return dmi::qnan();
     double s, c;
@@ -165,6 +178,7 @@ PT_HD float dm_sin(float x) {
     return (float)s;
 }
 PT_HD float dm_cos(float x) {
+    PT_LIBM(cosf(x));
     double xd = x;
     if (dmi::is_nan(xd) || dmi::is_inf(xd)) return dmi::qnan();
     double s, c;
@@ -172,6 +186,7 @@ PT_HD float dm_cos(float x) {
     return (float)c;
 }
 PT_HD float dm_tan(float x) {
+    PT_LIBM(tanf(x));
     double xd = x;
     if (dmi::is_nan(xd) || dmi::is_inf(xd)) return dmi::qnan();
     double s, c;
@@ -179,12 +194,14 @@ PT_HD float dm_tan(float x) {
     return (float)(s / c);
 }
 PT_HD float dm_atan(float x) {
+    PT_LIBM(atanf(x));
     double xd = x;
     if (dmi::is_nan(xd)) return dmi::qnan();
     double a = dmi::atan_core(xd < 0 ? -xd : xd);
     return (float)dmi::copysign_d(a, xd);
 }
 PT_HD float dm_atan2(float y, float x) {
+    PT_LIBM(atan2f(y, x));
     double yd = y, xd = x;
     if (dmi::is_nan(yd) || dmi::is_nan(xd)) return dmi::qnan();
     bool xneg = (xd < 0) || (xd == 0 && (1.0 / xd) < 0);
@@ -201,6 +218,7 @@ PT_HD float dm_atan2(float y, float x) {
     return (float)dmi::copysign_d(a, yd);
 }
 PT_HD float dm_asin(float x) {
+    PT_LIBM(asinf(x));
     double xd = x;
     if (dmi::is_nan(xd) || xd > 1.0 || xd < -1.0) return dmi::qnan();
     double c = sqrt((1.0 - xd) * (1.0 + xd));
@@ -209,6 +227,7 @@ PT_HD float dm_asin(float x) {
     return (float)dmi::copysign_d(a, xd);
 }
 PT_HD float dm_log(float x) {
+    PT_LIBM(logf(x));
     double xd = x;
     if (dmi::is_nan(xd) || xd < 0) return dmi::qnan();
     if (xd == 0) return (float)(-HUGE_VAL);
@@ -217,6 +236,7 @@ PT_HD float dm_log(float x) {
 }
 // x >= 0 is the only domain the integrator uses (colours, alpha^2); x < 0 -> NaN.
 PT_HD float dm_pow(float x, float y) {
+    PT_LIBM(powf(x, y));
     double xd = x, yd = y;
     if (yd == 0 || xd == 1.0) return 1.0f;
     if (dmi::is_nan(xd) || dmi::is_nan(yd) || xd < 0) return dmi::qnan();

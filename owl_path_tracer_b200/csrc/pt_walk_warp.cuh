@@ -48,8 +48,41 @@ __device__ __forceinline__ unsigned long long timeline_now() {
     return t;
 }
 #endif
+#ifndef PT_WALK_BLOCK
+#define PT_WALK_BLOCK 128       // threads per block of the persistent walker kernels
+#endif
+#ifndef PT_SMEM_STACK
+#define PT_SMEM_STACK 0         // traversal-stack entries per lane kept in shared memory (the rest in local memory)
+#endif
 constexpr int kRefill = PT_REFILL;
 constexpr int kWalkStack = 2 * kStackSize;  // per tree level at most one node group + one postponed triangle group
+constexpr int kSmemStack = PT_SMEM_STACK;
+
+// The entries of a lane's traversal stack BELOW its top (the top lives in registers).  Entry e < kSmemStack sits in
+// shared memory at [e][thread] (consecutive threads -> consecutive 8-byte words: conflict-free), deeper entries in the
+// lane's local-memory array.  With kSmemStack == 0 this is the plain local array.
+struct WalkStack {
+    uint2* local;
+#if PT_SMEM_STACK > 0
+    uint2* shared;   // &s_stack[threadIdx.x]
+#endif
+    __device__ __forceinline__ uint2 ld(int e) const {
+#if PT_SMEM_STACK > 0
+        if (e < kSmemStack) return shared[e * PT_WALK_BLOCK];
+        return local[e - kSmemStack];
+#else
+        return local[e];
+#endif
+    }
+    __device__ __forceinline__ void st(int e, uint2 v) const {
+#if PT_SMEM_STACK > 0
+        if (e < kSmemStack) shared[e * PT_WALK_BLOCK] = v;
+        else local[e - kSmemStack] = v;
+#else
+        local[e] = v;
+#endif
+    }
+};
 
 __device__ __forceinline__ u4 ldg4(const u4* p) {
     const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
@@ -96,15 +129,21 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
     // the entries below it in local memory: a pop hands out the registers at once and starts the
     // load of the next entry, which is not needed before the following pop or push — a whole node or
     // triangle step later (the pop used to wait for its own local load: 10 % of all stall samples).
-    uint2 stack[kWalkStack];
+    uint2 stack_local[kWalkStack - kSmemStack];
+#if PT_SMEM_STACK > 0
+    __shared__ uint2 s_stack[PT_SMEM_STACK * PT_WALK_BLOCK];
+    const WalkStack stack{stack_local, s_stack + threadIdx.x};
+#else
+    const WalkStack stack{stack_local};
+#endif
     uint32_t top_b = 0, top_m = 0;
     int sp = 0;
-#define PT_PUSH(B, M)                                        \
-    do {                                                     \
-        if (sp > 0) stack[sp - 1] = make_uint2(top_b, top_m); \
-        top_b = (B);                                         \
-        top_m = (M);                                         \
-        ++sp;                                                \
+#define PT_PUSH(B, M)                                         \
+    do {                                                      \
+        if (sp > 0) stack.st(sp - 1, make_uint2(top_b, top_m)); \
+        top_b = (B);                                          \
+        top_m = (M);                                          \
+        ++sp;                                                 \
     } while (0)
 
 #if PT_TIMELINE
@@ -133,7 +172,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
                 }
                 --sp;
                 if (sp > 0) {
-                    const uint2 nxt = stack[sp - 1];
+                    const uint2 nxt = stack.ld(sp - 1);
                     top_b = nxt.x;
                     top_m = nxt.y;
                 }

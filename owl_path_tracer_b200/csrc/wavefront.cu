@@ -26,9 +26,6 @@ namespace pt {
 #define PT_SHADE_MIN_BLOCKS 4   // register cap of k_shade: 65536 / (128 * blocks)
 #endif
 constexpr int kBlock = 128;
-#ifndef PT_WALK_BLOCK
-#define PT_WALK_BLOCK 128       // threads per block of the persistent walker kernels
-#endif
 constexpr int kWalkBlock = PT_WALK_BLOCK;
 constexpr int kWalkMinBlocks = PT_EXTEND_MIN_BLOCKS * 128 / kWalkBlock;   // same warps per SM whatever the block size
 
@@ -92,7 +89,7 @@ struct LaneRaySource {   // entry i of the current state set
         return (f2u(b.w) >> 31) != 0;   // k_shade sets bit 31 of the control word of a lane whose walk is parked
     }
     __device__ __forceinline__ void restore(uint32_t i, Hit& hit, uint32_t& ng_base, uint32_t& ng_mask, uint32_t& tg_base,
-                                            uint32_t& tg_mask, int& sp, uint32_t& top_b, uint32_t& top_m, uint2* stack) const {
+                                            uint32_t& tg_mask, int& sp, uint32_t& top_b, uint32_t& top_m, const WalkStack& stack) const {
         const u4* p = susp + (size_t)queue[i] * kSuspWords;
         const u4 h = p[0], g = p[1], t = p[2];
         hit = Hit{u2f(h.x), u2f(h.y), u2f(h.z), h.w};
@@ -105,8 +102,8 @@ struct LaneRaySource {   // entry i of the current state set
         top_m = t.z;
         for (int e = 0; e + 1 < sp; e += 2) {
             const u4 w = p[3 + (e >> 1)];
-            stack[e] = make_uint2(w.x, w.y);
-            if (e + 2 < sp) stack[e + 1] = make_uint2(w.z, w.w);
+            stack.st(e, make_uint2(w.x, w.y));
+            if (e + 2 < sp) stack.st(e + 1, make_uint2(w.z, w.w));
         }
     }
 };
@@ -116,14 +113,14 @@ struct LaneHitSink {
     u4* susp;
     __device__ __forceinline__ void store(uint32_t i, const Hit& h) const { st4(hit + i, f4{h.t, h.u, h.v, u2f(h.tri)}); }
     __device__ __forceinline__ void suspend(uint32_t i, const Hit& h, uint32_t ng_base, uint32_t ng_mask, uint32_t tg_base,
-                                            uint32_t tg_mask, int sp, uint32_t top_b, uint32_t top_m, const uint2* stack) const {
+                                            uint32_t tg_mask, int sp, uint32_t top_b, uint32_t top_m, const WalkStack& stack) const {
         u4* p = susp + (size_t)queue[i] * kSuspWords;
         p[0] = u4{f2u(h.t), f2u(h.u), f2u(h.v), h.tri};
         p[1] = u4{ng_base, ng_mask, tg_base, tg_mask};
         p[2] = u4{(uint32_t)sp, top_b, top_m, 0u};
         for (int e = 0; e + 1 < sp; e += 2) {   // entries 0 .. sp-2 live in local memory, the top in registers
-            const uint2 a = stack[e];
-            const uint2 b = (e + 2 < sp) ? stack[e + 1] : make_uint2(0u, 0u);
+            const uint2 a = stack.ld(e);
+            const uint2 b = (e + 2 < sp) ? stack.ld(e + 1) : make_uint2(0u, 0u);
             p[3 + (e >> 1)] = u4{a.x, a.y, b.x, b.y};
         }
         st4(hit + i, f4{0.0f, 0.0f, 0.0f, u2f(kPending)});
