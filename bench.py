@@ -154,6 +154,9 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (a smaller workload is NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity-check", action="store_true")
+    ap.add_argument("--pipeline", type=int, default=2, help="contexts per rank the frames of the timed region rotate over "
+                    "(b200pt_pipeline_*: frame k+1 starts while frame k drains); 1 = the blocking call")
+    ap.add_argument("--start-fraction", type=float, default=0.5)
     ap.add_argument("--detail", type=int, default=0, help="procedural mesh detail (0 = the 871,406-triangle headline stand-in; "
                     "larger values are NOT the headline: they exist to push the BVH out of L2)")
     args = ap.parse_args()
@@ -229,16 +232,55 @@ def main():
                    rays_all=int(r[0]), launches_all=int(r[1]))
         return acc
 
-    for _ in range(args.warmup):
-        step_resident()
+    # Frames back to back (the reference's test_loop renders a sweep of frames with only the materials changing): with
+    # --pipeline S > 1 the K steps go through b200pt_pipeline_* on S contexts of this rank bound to the same scene —
+    # frame k+1 starts while frame k drains; every frame is still one blocking-quality, bit-identical frame of the
+    # headline workload (checked below).  --pipeline 1 times the blocking call.
+    slots = [ctx]
+    for _ in range(max(1, args.pipeline) - 1):
+        c = pt.Context(device=local, rank=rank, world_size=world, shard_mode=pt.SHARD_SPP, flags=0)
+        c.bind(sc)
+        init_comm(c)
+        slots.append(c)
+    pipe = pt.Pipeline(slots, start_fraction=args.start_fraction) if len(slots) > 1 else None
+    step_resident()
+    per_frame = ctx.stats()          # rays / launches of one frame of this rank (every frame is the same frame)
+    outs = [np.empty((sc.height, sc.width), np.uint32) for _ in range(max(2, len(slots) + 1))]
+
+    def timed_frames(k, e2e_mode):
+        barrier()
+        t0 = time.perf_counter()
+        if pipe is None:
+            for _ in range(k):
+                (step_e2e if e2e_mode else step_resident)()
+        else:
+            for i in range(k):
+                # e2e: materials from host memory in (H2D inside), RGBA8 frame out to a host buffer (D2H inside)
+                pipe.submit(mats if e2e_mode else None, outs[i % len(outs)] if (e2e_mode and rank == 0) else None)
+            pipe.wait()
+        barrier()
+        ms = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        r = torch.tensor([per_frame["rays"] * k, per_frame["kernel_launches"] * k], dtype=torch.int64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(r, op=dist.ReduceOp.SUM)
+        return dict(wall_ms=float(t[0]), rays_all=int(r[0]), launches_all=int(r[1]))
+
+    timed_frames(args.warmup, False)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    res = timed(step_resident, args.steps)
+    res = timed_frames(args.steps, False)
     clocks = sampler.stop() if rank == 0 else None
-    for _ in range(min(args.warmup, 1)):
+    timed_frames(min(args.warmup, 1), True)
+    e2e = timed_frames(args.steps, True)
+    # the blocking call on one context, for the record: the latency of a single frame
+    blocking = timed(step_resident, min(args.steps, 3))
+    pipelined_equals_blocking = None
+    if pipe is not None and rank == 0:
         step_e2e()
-    e2e = timed(step_e2e, args.steps)
+        pipelined_equals_blocking = bool((outs[(args.steps - 1) % len(outs)] == frame_host).all())
 
     # what was timed is checked: rank 0 holds the resolved frame of the last step
     parity = None
@@ -257,11 +299,11 @@ def main():
         main_ctx, ctx = ctx, c8
         for _ in range(min(args.warmup, 2)):
             step_resident()
-        r8 = timed(step_resident, args.steps)
+        r8 = timed(step_resident, min(args.steps, 3))
         ctx = main_ctx
         c8.close()
         tm = dict(streams_per_pixel=args.streams_mode, value=r8["rays_all"] / (r8["wall_ms"] * 1e-3) * 1e-6, unit="Mrays/s",
-                  ms_per_step=r8["wall_ms"] / args.steps,
+                  ms_per_step=r8["wall_ms"] / min(args.steps, 3),
                   note="same frame, same total spp; every pixel rendered by %d concurrent RNG streams (the streams of a %d-rank "
                        "SPP-sharded job, bit-equal to the oracle with that keying: tests/test_gpu_parity.py); not the reference's "
                        "single-stream order, hence not the headline" % (args.streams_mode, world * args.streams_mode))
@@ -313,7 +355,7 @@ def main():
                     share_of_step=kt["extend_ms"] / kt["render_ms"] if kt["render_ms"] else None,
                     timing_pass="one extra frame of the workload on one stream with events around every launch "
                                 "(%.1f ms; the timed region runs 2 concurrent sub-frames, %.1f ms per frame)"
-                                % (kt["render_ms"], res["render_ms"] / args.steps),
+                                % (kt["render_ms"], blocking["wall_ms"] / min(args.steps, 3)),
                     note="BVH (%.0f MB) is L2-resident; HBM peak is the required denominator, see DESIGN.md" % (s2["bvh_bytes"] / 1e6))
 
     cpu = None
@@ -339,7 +381,11 @@ def main():
                         l2="inputs larger than L2: lane state 330 MB + BVH 49 MB per GPU vs 126 MB L2, no flush between steps",
                         rng="one stream per pixel through all its samples (reference order); rank r seeds random(x, y + r*H)"),
             spp_per_s=total_spp / (ms_step * 1e-3),
-            device_ms_per_step=res["render_ms"] / args.steps,
+            frames=dict(mode=("pipeline of %d contexts per rank (b200pt_pipeline_*), frame k+1 starts when frame k has < %.0f %% of its "
+                              "pixels in flight" % (len(slots), 100 * args.start_fraction)) if pipe is not None else "blocking call",
+                        single_frame_ms=blocking["wall_ms"] / min(args.steps, 3),
+                        single_frame_mrays=blocking["rays_all"] / (blocking["wall_ms"] * 1e-3) * 1e-6,
+                        pipelined_frame_equals_blocking_frame=pipelined_equals_blocking),
             e2e=dict(value=e2e["rays_all"] / (e2e["wall_ms"] * 1e-3) * 1e-6, unit="Mrays/s",
                      h2d_bytes_per_step=int(mats.nbytes), d2h_bytes_per_step=int(sc.width * sc.height * 4),
                      ms_per_step=e2e["wall_ms"] / args.steps),
@@ -350,7 +396,10 @@ def main():
                    "oracle == the reference's own device code bit for bit (tests/test_ref_device.py, oracle/_ref)",
             notes=sc.notes)
         emit(line)
-    ctx.close()
+    if pipe is not None:
+        pipe.close()
+    for c in slots:
+        c.close()
     if world > 1:
         dist.destroy_process_group()
 

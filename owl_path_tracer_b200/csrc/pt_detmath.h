@@ -4,7 +4,9 @@
 // (device.cu:25-26, disney_specular.cuh:69-74,177, disney_clearcoat.cuh:19,26,
 // disney_helper.cuh:6, sample_methods.hpp:38-41).  CUDA's libm and glibc do not
 // agree bit for bit, so paths would diverge after the first bounce and the GPU could
-// only be checked statistically.  These versions evaluate in binary64 with nothing
+// only be checked statistically.  log and pow evaluate in binary64 (below); since round 2 the trigonometric
+// functions evaluate in binary32 (namespace dmf further down) — same principle, same guarantee of identical bits on
+// both sides.  The binary64 versions evaluate with nothing
 // but +,-,*,/,fma,sqrt,floor,frexp,ldexp (all exactly specified by IEEE-754 / exact by
 // construction; the Horner steps of the polynomials are explicit fma() calls — one correctly rounded
 // operation on both sides, half the binary64 instructions of a separate multiply and add, which matter on
@@ -17,6 +19,16 @@
 // tests/test_detmath.py checks every function against numpy float64 on dense grids.
 #pragma once
 #include "pt_defs.h"
+
+// The binary64 routines are OUT OF LINE on the device.  Inlined, ptxas treated them as free arithmetic: k_shade
+// evaluated the three pow() of the sheen tint (3 x log + exp, ~400 binary64 instructions) for EVERY shaded vertex, hoisted
+// above the `sheen <= 0` test that skips them (ncu, round 2: 17 % of k_shade's instructions were binary64 on a scene
+// without sheen).  A call is never speculated.
+#if defined(__CUDACC__)
+#define PT_HD_CALL __host__ __device__ __noinline__ inline
+#else
+#define PT_HD_CALL __attribute__((noinline)) inline
+#endif
 
 namespace pt {
 namespace dmi {  // internals, binary64
@@ -157,6 +169,76 @@ PT_HD double copysign_d(double mag, double sgn) {
 
 }  // namespace dmi
 
+// ---------------------------------------------------------------------------- binary32 internals (round 2)
+// sin / cos / tan / atan / atan2 / asin are evaluated in binary32: Cody-Waite reduction and short minimax polynomials,
+// built from nothing but +, -, *, /, fmaf, sqrtf and floorf — every one of them a single correctly rounded IEEE
+// operation on both sides, so nvcc (-fmad=false) and g++ (-ffp-contract=off) still return the same bits.  Accuracy
+// 1-2 ulp (asin, tan <= 3), the class of CUDA's own sinf / atanf that the reference calls; the binary64 versions
+// they replace were 20 % of k_shade (profiles/r02b_walker_shade_variants_ab.jsonl: CUDA float math -20 %), these cost
+// about what CUDA's do.  log and pow stay in binary64 (rare on the path, and pow needs the extra bits).
+// Coefficients: Chebyshev-node interpolation in 50-digit arithmetic (mpmath), rounded to binary32.
+namespace dmf {
+constexpr float kTwoOverPi = 0.636619747f;
+constexpr float kPio2Hi = 1.57079637f;        // float(pi/2)
+constexpr float kPio2Lo = -4.37113883e-8f;    // float(pi/2 - kPio2Hi)
+constexpr float kPio2Lo2 = -1.7151245e-15f;   // what is left
+constexpr float kPio4Hi = 0.785398185f, kPio4Lo = -2.18556941e-8f;
+constexpr float kPiHi = 3.14159274f, kPiLo = -8.74227766e-8f;
+constexpr float kTrigMax = 100.0f;            // beyond: the binary64 route (the integrator's arguments are below 7; for large
+                                              // k the rounding of x - k pi/2 would cost accuracy next to the zeros)
+
+PT_HD bool is_nan(float v) { return v != v; }
+PT_HD bool is_inf(float v) { return v == (float)HUGE_VAL || v == -(float)HUGE_VAL; }
+PT_HD bool sign_bit(float v) { return (v < 0.0f) || (v == 0.0f && (1.0f / v) < 0.0f); }
+PT_HD float with_sign(float mag, float sgn) {
+    const float a = mag < 0.0f ? -mag : mag;
+    return sign_bit(sgn) ? -a : a;
+}
+// x = k pi/2 + r, |r| <= pi/4 (+ rounding); sin r and cos r; returns k mod 4
+PT_HD int sincos_reduced(float x, float& sr, float& cr) {
+    const float k = floorf(fmaf(x, kTwoOverPi, 0.5f));
+    float r = fmaf(-k, kPio2Hi, x);
+    r = fmaf(-k, kPio2Lo, r);
+    r = fmaf(-k, kPio2Lo2, r);
+    const float z = r * r;
+    float ps = 2.724378191e-06f;
+    ps = fmaf(ps, z, -1.984003902e-04f);
+    ps = fmaf(ps, z, 8.333331905e-03f);
+    ps = fmaf(ps, z, -1.666666716e-01f);
+    sr = fmaf(r * z, ps, r);                         // r + r^3 S(r^2)
+    float pc = -2.729583173e-07f;
+    pc = fmaf(pc, z, 2.480055991e-05f);
+    pc = fmaf(pc, z, -1.388888806e-03f);
+    pc = fmaf(pc, z, 4.166666791e-02f);
+    cr = fmaf(z * z, pc, fmaf(-0.5f, z, 1.0f));      // 1 - r^2/2 + r^4 C(r^2)
+    return (int)k & 3;
+}
+PT_HD void sincos_f(float x, float& s, float& c) {
+    float sr, cr;
+    const int q = sincos_reduced(x, sr, cr);
+    const float a = (q & 1) ? cr : sr, b = (q & 1) ? sr : cr;
+    s = (q & 2) ? -a : a;                            // q: 0 (s, c)  1 (c, -s)  2 (-s, -c)  3 (-c, s)
+    c = ((q + 1) & 2) ? -b : b;
+}
+PT_HD float atan_f(float a) {  // a >= 0 (may be +inf); result in [0, pi/2]
+    const bool inv = a > 1.0f;
+    const float t = inv ? 1.0f / a : a;
+    const bool shift = t > 0.414213562f;  // tan(pi/8)
+    const float u = shift ? (t - 1.0f) / (t + 1.0f) : t;
+    const float z = u * u;
+    float p = 5.044116825e-02f;
+    p = fmaf(p, z, -8.623115718e-02f);
+    p = fmaf(p, z, 1.107115597e-01f);
+    p = fmaf(p, z, -1.428413987e-01f);
+    p = fmaf(p, z, 1.999997646e-01f);
+    p = fmaf(p, z, -3.333333433e-01f);
+    float r = fmaf(u * z, p, u);                     // u + u^3 A(u^2)
+    if (shift) r = kPio4Hi + (r + kPio4Lo);
+    if (inv) r = (kPio2Hi - r) + kPio2Lo;
+    return r;
+}
+}  // namespace dmf
+
 // -DPT_LIBM_MATH=1 (measurement builds only, tools/build_variants.sh): the DEVICE code calls CUDA's float functions
 // instead — what the deterministic design costs (frames then differ from the oracle in the last ulp of some draws
 // and are compared by relMSE, not by bits).  The product is built without it.
@@ -169,64 +251,73 @@ PT_HD double copysign_d(double mag, double sgn) {
 #define PT_LIBM(expr)
 #endif
 
+// |x| > dmf::kTrigMax: binary64 route; which: 0 sin, 1 cos, 2 tan
+PT_HD_CALL float trig_big(float x, int which) {
+    double s, c;
+    dmi::sincos_d((double)x, s, c);
+    return which == 0 ? (float)s : (which == 1 ? (float)c : (float)(s / c));
+}
+
 PT_HD float dm_sin(float x) {
     PT_LIBM(sinf(x));
-    double xd = x;
-    if (dmi::is_nan(xd) || dmi::is_inf(xd)) return dmi::qnan();
-    double s, c;
-    dmi::sincos_d(xd, s, c);
-    return (float)s;
+    if (dmf::is_nan(x) || dmf::is_inf(x)) return dmi::qnan();
+    if (x <= dmf::kTrigMax && x >= -dmf::kTrigMax) {
+        float sf, cf;
+        dmf::sincos_f(x, sf, cf);
+        return sf;
+    }
+    return trig_big(x, 0);
 }
 PT_HD float dm_cos(float x) {
     PT_LIBM(cosf(x));
-    double xd = x;
-    if (dmi::is_nan(xd) || dmi::is_inf(xd)) return dmi::qnan();
-    double s, c;
-    dmi::sincos_d(xd, s, c);
-    return (float)c;
+    if (dmf::is_nan(x) || dmf::is_inf(x)) return dmi::qnan();
+    if (x <= dmf::kTrigMax && x >= -dmf::kTrigMax) {
+        float sf, cf;
+        dmf::sincos_f(x, sf, cf);
+        return cf;
+    }
+    return trig_big(x, 1);
 }
 PT_HD float dm_tan(float x) {
     PT_LIBM(tanf(x));
-    double xd = x;
-    if (dmi::is_nan(xd) || dmi::is_inf(xd)) return dmi::qnan();
-    double s, c;
-    dmi::sincos_d(xd, s, c);
-    return (float)(s / c);
+    if (dmf::is_nan(x) || dmf::is_inf(x)) return dmi::qnan();
+    if (x <= dmf::kTrigMax && x >= -dmf::kTrigMax) {
+        float sf, cf;
+        dmf::sincos_f(x, sf, cf);
+        return sf / cf;
+    }
+    return trig_big(x, 2);
 }
 PT_HD float dm_atan(float x) {
     PT_LIBM(atanf(x));
-    double xd = x;
-    if (dmi::is_nan(xd)) return dmi::qnan();
-    double a = dmi::atan_core(xd < 0 ? -xd : xd);
-    return (float)dmi::copysign_d(a, xd);
+    if (dmf::is_nan(x)) return dmi::qnan();
+    return dmf::with_sign(dmf::atan_f(x < 0.0f ? -x : x), x);
 }
 PT_HD float dm_atan2(float y, float x) {
     PT_LIBM(atan2f(y, x));
-    double yd = y, xd = x;
-    if (dmi::is_nan(yd) || dmi::is_nan(xd)) return dmi::qnan();
-    bool xneg = (xd < 0) || (xd == 0 && (1.0 / xd) < 0);
-    if (yd == 0) return (float)dmi::copysign_d(xneg ? dmi::kPiD : 0.0, yd);
-    if (xd == 0) return (float)dmi::copysign_d(dmi::kPio2Hi, yd);
-    double a;
-    if (dmi::is_inf(xd) && dmi::is_inf(yd))
-        a = dmi::kPio4;
+    if (dmf::is_nan(y) || dmf::is_nan(x)) return dmi::qnan();
+    const bool xneg = dmf::sign_bit(x);
+    if (y == 0.0f) return dmf::with_sign(xneg ? dmf::kPiHi : 0.0f, y);
+    if (x == 0.0f) return dmf::with_sign(dmf::kPio2Hi, y);
+    float a;
+    if (dmf::is_inf(x) && dmf::is_inf(y))
+        a = dmf::kPio4Hi;
     else {
-        double q = yd / xd;
-        a = dmi::atan_core(q < 0 ? -q : q);
+        const float q = y / x;   // an overflowing quotient gives pi/2, an underflowing one 0 (or pi): both within an ulp
+        a = dmf::atan_f(q < 0.0f ? -q : q);
     }
-    if (xneg) a = (dmi::kPiD - a) + 2.0 * dmi::kPio2Lo;
-    return (float)dmi::copysign_d(a, yd);
+    if (xneg) a = (dmf::kPiHi - a) + dmf::kPiLo;
+    return dmf::with_sign(a, y);
 }
 PT_HD float dm_asin(float x) {
     PT_LIBM(asinf(x));
-    double xd = x;
-    if (dmi::is_nan(xd) || xd > 1.0 || xd < -1.0) return dmi::qnan();
-    double c = sqrt((1.0 - xd) * (1.0 + xd));
-    double ax = xd < 0 ? -xd : xd;
-    double a = (c == 0.0) ? (dmi::kPio2Hi + dmi::kPio2Lo) : dmi::atan_core(ax / c);
-    return (float)dmi::copysign_d(a, xd);
+    if (dmf::is_nan(x) || x > 1.0f || x < -1.0f) return dmi::qnan();
+    const float c = sqrtf((1.0f - x) * (1.0f + x));
+    const float ax = x < 0.0f ? -x : x;
+    const float a = (c == 0.0f) ? dmf::kPio2Hi : dmf::atan_f(ax / c);
+    return dmf::with_sign(a, x);
 }
-PT_HD float dm_log(float x) {
+PT_HD_CALL float dm_log(float x) {
     PT_LIBM(logf(x));
     double xd = x;
     if (dmi::is_nan(xd) || xd < 0) return dmi::qnan();
@@ -235,7 +326,7 @@ PT_HD float dm_log(float x) {
     return (float)dmi::log_core(xd);
 }
 // x >= 0 is the only domain the integrator uses (colours, alpha^2); x < 0 -> NaN.
-PT_HD float dm_pow(float x, float y) {
+PT_HD_CALL float dm_pow(float x, float y) {
     PT_LIBM(powf(x, y));
     double xd = x, yd = y;
     if (yd == 0 || xd == 1.0) return 1.0f;

@@ -23,7 +23,9 @@ namespace pt {
                                 // two-triangle test spills at 64: 8 blocks/SM measured 10 % slower)
 #endif
 #ifndef PT_SHADE_MIN_BLOCKS
-#define PT_SHADE_MIN_BLOCKS 4   // register cap of k_shade: 65536 / (128 * blocks)
+#define PT_SHADE_MIN_BLOCKS 5   // register cap of k_shade: 65536 / (128 * blocks) = 102.  Round 1 ran at 4 (128 registers): the
+                                // inlined binary64 pow / log bodies needed them.  With those out of line (pt_detmath.h) 5 blocks
+                                // are 3 % of a frame faster than 4 and than 6 (profiles/r02d_shade_ab.jsonl)
 #endif
 constexpr int kBlock = 128;
 constexpr int kWalkBlock = PT_WALK_BLOCK;

