@@ -4,9 +4,7 @@
 // (device.cu:25-26, disney_specular.cuh:69-74,177, disney_clearcoat.cuh:19,26,
 // disney_helper.cuh:6, sample_methods.hpp:38-41).  CUDA's libm and glibc do not
 // agree bit for bit, so paths would diverge after the first bounce and the GPU could
-// only be checked statistically.  log and pow evaluate in binary64 (below); since round 2 the trigonometric
-// functions evaluate in binary32 (namespace dmf further down) — same principle, same guarantee of identical bits on
-// both sides.  The binary64 versions evaluate with nothing
+// only be checked statistically.  These versions evaluate in binary64 with nothing
 // but +,-,*,/,fma,sqrt,floor,frexp,ldexp (all exactly specified by IEEE-754 / exact by
 // construction; the Horner steps of the polynomials are explicit fma() calls — one correctly rounded
 // operation on both sides, half the binary64 instructions of a separate multiply and add, which matter on
@@ -169,13 +167,14 @@ PT_HD double copysign_d(double mag, double sgn) {
 
 }  // namespace dmi
 
-// ---------------------------------------------------------------------------- binary32 internals (round 2)
-// sin / cos / tan / atan / atan2 / asin are evaluated in binary32: Cody-Waite reduction and short minimax polynomials,
-// built from nothing but +, -, *, /, fmaf, sqrtf and floorf — every one of them a single correctly rounded IEEE
-// operation on both sides, so nvcc (-fmad=false) and g++ (-ffp-contract=off) still return the same bits.  Accuracy
-// 1-2 ulp (asin, tan <= 3), the class of CUDA's own sinf / atanf that the reference calls; the binary64 versions
-// they replace were 20 % of k_shade (profiles/r02b_walker_shade_variants_ab.jsonl: CUDA float math -20 %), these cost
-// about what CUDA's do.  log and pow stay in binary64 (rare on the path, and pow needs the extra bits).
+// ---------------------------------------------------------------------------- binary32 internals (build option)
+// -DPT_TRIG_F32=1 evaluates sin / cos / tan / atan / atan2 / asin in binary32: Cody-Waite reduction and short minimax
+// polynomials built from +, -, *, /, fmaf, sqrtf, floorf only — still the same bits from nvcc and g++, 1-3 ulp, the
+// accuracy class of CUDA's own float functions.  NOT the default: measured on the headline frame (dragon 1080p, 1024 spp,
+// 128x128 crop against the glibc-math oracle, profiles/r02f_trig_probe.jsonl) the binary64 route differs from glibc in
+// 1.5 % of the pixels, per-pixel relMSE 3.8e-4 — inside north_star's 1e-3 — while the binary32 route differs in 15 %
+// and reaches 4.3e-3 (a path that diverges by one ulp somewhere meets another firefly of this very noisy estimator).
+// Speed: the same on the dragon, 3 % of a frame on the car (profiles/r02f_trig_ab.jsonl).  Parity wins.
 // Coefficients: Chebyshev-node interpolation in 50-digit arithmetic (mpmath), rounded to binary32.
 namespace dmf {
 constexpr float kTwoOverPi = 0.636619747f;
@@ -242,6 +241,9 @@ PT_HD float atan_f(float a) {  // a >= 0 (may be +inf); result in [0, pi/2]
 // -DPT_LIBM_MATH=1 (measurement builds only, tools/build_variants.sh): the DEVICE code calls CUDA's float functions
 // instead — what the deterministic design costs (frames then differ from the oracle in the last ulp of some draws
 // and are compared by relMSE, not by bits).  The product is built without it.
+#ifndef PT_TRIG_F32
+#define PT_TRIG_F32 0
+#endif
 #ifndef PT_LIBM_MATH
 #define PT_LIBM_MATH 0
 #endif
@@ -251,7 +253,13 @@ PT_HD float atan_f(float a) {  // a >= 0 (may be +inf); result in [0, pi/2]
 #define PT_LIBM(expr)
 #endif
 
-// |x| > dmf::kTrigMax: binary64 route; which: 0 sin, 1 cos, 2 tan
+// binary64 sin / cos / tan (which: 0, 1, 2), inlined: a handful of polynomial steps, cheap enough to sit in line
+PT_HD float trig_d(float x, int which) {
+    double s, c;
+    dmi::sincos_d((double)x, s, c);
+    return which == 0 ? (float)s : (which == 1 ? (float)c : (float)(s / c));
+}
+// |x| > dmf::kTrigMax with the binary32 route: the binary64 one, out of line
 PT_HD_CALL float trig_big(float x, int which) {
     double s, c;
     dmi::sincos_d((double)x, s, c);
@@ -261,41 +269,75 @@ PT_HD_CALL float trig_big(float x, int which) {
 PT_HD float dm_sin(float x) {
     PT_LIBM(sinf(x));
     if (dmf::is_nan(x) || dmf::is_inf(x)) return dmi::qnan();
+#if PT_TRIG_F32
     if (x <= dmf::kTrigMax && x >= -dmf::kTrigMax) {
         float sf, cf;
         dmf::sincos_f(x, sf, cf);
         return sf;
     }
     return trig_big(x, 0);
+#else
+    return trig_d(x, 0);
+#endif
 }
 PT_HD float dm_cos(float x) {
     PT_LIBM(cosf(x));
     if (dmf::is_nan(x) || dmf::is_inf(x)) return dmi::qnan();
+#if PT_TRIG_F32
     if (x <= dmf::kTrigMax && x >= -dmf::kTrigMax) {
         float sf, cf;
         dmf::sincos_f(x, sf, cf);
         return cf;
     }
     return trig_big(x, 1);
+#else
+    return trig_d(x, 1);
+#endif
 }
 PT_HD float dm_tan(float x) {
     PT_LIBM(tanf(x));
     if (dmf::is_nan(x) || dmf::is_inf(x)) return dmi::qnan();
+#if PT_TRIG_F32
     if (x <= dmf::kTrigMax && x >= -dmf::kTrigMax) {
         float sf, cf;
         dmf::sincos_f(x, sf, cf);
         return sf / cf;
     }
     return trig_big(x, 2);
+#else
+    return trig_d(x, 2);
+#endif
 }
 PT_HD float dm_atan(float x) {
     PT_LIBM(atanf(x));
     if (dmf::is_nan(x)) return dmi::qnan();
+#if PT_TRIG_F32
     return dmf::with_sign(dmf::atan_f(x < 0.0f ? -x : x), x);
+#else
+    const double xd = x;
+    return (float)dmi::copysign_d(dmi::atan_core(xd < 0 ? -xd : xd), xd);
+#endif
 }
 PT_HD float dm_atan2(float y, float x) {
     PT_LIBM(atan2f(y, x));
     if (dmf::is_nan(y) || dmf::is_nan(x)) return dmi::qnan();
+#if !PT_TRIG_F32
+    {
+        const double yd = y, xd = x;
+        const bool xn = (xd < 0) || (xd == 0 && (1.0 / xd) < 0);
+        if (yd == 0) return (float)dmi::copysign_d(xn ? dmi::kPiD : 0.0, yd);
+        if (xd == 0) return (float)dmi::copysign_d(dmi::kPio2Hi, yd);
+        double a;
+        if (dmi::is_inf(xd) && dmi::is_inf(yd))
+            a = dmi::kPio4;
+        else {
+            const double q = yd / xd;
+            a = dmi::atan_core(q < 0 ? -q : q);
+        }
+        if (xn) a = (dmi::kPiD - a) + 2.0 * dmi::kPio2Lo;
+        return (float)dmi::copysign_d(a, yd);
+    }
+#endif
     const bool xneg = dmf::sign_bit(x);
     if (y == 0.0f) return dmf::with_sign(xneg ? dmf::kPiHi : 0.0f, y);
     if (x == 0.0f) return dmf::with_sign(dmf::kPio2Hi, y);
@@ -312,6 +354,15 @@ PT_HD float dm_atan2(float y, float x) {
 PT_HD float dm_asin(float x) {
     PT_LIBM(asinf(x));
     if (dmf::is_nan(x) || x > 1.0f || x < -1.0f) return dmi::qnan();
+#if !PT_TRIG_F32
+    {
+        const double xd = x;
+        const double cd = sqrt((1.0 - xd) * (1.0 + xd));
+        const double ax = xd < 0 ? -xd : xd;
+        const double a = (cd == 0.0) ? (dmi::kPio2Hi + dmi::kPio2Lo) : dmi::atan_core(ax / cd);
+        return (float)dmi::copysign_d(a, xd);
+    }
+#endif
     const float c = sqrtf((1.0f - x) * (1.0f + x));
     const float ax = x < 0.0f ? -x : x;
     const float a = (c == 0.0f) ? dmf::kPio2Hi : dmf::atan_f(ax / c);

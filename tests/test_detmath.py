@@ -1,7 +1,6 @@
 """The deterministic elementary functions (owl_path_tracer_b200/csrc/pt_detmath.h) against numpy
-float64, and against the glibc-built oracle.  Tolerances (ulp of binary32): log and pow round a binary64 evaluation
-once (<= 1); sin / cos / tan / atan / atan2 / asin are binary32 evaluations since round 2, in the accuracy class of
-CUDA's own float functions that the reference calls (CUDA documents sinf 2, cosf 2, tanf 4, atanf 2, atan2f 3, asinf 2)."""
+float64, and against the glibc-built oracle.  Tolerance: 1 ulp of binary32 (the functions round a binary64 evaluation
+once).  The binary32 build option (-DPT_TRIG_F32=1, measured 1.5 - 3.4 ulp) is not what the product ships."""
 import numpy as np
 import pytest
 
@@ -28,8 +27,8 @@ CASES = [
     ("asin", lambda x: np.arcsin(x), grid(-1, 1, 40000, 6)),
     ("log", lambda x: np.log(x), np.concatenate([grid(1e-7, 1e-1, 30000, 7), grid(0.1, 100, 10000, 8)])),
 ]
-#          max ulp, mean ulp   (measured: sin 1.50 / 0.32, cos 1.55 / 0.35, tan 3.4 / 0.52, atan 2.0 / 0.36, asin 3.1 / 0.44)
-BOUND = dict(sin=(1.75, 0.40), cos=(1.75, 0.40), tan=(3.75, 0.60), atan=(2.25, 0.42), asin=(3.4, 0.50), log=(1.0, 0.26))
+#          max ulp, mean ulp
+BOUND = {k: (1.0, 0.26) for k in ("sin", "cos", "tan", "atan", "asin", "log")}
 
 
 @pytest.mark.parametrize("name,ref,x", CASES, ids=[c[0] for c in CASES])
@@ -38,8 +37,7 @@ def test_unary_accuracy(name, ref, x):
     e = ulp_err(got, ref(x.astype(np.float64)))
     assert e.max() <= BOUND[name][0], f"{name}: {e.max()} ulp"
     assert e.mean() <= BOUND[name][1], f"{name}: mean {e.mean()} ulp"
-    if name == "log":
-        assert np.mean(e <= 0.5000001) > 0.999  # binary64 route: almost always correctly rounded
+    assert np.mean(e <= 0.5000001) > 0.999  # almost always correctly rounded
 
 
 def test_atan2_and_pow():
@@ -47,7 +45,7 @@ def test_atan2_and_pow():
     y = rs.normal(size=60000).astype(np.float32)
     x = rs.normal(size=60000).astype(np.float32)
     e = ulp_err(Emu().math("atan2", y, x), np.arctan2(y.astype(np.float64), x.astype(np.float64)))
-    assert e.max() <= 2.6 and e.mean() <= 0.45
+    assert e.max() <= 1.0
     b = np.concatenate([rs.uniform(0, 1, 30000), rs.uniform(1e-6, 1e-2, 30000)]).astype(np.float32)
     p = np.concatenate([np.full(30000, 2.2), rs.uniform(0, 1, 30000)]).astype(np.float32)
     e = ulp_err(Emu().math("pow", b, p), np.power(b.astype(np.float64), p.astype(np.float64)))
@@ -73,4 +71,4 @@ def test_det_oracle_uses_the_same_functions_and_libm_is_close():
     for fn in ("sin", "cos", "atan"):
         a, b, c = e.math(fn, x), od.math(fn, x), ol.math(fn, x)
         assert (a.view(np.uint32) == b.view(np.uint32)).all()
-        assert np.max(np.abs(a.astype(np.float64) - c) / np.spacing(np.abs(c)).astype(np.float64)) <= 3.0
+        assert np.max(np.abs(a.astype(np.float64) - c) / np.spacing(np.abs(c)).astype(np.float64)) <= 2.0
