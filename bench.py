@@ -278,9 +278,10 @@ def main():
     # the blocking call on one context, for the record: the latency of a single frame
     blocking = timed(step_resident, min(args.steps, 3))
     pipelined_equals_blocking = None
-    if pipe is not None and rank == 0:
-        step_e2e()
-        pipelined_equals_blocking = bool((outs[(args.steps - 1) % len(outs)] == frame_host).all())
+    if pipe is not None:
+        step_e2e()                   # collective: every rank renders its share
+        if rank == 0:
+            pipelined_equals_blocking = bool((outs[(args.steps - 1) % len(outs)] == frame_host).all())
 
     # what was timed is checked: rank 0 holds the resolved frame of the last step
     parity = None
@@ -343,7 +344,7 @@ def main():
         launches_extend = kt["iterations"]
         achieved = rank0_rays * bytes_per_ray / (kt["extend_ms"] * 1e-3) * 1e-9 if kt["extend_ms"] > 0 else None
         traffic = None
-        tf = REPO / "profiles" / "extend_traffic.json"
+        tf = REPO / "profiles" / ("extend_traffic.json" if not args.detail else f"extend_traffic_detail{args.detail}.json")
         if tf.exists():
             # ncu's capture is a full-queue launch; scaled per ray to the average launch of the timing pass
             per_ray = json.loads(tf.read_text()).get("dram_bytes_per_ray")
@@ -356,7 +357,11 @@ def main():
                     timing_pass="one extra frame of the workload on one stream with events around every launch "
                                 "(%.1f ms; the timed region runs 2 concurrent sub-frames, %.1f ms per frame)"
                                 % (kt["render_ms"], blocking["wall_ms"] / min(args.steps, 3)),
-                    note="BVH (%.0f MB) is L2-resident; HBM peak is the required denominator, see DESIGN.md" % (s2["bvh_bytes"] / 1e6))
+                    traffic_to_algorithmic=(traffic / (rank0_rays * bytes_per_ray / max(1, launches_extend))) if traffic else None,
+                    bvh_mb=s2["bvh_bytes"] / 1e6,
+                    note=("BVH (%.0f MB) is L2-resident (126 MB L2): HBM is the contract's denominator, not this kernel's roof on this mesh, see DESIGN.md"
+                          if s2["bvh_bytes"] < 100e6 else
+                          "BVH (%.0f MB) exceeds the 126 MB L2: nodes and triangles come from HBM, the fraction means what it says") % (s2["bvh_bytes"] / 1e6))
 
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
