@@ -153,8 +153,9 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (a smaller workload is NOT the headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lib", default="", help="development: time a variant build of libb200pt.so (tools/build_variants.sh); never the headline")
     ap.add_argument("--no-parity-check", action="store_true")
-    ap.add_argument("--pipeline", type=int, default=2, help="contexts per rank the frames of the timed region rotate over "
+    ap.add_argument("--pipeline", type=int, default=3, help="contexts per rank the frames of the timed region rotate over "
                     "(b200pt_pipeline_*: frame k+1 starts while frame k drains); 1 = the blocking call")
     ap.add_argument("--start-fraction", type=float, default=0.5)
     ap.add_argument("--detail", type=int, default=0, help="procedural mesh detail (0 = the 871,406-triangle headline stand-in; "
@@ -168,6 +169,8 @@ def main():
     import torch.distributed as dist
     import owl_path_tracer_b200 as pt
     from owl_path_tracer_b200.distributed import init_comm
+    if args.lib:
+        pt.use_library(args.lib)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -380,7 +383,7 @@ def main():
             metric="Mrays/s", value=res["rays_all"] / (res["wall_ms"] * 1e-3) * 1e-6, unit="Mrays/s", n_gpus=world,
             steps=args.steps, warmup=args.warmup, ms_per_step=ms_step, higher_is_better=True, scaling="strong",
             vs_baseline=None, dtype="f32", data="synthetic",
-            config=dict(workload=WORKLOAD_NAME if not (args.spp or args.detail) else
+            config=dict(workload=WORKLOAD_NAME if not (args.spp or args.detail or args.lib) else
                         f"secondary: dragon 1920x1080 at {total_spp} spp, {sc.n_triangles} triangles (not the headline)",
                         parallelism=f"spp-sharded x{world}, scene replicated, one NCCL reduce of the float4 sums per frame",
                         l2="inputs larger than L2: lane state 330 MB + BVH 49 MB per GPU vs 126 MB L2, no flush between steps",

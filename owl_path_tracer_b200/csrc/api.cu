@@ -99,6 +99,7 @@ struct b200pt_ctx {
     size_t fb_pixels = 0;
     bool rendered = false, resolved = false;
     bool mean_on_host = false;   // h_mean holds the float frame of the last resolve
+    int parts_override = 0;      // > 0: sub-frames per frame chosen by the frame pipeline (choose_parts)
     // b200pt_set_drain_callback
     float drain_fraction = 0.0f;
     b200pt_drain_fn drain_fn = nullptr;
@@ -602,6 +603,9 @@ static int sync_mesh_materials(b200pt_ctx* c) {
 static int choose_parts(const b200pt_ctx* c, const SceneView& sv) {
     int parts = (c->cfg.flags & B200PT_FLAG_TIMING) ? 1 : 2;
     if (sv.n_lanes < (1 << 18)) parts = 1;  // small frames: launch-bound already
+    // a slot of a frame pipeline renders its frame as ONE part: the other slots' frames fill the launch tails, and
+    // full-size launches beat half-size ones (dragon 1080p / 256 spp, 2 slots: 2175 -> 2285 Mrays/s, profiles/r02j_*)
+    if (c->parts_override > 0) parts = c->parts_override;
 #if B200PT_DEV
     if (const char* e = getenv("B200PT_PARTS")) parts = atoi(e);
 #endif
@@ -1528,6 +1532,7 @@ extern "C" int b200pt_pipeline_create(b200pt_ctx* const* slots, int32_t n, float
         s.owner = p;
         s.ctx = slots[i];
         b200pt_set_drain_callback(s.ctx, f, &b200pt_pipeline::on_drain, &s);
+        if (n > 1) s.ctx->parts_override = 1;
     }
     for (auto& s : p->slots) s.worker = std::thread([p, sp = &s] { p->run(sp); });
     *out = p;
@@ -1571,6 +1576,7 @@ extern "C" int b200pt_pipeline_destroy(b200pt_pipeline* p) {
     for (auto& s : p->slots) {
         s.worker.join();
         b200pt_set_drain_callback(s.ctx, 0.0f, nullptr, nullptr);
+        s.ctx->parts_override = 0;
     }
     delete p;
     return B200PT_OK;

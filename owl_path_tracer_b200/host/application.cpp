@@ -52,11 +52,16 @@ void bind_scene(const program_data& pdata, b200pt_ctx* ctx) {
           "set_render");
 }
 
+// "<scene>_<test>_<attribute>(<values>)", the file stem of application.cpp:364
+static std::string frame_stem(const program_data& pdata, const test_data& tdata, const std::string& values) {
+    return pdata.scene + "_" + tdata.name + "_" + tdata.attribute_name + "(" + values + ")";
+}
+
 // render_frame, application.cpp:363-371
 void render_frame(b200pt_ctx* ctx, const program_data& pdata, const test_data& tdata, const std::string& values,
                   const std::string& out_dir) {
     host::say("TRACING\n");
-    const std::string stem = pdata.scene + "_" + tdata.name + "_" + tdata.attribute_name + "(" + values + ")";
+    const std::string stem = frame_stem(pdata, tdata, values);
     if (pdata.progressive_pass > 0) {
         // the same frame in passes: every pass continues the pixels' RNG streams, so the last pass leaves the
         // image of the blocking launch (or, with a target, the reference's image at the sample count reached)
@@ -109,6 +114,17 @@ void test_loop(b200pt_ctx* ctx, program_data& pdata, const test_data& tdata, con
     const bool is_vec = !tdata.vec_values.empty();
     if ((is_vec && tdata.vec_values.size() < 2) || (!is_vec && tdata.flt_values.size() < 2))
         throw std::runtime_error("settings.test.values needs two entries");
+    // --pipeline: the frames are queued, rendered overlapped, and written afterwards (same files, same bytes)
+    const bool pipelined = !pdata.pipeline_slots.empty() && pdata.ranks.size() <= 1 && pdata.progressive_pass == 0;
+    b200pt_pipeline* pipe = nullptr;
+    std::vector<std::vector<uint32_t>> frames;
+    std::vector<std::string> labels;
+    if (pipelined) {
+        std::vector<b200pt_ctx*> slots{ctx};
+        slots.insert(slots.end(), pdata.pipeline_slots.begin(), pdata.pipeline_slots.end());
+        check(b200pt_pipeline_create(slots.data(), (int32_t)slots.size(), 0.0f, &pipe), "pipeline_create");
+        frames.reserve(128);   // submit() keeps pointers into the vectors: no reallocation of the outer one below
+    }
     for (int32_t i = 0; i <= 100; i += vstep) {
         const float c = i / 100.0f;
         char buf[96];
@@ -127,7 +143,26 @@ void test_loop(b200pt_ctx* ctx, program_data& pdata, const test_data& tdata, con
         check(b200pt_set_materials(ctx, mats.data(), (int)mats.size()), "set_materials");
         for (size_t r = 1; r < pdata.ranks.size(); ++r)
             check(b200pt_set_materials(pdata.ranks[r], mats.data(), (int)mats.size()), "set_materials");
+        if (pipelined) {
+            frames.emplace_back((size_t)pdata.buffer_size[0] * pdata.buffer_size[1]);
+            labels.emplace_back(buf);
+            check(b200pt_pipeline_submit(pipe, mats.data(), (int32_t)mats.size(), frames.back().data()), "pipeline_submit");
+            continue;
+        }
         render_frame(ctx, pdata, tdata, buf, out_dir);
+    }
+    if (pipelined) {
+        const int st = b200pt_pipeline_wait(pipe);
+        const std::string err = st != B200PT_OK ? b200pt_last_error() : "";
+        b200pt_pipeline_destroy(pipe);
+        if (st != B200PT_OK) throw std::runtime_error("pipeline: " + err);
+        for (size_t k = 0; k < frames.size(); ++k) {
+            image_buffer result;
+            result.width = pdata.buffer_size[0];
+            result.height = pdata.buffer_size[1];
+            result.pixels = std::move(frames[k]);
+            write_image(result, frame_stem(pdata, tdata, labels[k]) + ".png", out_dir);
+        }
     }
 }
 

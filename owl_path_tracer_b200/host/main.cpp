@@ -6,6 +6,8 @@
 // directory.  Optional flags (all default to the reference behaviour):
 //   --assets DIR  --scene NAME  --size W H  --spp N  --depth N  --env color|auto|map
 //   --env-intensity F  --detail N  --device K  --out DIR  --stats
+//   --pipeline N (N contexts on the device: the frames of the sweep are queued and frame k+1 starts while frame k drains;
+//                 same files, same bytes)
 //   --gpus N (devices K .. K+N-1, samples sharded over them, one NCCL reduce per frame; the reference's OWL context can
 //             span devices the same way, extern/owl/owl/RayGen.cpp:140-146, and asks for one, application.cpp:62)
 //   --nee (light sampling + MIS mode)  --streams V (RNG streams per pixel)  --pfm (float frame next to the PNG)
@@ -25,7 +27,7 @@ int main(int argc, char** argv) {
     std::string assets_path = std::filesystem::current_path().string() + "/assets";
     std::string out_dir = std::filesystem::current_path().string();
     host::load_options opt;
-    int device = 0, flags = 0, streams = 1, gpus = 1;
+    int device = 0, flags = 0, streams = 1, gpus = 1, pipeline = 1;
     bool stats = false, pfm = false, gamma = false, save_passes = false;
     int progressive = 0;
     double target_error = 0.0;
@@ -51,6 +53,7 @@ int main(int argc, char** argv) {
         else if (a == "--detail") { need(1); opt.detail = atoi(argv[++i]); }
         else if (a == "--device") { need(1); device = atoi(argv[++i]); }
         else if (a == "--gpus") { need(1); gpus = atoi(argv[++i]); }
+        else if (a == "--pipeline") { need(1); pipeline = atoi(argv[++i]); }
         else if (a == "--out") { need(1); out_dir = argv[++i]; }
         else if (a == "--stats") stats = true;
         else if (a == "--nee") flags |= B200PT_FLAG_NEE;
@@ -63,7 +66,7 @@ int main(int argc, char** argv) {
         else if (a == "--gamma") gamma = true;
         else if (a == "--help" || a == "-h") {
             printf("path_tracer [--assets DIR] [--scene NAME] [--size W H] [--spp N] [--depth N] [--env color|auto|map]\n"
-                   "            [--env-intensity F] [--detail N] [--device K] [--gpus N] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"
+                   "            [--env-intensity F] [--detail N] [--device K] [--gpus N] [--pipeline N] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"
                    "            [--env-float] [--progressive N] [--target-error E] [--save-passes] [--gamma]\n"
                    "without arguments: ./assets/settings.json and its scene, as the reference's executable\n");
             return 0;
@@ -110,6 +113,21 @@ int main(int argc, char** argv) {
             ranks.push_back(c);
         }
         b200pt_ctx* ctx = ranks[0];
+        for (int k = 1; k < pipeline && gpus == 1; ++k) {   // further slots of the frame pipeline (one GPU)
+            b200pt_config cfg{};
+            cfg.device_ordinal = device;
+            cfg.world_size = 1;
+            cfg.flags = flags;
+            cfg.streams_per_pixel = streams;
+            b200pt_ctx* c = nullptr;
+            if (b200pt_create(&cfg, &c) != B200PT_OK) {
+                fprintf(stderr, "b200pt_create (pipeline slot %d) failed: %s\n", k, b200pt_last_error());
+                return 1;
+            }
+            host::bind_scene(pdata, c);
+            if (gamma) b200pt_set_output(c, B200PT_TRANSFER_GAMMA22);
+            pdata.pipeline_slots.push_back(c);
+        }
         if (gpus > 1) {
             if (b200pt_comm_init_all(ranks.data(), gpus) != B200PT_OK) {
                 fprintf(stderr, "b200pt_comm_init_all failed: %s\n", b200pt_last_error());
@@ -127,6 +145,7 @@ int main(int argc, char** argv) {
                    (unsigned long long)st.paths, st.render_ms > 0 ? st.rays / st.render_ms * 1e-3 : 0.0, st.bvh_nodes,
                    st.bvh_tris);
         }
+        for (b200pt_ctx* c : pdata.pipeline_slots) b200pt_destroy(c);
         for (b200pt_ctx* c : ranks) b200pt_destroy(c);
     } catch (const std::exception& e) {
         fprintf(stderr, "error: %s\n", e.what());

@@ -95,6 +95,10 @@ struct program_data {
     // several GPUs from one process (path_tracer --gpus N): the contexts of ranks 0 .. N-1, samples sharded over them,
     // one NCCL reduce per frame inside b200pt_render_frame_all.  Empty: the single context handed to test_loop.
     std::vector<b200pt_ctx*> ranks;
+    // frames of the sweep back to back (path_tracer --pipeline N): further contexts of this rank bound to the same scene;
+    // test_loop then queues the frames on a b200pt_pipeline (frame k+1 starts while frame k drains) and writes the images
+    // when all are done.  Empty: one blocking frame after the other, like the reference.
+    std::vector<b200pt_ctx*> pipeline_slots;
 };
 
 }  // namespace host

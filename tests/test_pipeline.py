@@ -58,3 +58,20 @@ def test_pipeline_reports_a_frame_error():
     pipe.close()
     a.close()
     b.close()
+
+
+def test_path_tracer_pipeline_writes_the_same_files(tmp_path):
+    """path_tracer --pipeline 3: the sweep's frames are queued and overlapped; same file names, same bytes"""
+    import subprocess
+    from checkers import REPO
+    exe = REPO / "owl_path_tracer_b200" / "bin" / "path_tracer"
+    args = ["--assets", str(REPO / "assets"), "--scene", "mitsuba", "--size", "640", "360", "--spp", "4", "--depth", "6", "--env", "auto",
+            "--env-intensity", "1"]
+    outs = []
+    for extra in ([], ["--pipeline", "3"]):
+        d = tmp_path / ("p" if extra else "b")
+        d.mkdir()
+        r = subprocess.run([str(exe), *args, *extra, "--out", str(d)], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-500:]
+        outs.append({f.name: f.read_bytes() for f in sorted(d.glob("*.png"))})
+    assert len(outs[0]) == 5 and outs[0] == outs[1]
