@@ -226,6 +226,8 @@ static SceneView make_view(const b200pt_ctx* c, bool full_frame) {
 
 static void comm_release(b200pt_ctx* c);
 
+extern "C" int b200pt_destroy(b200pt_ctx* c);
+
 extern "C" int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
     if (!cfg || !out) return fail(B200PT_ERR_INVALID, "b200pt_create: null argument");
     if (cfg->world_size < 1 || cfg->rank < 0 || cfg->rank >= cfg->world_size)
@@ -243,14 +245,22 @@ extern "C" int b200pt_create(const b200pt_config* cfg, b200pt_ctx** out) {
         return fail(B200PT_ERR_CUDA, "device is sm_" + std::to_string(prop.major * 10 + prop.minor) + "; this library is built for sm_100a only");
     b200pt_ctx* c = new b200pt_ctx();
     c->cfg = *cfg;
-    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CU(cudaEventCreate(&c->ev0));
-    CU(cudaEventCreate(&c->ev1));
-    CU(cudaMalloc(&c->d_cursor, sizeof(uint32_t)));
-    c->part_stream[0] = c->stream;
-    for (int p = 1; p < kMaxParts; ++p) CU(cudaStreamCreateWithFlags(&c->part_stream[p], cudaStreamNonBlocking));
-    for (int p = 0; p < kMaxParts; ++p) CU(cudaEventCreateWithFlags(&c->part_done[p], cudaEventDisableTiming));
-    CU(cudaMallocHost(&c->h_counts, sizeof(uint32_t) * kMaxParts * kCountsStride));
+    const int st = [&]() -> int {   // any failure below releases what was created so far (b200pt_destroy copes with nulls)
+        CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        CU(cudaEventCreate(&c->ev0));
+        CU(cudaEventCreate(&c->ev1));
+        CU(cudaMalloc(&c->d_cursor, sizeof(uint32_t)));
+        c->part_stream[0] = c->stream;
+        for (int p = 1; p < kMaxParts; ++p) CU(cudaStreamCreateWithFlags(&c->part_stream[p], cudaStreamNonBlocking));
+        for (int p = 0; p < kMaxParts; ++p) CU(cudaEventCreateWithFlags(&c->part_done[p], cudaEventDisableTiming));
+        CU(cudaMallocHost(&c->h_counts, sizeof(uint32_t) * kMaxParts * kCountsStride));
+        return B200PT_OK;
+    }();
+    if (st != B200PT_OK) {
+        const std::string msg = g_error;
+        b200pt_destroy(c);
+        return fail(st, msg);
+    }
     set_persistent_blocks(prop.multiProcessorCount);
     *out = c;
     return B200PT_OK;
@@ -273,12 +283,14 @@ extern "C" int b200pt_destroy(b200pt_ctx* c) {
     cudaFree(c->d_light_cdf);
     cudaFree(c->d_cursor);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
-    cudaEventDestroy(c->ev0);
-    cudaEventDestroy(c->ev1);
-    for (int p = 1; p < kMaxParts; ++p) cudaStreamDestroy(c->part_stream[p]);
-    for (int p = 0; p < kMaxParts; ++p) cudaEventDestroy(c->part_done[p]);
-    cudaFreeHost(c->h_counts);
-    cudaStreamDestroy(c->stream);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    for (int p = 1; p < kMaxParts; ++p)
+        if (c->part_stream[p]) cudaStreamDestroy(c->part_stream[p]);
+    for (int p = 0; p < kMaxParts; ++p)
+        if (c->part_done[p]) cudaEventDestroy(c->part_done[p]);
+    if (c->h_counts) cudaFreeHost(c->h_counts);
+    if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return B200PT_OK;
 }

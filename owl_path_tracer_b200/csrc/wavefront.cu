@@ -377,6 +377,7 @@ __global__ void __launch_bounds__(256) k_fold_streams(const f4* __restrict__ sum
         a.x += b.x;
         a.y += b.y;
         a.z += b.z;
+        a.w += b.w;   // second moments add like the sums (b200pt_pass_stats on a folded frame)
     }
     st4(out + i, a);
 }
@@ -455,9 +456,19 @@ __global__ void k_sample_disney(const Material* __restrict__ mats, int n, const 
 }
 
 static inline unsigned blocks(uint32_t n, int b) { return n ? (n + b - 1) / b : 1; }
-static int g_persistent_blocks = 148 * PT_BLOCKS_PER_SM * 128 / kWalkBlock;
-void set_persistent_blocks(int sm_count) { g_persistent_blocks = sm_count * PT_BLOCKS_PER_SM * 128 / kWalkBlock; }
-static inline unsigned pblocks(uint32_t n) { return std::min<unsigned>(blocks(n, kWalkBlock), (unsigned)g_persistent_blocks); }
+// persistent grid of the walker kernels: blocks per SM x SMs of the CURRENT device (a process may hold contexts on
+// different GPUs; every launch wrapper runs with its context's device current)
+static int g_sm_count[64] = {};
+void set_persistent_blocks(int sm_count) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64) g_sm_count[dev] = sm_count;
+}
+static inline unsigned pblocks(uint32_t n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int sms = (dev >= 0 && dev < 64 && g_sm_count[dev] > 0) ? g_sm_count[dev] : 148;
+    return std::min<unsigned>(blocks(n, kWalkBlock), (unsigned)(sms * PT_BLOCKS_PER_SM * 128 / kWalkBlock));
+}
 
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, int part, int parts, uint32_t n_part, cudaStream_t st) {
     k_init_lanes<<<blocks(n_part, kBlock), kBlock, 0, st>>>(sv, la, part, parts, n_part);
