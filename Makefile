@@ -29,7 +29,7 @@ $(LIB)/%.o: $(CSRC)/%.cu $(CUHDR)
 	@mkdir -p $(LIB)
 	$(NVCC) $(NVFLAGS) -Xptxas -v -c -o $@ $< 2> $(LIB)/$*.ptxas.log || (cat $(LIB)/$*.ptxas.log; exit 1)
 
-$(LIB)/libb200pt.so: $(LIB)/api.o $(LIB)/wavefront.o $(LIB)/bvh_build.o
+$(LIB)/libb200pt.so: $(LIB)/api.o $(LIB)/wavefront.o $(LIB)/bvh_build.o $(LIB)/mesh_dedup.o
 	$(NVCC) -shared -cudart static -gencode arch=compute_100a,code=sm_100a -o $@ $^
 
 # libb200pt_scene.so: loaders + scene stages, NO CUDA dependency (CPU-only processes load scenes through it);

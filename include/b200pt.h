@@ -198,6 +198,20 @@ int b200pt_render(b200pt_ctx* ctx);
 int b200pt_accum_buffer(b200pt_ctx* ctx, void** device_ptr, size_t* n_floats);
 int b200pt_resolve(b200pt_ctx* ctx);
 
+/* create_mesh (utils/mesh_loader.cpp:9-83) on the device — SURVEY 8(f).4: the reference de-duplicates a shape's vertices
+ * by POSITION index with a std::map while walking its corners; a position index gets the next local id at its first
+ * corner and keeps that corner's normal / texcoord.  Same mapping here by atomicMin + prefix sum (csrc/mesh_dedup.cu).
+ * In:  the OBJ attribute arrays (host pointers; counts in elements of 3 / 3 / 2 floats) and, per triangle corner, the
+ *      indices into them (n_corners = 3 * triangles; corner_vn / corner_vt NULL or all >= 0: regular shapes only —
+ *      a mix of corners with and without an index gives B200PT_ERR_INVALID and the caller keeps the host routine).
+ * Out: caller-allocated arrays sized for n_corners vertices: positions (3 floats), normals (3, if corner_vn), texcoords
+ *      (2, if corner_vt), out_idx[n_corners] local vertex id per corner; *n_out_verts = local vertices written.
+ * The outputs are exactly the arrays b200pt_add_mesh takes. */
+int b200pt_dedup_mesh(b200pt_ctx* ctx, const float* attrib_vertices, int32_t n_vertices, const float* attrib_normals, int32_t n_normals,
+                      const float* attrib_texcoords, int32_t n_texcoords, const int32_t* corner_v, const int32_t* corner_vn,
+                      const int32_t* corner_vt, int32_t n_corners, float* out_verts, float* out_normals, float* out_uvs,
+                      int32_t* out_idx, int32_t* n_out_verts);
+
 /* ---- the frame's collective inside the library (NCCL over NVLink / NVSwitch).
  * Reference: the OWL runtime fans one launch over the devices of a context (extern/owl/owl/RayGen.cpp:140-146; the
  * reference asks for one device, application.cpp:62).  Here a job is world_size contexts (rank r, one GPU each),

@@ -91,6 +91,9 @@ typedef struct b200pt_shapes b200pt_shapes;
 /* load_obj (mesh_loader.cpp:85-121): every shape of the file, before the material match of application.cpp:166-179.
  * threads: 0 = automatic, n = cut the file into n chunks. */
 int b200pt_obj_load(const char* obj_file, int32_t threads, b200pt_shapes** out);
+/* the same with create_mesh's vertex de-duplication run on the device (b200pt_dedup_mesh; libb200pt_host.so):
+ * identical arrays, byte for byte */
+int b200pt_obj_load_gpu(b200pt_ctx* ctx, const char* obj_file, int32_t threads, b200pt_shapes** out);
 int32_t b200pt_obj_count(const b200pt_shapes* s);
 /* material_index = -1, no texture */
 int b200pt_obj_shape(const b200pt_shapes* s, int32_t i, b200pt_entity_view* view);

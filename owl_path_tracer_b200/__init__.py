@@ -160,6 +160,7 @@ def lib() -> C.CDLL:
     L.b200pt_framebuffer_f32.argtypes = [P, C.POINTER(P)]
     L.b200pt_primary_hits.argtypes = [P, P]
     L.b200pt_trace.argtypes = [P, P, P, C.c_int32, C.c_float, C.c_float, P]
+    L.b200pt_dedup_mesh.argtypes = [P, P, C.c_int32, P, C.c_int32, P, C.c_int32, P, P, P, C.c_int32, P, P, P, P, C.POINTER(C.c_int32)]
     L.b200pt_set_drain_callback.argtypes = [P, C.c_float, P, P]
     L.b200pt_pipeline_create.argtypes = [C.POINTER(P), C.c_int32, C.c_float, C.POINTER(P)]
     L.b200pt_pipeline_submit.argtypes = [P, P, C.c_int32, P]
@@ -185,6 +186,7 @@ def host_lib() -> C.CDLL:
     P = C.c_void_p
     H.b200pt_scene_bind.argtypes = [P, P]
     H.b200pt_scene_test_loop.argtypes = [P, P, C.c_char_p]
+    H.b200pt_obj_load_gpu.argtypes = [P, C.c_char_p, C.c_int32, C.POINTER(P)]
     H._typed = True
     return H
 

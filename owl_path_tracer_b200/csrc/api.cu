@@ -1593,3 +1593,74 @@ extern "C" int b200pt_pipeline_destroy(b200pt_pipeline* p) {
     delete p;
     return B200PT_OK;
 }
+
+// ---------------------------------------------------------------------------- b200pt_dedup_mesh
+extern "C" int b200pt_dedup_mesh(b200pt_ctx* c, const float* av, int32_t n_v, const float* an, int32_t n_vn, const float* at,
+                                 int32_t n_vt, const int32_t* cv, const int32_t* cn, const int32_t* ct, int32_t n_corners,
+                                 float* out_verts, float* out_normals, float* out_uvs, int32_t* out_idx, int32_t* n_out_verts) {
+    if (!c || !av || !cv || !out_verts || !out_idx || !n_out_verts || n_corners <= 0 || n_corners % 3 != 0 || n_v <= 0)
+        return fail(B200PT_ERR_INVALID, "dedup_mesh: null / empty input (corners come in triangles)");
+    if ((cn && (!an || !out_normals)) || (ct && (!at || !out_uvs))) return fail(B200PT_ERR_INVALID, "dedup_mesh: indices without their attribute / output array");
+    // host-side validation: ranges, and regularity of the optional indices
+    int32_t lo = INT32_MAX, hi = -1;
+    for (int32_t i = 0; i < n_corners; ++i) {
+        const int32_t v = cv[i];
+        if (v < 0 || v >= n_v) return fail(B200PT_ERR_BOUNDS, "dedup_mesh: vertex index out of range");
+        lo = std::min(lo, v);
+        hi = std::max(hi, v);
+        if (cn && (cn[i] < 0 || cn[i] >= n_vn))
+            return fail(cn[i] < 0 ? B200PT_ERR_INVALID : B200PT_ERR_BOUNDS, cn[i] < 0 ? "dedup_mesh: some corners have no normal index (irregular shape: host routine)" : "dedup_mesh: normal index out of range");
+        if (ct && (ct[i] < 0 || ct[i] >= n_vt))
+            return fail(ct[i] < 0 ? B200PT_ERR_INVALID : B200PT_ERR_BOUNDS, ct[i] < 0 ? "dedup_mesh: some corners have no texcoord index (irregular shape: host routine)" : "dedup_mesh: texcoord index out of range");
+    }
+    CU(cudaSetDevice(c->cfg.device_ordinal));
+    const uint32_t n = (uint32_t)n_corners, range = (uint32_t)(hi - lo) + 1u;
+    // only the slice [lo, hi] of the position array travels; normals / texcoords travel whole (their indices are not bounded
+    // by the shape's position range)
+    const size_t b_cv = sizeof(int32_t) * n, b_av = sizeof(float) * 3 * (size_t)range;
+    const size_t b_an = cn ? sizeof(float) * 3 * (size_t)n_vn : 0, b_at = ct ? sizeof(float) * 2 * (size_t)n_vt : 0;
+    const size_t scan_bytes = dedup_scan_bytes(n);
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t total = up(b_cv) * (1 + (cn ? 1 : 0) + (ct ? 1 : 0)) + up(b_av) + up(b_an) + up(b_at) + up(sizeof(uint32_t) * range) +
+                         2 * up(sizeof(uint32_t) * n) + up(scan_bytes) + up(b_cv) /*out_idx*/ + up(sizeof(float) * 3 * (size_t)n) * (1 + (cn ? 1 : 0)) +
+                         (ct ? up(sizeof(float) * 2 * (size_t)n) : 0);
+    unsigned char* arena = nullptr;
+    CU(cudaMalloc(&arena, total));
+    size_t off = 0;
+    auto take = [&](size_t b) { unsigned char* p = arena + off; off += up(b); return p; };
+    int32_t* d_cv = (int32_t*)take(b_cv);
+    int32_t* d_cn = cn ? (int32_t*)take(b_cv) : nullptr;
+    int32_t* d_ct = ct ? (int32_t*)take(b_cv) : nullptr;
+    float* d_av = (float*)take(b_av);
+    float* d_an = cn ? (float*)take(b_an) : nullptr;
+    float* d_at = ct ? (float*)take(b_at) : nullptr;
+    uint32_t* d_first = (uint32_t*)take(sizeof(uint32_t) * range);
+    uint32_t* d_flag = (uint32_t*)take(sizeof(uint32_t) * n);
+    uint32_t* d_rank = (uint32_t*)take(sizeof(uint32_t) * n);
+    void* d_scan = take(scan_bytes);
+    int32_t* d_idx = (int32_t*)take(b_cv);
+    float* d_ov = (float*)take(sizeof(float) * 3 * (size_t)n);
+    float* d_on = cn ? (float*)take(sizeof(float) * 3 * (size_t)n) : nullptr;
+    float* d_ot = ct ? (float*)take(sizeof(float) * 2 * (size_t)n) : nullptr;
+    cudaStream_t st = c->stream;
+    cudaError_t e = cudaMemcpyAsync(d_cv, cv, b_cv, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && cn) e = cudaMemcpyAsync(d_cn, cn, b_cv, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && ct) e = cudaMemcpyAsync(d_ct, ct, b_cv, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_av, av + 3 * (size_t)lo, b_av, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && cn) e = cudaMemcpyAsync(d_an, an, b_an, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && ct) e = cudaMemcpyAsync(d_at, at, b_at, cudaMemcpyHostToDevice, st);
+    uint32_t n_unique = 0;
+    // the position slice starts at index lo: the kernels index it with v, so hand them the pointer shifted back
+    if (e == cudaSuccess)
+        e = dedup_mesh_device(d_cv, d_cn, d_ct, n, lo, range, d_av - 3 * (size_t)lo, d_an, d_at, d_first, d_flag, d_rank, d_scan, scan_bytes,
+                              d_idx, d_ov, d_on, d_ot, &n_unique, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_idx, d_idx, b_cv, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_verts, d_ov, sizeof(float) * 3 * (size_t)n_unique, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && cn) e = cudaMemcpyAsync(out_normals, d_on, sizeof(float) * 3 * (size_t)n_unique, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess && ct) e = cudaMemcpyAsync(out_uvs, d_ot, sizeof(float) * 2 * (size_t)n_unique, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(arena);
+    if (e != cudaSuccess) return fail(B200PT_ERR_CUDA, std::string("dedup_mesh: ") + cudaGetErrorString(e));
+    *n_out_verts = (int32_t)n_unique;
+    return B200PT_OK;
+}

@@ -62,6 +62,13 @@ constexpr int kSuspWords = 3 + kSuspStack / 2;  // 176 bytes per lane: hit, grou
 constexpr int kMaxParts = 4;  // interleaved sub-frames walked on separate streams (api.cu: render_local)
 constexpr int kBatch = 32;  // wavefront iterations between host checks (even: the state sets alternate with k)
 
+// create_mesh on the device (mesh_dedup.cu)
+size_t dedup_scan_bytes(uint32_t n);
+cudaError_t dedup_mesh_device(const int32_t* cv, const int32_t* cn, const int32_t* ct, uint32_t n, int32_t lo, uint32_t range,
+                              const float* av, const float* an, const float* at, uint32_t* first, uint32_t* is_first, uint32_t* rank,
+                              void* scratch, size_t scratch_bytes, int32_t* out_idx, float* ov, float* on, float* ot,
+                              uint32_t* n_unique, cudaStream_t st);
+
 // launch wrappers (wavefront.cu)
 void launch_init_lanes(const SceneView& sv, const LaneArrays& la, int part, int parts, uint32_t n_part, cudaStream_t st);
 void launch_extend(const SceneView& sv, const LaneArrays& la, int k, uint32_t max_count, bool count, cudaStream_t st);

@@ -16,6 +16,33 @@ static void check(int status, const char* what) {
     if (status != B200PT_OK) throw std::runtime_error(std::string(what) + ": " + b200pt_last_error());
 }
 
+// create_mesh on the device (b200pt_dedup_mesh); irregular shapes go back to the host routine (nullptr)
+create_mesh_fn gpu_create_mesh(b200pt_ctx* ctx) {
+    return [ctx](const raw_shape& r) -> std::shared_ptr<mesh> {
+        bool any_n = false, all_n = true, any_t = false, all_t = true;
+        for (size_t i = 0; i < r.n_corners; ++i) {
+            (r.corner_vn[i] >= 0 ? any_n : all_n) = r.corner_vn[i] >= 0;
+            (r.corner_vt[i] >= 0 ? any_t : all_t) = r.corner_vt[i] >= 0;
+        }
+        if (r.n_corners == 0 || (any_n && !all_n) || (any_t && !all_t)) return nullptr;
+        auto m = std::make_shared<mesh>();
+        m->indices.resize(r.n_corners);
+        m->vertices.resize(3 * r.n_corners);
+        if (any_n) m->normals.resize(3 * r.n_corners);
+        if (any_t) m->texcoords.resize(2 * r.n_corners);
+        int32_t nv = 0;
+        check(b200pt_dedup_mesh(ctx, r.attrib_vertices, (int32_t)r.n_vertices, r.attrib_normals, (int32_t)r.n_normals, r.attrib_texcoords,
+                                (int32_t)r.n_texcoords, r.corner_v, any_n ? r.corner_vn : nullptr, any_t ? r.corner_vt : nullptr,
+                                (int32_t)r.n_corners, m->vertices.data(), any_n ? m->normals.data() : nullptr,
+                                any_t ? m->texcoords.data() : nullptr, m->indices.data(), &nv),
+              "dedup_mesh");
+        m->vertices.resize(3 * (size_t)nv);
+        if (any_n) m->normals.resize(3 * (size_t)nv);
+        if (any_t) m->texcoords.resize(2 * (size_t)nv);
+        return m;
+    };
+}
+
 // bind_sbt_data, application.cpp:184-294
 void bind_scene(const program_data& pdata, b200pt_ctx* ctx) {
     for (const entity& e : pdata.entities) {

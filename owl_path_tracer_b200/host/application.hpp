@@ -4,6 +4,7 @@
 #pragma once
 #include <functional>
 
+#include "loaders.hpp"
 #include "scene.hpp"
 
 namespace host {
@@ -18,10 +19,15 @@ struct load_options {
     int detail = 0;               // procedural stand-in detail knob
     bool allow_procedural = true; // generate stand-ins for assets missing from the checkout
     bool env_float = false;       // keep environment.hdr as float radiance instead of the reference's 8-bit conversion
+    create_mesh_fn create_mesh;   // optional replacement of the loader's create_mesh stage (gpu_create_mesh below)
 };
 
 // init_program_data, application.cpp:143-181
 void init_program_data(program_data& pdata, test_data& tdata, const std::string& assets_path, const load_options& opt);
+
+// create_mesh on the device (b200pt_dedup_mesh): plug into load_options::create_mesh.  Irregular shapes (some
+// corners with a normal / texcoord index, some without) are handed back to the host's create_mesh.  (application.cpp, links CUDA)
+create_mesh_fn gpu_create_mesh(b200pt_ctx* ctx);
 
 // bind_sbt_data, application.cpp:184-294: meshes, accel, env, materials, camera, frame size
 void bind_scene(const program_data& pdata, b200pt_ctx* ctx);

@@ -531,11 +531,37 @@ std::shared_ptr<mesh> create_mesh(const obj_shape& shape, const obj_attrib& at) 
 }
 }  // namespace
 
-std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::string& obj_file, int threads) {  // mesh_loader.cpp:85-121
+std::vector<std::pair<std::string, std::shared_ptr<mesh>>> load_obj(const std::string& obj_file, int threads,
+                                                                     const create_mesh_fn& create) {  // mesh_loader.cpp:85-121
     obj_attrib at;
     std::vector<obj_shape> shapes;
     std::string err;
     if (!parse_obj(obj_file, threads, at, shapes, err)) throw std::runtime_error(err);
+    if (create) {   // a pluggable create_mesh (the GPU de-duplication): shapes one after the other, corners fan-split here
+        std::vector<std::pair<std::string, std::shared_ptr<mesh>>> out;
+        std::vector<int32_t> cv, cn, ct;
+        for (const obj_shape& sh : shapes) {
+            cv.clear(); cn.clear(); ct.clear();
+            size_t offset = 0;
+            for (int fs : sh.face_sizes) {
+                for (int t = 1; t + 1 < fs; ++t)
+                    for (size_t k : {offset, offset + (size_t)t, offset + (size_t)t + 1}) {
+                        const obj_index& ix = sh.indices[k];
+                        if (ix.v < 0 || 3 * (size_t)ix.v + 2 >= at.vertices.size()) throw std::runtime_error("obj: vertex index out of range");
+                        if (ix.vn >= 0 && 3 * (size_t)ix.vn + 2 >= at.normals.size()) throw std::runtime_error("obj: normal index out of range");
+                        if (ix.vt >= 0 && 2 * (size_t)ix.vt + 1 >= at.texcoords.size()) throw std::runtime_error("obj: texcoord index out of range");
+                        cv.push_back(ix.v); cn.push_back(ix.vn); ct.push_back(ix.vt);
+                    }
+                offset += (size_t)fs;
+            }
+            const raw_shape raw{at.vertices.data(), at.vertices.size() / 3, at.normals.data(), at.normals.size() / 3,
+                                at.texcoords.data(), at.texcoords.size() / 2, cv.data(), cn.data(), ct.data(), cv.size()};
+            std::shared_ptr<mesh> m = create(raw);
+            if (!m) m = create_mesh(sh, at);
+            out.emplace_back(sh.name, std::move(m));
+        }
+        return out;
+    }
     // the shapes are independent: their vertex maps are built by concurrent threads, results keep the file order
     std::vector<std::pair<std::string, std::shared_ptr<mesh>>> out(shapes.size());
     std::atomic<size_t> next{0};

@@ -8,6 +8,7 @@
 //   --env-intensity F  --detail N  --device K  --out DIR  --stats
 //   --pipeline N (N contexts on the device: the frames of the sweep are queued and frame k+1 starts while frame k drains;
 //                 same files, same bytes)
+//   --gpu-dedup (create_mesh's vertex de-duplication on the device, b200pt_dedup_mesh; same meshes byte for byte)
 //   --gpus N (devices K .. K+N-1, samples sharded over them, one NCCL reduce per frame; the reference's OWL context can
 //             span devices the same way, extern/owl/owl/RayGen.cpp:140-146, and asks for one, application.cpp:62)
 //   --nee (light sampling + MIS mode)  --streams V (RNG streams per pixel)  --pfm (float frame next to the PNG)
@@ -28,7 +29,7 @@ int main(int argc, char** argv) {
     std::string out_dir = std::filesystem::current_path().string();
     host::load_options opt;
     int device = 0, flags = 0, streams = 1, gpus = 1, pipeline = 1;
-    bool stats = false, pfm = false, gamma = false, save_passes = false;
+    bool stats = false, pfm = false, gamma = false, save_passes = false, gpu_dedup = false;
     int progressive = 0;
     double target_error = 0.0;
     for (int i = 1; i < argc; ++i) {
@@ -54,6 +55,7 @@ int main(int argc, char** argv) {
         else if (a == "--device") { need(1); device = atoi(argv[++i]); }
         else if (a == "--gpus") { need(1); gpus = atoi(argv[++i]); }
         else if (a == "--pipeline") { need(1); pipeline = atoi(argv[++i]); }
+        else if (a == "--gpu-dedup") gpu_dedup = true;
         else if (a == "--out") { need(1); out_dir = argv[++i]; }
         else if (a == "--stats") stats = true;
         else if (a == "--nee") flags |= B200PT_FLAG_NEE;
@@ -66,7 +68,7 @@ int main(int argc, char** argv) {
         else if (a == "--gamma") gamma = true;
         else if (a == "--help" || a == "-h") {
             printf("path_tracer [--assets DIR] [--scene NAME] [--size W H] [--spp N] [--depth N] [--env color|auto|map]\n"
-                   "            [--env-intensity F] [--detail N] [--device K] [--gpus N] [--pipeline N] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"
+                   "            [--env-intensity F] [--detail N] [--device K] [--gpus N] [--pipeline N] [--gpu-dedup] [--out DIR] [--stats] [--nee] [--streams V] [--pfm]\n"
                    "            [--env-float] [--progressive N] [--target-error E] [--save-passes] [--gamma]\n"
                    "without arguments: ./assets/settings.json and its scene, as the reference's executable\n");
             return 0;
@@ -79,7 +81,19 @@ int main(int argc, char** argv) {
     try {
         host::program_data pdata;
         host::test_data tdata;
+        b200pt_ctx* loader_ctx = nullptr;   // --gpu-dedup: the loader's create_mesh stage runs on the device
+        if (gpu_dedup) {
+            b200pt_config lc{};
+            lc.device_ordinal = device;
+            lc.world_size = 1;
+            if (b200pt_create(&lc, &loader_ctx) != B200PT_OK) {
+                fprintf(stderr, "b200pt_create failed: %s\n", b200pt_last_error());
+                return 1;
+            }
+            opt.create_mesh = host::gpu_create_mesh(loader_ctx);
+        }
         host::init_program_data(pdata, tdata, assets_path, opt);
+        if (loader_ctx) b200pt_destroy(loader_ctx);
         for (const std::string& n : pdata.notes) printf("NOTE: %s\n", n.c_str());
 
         pdata.write_pfm = pfm;

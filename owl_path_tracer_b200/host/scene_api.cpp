@@ -153,9 +153,6 @@ int b200pt_write_obj(const b200pt_scene* s, const char* path) {
 
 // ---- single stages (differential tests against the reference's own loaders)
 }  // extern "C"
-struct b200pt_shapes {
-    std::vector<std::pair<std::string, std::shared_ptr<host::mesh>>> shapes;
-};
 struct b200pt_materials {
     std::vector<host::material_entry> entries;
 };

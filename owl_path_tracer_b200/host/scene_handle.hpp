@@ -3,6 +3,8 @@
 #pragma once
 #include <stdexcept>
 #include <string>
+#include <memory>
+#include <utility>
 #include <vector>
 
 #include "../../include/b200pt_host.h"
@@ -12,6 +14,10 @@ struct b200pt_scene {
     host::program_data pdata;
     host::test_data tdata;
     std::vector<host::material_data> mats;  // scratch for b200pt_scene_materials
+};
+
+struct b200pt_shapes {
+    std::vector<std::pair<std::string, std::shared_ptr<host::mesh>>> shapes;
 };
 
 namespace host {

@@ -60,7 +60,7 @@ void init_program_data(program_data& pdata, test_data& tdata, const std::string&
 
     const std::string obj_file = assets_path + "/" + scene + ".obj.scene";
     if (std::filesystem::exists(obj_file)) {
-        pdata.meshes = load_obj(obj_file);
+        pdata.meshes = load_obj(obj_file, 0, opt.create_mesh);
     } else if (opt.allow_procedural) {
         pdata.meshes = make_procedural_scene(scene, opt.detail);
         if (pdata.meshes.empty()) throw std::runtime_error("Cannot open file [" + obj_file + "]");

@@ -10,8 +10,8 @@ NVFLAGS="-std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=
 while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
   ( d=$(mktemp -d)
-    for f in api wavefront bvh_build; do nvcc $NVFLAGS $flags -c -o $d/$f.o $CSRC/$f.cu & done; wait
-    nvcc -shared -cudart static -gencode arch=compute_100a,code=sm_100a -o $OUT/libb200pt_$name.so $d/api.o $d/wavefront.o $d/bvh_build.o
+    for f in api wavefront bvh_build mesh_dedup; do nvcc $NVFLAGS $flags -c -o $d/$f.o $CSRC/$f.cu & done; wait
+    nvcc -shared -cudart static -gencode arch=compute_100a,code=sm_100a -o $OUT/libb200pt_$name.so $d/api.o $d/wavefront.o $d/bvh_build.o $d/mesh_dedup.o
     rm -rf $d; echo "built $OUT/libb200pt_$name.so  [$flags]" ) &
 done
 wait
