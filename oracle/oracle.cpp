@@ -886,7 +886,9 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays,
         if (material.emission > 0.0f) {                                                   // :157-161
             if (tri_l && prev_pdf > 0.0f && sc.mesh_light_first[mesh_index] >= 0) {
                 const Scene::Light& lt = sc.lights[sc.mesh_light_first[mesh_index] + prim];
-                V3 nl = add(add(scale(bw, mesh.normals[i0]), scale(bx, mesh.normals[i1])), scale(by, mesh.normals[i2]));
+                // the area -> solid-angle density needs the GEOMETRIC unit normal of the emitter (the reference's unused
+                // sample_triangle, lights.hpp:30-48, takes the interpolated shading normal: biased for smooth emitters)
+                V3 nl = normalize(cross(sub(mesh.verts[i1], mesh.verts[i0]), sub(mesh.verts[i2], mesh.verts[i0])));
                 float pdf_light = p_sel * (lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, h.t * h.t, dot(neg(dir), nl)));
                 radiance = v3(material.emission * power_heuristic(prev_pdf, pdf_light));
             } else {
@@ -939,7 +941,7 @@ V3 trace_path(Scene& sc, V3 org, V3 dir, Rng& rng, Finder find, uint64_t& nrays,
                 const float cx = 1.0f - su0, cy = u1 * su0;
                 const float cz = 1.0f - cx - cy;
                 V3 pos = add(add(scale(cz, lm.verts[j0]), scale(cx, lm.verts[j1])), scale(cy, lm.verts[j2]));
-                V3 nl = add(add(scale(cz, lm.normals[j0]), scale(cx, lm.normals[j1])), scale(cy, lm.normals[j2]));
+                V3 nl = normalize(cross(sub(lm.verts[j1], lm.verts[j0]), sub(lm.verts[j2], lm.verts[j0])));   // geometric unit normal
                 ldir = sub(pos, v_p);
                 const float dist2 = dot(ldir, ldir);
                 const float dist = sqrtf(dist2);

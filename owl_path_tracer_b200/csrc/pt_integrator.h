@@ -299,8 +299,9 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
             // the same emitter could have been reached by light sampling at the previous vertex:
             // power heuristic between the BSDF density and the light density of this very point
             const LightTri lt = load_ro(sv.lights + (mi.light_first + ((int)hit.tri - mi.first_tri)));
-            const float lw = 1.0f - hit.u - hit.v;
-            const f3 nl = lw * f3{n0.x, n0.y, n0.z} + hit.u * f3{n1.x, n1.y, n1.z} + hit.v * f3{n2.x, n2.y, n2.z};
+            // area -> solid-angle density with the GEOMETRIC unit normal of the emitter (the reference's unused
+            // sample_triangle, lights.hpp:30-48, takes the interpolated shading normal: biased for smooth emitters)
+            const f3 nl = normalize(cross(f3{p1.x, p1.y, p1.z} - f3{p0.x, p0.y, p0.z}, f3{p2.x, p2.y, p2.z} - f3{p0.x, p0.y, p0.z}));
             const float pdf_light = p_sel * (lt.prob * pdf_area_to_solid_angle(1.0f / lt.area, hit.t * hit.t, dot(-L.d, nl)));
             const float w = power_heuristic(L.prev_pdf, pdf_light);
             return end_sample(sv, L, px, py, mk3(m.emission * w) * L.thr);
@@ -363,12 +364,11 @@ PT_HD ShadeResult shade_lane(const SceneView& sv, LaneState& L, const Hit& hit, 
             const LightTri lt = load_ro(sv.lights + lo);
             const TriIdx lx = load_ro(reinterpret_cast<const TriIdx*>(sv.idx4) + lt.tri);
             const f4 q0 = load_ro(sv.vpos + lx.i0), q1 = load_ro(sv.vpos + lx.i1), q2 = load_ro(sv.vpos + lx.i2);
-            const f4 m0 = load_ro(sv.vnrm + lx.i0), m1 = load_ro(sv.vnrm + lx.i1), m2 = load_ro(sv.vnrm + lx.i2);
             const float su0 = sqrtf(u0);
             const float bx = 1.0f - su0, by = u1 * su0;
             const float bz = 1.0f - bx - by;
             const f3 pos = bz * f3{q0.x, q0.y, q0.z} + bx * f3{q1.x, q1.y, q1.z} + by * f3{q2.x, q2.y, q2.z};
-            const f3 nl = bz * f3{m0.x, m0.y, m0.z} + bx * f3{m1.x, m1.y, m1.z} + by * f3{m2.x, m2.y, m2.z};
+            const f3 nl = normalize(cross(f3{q1.x, q1.y, q1.z} - f3{q0.x, q0.y, q0.z}, f3{q2.x, q2.y, q2.z} - f3{q0.x, q0.y, q0.z}));
             dir = pos - vp;
             const float dist2 = dot(dir, dir);
             const float dist = sqrtf(dist2);
