@@ -358,7 +358,8 @@ def main():
                     algorithmic_bytes_per_launch=rank0_rays * bytes_per_ray / max(1, launches_extend),
                     share_of_step=kt["extend_ms"] / kt["render_ms"] if kt["render_ms"] else None,
                     timing_pass="one extra frame of the workload on one stream with events around every launch "
-                                "(%.1f ms; the timed region runs 2 concurrent sub-frames, %.1f ms per frame)"
+                                "(%.1f ms; without events and as two concurrent sub-frames the blocking frame takes %.1f ms; "
+                                "the timed region overlaps frames, see `frames`)"
                                 % (kt["render_ms"], blocking["wall_ms"] / min(args.steps, 3)),
                     traffic_to_algorithmic=(traffic / (rank0_rays * bytes_per_ray / max(1, launches_extend))) if traffic else None,
                     bvh_mb=s2["bvh_bytes"] / 1e6,

@@ -6,7 +6,7 @@ export B200PT_QUIET=1
 mkdir -p gpurun_out
 B="python bench.py --steps 1 --warmup 1 --pipeline 1 --streams-mode 0 --no-cpu-baseline --no-parity-check"
 timeout 600 $B --spp 16 > gpurun_out/bench_spp16.log 2>&1 || { echo "plain bench failed"; tail -5 gpurun_out/bench_spp16.log; exit 1; }
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches.csv $B --spp 16 > gpurun_out/ncu_launches.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/launches.csv $B --spp 8 > gpurun_out/ncu_launches.log 2>&1
 echo "launch list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_extend -s 4 -c 3 -f -o gpurun_out/extend $B --spp 16 > gpurun_out/ncu_extend.log 2>&1
 echo "extend capture rc=$?"
