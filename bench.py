@@ -121,6 +121,26 @@ def run_reference(args):
     cores = host_cores()
     spp = 4   # bounded sample: ~4 s per step on 16 cores, so steps+warmup stay within minutes
     rate, sec, rays = cpu_oracle_rate(spp, cores, steps=args.steps, warmup=args.warmup)
+    # beside it, when oracle/_ref travelled to this box: the reference's OWN ray_gen / trace_path / Disney code (device.cu
+    # compiled for the host, oracle/ref/) on a window of the same frame; its closest hits come from the oracle's finder
+    # one ray at a time through a callback, so it is reported, not used as the arm's value
+    ref_code = None
+    try:
+        sys.path.insert(0, str(REPO / "tests"))
+        from checkers import Oracle, Ref, REF_DIR
+        if (REF_DIR / "libref_device.so").exists():
+            import owl_path_tracer_b200 as pt
+            sc = pt.Scene(**dict(WORKLOAD, spp=2))
+            o = Oracle(det=False).load_scene(sc)
+            r = Ref().load_scene(sc)
+            t0 = time.perf_counter()
+            out = r.render(o, window=(640, 360, 1280, 720), threads=cores)
+            dt = time.perf_counter() - t0
+            ref_code = dict(value=out["rays"] / dt * 1e-6, unit="Mrays/s", cores=cores,
+                            sample="640x360 centre window of the 1080p dragon frame at 2 spp (%d rays, %.1f s): the reference's device.cu "
+                                   "+ disney/*.cuh compiled for the host (oracle/_ref/libref_device.so), closest hits by the oracle's BVH" % (out["rays"], dt))
+    except Exception as e:   # the arm must not fail because the optional measurement did
+        ref_code = dict(unavailable=str(e)[:200])
     sample = (f"full 1920x1080 dragon frame at {spp} spp per step ({rays} rays), oracle with glibc math, {cores} threads; "
               "a scalar port over a median-split binary BVH, NOT a tuned CPU ray tracer")
     line = dict(impl="reference", metric="Mrays/s", value=rate, unit="Mrays/s", n_gpus=args.gpus, steps=args.steps,
@@ -129,6 +149,7 @@ def run_reference(args):
                 spp_per_s=spp / sec,
                 cpu_baseline=dict(value=rate, unit="Mrays/s", cores=cores, kind="port", sample=sample),
                 e2e=dict(value=rate, unit="Mrays/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                reference_code_on_cpu=ref_code,
                 note="reference's own OWL/OptiX build is unavailable on this box (no OptiX SDK, no RT cores); this is the "
                      "scalar CPU restatement of its integrator (oracle/oracle.cpp)")
     emit(line)
