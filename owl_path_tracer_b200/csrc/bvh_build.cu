@@ -80,6 +80,43 @@ __global__ void k_refit(int n, const int32_t* __restrict__ leaf_parent, BinNode*
     refit_from_leaf(k, leaf_parent, nodes, flags, sorted_tri, tri_lo, tri_hi, plans);
 }
 
+// ---- reinsertion passes (pt_build.h, "reinsertion optimisation"); c = candidate = lock slot ----
+__global__ void k_ri_link(int n_inner, ReinsertTree t) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_inner) ri_link_children(i, t);
+}
+__global__ void k_ri_find(int m, ReinsertTree t, float* gain, int32_t* target, int32_t* pivot, uint8_t* state) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < m) ri_find(c, t, gain, target, pivot, state);
+}
+__global__ void k_ri_bid(int m, ReinsertTree t, const float* gain, const int32_t* target, uint8_t* state,
+                         unsigned long long* lock) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < m) ri_bid(c, t, gain, target, state, lock);
+}
+__global__ void k_ri_settle(int m, ReinsertTree t, const float* gain, const int32_t* target, uint8_t* state,
+                            const unsigned long long* lock) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < m) ri_settle(c, t, gain, target, state, lock);
+}
+__global__ void k_ri_hold(int m, ReinsertTree t, const int32_t* target, const uint8_t* state, unsigned long long* lock) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < m) ri_hold(c, t, target, state, lock);
+}
+__global__ void k_ri_mark(int m, const uint8_t* state, unsigned long long* lock) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < m) ri_mark_moved(c, state, lock);
+}
+__global__ void k_ri_drop(int m, ReinsertTree t, const int32_t* target, const int32_t* pivot, uint8_t* state,
+                          const unsigned long long* lock) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < m) ri_drop_crossing(c, t, target, pivot, state, lock);
+}
+__global__ void k_ri_apply(int m, ReinsertTree t, const int32_t* target, const uint8_t* state) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < m) ri_apply(c, t, target, state);
+}
+
 __global__ void k_collapse(const CollapseItem* __restrict__ items, uint32_t n_items, const BinNode* __restrict__ bin,
                            const uint32_t* __restrict__ sorted_tri, const float* __restrict__ tri_lo,
                            const float* __restrict__ tri_hi, const f4* __restrict__ pos,
@@ -214,6 +251,41 @@ bool build_bvh_device(const f4* d_pos, const int32_t* d_idx4, uint32_t n, const 
             }
             CK(cudaMemcpyAsync(&root, cid, sizeof root, cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
+            if (n >= 3 && kReinsertPasses > 0) {
+                // the sort keys, neighbour lists and cluster boxes are dead by now: their space holds the
+                // per-candidate results (2n-1 candidates) and the lock words
+                int32_t* leaf_parent = nn;
+                int32_t* arrive_flags = cid2;
+                float* gain = (float*)keys;
+                int32_t* target = (int32_t*)pscan;  // (keys2 stays: the radix-tree fallback reads it)
+                int32_t* pivot = (int32_t*)pflags;
+                unsigned long long* lock = (unsigned long long*)cbox;
+                uint8_t* state = (uint8_t*)cbox2;
+                static_assert(sizeof(Box6) >= 2 * sizeof(unsigned long long), "lock words fit the cluster boxes");
+                const int m = 2 * (int)n - 1;
+                const uint32_t cb = (uint32_t)(m + B - 1) / B;
+                const ReinsertTree rt{bin, leaf_parent, vals2, tri_lo, tri_hi, (int32_t)n, root};
+                k_ri_link<<<nb, B, 0, st>>>((int)n - 1, rt);
+                CK(cudaGetLastError());
+                for (int pass = 0; pass < kReinsertPasses; ++pass) {
+                    k_ri_find<<<cb, B, 0, st>>>(m, rt, gain, target, pivot, state);
+                    CK(cudaGetLastError());
+                    for (int round = 0; round < kReinsertRounds; ++round) {
+                        CK(cudaMemsetAsync(lock, 0, sizeof(unsigned long long) * (size_t)m, st));
+                        if (round > 0) k_ri_hold<<<cb, B, 0, st>>>(m, rt, target, state, lock);
+                        k_ri_bid<<<cb, B, 0, st>>>(m, rt, gain, target, state, lock);
+                        k_ri_settle<<<cb, B, 0, st>>>(m, rt, gain, target, state, lock);
+                        CK(cudaGetLastError());
+                    }
+                    CK(cudaMemsetAsync(lock, 0, sizeof(unsigned long long) * (size_t)m, st));
+                    k_ri_mark<<<cb, B, 0, st>>>(m, state, lock);
+                    k_ri_drop<<<cb, B, 0, st>>>(m, rt, target, pivot, state, lock);
+                    k_ri_apply<<<cb, B, 0, st>>>(m, rt, target, state);
+                    CK(cudaMemsetAsync(arrive_flags, 0, sizeof(int32_t) * (size_t)n, st));
+                    k_refit<<<nb, B, 0, st>>>((int)n, leaf_parent, bin, arrive_flags, vals2, tri_lo, tri_hi, plans);
+                    CK(cudaGetLastError());
+                }
+            }
         }
         if (n >= 2 && attempt == 1) {
             // fallback: binary radix tree over the Morton keys (Karras 2012), depth bounded by the key

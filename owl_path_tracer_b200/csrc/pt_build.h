@@ -8,6 +8,8 @@
 //   4. binary tree by parallel locally-ordered clustering over the Morton order
 //      (ploc_nearest / ploc_flags / scan / ploc_emit, rounds until one cluster is left);
 //      every new node gets its box, triangle count and collapse plan when it is created
+//  4b. reinsertion passes over that tree (ri_find / ri_bid / ri_settle / ri_hold / ri_apply, then
+//      refit_from_leaf for boxes, counts and plans): nodes move to where they cost the least area
 //   5. cost-optimal collapse plan per binary node (plan_node, dynamic programme over
 //      "subtree in at most i slots", Ylitie et al. 2017)
 //   6. top-down collapse to 8-wide nodes following the plan, subtrees of <= 3
@@ -18,6 +20,8 @@
 // Each step is a PT_HD function of the element index so that tests/emu can run the
 // very same code sequentially on the host.
 #pragma once
+#include <cstring>
+
 #include "pt_bvh8.h"
 
 namespace pt {
@@ -146,6 +150,13 @@ PT_HD float load_cg(const float* p) {
     return *p;
 #endif
 }
+PT_HD int32_t load_cg_i(const int32_t* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldcg(p);
+#else
+    return *p;
+#endif
+}
 PT_HD void fence() {
 #if defined(__CUDA_ARCH__)
     __threadfence();
@@ -261,6 +272,7 @@ PT_HD void refit_from_leaf(int k, const int32_t* leaf_parent, BinNode* nodes, in
         fence();
         BinNode& nd = nodes[cur];
         float lo[3], hi[3];
+        int32_t count = 0;
         for (int side = 0; side < 2; ++side) {
             const int32_t c = side == 0 ? nd.left : nd.right;
             const float *clo, *chi;
@@ -268,9 +280,11 @@ PT_HD void refit_from_leaf(int k, const int32_t* leaf_parent, BinNode* nodes, in
                 const uint32_t t = sorted_tri[~c];
                 clo = tri_lo + 3 * (size_t)t;
                 chi = tri_hi + 3 * (size_t)t;
+                count += 1;
             } else {
                 clo = nodes[c].lo;
                 chi = nodes[c].hi;
+                count += load_cg_i(&nodes[c].count);
             }
             for (int a = 0; a < 3; ++a) {
                 // child boxes were written by another thread: read them past L1
@@ -283,6 +297,7 @@ PT_HD void refit_from_leaf(int k, const int32_t* leaf_parent, BinNode* nodes, in
             nd.lo[a] = lo[a];
             nd.hi[a] = hi[a];
         }
+        nd.count = count;  // (the radix tree already knows it; a tree changed by reinsertion does not)
         plan_node(cur, nodes, plans, sorted_tri, tri_lo, tri_hi);
         cur = nd.parent;
     }
@@ -393,6 +408,234 @@ PT_HD void ploc_emit(int i, const int32_t* nn, uint64_t excl, const int32_t* cid
         u.hi[k] = nd.hi[k];
     }
     out_cbox[pos] = u;
+}
+
+// ---- reinsertion optimisation of the binary tree ---------------------------------------------
+// Between the clustering and the wide collapse: every node (inner node or triangle) looks for the
+// place in the tree where its subtree would cost the least surface area, and a conflict-free
+// subset of those moves is applied; a few passes.  The search is the branch-and-bound walk of
+// Meister & Bittner 2018 ("Parallel reinsertion for bounding volume hierarchy optimization"):
+// from the node's parent upwards, into the sibling subtree at every level.  Conflicts are settled
+// without any order dependence, so the device and its host emulation produce the same tree:
+//   * a move touches six nodes (x, its parent p, sibling s, grandparent g, the target o and o's
+//     parent); it takes part in a round by atomicMax of (gain, candidate) on their lock words and
+//     wins when all six hold its key; winners keep their nodes (~0) and the rest try again,
+//   * boxes and triangle counts along the two paths are not locked: one refit of the whole tree
+//     after the pass restores them, so a gain is an estimate once several moves share ancestors,
+//   * a winner whose insertion path (o up to the common ancestor) runs through the root of
+//     another winner's moved subtree is dropped: two such moves could close a cycle.
+#ifndef PT_REINSERT_PASSES
+#define PT_REINSERT_PASSES 4
+#endif
+constexpr int kReinsertPasses = PT_REINSERT_PASSES;
+constexpr int kReinsertRounds = 3;
+constexpr int kReinsertStack = 64;
+constexpr unsigned long long kRiHeld = ~0ull;
+enum : uint8_t { kRiNone = 0, kRiActive = 1, kRiWin = 2, kRiDead = 3 };
+
+struct ReinsertTree {
+    BinNode* bin;          // inner nodes 0..n-2
+    int32_t* leaf_parent;  // per sorted position
+    const uint32_t* sorted_tri;
+    const float *tri_lo, *tri_hi;
+    int32_t n;     // triangles
+    int32_t root;  // never moves
+};
+// candidates and lock slots: 0..n-2 the inner nodes, n-1..2n-2 the leaves by sorted position
+PT_HD int32_t ri_ref(const ReinsertTree& t, int c) { return c < t.n - 1 ? c : ~(c - (t.n - 1)); }
+PT_HD int ri_slot(const ReinsertTree& t, int32_t ref) { return ref >= 0 ? ref : (t.n - 1) + ~ref; }
+PT_HD int32_t ri_parent(const ReinsertTree& t, int32_t ref) { return ref >= 0 ? t.bin[ref].parent : t.leaf_parent[~ref]; }
+PT_HD void ri_set_parent(const ReinsertTree& t, int32_t ref, int32_t p) {
+    if (ref >= 0)
+        t.bin[ref].parent = p;
+    else
+        t.leaf_parent[~ref] = p;
+}
+PT_HD void ri_box(const ReinsertTree& t, int32_t ref, Box6& b) {
+    if (ref >= 0) {
+        const BinNode& nd = t.bin[ref];
+        for (int a = 0; a < 3; ++a) {
+            b.lo[a] = nd.lo[a];
+            b.hi[a] = nd.hi[a];
+        }
+    } else {
+        const uint32_t tri = t.sorted_tri[~ref];
+        for (int a = 0; a < 3; ++a) {
+            b.lo[a] = t.tri_lo[3 * (size_t)tri + a];
+            b.hi[a] = t.tri_hi[3 * (size_t)tri + a];
+        }
+    }
+}
+// the clustering leaves parent links unset: inner node i names itself in its two children
+PT_HD void ri_link_children(int i, const ReinsertTree& t) {
+    ri_set_parent(t, t.bin[i].left, i);
+    ri_set_parent(t, t.bin[i].right, i);
+    if (i == t.root) t.bin[i].parent = -1;
+}
+
+// best new sibling `target` of candidate c, the common ancestor `pivot` of old and new place, and the
+// surface area the move saves (0: stay).  Removing x deletes its parent p (the sibling s moves up) and
+// shrinks the ancestors of p; inserting x next to o re-creates p above o and grows o's ancestors below
+// the pivot.  `save` collects the first, `ind` (per search branch) the second.
+PT_HD void ri_find(int c, const ReinsertTree& t, float* gain, int32_t* target, int32_t* pivot, uint8_t* state) {
+    gain[c] = 0.0f;
+    state[c] = kRiNone;
+    const int32_t x = ri_ref(t, c);
+    if (x == t.root) return;
+    const int32_t p = ri_parent(t, x);
+    if (p < 0 || p == t.root) return;
+    Box6 bx;
+    ri_box(t, x, bx);
+    const float ax = half_area(bx.lo, bx.hi);
+    const int32_t s = t.bin[p].left == x ? t.bin[p].right : t.bin[p].left;
+    float save = half_area(t.bin[p].lo, t.bin[p].hi);
+    Box6 shrunk;  // box of the path node below the pivot once x is gone
+    ri_box(t, s, shrunk);
+    float best = 0.0f;
+    int32_t best_o = 0, best_pivot = p;
+    int32_t piv = p, start = s, cur = p;
+    int32_t st_o[kReinsertStack];
+    float st_ind[kReinsertStack];
+    for (;;) {
+        // places in the subtree of `start`, reached from the common ancestor piv
+        int sp = 0;
+        st_o[sp] = start;
+        st_ind[sp++] = 0.0f;
+        while (sp > 0) {
+            --sp;
+            const int32_t o = st_o[sp];
+            const float ind = st_ind[sp];
+            Box6 b;
+            ri_box(t, o, b);
+            const float m = merged_half_area(b, bx);
+            const float g = save - ind - m;
+            if (g > best) {
+                best = g;
+                best_o = o;
+                best_pivot = piv;
+            }
+            if (o >= 0) {
+                const float ind2 = ind + (m - half_area(b.lo, b.hi));
+                // nothing below o saves more than save - ind2 - area(x)
+                if (save - ind2 - ax > best && sp + 2 <= kReinsertStack) {
+                    st_o[sp] = t.bin[o].right;
+                    st_ind[sp++] = ind2;
+                    st_o[sp] = t.bin[o].left;
+                    st_ind[sp++] = ind2;
+                }
+            }
+        }
+        const int32_t q = t.bin[cur].parent;
+        if (q < 0) break;
+        if (cur != p) {  // places above cur also save what cur shrinks by
+            const float shrink = half_area(t.bin[cur].lo, t.bin[cur].hi) - half_area(shrunk.lo, shrunk.hi);
+            if (!(shrink > 0.0f) && !(save - ax > best)) break;
+            save += shrink;
+        }
+        start = t.bin[q].left == cur ? t.bin[q].right : t.bin[q].left;
+        Box6 bo;
+        ri_box(t, start, bo);
+        for (int a = 0; a < 3; ++a) {  // q without x
+            shrunk.lo[a] = fminf(shrunk.lo[a], bo.lo[a]);
+            shrunk.hi[a] = fmaxf(shrunk.hi[a], bo.hi[a]);
+        }
+        piv = q;
+        cur = q;
+    }
+    gain[c] = best;
+    target[c] = best_o;
+    pivot[c] = best_pivot;
+    if (best > 0.0f) state[c] = kRiActive;
+}
+
+PT_HD unsigned long long ri_key(float gain, int c) {
+    uint32_t g;
+    memcpy(&g, &gain, 4);
+    return ((unsigned long long)g << 32) | (uint32_t)c;
+}
+PT_HD void ri_lock_max(unsigned long long* w, unsigned long long key) {
+#if defined(__CUDA_ARCH__)
+    atomicMax(w, key);
+#else
+    if (*w < key) *w = key;
+#endif
+}
+// the six lock slots of candidate c's move
+PT_HD void ri_slots(int c, const ReinsertTree& t, const int32_t* target, int out[6]) {
+    const int32_t x = ri_ref(t, c), p = ri_parent(t, x);
+    const int32_t s = t.bin[p].left == x ? t.bin[p].right : t.bin[p].left;
+    const int32_t o = target[c];
+    out[0] = c;
+    out[1] = ri_slot(t, p);
+    out[2] = ri_slot(t, s);
+    out[3] = ri_slot(t, t.bin[p].parent);
+    out[4] = ri_slot(t, o);
+    out[5] = ri_slot(t, ri_parent(t, o));
+}
+// one round: (1) ri_bid, (2) ri_settle, then lock words are cleared and (3) ri_hold re-marks what winners own
+PT_HD void ri_bid(int c, const ReinsertTree& t, const float* gain, const int32_t* target, uint8_t* state,
+                  unsigned long long* lock) {
+    if (state[c] != kRiActive) return;
+    int sl[6];
+    ri_slots(c, t, target, sl);
+    for (int k = 0; k < 6; ++k)
+        if (lock[sl[k]] == kRiHeld) {  // a winner of an earlier round owns one of the nodes
+            state[c] = kRiDead;
+            return;
+        }
+    const unsigned long long key = ri_key(gain[c], c);
+    for (int k = 0; k < 6; ++k) ri_lock_max(&lock[sl[k]], key);
+}
+PT_HD void ri_settle(int c, const ReinsertTree& t, const float* gain, const int32_t* target, uint8_t* state,
+                     const unsigned long long* lock) {
+    if (state[c] != kRiActive) return;
+    int sl[6];
+    ri_slots(c, t, target, sl);
+    const unsigned long long key = ri_key(gain[c], c);
+    bool all = true;
+    for (int k = 0; k < 6; ++k) all = all && lock[sl[k]] == key;
+    if (all) state[c] = kRiWin;
+}
+PT_HD void ri_hold(int c, const ReinsertTree& t, const int32_t* target, const uint8_t* state, unsigned long long* lock) {
+    if (state[c] != kRiWin) return;
+    int sl[6];
+    ri_slots(c, t, target, sl);
+    for (int k = 0; k < 6; ++k) lock[sl[k]] = kRiHeld;
+}
+// after the rounds (lock words cleared again): winners mark the root of the subtree they move ...
+PT_HD void ri_mark_moved(int c, const uint8_t* state, unsigned long long* lock) {
+    if (state[c] == kRiWin) lock[c] = 1ull;
+}
+// ... and give up when their insertion path crosses somebody else's
+PT_HD void ri_drop_crossing(int c, const ReinsertTree& t, const int32_t* target, const int32_t* pivot, uint8_t* state,
+                            const unsigned long long* lock) {
+    if (state[c] != kRiWin) return;
+    for (int32_t a = ri_parent(t, target[c]); a != pivot[c]; a = t.bin[a].parent)
+        if (lock[a] != 0ull) {
+            state[c] = kRiDead;
+            return;
+        }
+}
+PT_HD void ri_apply(int c, const ReinsertTree& t, const int32_t* target, const uint8_t* state) {
+    if (state[c] != kRiWin) return;
+    const int32_t x = ri_ref(t, c), o = target[c];
+    const int32_t p = ri_parent(t, x);
+    const int32_t s = t.bin[p].left == x ? t.bin[p].right : t.bin[p].left;
+    const int32_t g = t.bin[p].parent;
+    if (t.bin[g].left == p)  // s takes p's place
+        t.bin[g].left = s;
+    else
+        t.bin[g].right = s;
+    ri_set_parent(t, s, g);
+    const int32_t po = ri_parent(t, o);  // p is re-used above o
+    if (t.bin[po].left == o)
+        t.bin[po].left = p;
+    else
+        t.bin[po].right = p;
+    t.bin[p].parent = po;
+    t.bin[p].left = o;
+    t.bin[p].right = x;
+    ri_set_parent(t, o, p);
 }
 
 struct CollapseItem {

@@ -259,6 +259,8 @@ class Emu(_SceneChecker):
         L.emu_set_render.argtypes = [P, C.c_int, C.c_int, C.c_int, C.c_int]
         L.emu_build.argtypes = [P]
         L.emu_levels.argtypes = [P]
+        L.emu_reinsert_stats.argtypes = [P, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.emu_reinsert_stats.restype = C.c_long
         L.emu_update_mesh.argtypes = [P, C.c_int, P, P, C.c_int]
         L.emu_refit.argtypes = [P]
         L.emu_walk_counters.argtypes = [P, P]
@@ -297,6 +299,12 @@ class Emu(_SceneChecker):
     @property
     def levels(self):
         return self.L.emu_levels(self.h)
+
+    def reinsert_stats(self):
+        """(moves applied, binary-tree inner-node area after clustering, after the reinsertion passes)"""
+        a, b = C.c_double(), C.c_double()
+        moves = self.L.emu_reinsert_stats(self.h, C.byref(a), C.byref(b))
+        return int(moves), a.value, b.value
 
     def import_bvh(self, nodes, tris):
         nodes = np.ascontiguousarray(nodes)

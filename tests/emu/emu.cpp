@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 #include <thread>
@@ -39,6 +40,8 @@ struct emu_scene {
     std::vector<uint32_t> level_end;          // DeviceBVH::level_end of the emulated build
     std::vector<int32_t> mesh_vbase, mesh_nv;  // vertex range of every mesh (emu_update_mesh)
     int ploc_rounds = 0;
+    long reinsert_moves = 0;
+    double area_clustered = 0, area_reinserted = 0;  // sum of the binary tree's inner-node half areas
     int debug_px = -1, debug_py = -1;  // print every ray of this pixel (debugging aid)
     int force_lbvh = 0;  // tools/bvh_quality.py: build the fallback tree on purpose
     uint64_t walk_nodes = 0, walk_tris = 0;  // node fetches / triangle tests of the last emu_render
@@ -254,6 +257,46 @@ int emu_build(emu_scene* s) {
             ++s->ploc_rounds;
         }
         root = cid[0];
+        if (n >= 3 && kReinsertPasses > 0) {  // same passes and rounds as build_bvh_device
+            const int mc = 2 * (int)n - 1;
+            std::vector<int32_t> leaf_parent(n, -1), arrive_flags(n), target(mc), pivot(mc);
+            std::vector<float> gain(mc);
+            std::vector<uint8_t> state(mc);
+            std::vector<unsigned long long> lock(mc);
+            const ReinsertTree rt{bin.data(), leaf_parent.data(), order.data(), tri_lo.data(), tri_hi.data(), (int32_t)n, root};
+            for (int i = 0; i < (int)n - 1; ++i) ri_link_children(i, rt);
+            auto inner_area = [&] {
+                double a = 0;
+                for (int i = 0; i < (int)n - 1; ++i) a += half_area(bin[i].lo, bin[i].hi);
+                return a;
+            };
+            s->reinsert_moves = 0;
+            s->area_clustered = inner_area();
+            for (int pass = 0; pass < kReinsertPasses; ++pass) {
+                for (int c = 0; c < mc; ++c) ri_find(c, rt, gain.data(), target.data(), pivot.data(), state.data());
+                for (int round = 0; round < kReinsertRounds; ++round) {
+                    std::fill(lock.begin(), lock.end(), 0ull);
+                    if (round > 0)
+                        for (int c = 0; c < mc; ++c) ri_hold(c, rt, target.data(), state.data(), lock.data());
+                    for (int c = 0; c < mc; ++c) ri_bid(c, rt, gain.data(), target.data(), state.data(), lock.data());
+                    for (int c = 0; c < mc; ++c) ri_settle(c, rt, gain.data(), target.data(), state.data(), lock.data());
+                }
+                std::fill(lock.begin(), lock.end(), 0ull);
+                for (int c = 0; c < mc; ++c) ri_mark_moved(c, state.data(), lock.data());
+                for (int c = 0; c < mc; ++c) ri_drop_crossing(c, rt, target.data(), pivot.data(), state.data(), lock.data());
+                long moved = 0;
+                for (int c = 0; c < mc; ++c) {
+                    moved += state[c] == kRiWin;
+                    ri_apply(c, rt, target.data(), state.data());
+                }
+                s->reinsert_moves += moved;
+                std::fill(arrive_flags.begin(), arrive_flags.end(), 0);
+                for (int k = 0; k < (int)n; ++k)
+                    refit_from_leaf(k, leaf_parent.data(), bin.data(), arrive_flags.data(), order.data(), tri_lo.data(),
+                                    tri_hi.data(), plans.data());
+            }
+            s->area_reinserted = inner_area();
+        }
     }
     if (n >= 2 && attempt == 1) {  // fallback of build_bvh_device: binary radix tree + refit
         std::vector<int32_t> leaf_parent(n, -1), flags(n, 0);
@@ -293,6 +336,11 @@ int emu_build(emu_scene* s) {
 }
 
 int emu_levels(emu_scene* s) { return s->levels; }
+long emu_reinsert_stats(emu_scene* s, double* area_before, double* area_after) {
+    *area_before = s->area_clustered;
+    *area_after = s->area_reinserted;
+    return s->reinsert_moves;
+}
 
 // b200pt_update_mesh + b200pt_refit_accel: same per-node function as k_refit_wide, levels bottom-up
 int emu_update_mesh(emu_scene* s, int mesh, const float* verts, const float* normals, int nv) {

@@ -231,6 +231,19 @@ def test_tree_invariants():
     assert e.levels <= 32
 
 
+def test_reinsertion_passes_lower_the_tree_area():
+    """pt_build.h "reinsertion optimisation": the passes between clustering and collapse move nodes, the
+    binary tree's surface area drops, and the finished tree still holds every triangle once (the closest
+    hits of test_surface_rays_vs_brute_force and the invariants above run on the tree they leave)."""
+    sc = pt.Scene(scene="cornell-box", width=8, height=8, spp=1, depth=1)
+    e = Emu().load_scene(sc)
+    moves, before, after = e.reinsert_stats()
+    assert moves > 100
+    assert after < before * 0.995
+    ids = unpack_pairs(e.export()[1])[0]
+    assert (np.sort(ids) == np.arange(sc.n_triangles)).all()
+
+
 def test_sharded_renders_match_oracle_keys():
     sc = pt.Scene(scene="cornell-box", width=20, height=18, spp=5, depth=5, env="color", env_intensity=0.0)
     o, e = Oracle(det=True).load_scene(sc), Emu().load_scene(sc)

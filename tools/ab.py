@@ -36,7 +36,7 @@ def child(lib, scenes, spp, timing, check):
         ms = []
         for _ in range(4):
             ctx.render(); st = ctx.stats(); ms.append(st["render_ms"])
-        row = dict(scene=scene, spp=spp, frame_ms=min(ms[1:]), mrays=st["rays"] / min(ms[1:]) * 1e-3, rays=st["rays"], iters=st["iterations"])
+        row = dict(scene=scene, spp=spp, frame_ms=min(ms[1:]), mrays=st["rays"] / min(ms[1:]) * 1e-3, rays=st["rays"], iters=st["iterations"], build_ms=st.get("build_ms"), nodes=st.get("bvh_nodes"))
         ctx.close()
         if timing:
             c = pt.Context(flags=pt.FLAG_TIMING | pt.FLAG_COUNTERS); c.bind(sc); c.render(); c.render(); t = c.stats()
