@@ -1,6 +1,11 @@
-// Experiment only (EMU_REINSERT=<passes>): sequential reinsertion optimisation of the binary tree between the
-// PLOC rounds and the wide collapse, to learn how many node visits per ray a better tree would save before any
-// device code is written for it.  Not part of the product build.
+// Experiment only, kept for the record ("reinsertion passes in the builder"): reinsertion of the
+// binary tree between the clustering rounds and the wide collapse, run inside tests/emu/emu.cpp (included after
+// pt_build.h, called as  root = reinsert_exp::optimise(bin, n, root, order, tri_lo, tri_hi, plans, passes)  right after
+// the clustering) to learn how many node visits per ray a better tree saves before any device code was written.
+//   EMU_REINSERT=<passes>                           sequential greedy passes, largest area first (the quality limit)
+//   + EMU_REINSERT_PAR=1 [EMU_REINSERT_ROUNDS=r]    semantics of a parallel pass with path locks (Meister & Bittner)
+//   + EMU_REINSERT_LIGHT=1                          six-node locks + cycle check: what pt_build.h now implements
+// Not part of any build.
 #pragma once
 #include <cstdint>
 #include <vector>
