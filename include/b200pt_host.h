@@ -82,6 +82,8 @@ int b200pt_scene_test_loop(b200pt_scene* s, b200pt_ctx* ctx, const char* out_dir
 int b200pt_write_png(const char* path, int32_t w, int32_t h, const uint32_t* rgba);
 /* float frame (b200pt_framebuffer_f32: RGBA, top row first) as a Portable Float Map, RGB, little endian */
 int b200pt_write_pfm(const char* path, int32_t w, int32_t h, const float* rgba_top_first);
+/* the same frame as OpenEXR: one part, scan lines top row first, uncompressed, FLOAT channels B G R */
+int b200pt_write_exr(const char* path, int32_t w, int32_t h, const float* rgba_top_first);
 int b200pt_write_obj(const b200pt_scene* s, const char* path);
 
 /* ---- the loaders one stage at a time.  The application above is built from exactly these functions; they are exported

@@ -219,6 +219,7 @@ def _type_scene_api(H):
     H.b200pt_scene_set_material_color.argtypes = [P, C.c_char_p, P]
     H.b200pt_write_png.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
     H.b200pt_write_pfm.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
+    H.b200pt_write_exr.argtypes = [C.c_char_p, C.c_int32, C.c_int32, P]
     H.b200pt_write_obj.argtypes = [P, C.c_char_p]
     H.b200pt_obj_load.argtypes = [C.c_char_p, C.c_int32, C.POINTER(P)]
     H.b200pt_obj_count.argtypes = [P]

@@ -127,10 +127,11 @@ void render_frame(b200pt_ctx* ctx, const program_data& pdata, const test_data& t
     result.height = pdata.buffer_size[1];
     result.pixels.assign(fb, fb + (size_t)result.width * result.height);
     write_image(result, stem + ".png", out_dir);
-    if (pdata.write_pfm) {  // float output next to the PNG (the reference only has the 8-bit image)
+    if (pdata.write_pfm || pdata.write_exr) {  // float output next to the PNG (the reference only has the 8-bit image)
         const float* mean = nullptr;
         check(b200pt_framebuffer_f32(ctx, &mean), "framebuffer_f32");
-        write_pfm(out_dir + "/" + stem + ".pfm", result.width, result.height, mean);
+        if (pdata.write_pfm) write_pfm(out_dir + "/" + stem + ".pfm", result.width, result.height, mean);
+        if (pdata.write_exr) write_exr(out_dir + "/" + stem + ".exr", result.width, result.height, mean);
     }
 }
 

@@ -610,6 +610,74 @@ void write_pfm(const std::string& file_path, int w, int h, const float* rgba_top
     fclose(f);
 }
 
+// OpenEXR, single part, scan lines, no compression, three FLOAT channels (stored in the file format's
+// alphabetical channel order B, G, R; each scan line holds its channels one after the other)
+void write_exr(const std::string& file_path, int w, int h, const float* rgba_top_first) {
+    if (w <= 0 || h <= 0) throw std::runtime_error("write_exr: empty image");
+    std::vector<unsigned char> head;
+    auto put = [&](const void* p, size_t n) { head.insert(head.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
+    auto put_str = [&](const char* z) { put(z, strlen(z) + 1); };
+    auto put_i32 = [&](int32_t v) { put(&v, 4); };
+    auto put_f32 = [&](float v) { put(&v, 4); };
+    auto attr = [&](const char* name, const char* type, int32_t size) {
+        put_str(name);
+        put_str(type);
+        put_i32(size);
+    };
+    const unsigned char magic[8] = {0x76, 0x2f, 0x31, 0x01, 2, 0, 0, 0};  // magic, version 2, no flags
+    put(magic, 8);
+    attr("channels", "chlist", 3 * (2 + 16) + 1);
+    for (const char* c : {"B", "G", "R"}) {
+        put_str(c);
+        put_i32(2);  // FLOAT
+        put_i32(0);  // pLinear + 3 reserved bytes
+        put_i32(1);  // x sampling
+        put_i32(1);  // y sampling
+    }
+    head.push_back(0);
+    attr("compression", "compression", 1);
+    head.push_back(0);  // NO_COMPRESSION
+    for (const char* win : {"dataWindow", "displayWindow"}) {
+        attr(win, "box2i", 16);
+        put_i32(0);
+        put_i32(0);
+        put_i32(w - 1);
+        put_i32(h - 1);
+    }
+    attr("lineOrder", "lineOrder", 1);
+    head.push_back(0);  // INCREASING_Y: the top row first, as the frame is stored
+    attr("pixelAspectRatio", "float", 4);
+    put_f32(1.0f);
+    attr("screenWindowCenter", "v2f", 8);
+    put_f32(0.0f);
+    put_f32(0.0f);
+    attr("screenWindowWidth", "float", 4);
+    put_f32(1.0f);
+    head.push_back(0);  // end of header
+    FILE* f = fopen(file_path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + file_path);
+    fwrite(head.data(), 1, head.size(), f);
+    const uint64_t line_bytes = (uint64_t)w * 3 * sizeof(float), chunk = 8 + line_bytes;
+    for (int y = 0; y < h; ++y) {  // offset table
+        const uint64_t off = head.size() + (uint64_t)h * 8 + (uint64_t)y * chunk;
+        fwrite(&off, 8, 1, f);
+    }
+    std::vector<float> row((size_t)w * 3);
+    for (int y = 0; y < h; ++y) {
+        const float* src = rgba_top_first + (size_t)y * (size_t)w * 4;
+        for (int x = 0; x < w; ++x) {
+            row[(size_t)x] = src[4 * (size_t)x + 2];
+            row[(size_t)w + x] = src[4 * (size_t)x + 1];
+            row[2 * (size_t)w + x] = src[4 * (size_t)x + 0];
+        }
+        const int32_t yy = y, size = (int32_t)line_bytes;
+        fwrite(&yy, 4, 1, f);
+        fwrite(&size, 4, 1, f);
+        fwrite(row.data(), sizeof(float), row.size(), f);
+    }
+    fclose(f);
+}
+
 void write_png(const std::string& file_path, int w, int h, const uint32_t* rgba) {
     std::vector<unsigned char> raw((size_t)h * (1 + (size_t)w * 4));
     for (int y = 0; y < h; ++y) {

@@ -38,6 +38,7 @@ void float_from_rgbe(int w, int h, const unsigned char* rgbe, std::vector<float>
 bool load_hdr_float(const std::string& name, const std::string& path, int& w, int& h, std::vector<float>& rgb_flipped);
 // Portable Float Map ("PF", little endian, rows bottom to top) of a top-row-first float RGBA frame
 void write_pfm(const std::string& file_path, int w, int h, const float* rgba_top_first);
+void write_exr(const std::string& file_path, int w, int h, const float* rgba_top_first);
 image_buffer ldr_from_rgbe(int w, int h, const unsigned char* rgbe);          // stb hdr -> 8 bit route
 void rgbe_from_float(const float* rgb, unsigned char* rgbe);
 void flip_rows(image_buffer& img);                                             // image_buffer.cpp:50-55

@@ -11,7 +11,7 @@
 //   --gpu-dedup (create_mesh's vertex de-duplication on the device, b200pt_dedup_mesh; same meshes byte for byte)
 //   --gpus N (devices K .. K+N-1, samples sharded over them, one NCCL reduce per frame; the reference's OWL context can
 //             span devices the same way, extern/owl/owl/RayGen.cpp:140-146, and asks for one, application.cpp:62)
-//   --nee (light sampling + MIS mode)  --streams V (RNG streams per pixel)  --pfm (float frame next to the PNG)
+//   --nee (light sampling + MIS mode)  --streams V (RNG streams per pixel)  --pfm / --exr (float frame next to the PNG)
 //   --env-float (environment.hdr as float radiance instead of the reference's 8-bit conversion)
 //   --progressive N (frame in passes of N samples)  --target-error E (stop once the relative-variance figure <= E)
 //   --save-passes (PNG after every pass)  --gamma (RGBA8 through saturate(pow(c, 1/2.2)), the reference's device.cu:248)
@@ -29,7 +29,7 @@ int main(int argc, char** argv) {
     std::string out_dir = std::filesystem::current_path().string();
     host::load_options opt;
     int device = 0, flags = 0, streams = 1, gpus = 1, pipeline = 1;
-    bool stats = false, pfm = false, gamma = false, save_passes = false, gpu_dedup = false;
+    bool stats = false, pfm = false, exr = false, gamma = false, save_passes = false, gpu_dedup = false;
     int progressive = 0;
     double target_error = 0.0;
     for (int i = 1; i < argc; ++i) {
@@ -61,6 +61,7 @@ int main(int argc, char** argv) {
         else if (a == "--nee") flags |= B200PT_FLAG_NEE;
         else if (a == "--streams") { need(1); streams = atoi(argv[++i]); }
         else if (a == "--pfm") pfm = true;
+        else if (a == "--exr") exr = true;
         else if (a == "--env-float") opt.env_float = true;
         else if (a == "--progressive") { need(1); progressive = atoi(argv[++i]); }
         else if (a == "--target-error") { need(1); target_error = atof(argv[++i]); }
@@ -97,6 +98,7 @@ int main(int argc, char** argv) {
         for (const std::string& n : pdata.notes) printf("NOTE: %s\n", n.c_str());
 
         pdata.write_pfm = pfm;
+        pdata.write_exr = exr;
         pdata.progressive_pass = progressive;
         pdata.target_error = target_error;
         pdata.save_passes = save_passes;

@@ -87,6 +87,7 @@ struct program_data {
     std::vector<entity> entities;
     std::vector<std::string> notes;  // which inputs were procedural stand-ins
     bool write_pfm = false;          // also write the float frame (mean radiance before quantisation) as .pfm
+    bool write_exr = false;          // ... and / or as an uncompressed OpenEXR
     // progressive frames (b200pt_render_progressive): passes of this many samples (0: one blocking
     // launch, the reference's render_frame), stop early once the relative-variance figure reaches the target
     int progressive_pass = 0;

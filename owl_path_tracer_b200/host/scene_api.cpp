@@ -127,6 +127,9 @@ int b200pt_scene_set_material_color(b200pt_scene* s, const char* material, const
 int b200pt_write_png(const char* path, int32_t w, int32_t h, const uint32_t* rgba) {
     return host::api_guard([&] { host::write_png(path, w, h, rgba); });
 }
+int b200pt_write_exr(const char* path, int32_t w, int32_t h, const float* rgba_top_first) {
+    return host::api_guard([&] { host::write_exr(path, w, h, rgba_top_first); });
+}
 int b200pt_write_pfm(const char* path, int32_t w, int32_t h, const float* rgba_top_first) {
     return host::api_guard([&] { host::write_pfm(path, w, h, rgba_top_first); });
 }

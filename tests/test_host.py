@@ -201,6 +201,45 @@ def test_pfm_writer(tmp_path):
     assert np.array_equal(back, img[..., :3])
 
 
+def test_exr_writer(tmp_path):
+    """path_tracer --exr: single-part scan-line OpenEXR, uncompressed, FLOAT channels in the format's B G R order,
+    top row first; read back here with a reader written from the file layout (magic, attributes, offset table)."""
+    import struct
+    H = pt.host_lib()
+    rs = np.random.RandomState(2)
+    w, h = 9, 6
+    img = (rs.rand(h, w, 4).astype(np.float32) - 0.2) * 1000.0
+    p = tmp_path / "x.exr"
+    assert H.b200pt_write_exr(str(p).encode(), w, h, img.ctypes.data) == 0
+    raw = p.read_bytes()
+    assert raw[:4] == bytes([0x76, 0x2F, 0x31, 0x01]) and struct.unpack("<I", raw[4:8])[0] == 2
+    at, attrs = 8, {}
+    while raw[at] != 0:
+        e = raw.index(b"\0", at); name = raw[at:e].decode(); at = e + 1
+        e = raw.index(b"\0", at); typ = raw[at:e].decode(); at = e + 1
+        size = struct.unpack("<i", raw[at:at + 4])[0]; at += 4
+        attrs[name] = (typ, raw[at:at + size]); at += size
+    at += 1
+    assert attrs["compression"] == ("compression", b"\0") and attrs["lineOrder"] == ("lineOrder", b"\0")
+    assert struct.unpack("<4i", attrs["dataWindow"][1]) == (0, 0, w - 1, h - 1) == struct.unpack("<4i", attrs["displayWindow"][1])
+    ch, names, c = attrs["channels"][1], [], 0
+    while ch[c] != 0:
+        e = ch.index(b"\0", c); names.append(ch[c:e].decode())
+        assert struct.unpack("<iB3xii", ch[e + 1:e + 17]) == (2, 0, 1, 1)       # FLOAT, not linear-hinted, sampling 1 x 1
+        c = e + 17
+    assert names == ["B", "G", "R"]
+    offsets = struct.unpack(f"<{h}Q", raw[at:at + 8 * h])
+    back = np.empty((h, w, 3), np.float32)
+    for y, off in enumerate(offsets):
+        yy, size = struct.unpack("<ii", raw[off:off + 8])
+        assert yy == y and size == w * 12
+        planes = np.frombuffer(raw[off + 8:off + 8 + size], "<f4").reshape(3, w)
+        back[y] = planes[::-1].T                                                # B G R planes -> R G B pixels
+    assert offsets[-1] + 8 + w * 12 == len(raw)
+    assert np.array_equal(back, img[..., :3])
+    assert H.b200pt_write_exr(str(tmp_path / "no" / "dir.exr").encode(), w, h, img.ctypes.data) != 0
+
+
 def test_png_writer_and_texture_reader_round_trip(tmp_path):
     H = pt.host_lib()
     rs = np.random.RandomState(0)
