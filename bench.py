@@ -408,7 +408,7 @@ def main():
             config=dict(workload=WORKLOAD_NAME if not (args.spp or args.detail or args.lib) else
                         f"secondary: dragon 1920x1080 at {total_spp} spp, {sc.n_triangles} triangles (not the headline)",
                         parallelism=f"spp-sharded x{world}, scene replicated, one NCCL reduce of the float4 sums per frame",
-                        l2="inputs larger than L2: lane state 330 MB + BVH 49 MB per GPU vs 126 MB L2, no flush between steps",
+                        l2="inputs larger than L2: lane state 330 MB + BVH %.0f MB per GPU vs 126 MB L2, no flush between steps" % (kt["bvh_bytes"] / 1e6),
                         rng="one stream per pixel through all its samples (reference order); rank r seeds random(x, y + r*H)"),
             spp_per_s=total_spp / (ms_step * 1e-3),
             frames=dict(mode=("pipeline of %d contexts per rank (b200pt_pipeline_*), frame k+1 starts when frame k has < %.0f %% of its "
