@@ -93,6 +93,51 @@ __device__ __forceinline__ f4 ldg4f(const f4* p) {
     return f4{v.x, v.y, v.z, v.w};
 }
 
+#ifndef PT_TRI_POOL
+#define PT_TRI_POOL 1   // 1: the triangle phase pools the pending blocks of all lanes of the warp (see warp_walk);
+                        // 0: every lane tests its own blocks, one per step (the walker up to profiles/r02o)
+#endif
+
+// The packed two-triangle test of warp_walk's triangle phase for an arbitrary ray: the better accepted hit of the
+// block by (t, triangle id), id == kNoHit when neither triangle is hit.  Same operations, same bits.
+struct BlockHit {
+    float t, u, v;
+    uint32_t id;
+};
+__device__ __forceinline__ BlockHit test_block(const TriPair* __restrict__ tp, const f3 o, const f3 d, const float tmin,
+                                               const float tmax, uint32_t& n_tested) {
+    const f4 w0 = ldg4f(&tp->w[0]), w1 = ldg4f(&tp->w[1]), w2 = ldg4f(&tp->w[2]), w3 = ldg4f(&tp->w[3]), w4 = ldg4f(&tp->w[4]);
+    const float2 v0x = make_float2(w0.x, w0.y), v0y = make_float2(w0.z, w0.w), v0z = make_float2(w1.x, w1.y);
+    const float2 e1x = make_float2(w1.z, w1.w), e1y = make_float2(w2.x, w2.y), e1z = make_float2(w2.z, w2.w);
+    const float2 e2x = make_float2(w3.x, w3.y), e2y = make_float2(w3.z, w3.w), e2z = make_float2(w4.x, w4.y);
+    const float2 dx = make_float2(d.x, d.x), dy = make_float2(d.y, d.y), dz = make_float2(d.z, d.z);
+    const float2 ndx = make_float2(-d.x, -d.x), ndy = make_float2(-d.y, -d.y), ndz = make_float2(-d.z, -d.z);
+    const float2 px = __ffma2_rn(dy, e2z, __fmul2_rn(ndz, e2y));
+    const float2 py = __ffma2_rn(dz, e2x, __fmul2_rn(ndx, e2z));
+    const float2 pz = __ffma2_rn(dx, e2y, __fmul2_rn(ndy, e2x));
+    const float2 det = __ffma2_rn(e1z, pz, __ffma2_rn(e1y, py, __fmul2_rn(e1x, px)));
+    const float2 inv = make_float2(1.0f / det.x, 1.0f / det.y);
+    const float2 sx = __fadd2_rn(make_float2(o.x, o.x), make_float2(-v0x.x, -v0x.y));
+    const float2 sy = __fadd2_rn(make_float2(o.y, o.y), make_float2(-v0y.x, -v0y.y));
+    const float2 sz = __fadd2_rn(make_float2(o.z, o.z), make_float2(-v0z.x, -v0z.y));
+    const float2 uu = __fmul2_rn(__ffma2_rn(sz, pz, __ffma2_rn(sy, py, __fmul2_rn(sx, px))), inv);
+    const float2 qx = __ffma2_rn(sy, e1z, __fmul2_rn(make_float2(-sz.x, -sz.y), e1y));
+    const float2 qy = __ffma2_rn(sz, e1x, __fmul2_rn(make_float2(-sx.x, -sx.y), e1z));
+    const float2 qz = __ffma2_rn(sx, e1y, __fmul2_rn(make_float2(-sy.x, -sy.y), e1x));
+    const float2 vv = __fmul2_rn(__ffma2_rn(dz, qz, __ffma2_rn(dy, qy, __fmul2_rn(dx, qx))), inv);
+    const float2 tt = __fmul2_rn(__ffma2_rn(e2z, qz, __ffma2_rn(e2y, qy, __fmul2_rn(e2x, qx))), inv);
+    const uint32_t idA = f2u(w4.z), idB = f2u(w4.w);
+    n_tested = 1u + (idB != kNoHit ? 1u : 0u);
+    const bool okA = (det.x != 0.0f) && (uu.x >= 0.0f && uu.x <= 1.0f) && (vv.x >= 0.0f && uu.x + vv.x <= 1.0f) &&
+                     (tt.x > tmin && tt.x < tmax);
+    const bool okB = (det.y != 0.0f) && (uu.y >= 0.0f && uu.y <= 1.0f) && (vv.y >= 0.0f && uu.y + vv.y <= 1.0f) &&
+                     (tt.y > tmin && tt.y < tmax);
+    BlockHit h{0.0f, 0.0f, 0.0f, kNoHit};
+    if (okA) h = BlockHit{tt.x, uu.x, vv.x, idA};
+    if (okB && (!okA || tt.y < h.t || (tt.y == h.t && idB < h.id))) h = BlockHit{tt.y, uu.y, vv.y, idB};
+    return h;
+}
+
 // magic: 0x3F800000 handed in as a RUNTIME value (SceneView::plane_magic, a kernel parameter), so that
 //        it sits in a register and the byte-permute selector of plane_q is the immediate.
 // ANY:  shadow rays — the first accepted triangle ends the ray (any hit in (tmin, tmax)); the hit record then
@@ -245,6 +290,85 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
         }
 #endif
         if (tri_phase) {
+#if PT_TRI_POOL
+            // Pooled triangle phase: the pending blocks of ALL lanes are dealt out over the 32 lanes, whoever owns
+            // them (a lane tests block k of the warp with its owner's ray, fetched by shuffles), so a phase that
+            // found 12 lanes with two or three blocks each runs as one full step instead of three thinning ones.
+            // The closest hit of a ray is the minimum of (t, triangle id) over its blocks whatever the order: owners
+            // publish their current (t, id) as one 64-bit key in shared memory, testers atomicMin theirs in, the
+            // tester that ends up holding an owner's key hands over (u, v).  Voting by the number of pending blocks
+            // (16 / 24 / 32) or leaving a thin last round for the next phase were both slower than this lane vote
+            // followed by all rounds (profiles/r02s_*).
+            {
+                __shared__ unsigned long long s_key[PT_WALK_BLOCK];
+                __shared__ float s_u[PT_WALK_BLOCK], s_v[PT_WALK_BLOCK];
+                const int wbase = (int)(threadIdx.x & ~31u);
+                const uint32_t my_mask = has_ray ? tg_mask : 0u;
+                const int c = __popc(my_mask);
+                int incl = c;
+#pragma unroll
+                for (int dl = 1; dl < 32; dl <<= 1) {
+                    const int up = __shfl_up_sync(FULL, incl, dl);
+                    if (lid >= dl) incl += up;
+                }
+                const int excl = incl - c;
+                const int total = __shfl_sync(FULL, incl, 31);
+                const unsigned long long my_key = ((unsigned long long)__float_as_uint(hit.t) << 32) | hit.tri;
+                s_key[wbase + lid] = my_key;
+                __syncwarp();
+                for (int k0 = 0; k0 < total; k0 += 32) {
+                    const int k = k0 + lid;
+                    int own = 0;  // first lane whose inclusive count exceeds k
+#pragma unroll
+                    for (int step = 16; step >= 1; step >>= 1) {
+                        const int probe = __shfl_sync(FULL, incl, own + step - 1);
+                        if (probe <= k) own += step;
+                    }
+                    const int o_excl = __shfl_sync(FULL, excl, own);
+                    uint32_t o_mask = __shfl_sync(FULL, my_mask, own);
+                    const uint32_t o_base = __shfl_sync(FULL, tg_base, own);
+                    const f3 bo{__shfl_sync(FULL, o.x, own), __shfl_sync(FULL, o.y, own), __shfl_sync(FULL, o.z, own)};
+                    const f3 bd{__shfl_sync(FULL, d.x, own), __shfl_sync(FULL, d.y, own), __shfl_sync(FULL, d.z, own)};
+                    const float btmin = __shfl_sync(FULL, tmin, own), btmax = __shfl_sync(FULL, tmax, own);
+                    unsigned long long key = ~0ull;
+                    float bu = 0.0f, bv = 0.0f;
+                    if (k < total) {
+                        for (int i = k - o_excl; i > 0; --i) o_mask &= ~(1u << (31 - __clz(o_mask)));
+                        const int bit = 31 - __clz(o_mask);
+                        uint32_t n_tested;
+                        const BlockHit h = test_block(tris + (o_base + (uint32_t)bit), bo, bd, btmin, btmax, n_tested);
+                        if (COUNT) wc.tris += n_tested;
+                        if (h.id != kNoHit) {
+                            key = ((unsigned long long)__float_as_uint(h.t) << 32) | h.id;
+                            bu = h.u;
+                            bv = h.v;
+                            atomicMin(&s_key[wbase + own], key);
+                        }
+                    }
+                    __syncwarp();
+                    if (key != ~0ull && s_key[wbase + own] == key) {
+                        s_u[wbase + own] = bu;
+                        s_v[wbase + own] = bv;
+                    }
+                    __syncwarp();
+                }
+                if (c > 0) {
+                    const unsigned long long best = s_key[wbase + lid];
+                    if (best != my_key) {
+                        hit.t = __uint_as_float((uint32_t)(best >> 32));
+                        hit.tri = (uint32_t)best;
+                        hit.u = s_u[wbase + lid];
+                        hit.v = s_v[wbase + lid];
+                    }
+                    tg_mask = 0;
+                    if (ANY && hit.tri != kNoHit) {  // occluded: drop the rest of the traversal
+                        ng_mask = 0;
+                        sp = 0;
+                    }
+                }
+                __syncwarp();
+            }
+#else
 #if PT_TRI_LOOP
             const int n_act = __popc(act);
             bool again;
@@ -318,6 +442,7 @@ __device__ __forceinline__ void warp_walk(const Node8* __restrict__ nodes, const
 #endif
             } while (again);
 #endif
+#endif  // PT_TRI_POOL
         } else if (can_node) {
             if (tg_mask != 0) {  // lost the vote: keep the leaf triangles for later
                 PT_PUSH(tg_base, tg_mask);

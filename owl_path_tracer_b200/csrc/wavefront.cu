@@ -16,11 +16,13 @@
 namespace pt {
 
 #ifndef PT_BLOCKS_PER_SM
-#define PT_BLOCKS_PER_SM 7     // persistent blocks of 128 threads per SM for the walker kernels
+#define PT_BLOCKS_PER_SM 6     // persistent blocks of 128 threads per SM for the walker kernels
 #endif
 #ifndef PT_EXTEND_MIN_BLOCKS
-#define PT_EXTEND_MIN_BLOCKS 7  // register cap of the walker kernels: 65536 / (128 * blocks) -> 72 (the packed
-                                // two-triangle test spills at 64: 8 blocks/SM measured 10 % slower)
+#define PT_EXTEND_MIN_BLOCKS 6  // register cap of the walker kernels: 65536 / (128 * blocks) -> 85; the pooled triangle phase
+                                // holds a borrowed ray next to the lane's own and takes 80.  At 7 blocks (72 registers) it spills
+                                // 27 registers and loses what pooling gains; the lane-per-block walker was indifferent between
+                                // 6 and 7 blocks and 10 % slower at 8 (64 registers) -- profiles/r02s_*
 #endif
 #ifndef PT_SHADE_MIN_BLOCKS
 #define PT_SHADE_MIN_BLOCKS 5   // register cap of k_shade: 65536 / (128 * blocks) = 102.  Round 1 ran at 4 (128 registers): the
